@@ -1,0 +1,148 @@
+/* include/bvc_gpu.h -- the C-ABI drop-in boundary of the B200 `basetype` calling core.
+ *
+ * The reference (Zilong-Li/BaseVarC) has no FFI: its per-site caller is reached by direct C++
+ * calls inside one translation unit.  This header is the boundary a maintainer binds instead of
+ * those calls; each entry point names the reference code it replaces (paths under /root/reference):
+ *
+ *   bvc_create / bvc_destroy     the per-thread state of bt_s            src/BaseVarC.cpp:316-398
+ *                                + the constants of BaseType/UpdateF     src/BaseType.h:9-13, src/BaseType.cpp:45-46
+ *                                + min_af of bt_f                        src/BaseVarC.cpp:541-543
+ *   bvc_enqueue / bvc_wait       the body of the site loop: one bt_f()   src/BaseVarC.cpp:442-443, 536-669
+ *                                per site, i.e. BaseType ctor + LRT()    src/BaseType.cpp:5-139
+ *                                + the numeric part of WriteVcf()        src/BaseType.cpp:149-197
+ *                                + Algorithm.cpp / kfunc.c underneath    src/Algorithm.cpp:3-130
+ *   bvc_tile                     AlleleInfoVector + DepM idx per site    src/BamProcess.h:30-39, src/BaseType.h:21
+ *   bvc_site_result              what bt_f/WriteVcf format into text     src/BaseVarC.cpp:609-610, src/BaseType.cpp:198-233
+ *
+ * Plain C: no STL, no exceptions, no torch types.  All host memory is caller-owned.  A context is
+ * bound to one GPU and is NOT thread-safe (one dispatcher thread per GPU).  There is no CPU
+ * fallback: every call fails with BVC_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef BVC_GPU_H
+#define BVC_GPU_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BVC_ABI_VERSION 1
+
+/* error codes (negative); 0 = success */
+#define BVC_OK             0
+#define BVC_ERR_ARG       -1   /* NULL pointer, bad size, qual > 127, non-indel base > 3, ... */
+#define BVC_ERR_CUDA      -2   /* CUDA runtime error or no usable device (see bvc_last_error) */
+#define BVC_ERR_CAPACITY  -3   /* tile larger than the capacity given at bvc_create */
+#define BVC_ERR_STATE     -4   /* unknown ticket / nothing in flight */
+
+/* entry code byte: base:3 | strand:1 | is_indel:1 (AlleleInfo, src/BamProcess.h:30-39).
+ * For an indel entry base/strand (and qual/mapq/rpr) carry the STALE values of the last numeric
+ * token, exactly as the reference's reused `ai` does (src/BaseVarC.cpp:393,432-435). */
+#define BVC_CODE_BASE(c)    ((c) & 7u)
+#define BVC_CODE_STRAND(c)  (((c) >> 3) & 1u)
+#define BVC_CODE_INDEL(c)   (((c) >> 4) & 1u)
+#define BVC_MAKE_CODE(base, strand, indel) ((uint8_t)(((base) & 7u) | (((strand) & 1u) << 3) | (((indel) & 1u) << 4)))
+
+typedef struct bvc_params {
+    int32_t abi_version;        /* = BVC_ABI_VERSION */
+    int32_t n_samples;          /* N = lines of bam.list (src/BaseVarC.cpp:189); upper bound of entries per site */
+    double  min_af;             /* min(100.0/N, 0.001, --maf)   src/BaseVarC.cpp:541-543 ; must be > 0 */
+    double  lrt_threshold;      /* LRT_THRESHOLD 24.0           src/BaseType.h:9  */
+    double  em_epsilon;         /* 0.001                        src/BaseType.cpp:45 */
+    int32_t em_max_iter;        /* 100                          src/BaseType.cpp:46 */
+    int32_t n_groups;           /* 0 = no --group file          src/BaseVarC.cpp:340-370 */
+    const int32_t* sample_group;/* [n_samples] group id in [0,n_groups) or -1; NULL iff n_groups == 0 (copied) */
+    int32_t max_sites;          /* capacity of one tile (sites)   */
+    int32_t reserved0;
+    int64_t max_entries;        /* capacity of one tile (entries) */
+} bvc_params;
+
+/* Fills *p with the reference's constants for a cohort of n_samples and `--maf maf`. */
+void bvc_default_params(bvc_params* p, int32_t n_samples, double maf);
+
+/* A tile = n_sites consecutive sites of one window, CSR over covered entries, entries of a site in
+ * ascending sample order (the order bt_s pushes them, src/BaseVarC.cpp:407-441). */
+typedef struct bvc_tile {
+    int32_t n_sites;
+    int32_t reserved0;
+    const uint8_t*  ref_base;   /* [n_sites]   BASE_INT8_TABLE[refseq[p-rg_s]] in 0..3  (src/BaseVarC.cpp:548) */
+    const uint32_t* entry_off;  /* [n_sites+1] entry_off[0] == 0 */
+    const uint8_t*  code;       /* [R] BVC_MAKE_CODE(base, strand, is_indel) */
+    const uint8_t*  qual;       /* [R] 0..127 (the reference keeps quals in int8_t, src/BaseType.h:18) */
+    const uint8_t*  mapq;       /* [R] */
+    const uint8_t*  rpr;        /* [R] read position + 1, truncated to 8 bits as the bitfield does */
+    const uint32_t* sample;     /* [R] global sample index; may be NULL when n_groups == 0 */
+} bvc_tile;
+
+/* boundary-flag bits: a hard FP64 threshold of the reference was met within a 1e-9 relative margin
+ * at this site, so a differently-ordered summation may legitimately land on the other side. */
+#define BVC_FLAG_EM_DELTA   1u   /* delta vs epsilon            src/Algorithm.cpp:124 */
+#define BVC_FLAG_LRT_CHI    2u   /* chi vs LRT_THRESHOLD        src/BaseType.cpp:102  */
+#define BVC_FLAG_MIN_AF     4u   /* depth/total vs min_af       src/BaseType.cpp:79   */
+#define BVC_FLAG_ARGMIN_TIE 8u   /* two null models within 1e-9 src/BaseType.cpp:99   */
+#define BVC_FLAG_QUAL60     16u  /* var_qual vs QUAL_THRESHOLD  src/BaseType.cpp:221  */
+
+/* Fixed 176-byte record per site (little-endian, natural alignment). */
+typedef struct bvc_site_result {
+    double  cvg_fs;          /* bt_fisher_exact on cvg_strand            src/BaseVarC.cpp:603 */
+    double  cvg_sor;         /*                                          src/BaseVarC.cpp:604-608 */
+    double  af_lrt[4];       /* by base code; 0 unless base in alt_bases src/BaseType.cpp:111-116 */
+    double  chi;             /* chi_sqrt_t after the ladder              src/BaseType.cpp:93-110 */
+    double  var_qual;        /*                                          src/BaseType.cpp:117-135 */
+    double  vcf_fs;          /* valid iff lrt_ok                         src/BaseType.cpp:192 */
+    double  vcf_sor;         /*                                          src/BaseType.cpp:193-197 */
+    double  ranksum[3];      /* mapq, qual, rpr                          src/BaseType.cpp:189-191 */
+    int32_t n_entries;       /* aiv.size() */
+    int32_t depth[4];        /* na,nc,ng,nt over non-indel entries       src/BaseVarC.cpp:550-559 */
+    int32_t cvg_strand[4];   /* ref_fwd,ref_rev,alt_fwd,alt_rev, ALL entries   src/BaseVarC.cpp:587-602 */
+    int32_t vcf_strand[4];   /* same, non-indel entries, alt = any LRT alt     src/BaseType.cpp:174-187 */
+    int32_t em_fits;         /* diagnostics: EM() calls the reference would make */
+    int32_t em_passes;       /* diagnostics: singleEM passes over all fits */
+    uint32_t flags;          /* BVC_FLAG_* */
+    int8_t  cvg_alt_base;    /* top-count non-ref base                   src/BaseVarC.cpp:576-583 */
+    int8_t  lrt_ok;          /* BaseType::LRT() return value */
+    int8_t  n_alt;           /* alt_bases.size() */
+    int8_t  alt_bases[3];    /* in surviving-base order */
+    int8_t  pad[2];
+} bvc_site_result;
+
+typedef struct bvc_ctx bvc_ctx;
+
+int  bvc_create(bvc_ctx** out, int device, const bvc_params* params);
+void bvc_destroy(bvc_ctx* ctx);
+const char* bvc_last_error(const bvc_ctx* ctx);   /* ctx may be NULL: returns the last create() error */
+
+/* Asynchronous host-buffer path (the reference-facing call): copies the tile H2D, runs the kernels,
+ * copies n_sites records D2H into `out` (caller-owned; pinned memory makes the copies async).
+ * Up to two tickets may be in flight; a third bvc_enqueue waits for the oldest. */
+int  bvc_enqueue(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_result* out, uint64_t* ticket);
+int  bvc_wait(bvc_ctx* ctx, uint64_t ticket);
+/* Optional per-group outputs of the most recently enqueued tile (n_groups > 0), valid after bvc_wait:
+ * group_depth [n_sites][n_groups][4] int32 (src/BaseVarC.cpp:622-640) and
+ * group_af    [n_sites][n_groups][4] double by base code, NaN-free (src/BaseVarC.cpp:641-660). */
+int  bvc_fetch_groups(bvc_ctx* ctx, uint64_t ticket, int32_t* group_depth, double* group_af);
+
+/* Pinned host allocation helpers (cudaHostAlloc / cudaFreeHost). */
+void* bvc_host_alloc(size_t bytes);
+void  bvc_host_free(void* p);
+
+/* Device-resident path, used by bench.py for the kernel-only figure: upload once, run many times.
+ * bvc_resident_run launches the site kernels `iters` times on the context's stream, optionally
+ * flushing L2 (a >126 MB memset) before each timed launch, and returns the mean device time per
+ * launch in milliseconds measured with CUDA events on that stream.  per_kernel_ms (may be NULL)
+ * receives [n_kernels] mean times; n_kernels is returned through *n_kernels_out. */
+int  bvc_resident_upload(bvc_ctx* ctx, const bvc_tile* tile);
+int  bvc_resident_run(bvc_ctx* ctx, int iters, int flush_l2, float* ms_per_launch,
+                      float* per_kernel_ms, int* n_kernels_out);
+int  bvc_resident_download(bvc_ctx* ctx, bvc_site_result* out);
+int64_t bvc_kernel_launch_count(const bvc_ctx* ctx);   /* kernels of ours launched so far */
+
+/* FP64 pipe microbenchmark (dependent-free DFMA chains on all SMs): returns TFLOP/s (2 flop/FMA). */
+int  bvc_measure_fp64_peak(int device, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BVC_GPU_H */
