@@ -1,0 +1,163 @@
+"""Host-side mirror of the C-ABI (include/bvc_gpu.h) through ctypes.
+
+`BaseTypeCaller.call_sites(tile)` is the tile-granular replacement of the reference's per-site
+`bt_f(...)` call (src/BaseVarC.cpp:442-443): same inputs (the site's AlleleInfo entries), same
+numeric outputs (what bt_f / WriteVcf format into the CVG / VCF text).  There is NO CPU fallback:
+a missing library or a missing GPU raises `BvcError`.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from ._abi import SITE_RESULT_DTYPE, Params, Tile, default_params
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libbvc_gpu.so")
+
+EXPORTS = (
+    "bvc_default_params", "bvc_create", "bvc_destroy", "bvc_last_error", "bvc_enqueue", "bvc_wait",
+    "bvc_fetch_groups", "bvc_host_alloc", "bvc_host_free", "bvc_resident_upload", "bvc_resident_run",
+    "bvc_resident_download", "bvc_kernel_launch_count", "bvc_measure_fp64_peak",
+)
+
+
+class BvcError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen basevarc_b200/libbvc_gpu.so (built in-tree by `make -C basevarc_b200/csrc`)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise BvcError("CUDA extension %s is missing: run __graft_entry__.build() (no CPU fallback exists)" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    L.bvc_default_params.argtypes = [C.POINTER(Params), C.c_int32, C.c_double]
+    L.bvc_default_params.restype = None
+    L.bvc_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(Params)]
+    L.bvc_destroy.argtypes = [C.c_void_p]
+    L.bvc_destroy.restype = None
+    L.bvc_last_error.argtypes = [C.c_void_p]
+    L.bvc_last_error.restype = C.c_char_p
+    L.bvc_enqueue.argtypes = [C.c_void_p, C.POINTER(Tile), C.c_void_p, C.POINTER(C.c_uint64)]
+    L.bvc_wait.argtypes = [C.c_void_p, C.c_uint64]
+    L.bvc_fetch_groups.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    L.bvc_host_alloc.argtypes = [C.c_size_t]
+    L.bvc_host_alloc.restype = C.c_void_p
+    L.bvc_host_free.argtypes = [C.c_void_p]
+    L.bvc_host_free.restype = None
+    L.bvc_resident_upload.argtypes = [C.c_void_p, C.POINTER(Tile)]
+    L.bvc_resident_run.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_int)]
+    L.bvc_resident_download.argtypes = [C.c_void_p, C.c_void_p]
+    L.bvc_kernel_launch_count.argtypes = [C.c_void_p]
+    L.bvc_kernel_launch_count.restype = C.c_int64
+    L.bvc_measure_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
+    _lib = L
+    return L
+
+
+def measure_fp64_peak(device=0):
+    L = load_library()
+    t = C.c_double(0.0)
+    rc = L.bvc_measure_fp64_peak(device, C.byref(t))
+    if rc != 0:
+        raise BvcError("bvc_measure_fp64_peak: %s" % L.bvc_last_error(None).decode())
+    return t.value
+
+
+class PinnedArray:
+    """A numpy view over cudaHostAlloc memory (freed with the object)."""
+
+    def __init__(self, shape, dtype):
+        L = load_library()
+        self.dtype = np.dtype(dtype)
+        n = int(np.prod(shape)) * self.dtype.itemsize
+        self.ptr = L.bvc_host_alloc(max(n, 1))
+        if not self.ptr:
+            raise BvcError("bvc_host_alloc(%d) failed" % n)
+        buf = (C.c_char * max(n, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def __del__(self):
+        try:
+            if getattr(self, "ptr", None):
+                load_library().bvc_host_free(self.ptr)
+                self.ptr = None
+        except Exception:
+            pass
+
+
+class BaseTypeCaller:
+    """One context = one GPU.  Not thread-safe (as the C ABI)."""
+
+    def __init__(self, n_samples, maf=0.001, device=0, max_sites=1 << 16, max_entries=None, sample_group=None,
+                 n_groups=0):
+        self.lib = load_library()
+        p = default_params(n_samples, maf, max_sites, 0)
+        p.max_entries = int(max_entries if max_entries is not None else min(max_sites * n_samples, (1 << 32) - 1))
+        self._sg = None
+        if n_groups > 0:
+            self._sg = np.ascontiguousarray(np.asarray(sample_group, np.int32))
+            assert self._sg.size == n_samples
+            p.n_groups = int(n_groups)
+            p.sample_group = self._sg.ctypes.data_as(C.POINTER(C.c_int32))
+        self.params = p
+        self.ctx = C.c_void_p()
+        rc = self.lib.bvc_create(C.byref(self.ctx), int(device), C.byref(p))
+        if rc != 0:
+            raise BvcError("bvc_create failed (%d): %s" % (rc, self.lib.bvc_last_error(None).decode()))
+
+    def close(self):
+        if getattr(self, "ctx", None) and self.ctx.value:
+            self.lib.bvc_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    __del__ = close
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise BvcError("%s failed (%d): %s" % (what, rc, self.lib.bvc_last_error(self.ctx).decode()))
+
+    # -- reference-facing call: host buffers in, host records out ------------------------------------
+    def enqueue(self, tile, out):
+        ct = tile.as_ctypes(with_sample=self.params.n_groups > 0)
+        tk = C.c_uint64(0)
+        self._check(self.lib.bvc_enqueue(self.ctx, C.byref(ct), out.ctypes.data, C.byref(tk)), "bvc_enqueue")
+        return tk.value
+
+    def wait(self, ticket):
+        self._check(self.lib.bvc_wait(self.ctx, C.c_uint64(ticket)), "bvc_wait")
+
+    def call_sites(self, tile, out=None):
+        if out is None:
+            out = np.zeros(tile.n_sites, SITE_RESULT_DTYPE)
+        self.wait(self.enqueue(tile, out))
+        return out
+
+    # -- device-resident path (kernel-only timing) ---------------------------------------------------
+    def resident_upload(self, tile):
+        ct = tile.as_ctypes(with_sample=self.params.n_groups > 0)
+        self._check(self.lib.bvc_resident_upload(self.ctx, C.byref(ct)), "bvc_resident_upload")
+        self._resident_sites = tile.n_sites
+
+    def resident_run(self, iters=1, flush_l2=True):
+        ms = C.c_float(0)
+        per = (C.c_float * 8)()
+        nk = C.c_int(0)
+        self._check(self.lib.bvc_resident_run(self.ctx, int(iters), int(bool(flush_l2)), C.byref(ms), per, C.byref(nk)),
+                    "bvc_resident_run")
+        return ms.value, [per[i] for i in range(nk.value)]
+
+    def resident_download(self):
+        out = np.zeros(self._resident_sites, SITE_RESULT_DTYPE)
+        self._check(self.lib.bvc_resident_download(self.ctx, out.ctypes.data), "bvc_resident_download")
+        return out
+
+    @property
+    def kernel_launches(self):
+        return int(self.lib.bvc_kernel_launch_count(self.ctx))

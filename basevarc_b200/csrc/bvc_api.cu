@@ -1,0 +1,358 @@
+// bvc_api.cu -- the C-ABI of include/bvc_gpu.h: context, double-buffered tile pipeline, resident
+// (device-timed) path.  No CPU fallback: every entry point needs a CUDA device.
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+#include "../../include/bvc_gpu.h"
+#include "bvc_kernels.h"
+#include "bvc_site_kernel.cuh"
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    uint8_t *d_ref = nullptr, *d_code = nullptr, *d_qual = nullptr, *d_mapq = nullptr, *d_rpr = nullptr;
+    uint32_t *d_off = nullptr, *d_sample = nullptr;
+    bvc_site_result* d_out = nullptr;
+    unsigned int* d_counter = nullptr;
+    uint64_t ticket = 0;       // 0 = idle
+    int n_sites = 0;
+    int64_t n_entries = 0;
+};
+
+}  // namespace
+
+struct bvc_ctx {
+    int device = 0;
+    int n_sm = 0;
+    bvc_params prm;
+    std::vector<int32_t> sample_group;
+    Slot slot[2];
+    double* d_lut = nullptr;
+    double* d_lgam = nullptr;
+    void* d_flush = nullptr;
+    size_t flush_bytes = 0;
+    uint64_t next_ticket = 1;
+    int64_t launches = 0;
+    std::string err;
+    bool resident = false;
+};
+
+namespace {
+
+#define CK(call)                                                                               \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess) {                                                               \
+            char b_[512];                                                                      \
+            snprintf(b_, sizeof b_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            set_err(ctx, b_);                                                                  \
+            return BVC_ERR_CUDA;                                                               \
+        }                                                                                      \
+    } while (0)
+
+void set_err(bvc_ctx* ctx, const char* m)
+{
+    if (ctx) ctx->err = m; else g_create_error = m;
+}
+
+int alloc_slot(bvc_ctx* ctx, Slot& s)
+{
+    const size_t S = (size_t)ctx->prm.max_sites, R = (size_t)ctx->prm.max_entries;
+    CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+    CK(cudaMalloc(&s.d_ref, S + 16));
+    CK(cudaMalloc(&s.d_off, (S + 1) * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.d_code, R + 16));
+    CK(cudaMalloc(&s.d_qual, R + 16));
+    CK(cudaMalloc(&s.d_mapq, R + 16));
+    CK(cudaMalloc(&s.d_rpr, R + 16));
+    if (ctx->prm.n_groups > 0) CK(cudaMalloc(&s.d_sample, (R + 4) * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.d_out, (S + 1) * sizeof(bvc_site_result)));
+    CK(cudaMalloc(&s.d_counter, sizeof(unsigned int)));
+    return BVC_OK;
+}
+
+void free_slot(Slot& s)
+{
+    cudaFree(s.d_ref); cudaFree(s.d_off); cudaFree(s.d_code); cudaFree(s.d_qual); cudaFree(s.d_mapq);
+    cudaFree(s.d_rpr); cudaFree(s.d_sample); cudaFree(s.d_out); cudaFree(s.d_counter);
+    if (s.done) cudaEventDestroy(s.done);
+    if (s.stream) cudaStreamDestroy(s.stream);
+    s = Slot();
+}
+
+int check_tile(bvc_ctx* ctx, const bvc_tile* t, int64_t* n_entries)
+{
+    if (!t || t->n_sites < 0 || !t->entry_off || (t->n_sites > 0 && !t->ref_base)) { set_err(ctx, "bad tile: NULL array or n_sites < 0"); return BVC_ERR_ARG; }
+    if (t->entry_off[0] != 0) { set_err(ctx, "bad tile: entry_off[0] != 0"); return BVC_ERR_ARG; }
+    const int64_t R = t->entry_off[t->n_sites];
+    if (R > 0 && (!t->code || !t->qual || !t->mapq || !t->rpr)) { set_err(ctx, "bad tile: NULL entry array"); return BVC_ERR_ARG; }
+    if (ctx->prm.n_groups > 0 && R > 0 && !t->sample) { set_err(ctx, "bad tile: groups need the sample array"); return BVC_ERR_ARG; }
+    if (t->n_sites > ctx->prm.max_sites || R > ctx->prm.max_entries) { set_err(ctx, "tile exceeds the capacity given at bvc_create"); return BVC_ERR_CAPACITY; }
+    *n_entries = R;
+    return BVC_OK;
+}
+
+int upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R)
+{
+    const size_t S = (size_t)t->n_sites;
+    s.n_sites = t->n_sites; s.n_entries = R;
+    if (S) CK(cudaMemcpyAsync(s.d_ref, t->ref_base, S, cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.d_off, t->entry_off, (S + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
+    if (R) {
+        CK(cudaMemcpyAsync(s.d_code, t->code, (size_t)R, cudaMemcpyHostToDevice, s.stream));
+        CK(cudaMemcpyAsync(s.d_qual, t->qual, (size_t)R, cudaMemcpyHostToDevice, s.stream));
+        CK(cudaMemcpyAsync(s.d_mapq, t->mapq, (size_t)R, cudaMemcpyHostToDevice, s.stream));
+        CK(cudaMemcpyAsync(s.d_rpr, t->rpr, (size_t)R, cudaMemcpyHostToDevice, s.stream));
+        if (s.d_sample && t->sample) CK(cudaMemcpyAsync(s.d_sample, t->sample, (size_t)R * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
+    }
+    return BVC_OK;
+}
+
+int launch(bvc_ctx* ctx, Slot& s)
+{
+    if (s.n_sites == 0) return BVC_OK;
+    CK(cudaMemsetAsync(s.d_counter, 0, sizeof(unsigned int), s.stream));
+    bvc::SiteArgs a;
+    a.ref_base = s.d_ref; a.entry_off = s.d_off; a.code = s.d_code; a.qual = s.d_qual; a.mapq = s.d_mapq; a.rpr = s.d_rpr;
+    a.out = s.d_out; a.counter = s.d_counter; a.lut = ctx->d_lut; a.lgam = ctx->d_lgam;
+    a.n_sites = s.n_sites; a.max_iter = ctx->prm.em_max_iter;
+    a.min_af = ctx->prm.min_af; a.lrt_thr = ctx->prm.lrt_threshold; a.eps = ctx->prm.em_epsilon;
+    CK(bvc::launch_site_call(a, ctx->n_sm, s.stream));
+    ctx->launches += 1;
+    return BVC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void bvc_default_params(bvc_params* p, int32_t n_samples, double maf)
+{
+    memset(p, 0, sizeof(*p));
+    p->abi_version = BVC_ABI_VERSION;
+    p->n_samples = n_samples;
+    double min_af = 100.0 / n_samples;             // src/BaseVarC.cpp:541-543
+    if (min_af > 0.001) min_af = 0.001;
+    if (maf < min_af) min_af = maf;
+    p->min_af = min_af;
+    p->lrt_threshold = 24.0;                       // src/BaseType.h:9
+    p->em_epsilon = 0.001;                         // src/BaseType.cpp:45
+    p->em_max_iter = 100;                          // src/BaseType.cpp:46
+    p->max_sites = 1 << 16;
+    p->max_entries = (int64_t)p->max_sites * (n_samples > 0 ? n_samples : 1);
+    if (p->max_entries > ((int64_t)1 << 31)) p->max_entries = (int64_t)1 << 31;
+}
+
+int bvc_create(bvc_ctx** out, int device, const bvc_params* prm)
+{
+    bvc_ctx* ctx = nullptr;
+    if (!out || !prm) { set_err(nullptr, "bvc_create: NULL argument"); return BVC_ERR_ARG; }
+    *out = nullptr;
+    if (prm->abi_version != BVC_ABI_VERSION) { set_err(nullptr, "bvc_create: abi_version mismatch"); return BVC_ERR_ARG; }
+    if (prm->n_samples <= 0 || !(prm->min_af > 0) || prm->em_max_iter < 0 || prm->max_sites <= 0 || prm->max_entries < 0 ||
+        prm->max_entries >= ((int64_t)1 << 32) || prm->n_groups < 0 || (prm->n_groups > 0 && !prm->sample_group)) {
+        set_err(nullptr, "bvc_create: bad parameter (n_samples, min_af > 0, capacities, groups)");
+        return BVC_ERR_ARG;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        set_err(nullptr, "bvc_create: no CUDA device (this library has no CPU path)");
+        cudaGetLastError();
+        return BVC_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) { set_err(nullptr, "bvc_create: device index out of range"); return BVC_ERR_ARG; }
+    ctx = new bvc_ctx();
+    ctx->device = device;
+    ctx->prm = *prm;
+    if (prm->n_groups > 0) {
+        ctx->sample_group.assign(prm->sample_group, prm->sample_group + prm->n_samples);
+        ctx->prm.sample_group = ctx->sample_group.data();
+    } else ctx->prm.sample_group = nullptr;
+
+    auto fail = [&](int rc) { g_create_error = ctx->err; bvc_destroy(ctx); return rc; };
+    cudaDeviceProp prop;
+    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+        ctx->err = "bvc_create: cudaSetDevice/cudaGetDeviceProperties failed"; return fail(BVC_ERR_CUDA);
+    }
+    if (prop.major < 10) { ctx->err = "bvc_create: device is not sm_100 class (kernels are built for sm_100a only)"; return fail(BVC_ERR_CUDA); }
+    ctx->n_sm = prop.multiProcessorCount;
+
+    // host-built tables (glibc): per-qual likelihoods (src/BaseType.cpp:13-15) and lgamma(k)
+    std::vector<double> lut(4 * bvc::kNQ), lgam((size_t)prm->n_samples + 3);
+    for (int q = 0; q < bvc::kNQ; ++q) {
+        const double e = exp(-0.23025850929940458 * q);      // MLN10TO10, src/BaseType.h:10
+        lut[q] = e / 3.0; lut[bvc::kNQ + q] = 1.0 - e;
+        lut[2 * bvc::kNQ + q] = log(e / 3.0); lut[3 * bvc::kNQ + q] = log(1.0 - e);
+    }
+    for (size_t k = 0; k < lgam.size(); ++k) lgam[k] = k == 0 ? 0.0 : lgamma((double)k);
+    auto ck = [&](cudaError_t e, const char* what) {
+        if (e == cudaSuccess) return true;
+        ctx->err = std::string(what) + ": " + cudaGetErrorString(e); return false;
+    };
+    if (!ck(cudaMalloc(&ctx->d_lut, lut.size() * sizeof(double)), "cudaMalloc lut") ||
+        !ck(cudaMalloc(&ctx->d_lgam, lgam.size() * sizeof(double)), "cudaMalloc lgam") ||
+        !ck(cudaMemcpy(ctx->d_lut, lut.data(), lut.size() * sizeof(double), cudaMemcpyHostToDevice), "copy lut") ||
+        !ck(cudaMemcpy(ctx->d_lgam, lgam.data(), lgam.size() * sizeof(double), cudaMemcpyHostToDevice), "copy lgam"))
+        return fail(BVC_ERR_CUDA);
+    for (int i = 0; i < 2; ++i) { int rc = alloc_slot(ctx, ctx->slot[i]); if (rc != BVC_OK) return fail(rc); }
+    *out = ctx;
+    return BVC_OK;
+}
+
+void bvc_destroy(bvc_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    for (int i = 0; i < 2; ++i) { if (ctx->slot[i].stream) cudaStreamSynchronize(ctx->slot[i].stream); free_slot(ctx->slot[i]); }
+    cudaFree(ctx->d_lut); cudaFree(ctx->d_lgam); cudaFree(ctx->d_flush);
+    delete ctx;
+}
+
+const char* bvc_last_error(const bvc_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int bvc_enqueue(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_result* out, uint64_t* ticket)
+{
+    if (!ctx) return BVC_ERR_ARG;
+    if (!out || !ticket) { set_err(ctx, "bvc_enqueue: NULL out/ticket"); return BVC_ERR_ARG; }
+    int64_t R = 0;
+    int rc = check_tile(ctx, tile, &R);
+    if (rc != BVC_OK) return rc;
+    CK(cudaSetDevice(ctx->device));
+    const uint64_t tk = ctx->next_ticket;
+    Slot& s = ctx->slot[tk & 1];
+    if (s.ticket) { CK(cudaStreamSynchronize(s.stream)); s.ticket = 0; }
+    if ((rc = upload(ctx, s, tile, R)) != BVC_OK) return rc;
+    if ((rc = launch(ctx, s)) != BVC_OK) return rc;
+    if (s.n_sites) CK(cudaMemcpyAsync(out, s.d_out, (size_t)s.n_sites * sizeof(bvc_site_result), cudaMemcpyDeviceToHost, s.stream));
+    CK(cudaEventRecord(s.done, s.stream));
+    s.ticket = tk;
+    ctx->next_ticket += 1;
+    ctx->resident = false;
+    *ticket = tk;
+    return BVC_OK;
+}
+
+int bvc_wait(bvc_ctx* ctx, uint64_t ticket)
+{
+    if (!ctx) return BVC_ERR_ARG;
+    Slot& s = ctx->slot[ticket & 1];
+    if (ticket == 0 || ticket >= ctx->next_ticket) { set_err(ctx, "bvc_wait: unknown ticket"); return BVC_ERR_STATE; }
+    if (s.ticket != ticket) return BVC_OK;      // already retired by a later enqueue on the same slot
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(s.stream));
+    s.ticket = 0;
+    return BVC_OK;
+}
+
+int bvc_fetch_groups(bvc_ctx* ctx, uint64_t, int32_t*, double*)
+{
+    if (!ctx) return BVC_ERR_ARG;
+    set_err(ctx, "bvc_fetch_groups: the --group path is not built yet");
+    return BVC_ERR_STATE;
+}
+
+void* bvc_host_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void bvc_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int bvc_resident_upload(bvc_ctx* ctx, const bvc_tile* tile)
+{
+    if (!ctx) return BVC_ERR_ARG;
+    int64_t R = 0;
+    int rc = check_tile(ctx, tile, &R);
+    if (rc != BVC_OK) return rc;
+    CK(cudaSetDevice(ctx->device));
+    Slot& s = ctx->slot[0];
+    CK(cudaStreamSynchronize(s.stream));
+    s.ticket = 0;
+    if ((rc = upload(ctx, s, tile, R)) != BVC_OK) return rc;
+    CK(cudaStreamSynchronize(s.stream));
+    ctx->resident = true;
+    return BVC_OK;
+}
+
+int bvc_resident_run(bvc_ctx* ctx, int iters, int flush_l2, float* ms_per_launch, float* per_kernel_ms, int* n_kernels_out)
+{
+    if (!ctx) return BVC_ERR_ARG;
+    if (!ctx->resident || iters <= 0) { set_err(ctx, "bvc_resident_run: no resident tile / iters <= 0"); return BVC_ERR_STATE; }
+    CK(cudaSetDevice(ctx->device));
+    Slot& s = ctx->slot[0];
+    if (flush_l2 && !ctx->d_flush) { ctx->flush_bytes = (size_t)256 << 20; CK(cudaMalloc(&ctx->d_flush, ctx->flush_bytes)); }
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    double total = 0.0;
+    for (int i = 0; i < iters; ++i) {
+        if (flush_l2) CK(cudaMemsetAsync(ctx->d_flush, i & 0xff, ctx->flush_bytes, s.stream));
+        CK(cudaMemsetAsync(s.d_counter, 0, sizeof(unsigned int), s.stream));
+        CK(cudaEventRecord(e0, s.stream));
+        int rc = launch(ctx, s);
+        if (rc != BVC_OK) return rc;
+        CK(cudaEventRecord(e1, s.stream));
+        CK(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        total += ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (ms_per_launch) *ms_per_launch = (float)(total / iters);
+    if (per_kernel_ms) per_kernel_ms[0] = (float)(total / iters);
+    if (n_kernels_out) *n_kernels_out = 1;
+    return BVC_OK;
+}
+
+int bvc_resident_download(bvc_ctx* ctx, bvc_site_result* out)
+{
+    if (!ctx || !out) return BVC_ERR_ARG;
+    if (!ctx->resident) { set_err(ctx, "bvc_resident_download: no resident tile"); return BVC_ERR_STATE; }
+    CK(cudaSetDevice(ctx->device));
+    Slot& s = ctx->slot[0];
+    CK(cudaStreamSynchronize(s.stream));
+    if (s.n_sites) CK(cudaMemcpy(out, s.d_out, (size_t)s.n_sites * sizeof(bvc_site_result), cudaMemcpyDeviceToHost));
+    return BVC_OK;
+}
+
+int64_t bvc_kernel_launch_count(const bvc_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int bvc_measure_fp64_peak(int device, double* tflops)
+{
+    bvc_ctx* ctx = nullptr;
+    if (!tflops) return BVC_ERR_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) { cudaGetLastError(); set_err(nullptr, "bvc_measure_fp64_peak: no such CUDA device"); return BVC_ERR_CUDA; }
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 15;
+    double* d = nullptr;
+    CK(cudaMalloc(&d, (size_t)blocks * threads * sizeof(double)));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        CK(cudaEventRecord(e0, 0));
+        CK(bvc::launch_fp64_peak(d, blocks, threads, iters, 0));
+        CK(cudaEventRecord(e1, 0));
+        CK(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    *tflops = 2.0 * 8.0 * (double)iters * blocks * threads / (best * 1e-3) / 1e12;
+    return BVC_OK;
+}
+
+}  // extern "C"

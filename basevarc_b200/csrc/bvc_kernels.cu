@@ -1,0 +1,201 @@
+// bvc_kernels.cu -- kernel entry points (sm_100a) and their launchers.
+// See bvc_site_kernel.cuh for the design and the reference code each phase replaces.
+#include "bvc_kernels.h"
+#include "bvc_site_kernel.cuh"
+
+namespace bvc {
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+site_call_kernel(SiteArgs a)
+{
+    __shared__ __align__(16) unsigned char smem_w[kWarpsPerBlock][kWarpSmemBytes];
+    __shared__ double lut_s[4 * kNQ];
+
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 4 * kNQ; i += blockDim.x) lut_s[i] = a.lut[i];
+
+    WarpSmem w;
+    w.lml = reinterpret_cast<double*>(smem_w[wid]);
+    w.hist = reinterpret_cast<uint32_t*>(smem_w[wid] + kNBins * 8);
+    w.keys = reinterpret_cast<uint16_t*>(smem_w[wid] + kNBins * 12);
+    w.codehist = reinterpret_cast<uint32_t*>(smem_w[wid] + kNBins * 14);
+    for (int i = lane; i < kNBins; i += 32) w.hist[i] = 0;
+    w.codehist[lane] = 0;
+    __syncthreads();
+
+    for (;;) {
+        int site = 0;
+        if (lane == 0) site = (int)atomicAdd(a.counter, 1u);
+        site = __shfl_sync(0xffffffffu, site, 0);
+        if (site >= a.n_sites) break;
+
+        const uint32_t b0 = a.entry_off[site], b1 = a.entry_off[site + 1];
+        const int ref = a.ref_base[site] & 3;
+
+        // ---- Phase A: one coalesced pass over the packed entries -> histograms ------------------
+        unsigned qmin = 127, qmax = 0;
+        for (uint32_t e = b0 + lane; e < b1; e += 32) {
+            const unsigned c = a.code[e];
+            const unsigned q = a.qual[e] & (kNQ - 1);
+            atomicAdd(&w.codehist[c & 31], 1u);
+            if (!(c & 16)) {
+                atomicAdd(&w.hist[((c & 3) << 7) | q], 1u);
+                qmin = min(qmin, q); qmax = max(qmax, q);
+            }
+        }
+        __syncwarp();
+        const int cnt = (int)w.codehist[lane];      // lane = base | strand<<3 | indel<<4
+        w.codehist[lane] = 0;
+        qmin = __reduce_min_sync(0xffffffffu, qmin);
+        qmax = __reduce_max_sync(0xffffffffu, qmax);
+
+        SiteState st;
+        st.em_fits = 0; st.em_passes = 0; st.flags = 0; st.n_reads = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {               // src/BaseVarC.cpp:550-559
+            st.depth[b] = __shfl_sync(0xffffffffu, cnt, b) + __shfl_sync(0xffffffffu, cnt, b | 8);
+            st.n_reads += st.depth[b];
+        }
+        st.has_q0 = (st.n_reads > 0 && qmin == 0);
+
+        // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
+        int order[4] = {0, 1, 2, 3};
+#pragma unroll
+        for (int i = 1; i < 4; ++i)
+#pragma unroll
+            for (int j = i; j > 0; --j)
+                if (st.depth[order[j]] > st.depth[order[j - 1]]) { int x = order[j]; order[j] = order[j - 1]; order[j - 1] = x; }
+        const int alt = (order[0] != ref) ? order[0] : order[1];
+
+        // src/BaseVarC.cpp:587-602: 2x2 table over ALL entries (indel entries carry stale base/strand)
+        int cs[4];
+        cs[0] = __shfl_sync(0xffffffffu, cnt, ref | 8) + __shfl_sync(0xffffffffu, cnt, ref | 8 | 16);
+        cs[1] = __shfl_sync(0xffffffffu, cnt, ref)     + __shfl_sync(0xffffffffu, cnt, ref | 16);
+        cs[2] = __shfl_sync(0xffffffffu, cnt, alt | 8) + __shfl_sync(0xffffffffu, cnt, alt | 8 | 16);
+        cs[3] = __shfl_sync(0xffffffffu, cnt, alt)     + __shfl_sync(0xffffffffu, cnt, alt | 16);
+        const double cvg_fs = dm_fisher(a.lgam, cs[0], cs[1], cs[2], cs[3]);
+        const double cvg_sor = dm_sor(cs[0], cs[1], cs[2], cs[3]);
+
+        // ---- Phase B: compact the non-empty (base, qual) classes in place ------------------------
+        int ncls = 0;
+        if (st.n_reads > 0) {
+            for (int b = 0; b < 4; ++b) {
+                if (st.depth[b] == 0) continue;
+                for (unsigned q0 = qmin & ~31u; q0 <= qmax; q0 += 32) {
+                    const unsigned bin = (b << 7) + q0 + lane;
+                    const uint32_t v = w.hist[bin];
+                    const unsigned m = __ballot_sync(0xffffffffu, v != 0);
+                    const int pos = ncls + __popc(m & ((1u << lane) - 1));
+                    __syncwarp();
+                    if (v) w.hist[bin] = 0;
+                    __syncwarp();
+                    if (v) { w.hist[pos] = v; w.keys[pos] = (uint16_t)bin; }
+                    ncls += __popc(m);
+                    __syncwarp();
+                }
+            }
+        }
+        st.ncls = ncls;
+
+        // ---- Phase C: LRT ladder over EM fits ----------------------------------------------------
+        const int comb[4] = {0, 1, 2, 3};
+        LrtOut L;
+        lrt_ladder(a, w, lut_s, st, ref, comb, 4, lane, L);
+
+        // ---- Phase D: VCF-side summaries for LRT-positive sites ----------------------------------
+        int vs[4] = {0, 0, 0, 0};
+        double vcf_fs = 0.0, vcf_sor = 0.0, rs[3] = {0.0, 0.0, 0.0};
+        __syncwarp();
+        if (L.ok) {
+            unsigned altmask = 0;
+            for (int i = 0; i < L.n_alt; ++i) altmask |= 1u << L.alt_bases[i];
+            // src/BaseType.cpp:174-187: non-indel entries only, alt = any surviving alt base
+            vs[0] = __shfl_sync(0xffffffffu, cnt, ref | 8);
+            vs[1] = __shfl_sync(0xffffffffu, cnt, ref);
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int f = __shfl_sync(0xffffffffu, cnt, b | 8), r = __shfl_sync(0xffffffffu, cnt, b);
+                if (altmask >> b & 1) { vs[2] += f; vs[3] += r; }
+            }
+            vcf_fs = dm_fisher(a.lgam, vs[0], vs[1], vs[2], vs[3]);
+            vcf_sor = dm_sor(vs[0], vs[1], vs[2], vs[3]);
+            // six 256-bin histograms alias lml+hist (6144 B): [feature][ref|alt][256]
+            uint32_t* H = reinterpret_cast<uint32_t*>(w.lml);
+            for (int i = lane; i < 6 * 256; i += 32) H[i] = 0;
+            __syncwarp();
+            for (uint32_t e = b0 + lane; e < b1; e += 32) {
+                const unsigned c = a.code[e];
+                if (c & 16) continue;
+                const int base = c & 7;
+                int g = -1;
+                if (base == ref) g = 0; else if (base < 4 && (altmask >> base & 1)) g = 1;
+                if (g < 0) continue;
+                atomicAdd(&H[(0 * 2 + g) * 256 + a.mapq[e]], 1u);
+                atomicAdd(&H[(1 * 2 + g) * 256 + a.qual[e]], 1u);
+                atomicAdd(&H[(2 * 2 + g) * 256 + a.rpr[e]], 1u);
+            }
+            __syncwarp();
+#pragma unroll
+            for (int f = 0; f < 3; ++f) rs[f] = ranksum_hist(H + f * 512, H + f * 512 + 256, lane);
+            __syncwarp();
+            for (int i = lane; i < kNBins; i += 32) w.hist[i] = 0;
+        } else {
+            for (int i = lane; i < ncls; i += 32) w.hist[i] = 0;
+        }
+        __syncwarp();
+
+        // ---- write the 176-byte record: stage in shared memory, store as 11 x 16 B ----------------
+        bvc_site_result* rec = reinterpret_cast<bvc_site_result*>(w.keys);
+        if (lane == 0) {
+            rec->cvg_fs = cvg_fs; rec->cvg_sor = cvg_sor;
+            for (int j = 0; j < 4; ++j) rec->af_lrt[j] = L.af[j];
+            rec->chi = L.chi; rec->var_qual = L.var_qual;
+            rec->vcf_fs = vcf_fs; rec->vcf_sor = vcf_sor;
+            for (int f = 0; f < 3; ++f) rec->ranksum[f] = rs[f];
+            rec->n_entries = (int32_t)(b1 - b0);
+            for (int j = 0; j < 4; ++j) { rec->depth[j] = st.depth[j]; rec->cvg_strand[j] = cs[j]; rec->vcf_strand[j] = vs[j]; }
+            rec->em_fits = st.em_fits; rec->em_passes = st.em_passes; rec->flags = st.flags;
+            rec->cvg_alt_base = (int8_t)alt; rec->lrt_ok = (int8_t)L.ok; rec->n_alt = (int8_t)L.n_alt;
+            for (int i = 0; i < 3; ++i) rec->alt_bases[i] = (int8_t)L.alt_bases[i];
+            rec->pad[0] = rec->pad[1] = 0;
+        }
+        __syncwarp();
+        if (lane < (int)(sizeof(bvc_site_result) / 16))
+            reinterpret_cast<uint4*>(a.out + site)[lane] = reinterpret_cast<const uint4*>(rec)[lane];
+        __syncwarp();
+    }
+}
+
+// Dependent-free DFMA chains: 8 independent accumulators per thread.
+__global__ void fp64_peak_kernel(double* out, int iters)
+{
+    double x0 = threadIdx.x * 1e-9, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    const double m = 1.0000001, c = 1e-7;
+    for (int i = 0; i < iters; ++i) {
+        x0 = fma(x0, m, c); x1 = fma(x1, m, c); x2 = fma(x2, m, c); x3 = fma(x3, m, c);
+        x4 = fma(x4, m, c); x5 = fma(x5, m, c); x6 = fma(x6, m, c); x7 = fma(x7, m, c);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+}
+
+cudaError_t launch_site_call(const SiteArgs& a, int n_sm, cudaStream_t stream)
+{
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, site_call_kernel, kWarpsPerBlock * 32, 0);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) per_sm = 1;
+    long long want = ((long long)a.n_sites + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    long long grid = (long long)n_sm * per_sm;          // persistent: a whole number of waves
+    if (grid > want) grid = want;
+    if (grid < 1) grid = 1;
+    site_call_kernel<<<(unsigned)grid, kWarpsPerBlock * 32, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream)
+{
+    fp64_peak_kernel<<<blocks, threads, 0, stream>>>(out, iters);
+    return cudaGetLastError();
+}
+
+}  // namespace bvc

@@ -124,6 +124,8 @@ def synth_tile(n_samples, n_sites, depth, model="lowpass", seed=1, indel_frac=0.
     if model == "highpoly":
         site_cov = site_cov * rng.uniform(0.1, 1.0, S)
     cum_af = np.cumsum(af, axis=1)
+    is_var = af.max(1) < 1.0
+    perr_lut = np.power(10.0, -np.arange(256) / 10.0).astype(np.float32)
     counts = np.empty(S, np.int64)
     parts = []
     rows = max(1, chunk_cells // N)
@@ -138,12 +140,17 @@ def synth_tile(n_samples, n_sites, depth, model="lowpass", seed=1, indel_frac=0.
         mapq = rng.integers(20, 61, R, dtype=np.uint8)
         rpr = rng.integers(1, 101, R, dtype=np.uint8)
         strand = rng.integers(0, 2, R, dtype=np.uint8)
-        u = rng.random(R)
-        true_b = (u[:, None] >= cum_af[site_i, :3]).sum(1).astype(np.uint8)
-        perr = np.power(10.0, -qual.astype(np.float64) / 10.0)
-        flip = rng.random(R) < perr
-        obs = np.where(flip, (true_b + rng.integers(1, 4, R, dtype=np.uint8)) % 4, true_b).astype(np.uint8)
-        indel = (rng.random(R) < indel_frac).astype(np.uint8)
+        # true allele: REF except at the (rare) variant sites, where it is drawn from the site's AF vector
+        true_b = ref[site_i]
+        at_var = np.nonzero(is_var[site_i])[0]
+        if at_var.size:
+            u = rng.random(at_var.size)
+            true_b[at_var] = (u[:, None] >= cum_af[site_i[at_var], :3]).sum(1).astype(np.uint8)
+        flip = rng.random(R, dtype=np.float32) < perr_lut[qual]
+        obs = true_b
+        nf = np.nonzero(flip)[0]
+        obs[nf] = (true_b[nf] + rng.integers(1, 4, nf.size, dtype=np.uint8)) % 4
+        indel = (rng.random(R, dtype=np.float32) < indel_frac).astype(np.uint8)
         parts.append((obs, strand, indel, qual, mapq, rpr, samp.astype(np.uint32)))
     cat = lambda k: np.concatenate([p[k] for p in parts]) if parts else np.zeros(0, np.uint8)
     obs, strand, indel, qual, mapq, rpr, samp = (cat(k) for k in range(7))

@@ -1,0 +1,281 @@
+#!/usr/bin/env python
+"""bench.py -- site*samples/s of the basetype calling core (EM + LRT + strand/Fisher/rank-sum).
+
+A step = one pass of the hot path over one window of the BASELINE.json workload C2 (synthetic
+1,000 samples x 1 Mb at 0.5x, SURVEY.md section 8(d) generator) per GPU.  N GPUs = N windows
+(sites are independent: window sharding, no collective, weak scaling).
+
+  value : whole-job site*samples/s with the packed pileup already resident in HBM (device events)
+  e2e   : the same through the C ABI with HOST buffers (pinned H2D of the tile + D2H of the records
+          inside the timed region), double-buffered over sub-tiles
+  roofline / fp64 / cpu_baseline : see DESIGN.md "Measurement"
+
+`--impl reference` times the reference's own CPU implementation on the host cores instead.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "site*samples/sec for basetype EM+LRT"
+UNIT = "site*samples/s"
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json, burst copy)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.proc = None
+        self.lines = []
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def _workload(name, n_sites, rank):
+    import basevarc_b200 as B
+    cfg = B.CONFIGS[name]
+    S = n_sites or cfg["n_sites"]
+    tile = B.synth_config(name, n_sites=S, seed=int(name[1:]) + 1000 * rank)
+    return cfg, tile
+
+
+def _alg_bytes(tile):
+    """4 B per covered entry + 8 B per site header + 192 B result per non-empty site."""
+    nonempty = int((np.diff(tile.entry_off.astype(np.int64)) > 0).sum())
+    return 4 * tile.n_entries + 8 * tile.n_sites + 192 * nonempty
+
+
+def cpu_port_baseline(tile, params, budget_sites_per_thread, threads):
+    """The oracle's C restatement (per-read, reference operation order) on `threads` host threads."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py
+    oracle_py.port()
+    S = min(tile.n_sites, budget_sites_per_thread * threads)
+    bounds = np.linspace(0, S, threads + 1).astype(int)
+    ths = [threading.Thread(target=oracle_py.call_sites, args=(tile, params, int(bounds[i]), int(bounds[i + 1])))
+           for i in range(threads)]
+    t0 = time.perf_counter()
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    dt = time.perf_counter() - t0
+    return S * tile.n_samples / dt, S, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path on all host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import basevarc_b200 as B
+    cores = os.cpu_count() or 1
+    per_thread = args.ref_sites_per_thread
+    cfg, tile = _workload(args.workload, per_thread * cores, 0)
+    params = B.default_params(tile.n_samples)
+    for _ in range(args.warmup):
+        cpu_port_baseline(tile, params, max(per_thread // 8, 1), cores)
+    vals, t_all = [], 0.0
+    for _ in range(args.steps):
+        v, S, dt = cpu_port_baseline(tile, params, per_thread, cores)
+        vals.append(v); t_all += dt
+    value = float(np.mean(vals))
+    sample = "%d sites x %d samples of %s per step on %d threads (oracle C restatement, per-read)" % (
+        tile.n_sites, tile.n_samples, args.workload, cores)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "%s: synthetic %d samples x 1 Mb at %.1fx (bounded sample)" % (args.workload, tile.n_samples, cfg["depth"])},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C4", "C5"])
+    ap.add_argument("--sites", type=int, default=0, help="sites per GPU (default: the configuration's full window, C2 = 1e6)")
+    ap.add_argument("--subtiles", type=int, default=8, help="sub-tiles per step on the host-buffer (e2e) path")
+    ap.add_argument("--ref-sites-per-thread", type=int, default=6000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    import torch
+    import basevarc_b200 as B
+    from basevarc_b200.caller import PinnedArray
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    cfg, tile = _workload(args.workload, args.sites, rank)
+    S, N, R = tile.n_sites, tile.n_samples, tile.n_entries
+    caller = B.BaseTypeCaller(N, device=local, max_sites=S, max_entries=R)
+    units_per_gpu = S * N
+
+    # ---- kernel-only leg: inputs resident in HBM, device events on the launching stream -----------
+    caller.resident_upload(tile)
+    for _ in range(args.warmup):
+        caller.resident_run(1, flush_l2=False)
+    sampler = ClockSampler(local) if rank == 0 else None
+    barrier()
+    l0 = caller.kernel_launches
+    ms, per_kernel = caller.resident_run(args.steps, flush_l2=False)
+    barrier()
+    launches = caller.kernel_launches - l0
+    ms_step = max_over_ranks(ms)
+    recs = caller.resident_download()
+    value = world * units_per_gpu / (ms_step * 1e-3)
+
+    # ---- e2e leg: host buffers through bvc_enqueue / bvc_wait (pinned H2D + D2H inside the region) --
+    nsub = max(1, min(args.subtiles, S))
+    bounds = np.linspace(0, S, nsub + 1).astype(int)
+    subs, pins = [], []
+    for i in range(nsub):
+        t = tile.slice_sites(int(bounds[i]), int(bounds[i + 1]))
+        for k in ("ref_base", "entry_off", "code", "qual", "mapq", "rpr"):
+            src = getattr(t, k)
+            pa = PinnedArray(src.shape, src.dtype)
+            pa.array[...] = src
+            pins.append(pa)
+            setattr(t, k, pa.array)
+        subs.append(t)
+    outs = [PinnedArray((t.n_sites,), B.SITE_RESULT_DTYPE) for t in subs]
+    h2d = sum(t.nbytes() for t in subs)
+    d2h = sum(o.array.nbytes for o in outs)
+
+    def e2e_step():
+        tks = [caller.enqueue(t, o.array) for t, o in zip(subs, outs)]
+        for tk in tks:
+            caller.wait(tk)
+
+    for _ in range(args.warmup):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+    clocks = sampler.stop() if sampler else None
+    e2e_value = world * units_per_gpu / e2e_s
+    same = all(np.array_equal(np.concatenate([o.array for o in outs])[f], recs[f]) for f in ("depth", "lrt_ok", "alt_bases"))
+
+    # ---- roofline of the dominant (only) kernel ---------------------------------------------------
+    peak, peak_src = _peaks()
+    alg_bytes = _alg_bytes(tile)
+    achieved = alg_bytes / (ms * 1e-3) / 1e9
+    n_reads = recs["depth"].sum(1).astype(np.float64)
+    f_alg = float((n_reads * (21.0 * recs["em_passes"] - 3.0 * recs["em_fits"])).sum())
+    fp64_peak = B.measure_fp64_peak(local)
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        v, s_cpu, dt = cpu_port_baseline(tile, caller.params, args.ref_sites_per_thread, cores)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "first %d sites x %d samples of the same window, %.1f s (oracle C restatement, per-read)" % (s_cpu, N, dt)}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "%s: synthetic %d samples x %d sites at %.1fx depth per GPU" % (args.workload, N, S, cfg["depth"]),
+                   "sites_per_gpu": S, "n_samples": N, "entries_per_gpu": R, "parallelism": "window-sharded x%d, no collective" % world,
+                   "l2": "inputs (%.0f MB per launch) exceed the 126 MB L2; no flush needed" % (tile.nbytes() / 1e6)},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "matches_resident": bool(same)},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                     "kernel": "site_call_kernel", "kernel_ms": ms},
+        "fp64": {"algorithmic_tflops": f_alg / (ms * 1e-3) / 1e12, "peak_tflops_measured": fp64_peak,
+                 "frac": f_alg / (ms * 1e-3) / 1e12 / fp64_peak, "algorithmic_flop_per_launch": f_alg,
+                 "note": "F_alg counts the reference's per-read E/M/delta flops (SURVEY 8d); the kernel does fewer (class collapse)"},
+        "cpu_baseline": cpu,
+        "clocks": clocks,
+        "sites_lrt_positive": int(recs["lrt_ok"].sum()), "em_passes_per_site": float(recs["em_passes"].mean()),
+    }
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

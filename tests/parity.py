@@ -1,0 +1,63 @@
+"""Record-level comparison between two bvc_site_result arrays (tests only).
+
+Integer / index fields: bit-exact.  FP64 fields: |a-b| <= RTOL*max(|a|,|b|) with RTOL = 1e-9 (the
+tolerance BASELINE.json's north_star states), NaN == NaN, and an absolute floor of 1e-12 for values
+that are differences of O(1..1e4) log-likelihood sums (chi, and var_qual derived from it).
+"""
+import numpy as np
+
+from basevarc_b200._abi import EXACT_FIELDS, EXACT_FIELDS_IF_OK, FLOAT_FIELDS, FLOAT_FIELDS_IF_OK
+
+RTOL = 1e-9
+
+
+def _close(a, b, rtol=RTOL, atol=0.0):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    both_nan = np.isnan(a) & np.isnan(b)
+    with np.errstate(invalid="ignore"):
+        ok = np.abs(a - b) <= np.maximum(rtol * np.maximum(np.abs(a), np.abs(b)), atol)
+        ok |= (a == b)
+    return ok | both_nan
+
+
+def compare_records(got, want, allow_flagged=True):
+    """Returns (n_mismatching_sites, report lines).  Sites whose GPU record carries a boundary flag
+    (BVC_FLAG_*) are the stated threshold-boundary sites: they are listed, not counted."""
+    assert got.shape == want.shape
+    bad = np.zeros(got.shape[0], bool)
+    lines = []
+
+    def note(name, mask):
+        nonlocal bad
+        m = mask if mask.ndim == 1 else mask.any(axis=tuple(range(1, mask.ndim)))
+        if m.any():
+            idx = np.nonzero(m)[0]
+            lines.append("%s differs at %d sites, first %s: got %r want %r" % (
+                name, idx.size, idx[:5].tolist(), got[name][idx[0]].tolist(), want[name][idx[0]].tolist()))
+            bad |= m
+
+    ok_site = (want["lrt_ok"] == 1) & (got["lrt_ok"] == 1)
+    for f in EXACT_FIELDS:
+        note(f, got[f] != want[f])
+    for f in EXACT_FIELDS_IF_OK:
+        m = got[f] != want[f]
+        note(f, m & ok_site[:, None])
+    for f in FLOAT_FIELDS:
+        note(f, ~_close(got[f], want[f]))
+    # chi = 2*(lr_alt - lr_null) cancels two sums of magnitude ~n*|log L|: absolute floor scaled by depth
+    scale = np.maximum(1.0, want["depth"].sum(1).astype(np.float64)) * 1e-12
+    for f in FLOAT_FIELDS_IF_OK:
+        a, b = got[f], want[f]
+        if f in ("chi", "var_qual"):
+            m = ~_close(a, b, atol=0.0) & ~(np.abs(a - b) <= scale * 50)
+        else:
+            m = ~_close(a, b)
+        m = m if m.ndim == 1 else m.any(1)
+        note(f, m & ok_site)
+    flagged = got["flags"] != 0
+    n_flagged_bad = int((bad & flagged).sum())
+    if allow_flagged and n_flagged_bad:
+        lines.append("%d mismatching sites carry a threshold-boundary flag (listed, not counted): %s" % (
+            n_flagged_bad, np.nonzero(bad & flagged)[0][:20].tolist()))
+        bad &= ~flagged
+    return int(bad.sum()), lines
