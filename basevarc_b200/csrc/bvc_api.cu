@@ -9,7 +9,6 @@
 
 #include "../../include/bvc_gpu.h"
 #include "bvc_kernels.h"
-#include "bvc_site_kernel.cuh"
 
 namespace {
 

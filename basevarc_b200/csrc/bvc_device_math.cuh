@@ -40,7 +40,7 @@ __device__ inline double dm_lgamma_as245(double z)
 }
 
 // kfunc.c:56-82 (AS66)
-__device__ inline double dm_erfc(double x)
+__device__ __noinline__ double dm_erfc(double x)
 {
     const double SQRT2 = 1.41421356237309504880;
     double z = fabs(x) * SQRT2;
@@ -72,7 +72,7 @@ __device__ inline double dm_erfc(double x)
 __device__ inline double dm_normsf(double x) { return dm_erfc(x / sqrt(2.0)) / 2.0; }
 
 // kfunc.c:101-131,138-141
-__device__ inline double dm_gammaq(double s, double z)
+__device__ __noinline__ double dm_gammaq(double s, double z)
 {
     const double EPS = 1e-14, TINY = 1e-290;
     if (z <= 1. || z < s) {
@@ -136,7 +136,7 @@ __device__ __forceinline__ double dm_hg_move(const double* __restrict__ lgam, Hg
 }
 
 // kfunc.c:243-279 (two-sided p) + Algorithm.cpp:16-25.  Serial recurrence, warp-uniform.
-__device__ inline double dm_fisher(const double* __restrict__ lgam, int n11, int n12, int n21, int n22)
+__device__ __noinline__ double dm_fisher(const double* __restrict__ lgam, int n11, int n12, int n21, int n22)
 {
     int n1_ = n11 + n12, n_1 = n11 + n21, n = n11 + n12 + n21 + n22;
     int hi = n_1 < n1_ ? n_1 : n1_;

@@ -1,10 +1,33 @@
-// bvc_kernels.h -- launcher declarations shared by bvc_kernels.cu and bvc_api.cu
+// bvc_kernels.h -- kernel argument block + launcher declarations shared by bvc_kernels.cu and bvc_api.cu
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "../../include/bvc_gpu.h"
 
 namespace bvc {
-struct SiteArgs;
+
+constexpr int kWarpsPerBlock = 4;
+constexpr int kNQ = 128;                 // qual bins per base (int8 quals, src/BaseType.h:18)
+constexpr int kNBins = 4 * kNQ;          // (base, qual) classes
+// per-warp shared memory: lml f64[512] | hist u32[512] | keys u16[512] | codehist u32[32]
+constexpr int kWarpSmemBytes = kNBins * 8 + kNBins * 4 + kNBins * 2 + 32 * 4;
+
+struct SiteArgs {
+    const uint8_t*  ref_base;
+    const uint32_t* entry_off;
+    const uint8_t*  code;
+    const uint8_t*  qual;
+    const uint8_t*  mapq;
+    const uint8_t*  rpr;
+    bvc_site_result* out;
+    unsigned int*   counter;     // dynamic site fetch
+    const double*   lut;         // [4][128]: e/3, 1-e, log(e/3), log(1-e) with e = exp(MLN10TO10*q)
+    const double*   lgam;        // [n_samples+3] lgamma(k)
+    int    n_sites;
+    int    max_iter;
+    double min_af, lrt_thr, eps;
+};
+
 cudaError_t launch_site_call(const SiteArgs& a, int n_sm, cudaStream_t stream);
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream);
 }  // namespace bvc

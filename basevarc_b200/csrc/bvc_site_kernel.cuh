@@ -28,30 +28,9 @@
 #include <stdint.h>
 #include "../../include/bvc_gpu.h"
 #include "bvc_device_math.cuh"
+#include "bvc_kernels.h"
 
 namespace bvc {
-
-constexpr int kWarpsPerBlock = 4;
-constexpr int kNQ = 128;                 // qual bins per base (int8 quals, src/BaseType.h:18)
-constexpr int kNBins = 4 * kNQ;          // (base, qual) classes
-// per-warp shared memory: lml f64[512] | hist u32[512] | keys u16[512] | codehist u32[32]
-constexpr int kWarpSmemBytes = kNBins * 8 + kNBins * 4 + kNBins * 2 + 32 * 4;
-
-struct SiteArgs {
-    const uint8_t*  ref_base;
-    const uint32_t* entry_off;
-    const uint8_t*  code;
-    const uint8_t*  qual;
-    const uint8_t*  mapq;
-    const uint8_t*  rpr;
-    bvc_site_result* out;
-    unsigned int*   counter;     // dynamic site fetch
-    const double*   lut;         // [4][128]: e/3, 1-e, log(e/3), log(1-e) with e = exp(MLN10TO10*q)
-    const double*   lgam;        // [n_samples+3] lgamma(k)
-    int    n_sites;
-    int    max_iter;
-    double min_af, lrt_thr, eps;
-};
 
 struct WarpSmem {
     double*   lml;       // log marginal likelihood per class (state between EM passes)
@@ -73,7 +52,7 @@ __device__ __forceinline__ bool near_rel(double x, double thr) { return fabs(x -
 
 // One EM fit over the classes for the allele subset `mask` (bit b = base b).  Warp-uniform result.
 // Algorithm.cpp:115-130 with UpdateF's start vector and log-likelihood sum (BaseType.cpp:25-39,57-60).
-__device__ inline void em_fit(const SiteArgs& a, const WarpSmem& w, const double* lut_s, SiteState& st,
+__device__ __noinline__ void em_fit(const SiteArgs& a, const WarpSmem& w, const double* lut_s, SiteState& st,
                               unsigned mask, int lane, double& lr, double frq[4])
 {
     st.em_fits += 1;
@@ -95,9 +74,13 @@ __device__ inline void em_fit(const SiteArgs& a, const WarpSmem& w, const double
     }
     int dsum = 0;
     for (int j = 0; j < 4; ++j) if (mask >> j & 1) dsum += st.depth[j];
-    double f[4], eap[4];
-    for (int j = 0; j < 4; ++j) f[j] = (dsum > 0 && (mask >> j & 1)) ? (double)st.depth[j] / dsum : 0.0;
-    const int n = st.n_reads;
+    double f0, f1, f2, f3;
+    f0 = (dsum > 0 && (mask & 1)) ? (double)st.depth[0] / dsum : 0.0;
+    f1 = (dsum > 0 && (mask & 2)) ? (double)st.depth[1] / dsum : 0.0;
+    f2 = (dsum > 0 && (mask & 4)) ? (double)st.depth[2] / dsum : 0.0;
+    f3 = (dsum > 0 && (mask & 8)) ? (double)st.depth[3] / dsum : 0.0;
+    double e0 = 0, e1 = 0, e2 = 0, e3v = 0;
+    const double n = (double)st.n_reads;
     for (int it = 0; it <= a.max_iter; ++it) {
         double acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0, dl = 0;
         for (int c = lane; c < st.ncls; c += 32) {
@@ -105,19 +88,24 @@ __device__ inline void em_fit(const SiteArgs& a, const WarpSmem& w, const double
             const int q = key & (kNQ - 1), b = key >> 7;
             const double cnt = (double)w.hist[c];
             const double e3 = lut_s[q], ome = lut_s[kNQ + q];
-            const double l0 = f[0] * (b == 0 ? ome : e3);
-            const double l1 = f[1] * (b == 1 ? ome : e3);
-            const double l2 = f[2] * (b == 2 ? ome : e3);
-            const double l3 = f[3] * (b == 3 ? ome : e3);
-            double ml = l0; ml += l1; ml += l2; ml += l3;            // Algorithm.cpp:76-79
-            acc0 += cnt * (l0 / ml); acc1 += cnt * (l1 / ml);         // :80-84 then :87-91
-            acc2 += cnt * (l2 / ml); acc3 += cnt * (l3 / ml);
+            const double l0 = f0 * (b == 0 ? ome : e3);
+            const double l1 = f1 * (b == 1 ? ome : e3);
+            const double l2 = f2 * (b == 2 ? ome : e3);
+            const double l3 = f3 * (b == 3 ? ome : e3);
+            const double ml = ((l0 + l1) + l2) + l3;                   // Algorithm.cpp:76-79
+            // post_j = l_j / ml (:80-84) as l_j * (1/ml): one IEEE division per class instead of four
+            // (<= 1.5 ulp from the reference; 0 * (1/0) = NaN keeps the 0/0 semantics of qual-0 reads).
+            const double r = cnt / ml;
+            acc0 += l0 * r; acc1 += l1 * r; acc2 += l2 * r; acc3 += l3 * r;   // :87-91, count-weighted
             const double lg = log(ml);
             if (it > 0) dl += cnt * fabs(lg - w.lml[c]);              // :103-113
             w.lml[c] = lg;
         }
-        eap[0] = warp_sum(acc0) / n; eap[1] = warp_sum(acc1) / n;
-        eap[2] = warp_sum(acc2) / n; eap[3] = warp_sum(acc3) / n;
+        // only alleles inside the subset carry mass; the others stay exactly 0
+        if (mask & 1) e0 = warp_sum(acc0) / n;
+        if (mask & 2) e1 = warp_sum(acc1) / n;
+        if (mask & 4) e2 = warp_sum(acc2) / n;
+        if (mask & 8) e3v = warp_sum(acc3) / n;
         st.em_passes += 1;
         if (it > 0) {
             const double delta = warp_sum(dl);
@@ -125,12 +113,12 @@ __device__ inline void em_fit(const SiteArgs& a, const WarpSmem& w, const double
             if (delta < a.eps) break;                                  // :124
         }
         if (it == a.max_iter) break;
-        for (int j = 0; j < 4; ++j) f[j] = eap[j];                     // :95-101
+        f0 = e0; f1 = e1; f2 = e2; f3 = e3v;                            // :95-101
     }
     double s = 0.0;
     for (int c = lane; c < st.ncls; c += 32) s += (double)w.hist[c] * w.lml[c];   // BaseType.cpp:57-60
     lr = warp_sum(s);
-    for (int j = 0; j < 4; ++j) frq[j] = eap[j];
+    frq[0] = e0; frq[1] = e1; frq[2] = e2; frq[3] = e3v;
 }
 
 struct LrtOut {
@@ -141,7 +129,7 @@ struct LrtOut {
 };
 
 // BaseType::LRT (BaseType.cpp:73-139) over the candidate list comb[0..n_comb) (base codes, in order).
-__device__ inline void lrt_ladder(const SiteArgs& a, const WarpSmem& w, const double* lut_s, SiteState& st,
+__device__ __noinline__ void lrt_ladder(const SiteArgs& a, const WarpSmem& w, const double* lut_s, SiteState& st,
                                   int ref, const int* comb, int n_comb, int lane, LrtOut& o)
 {
     o.ok = 0; o.n_alt = 0; o.chi = 0.0; o.var_qual = 0.0;
@@ -203,7 +191,7 @@ __device__ inline void lrt_ladder(const SiteArgs& a, const WarpSmem& w, const do
 }
 
 // Exact Mann-Whitney from two 256-bin histograms (ref = x, alt = y), Algorithm.cpp:27-67.
-__device__ inline double ranksum_hist(const uint32_t* hr, const uint32_t* ha, int lane)
+__device__ __noinline__ double ranksum_hist(const uint32_t* hr, const uint32_t* ha, int lane)
 {
     // lane L owns values 255-8L .. 248-8L (descending order overall)
     uint32_t r[8], t[8]; uint32_t tl = 0, rl = 0;

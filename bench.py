@@ -58,6 +58,12 @@ class ClockSampler:
         for ln in self.proc.stdout:
             self.lines.append(ln.strip())
 
+    def wait_started(self, timeout=15.0):
+        """nvidia-smi's start-up can stall GPU work for seconds: let it settle before the timed region."""
+        t0 = time.time()
+        while self.proc and len(self.lines) < 3 and time.time() - t0 < timeout:
+            time.sleep(0.05)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -191,6 +197,8 @@ def main():
     for _ in range(args.warmup):
         caller.resident_run(1, flush_l2=False)
     sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.wait_started()
     barrier()
     l0 = caller.kernel_launches
     ms, per_kernel = caller.resident_run(args.steps, flush_l2=False)

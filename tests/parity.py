@@ -9,6 +9,7 @@ import numpy as np
 from basevarc_b200._abi import EXACT_FIELDS, EXACT_FIELDS_IF_OK, FLOAT_FIELDS, FLOAT_FIELDS_IF_OK
 
 RTOL = 1e-9
+PHRED_ATOL = 1e-12
 
 
 def _close(a, b, rtol=RTOL, atol=0.0):
@@ -42,8 +43,10 @@ def compare_records(got, want, allow_flagged=True):
     for f in EXACT_FIELDS_IF_OK:
         m = got[f] != want[f]
         note(f, m & ok_site[:, None])
+    # phred-scaled p-values (-10*log10 p): for p -> 1 the value -> 0 by cancellation, so a 1e-15 relative
+    # difference in p shows as ~1e-15 ABSOLUTE in the phred value; PHRED_ATOL covers exactly that.
     for f in FLOAT_FIELDS:
-        note(f, ~_close(got[f], want[f]))
+        note(f, ~_close(got[f], want[f], atol=PHRED_ATOL))
     # chi = 2*(lr_alt - lr_null) cancels two sums of magnitude ~n*|log L|: absolute floor scaled by depth
     scale = np.maximum(1.0, want["depth"].sum(1).astype(np.float64)) * 1e-12
     for f in FLOAT_FIELDS_IF_OK:
@@ -51,7 +54,7 @@ def compare_records(got, want, allow_flagged=True):
         if f in ("chi", "var_qual"):
             m = ~_close(a, b, atol=0.0) & ~(np.abs(a - b) <= scale * 50)
         else:
-            m = ~_close(a, b)
+            m = ~_close(a, b, atol=PHRED_ATOL if f in ("vcf_fs", "ranksum") else 0.0)
         m = m if m.ndim == 1 else m.any(1)
         note(f, m & ok_site)
     flagged = got["flags"] != 0
