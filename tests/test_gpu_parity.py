@@ -86,3 +86,15 @@ def test_capacity_and_argument_errors():
     caller.close()
     with pytest.raises(B.BvcError):
         B.BaseTypeCaller(100, maf=0.0)
+
+
+@pytest.mark.parametrize("name", ["synth_ref_lowpass", "synth_ref_highpoly"])
+def test_gpu_vs_reference_binary_golden(name):
+    """CUDA path against the text the unmodified reference binary printed (tests/golden, no oracle involved)."""
+    import refrun
+    tile, cvg, vcf = refrun.load_golden_tile(name)
+    caller = B.BaseTypeCaller(tile.n_samples, max_sites=tile.n_sites, max_entries=tile.n_entries)
+    rec = caller.call_sites(tile)
+    caller.close()
+    bad = refrun.compare_records_to_text(tile, rec, cvg, vcf)
+    assert not bad, "\n".join(bad[:5])
