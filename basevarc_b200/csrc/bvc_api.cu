@@ -9,6 +9,7 @@
 
 #include "../../include/bvc_gpu.h"
 #include "bvc_kernels.h"
+#include "bvc_pipeline_args.h"
 
 namespace {
 
@@ -21,6 +22,14 @@ struct Slot {
     uint32_t *d_off = nullptr, *d_sample = nullptr;
     bvc_site_result* d_out = nullptr;
     unsigned int* d_counter = nullptr;
+    // staged-pipeline intermediates (bvc_pipeline.cuh)
+    bvc::SiteSum* d_sum = nullptr;
+    uint32_t* d_cls = nullptr;
+    bvc::Ladder* d_lad = nullptr;
+    bvc::FitRes* d_fit = nullptr;
+    uint8_t* d_state = nullptr;
+    uint32_t *d_qa = nullptr, *d_qb = nullptr, *d_vcf_list = nullptr, *d_legacy_list = nullptr;
+    uint32_t* d_ctr = nullptr;     // [16]: cls_cursor, qa_n, qb_n, q_head, vcf_n, legacy_n
     uint64_t ticket = 0;       // 0 = idle
     int n_sites = 0;
     int64_t n_entries = 0;
@@ -40,6 +49,7 @@ struct bvc_ctx {
     size_t flush_bytes = 0;
     uint64_t next_ticket = 1;
     int64_t launches = 0;
+    bool legacy_only = false;      // BVC_LEGACY_KERNEL=1: the single warp-per-site kernel for every site (A/B checks)
     std::string err;
     bool resident = false;
 };
@@ -76,6 +86,17 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
     if (ctx->prm.n_groups > 0) CK(cudaMalloc(&s.d_sample, (R + 4) * sizeof(uint32_t)));
     CK(cudaMalloc(&s.d_out, (S + 1) * sizeof(bvc_site_result)));
     CK(cudaMalloc(&s.d_counter, sizeof(unsigned int)));
+    size_t pool = R < S * (size_t)bvc::kNBins ? R : S * (size_t)bvc::kNBins;
+    CK(cudaMalloc(&s.d_sum, (S + 1) * sizeof(bvc::SiteSum)));
+    CK(cudaMalloc(&s.d_cls, (pool + 64) * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.d_lad, (S + 1) * sizeof(bvc::Ladder)));
+    CK(cudaMalloc(&s.d_fit, (S + 1) * 4 * sizeof(bvc::FitRes)));
+    CK(cudaMalloc(&s.d_state, S + 16));
+    CK(cudaMalloc(&s.d_qa, (4 * S + 16) * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.d_qb, (4 * S + 16) * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.d_vcf_list, (S + 16) * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.d_legacy_list, (S + 16) * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.d_ctr, 16 * sizeof(uint32_t)));
     return BVC_OK;
 }
 
@@ -83,6 +104,8 @@ void free_slot(Slot& s)
 {
     cudaFree(s.d_ref); cudaFree(s.d_off); cudaFree(s.d_code); cudaFree(s.d_qual); cudaFree(s.d_mapq);
     cudaFree(s.d_rpr); cudaFree(s.d_sample); cudaFree(s.d_out); cudaFree(s.d_counter);
+    cudaFree(s.d_sum); cudaFree(s.d_cls); cudaFree(s.d_lad); cudaFree(s.d_fit); cudaFree(s.d_state);
+    cudaFree(s.d_qa); cudaFree(s.d_qb); cudaFree(s.d_vcf_list); cudaFree(s.d_legacy_list); cudaFree(s.d_ctr);
     if (s.done) cudaEventDestroy(s.done);
     if (s.stream) cudaStreamDestroy(s.stream);
     s = Slot();
@@ -125,8 +148,25 @@ int launch(bvc_ctx* ctx, Slot& s)
     a.out = s.d_out; a.counter = s.d_counter; a.lut = ctx->d_lut; a.lgam = ctx->d_lgam;
     a.n_sites = s.n_sites; a.max_iter = ctx->prm.em_max_iter;
     a.min_af = ctx->prm.min_af; a.lrt_thr = ctx->prm.lrt_threshold; a.eps = ctx->prm.em_epsilon;
-    CK(bvc::launch_site_call(a, ctx->n_sm, s.stream));
-    ctx->launches += 1;
+    a.site_list = nullptr; a.list_n = nullptr;
+    if (ctx->legacy_only) {
+        CK(bvc::launch_site_call(a, ctx->n_sm, s.stream));
+        ctx->launches += 1;
+        return BVC_OK;
+    }
+    CK(cudaMemsetAsync(s.d_ctr, 0, 16 * sizeof(uint32_t), s.stream));
+    bvc::PipeArgs p;
+    p.s = a;
+    p.sum = s.d_sum; p.cls = s.d_cls; p.cls_cursor = s.d_ctr + 0;
+    p.lad = s.d_lad; p.fit = s.d_fit; p.state = s.d_state;
+    p.q_in = s.d_qb; p.q_in_n = s.d_ctr + 2;          // swapped before the first EM stage
+    p.q_out = s.d_qa; p.q_out_n = s.d_ctr + 1;
+    p.q_in_head = s.d_ctr + 3;
+    p.vcf_list = s.d_vcf_list; p.vcf_n = s.d_ctr + 4;
+    p.legacy_list = s.d_legacy_list; p.legacy_n = s.d_ctr + 5;
+    int nl = 0;
+    CK(bvc::launch_pipeline(p, ctx->n_sm, s.stream, &nl));
+    ctx->launches += nl;
     return BVC_OK;
 }
 
@@ -184,13 +224,16 @@ int bvc_create(bvc_ctx** out, int device, const bvc_params* prm)
     }
     if (prop.major < 10) { ctx->err = "bvc_create: device is not sm_100 class (kernels are built for sm_100a only)"; return fail(BVC_ERR_CUDA); }
     ctx->n_sm = prop.multiProcessorCount;
+    { const char* e = getenv("BVC_LEGACY_KERNEL"); ctx->legacy_only = (e && e[0] == '1'); }
+    if (!(prm->em_epsilon <= 0.01)) { ctx->err = "bvc_create: em_epsilon must be <= 0.01 (see the delta bound in bvc_pipeline.cuh)"; return fail(BVC_ERR_ARG); }
 
     // host-built tables (glibc): per-qual likelihoods (src/BaseType.cpp:13-15) and lgamma(k)
-    std::vector<double> lut(4 * bvc::kNQ), lgam((size_t)prm->n_samples + 3);
+    std::vector<double> lut(5 * bvc::kNQ), lgam((size_t)prm->n_samples + 3);
     for (int q = 0; q < bvc::kNQ; ++q) {
         const double e = exp(-0.23025850929940458 * q);      // MLN10TO10, src/BaseType.h:10
         lut[q] = e / 3.0; lut[bvc::kNQ + q] = 1.0 - e;
         lut[2 * bvc::kNQ + q] = log(e / 3.0); lut[3 * bvc::kNQ + q] = log(1.0 - e);
+        lut[4 * bvc::kNQ + q] = (1.0 - e) - e / 3.0;
     }
     for (size_t k = 0; k < lgam.size(); ++k) lgam[k] = k == 0 ? 0.0 : lgamma((double)k);
     auto ck = [&](cudaError_t e, const char* what) {

@@ -15,6 +15,9 @@
 
 namespace bvc {
 
+// a hard FP64 threshold met within 1e-9 relative: the site is reported as a threshold-boundary site
+__device__ __forceinline__ bool near_rel(double x, double thr) { return fabs(x - thr) <= 1e-9 * fabs(thr); }
+
 __device__ __forceinline__ double dm_phred(double p)
 {
     double v = -10.0 * log10(p);

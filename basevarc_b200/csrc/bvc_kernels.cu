@@ -2,6 +2,7 @@
 // See bvc_site_kernel.cuh for the design and the reference code each phase replaces.
 #include "bvc_kernels.h"
 #include "bvc_site_kernel.cuh"
+#include "bvc_pipeline.cuh"
 
 namespace bvc {
 
@@ -27,7 +28,10 @@ site_call_kernel(SiteArgs a)
         int site = 0;
         if (lane == 0) site = (int)atomicAdd(a.counter, 1u);
         site = __shfl_sync(0xffffffffu, site, 0);
-        if (site >= a.n_sites) break;
+        if (a.site_list) {
+            if (site >= (int)*a.list_n) break;
+            site = (int)a.site_list[site];
+        } else if (site >= a.n_sites) break;
 
         const uint32_t b0 = a.entry_off[site], b1 = a.entry_off[site + 1];
         const int ref = a.ref_base[site] & 3;
@@ -189,6 +193,46 @@ cudaError_t launch_site_call(const SiteArgs& a, int n_sm, cudaStream_t stream)
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
     site_call_kernel<<<(unsigned)grid, kWarpsPerBlock * 32, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, int* n_launches)
+{
+    PipeArgs a = a0;
+    const int S = a.s.n_sites;
+    int launches = 0;
+    static int occ_hist = 0, occ_em = 0, occ_vcf = 0, occ_leg = 0;
+    if (!occ_hist) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist, site_hist_kernel, kHistWarps * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_em, em_fit_kernel, kEmThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_vcf, vcf_stats_kernel, kVcfWarps * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_leg, site_call_kernel, kWarpsPerBlock * 32, 0);
+        if (occ_hist < 1) occ_hist = 1; if (occ_em < 1) occ_em = 1; if (occ_vcf < 1) occ_vcf = 1; if (occ_leg < 1) occ_leg = 1;
+    }
+    auto capped = [&](long long want, int per_sm) { long long g = (long long)n_sm * per_sm; if (g > want) g = want; return (unsigned)(g < 1 ? 1 : g); };
+    const unsigned site_blocks = (unsigned)((S + 127) / 128);
+
+    site_hist_kernel<<<capped((S + kHistWarps - 1) / kHistWarps, occ_hist), kHistWarps * 32, 0, stream>>>(a);
+    site_prepare_kernel<<<site_blocks, 128, 0, stream>>>(a);
+    launches += 2;
+    // at most three EM stages: the full model, the (n-1)-subsets (n >= 3), the pairs of a reduced 4-candidate site
+    for (int stage = 0; stage < 3; ++stage) {
+        uint32_t* t;
+        t = a.q_in; a.q_in = a.q_out; a.q_out = t;
+        t = a.q_in_n; a.q_in_n = a.q_out_n; a.q_out_n = t;
+        cudaMemsetAsync(a.q_out_n, 0, sizeof(uint32_t), stream);
+        cudaMemsetAsync(a.q_in_head, 0, sizeof(uint32_t), stream);
+        em_fit_kernel<<<(unsigned)(n_sm * occ_em), kEmThreads, 0, stream>>>(a);
+        ladder_kernel<<<site_blocks, 128, 0, stream>>>(a);
+        launches += 2;
+    }
+    vcf_stats_kernel<<<capped(S, occ_vcf), kVcfWarps * 32, 0, stream>>>(a);
+    // qual-0 sites: the IEEE-faithful warp-per-site kernel over the legacy list
+    SiteArgs leg = a.s;
+    leg.site_list = a.legacy_list; leg.list_n = a.legacy_n;
+    site_call_kernel<<<(unsigned)(n_sm * occ_leg), kWarpsPerBlock * 32, 0, stream>>>(leg);
+    launches += 2;
+    if (n_launches) *n_launches = launches;
     return cudaGetLastError();
 }
 

@@ -21,6 +21,8 @@ struct SiteArgs {
     const uint8_t*  rpr;
     bvc_site_result* out;
     unsigned int*   counter;     // dynamic site fetch
+    const uint32_t* site_list;   // optional: process only these sites (legacy path of the pipeline) ...
+    const uint32_t* list_n;      // ... their count (device memory)
     const double*   lut;         // [4][128]: e/3, 1-e, log(e/3), log(1-e) with e = exp(MLN10TO10*q)
     const double*   lgam;        // [n_samples+3] lgamma(k)
     int    n_sites;
@@ -28,6 +30,9 @@ struct SiteArgs {
     double min_af, lrt_thr, eps;
 };
 
+struct PipeArgs;
 cudaError_t launch_site_call(const SiteArgs& a, int n_sm, cudaStream_t stream);
+// The staged pipeline (bvc_pipeline.cuh).  q_a/q_b + their counters ping-pong between stages.
+cudaError_t launch_pipeline(const PipeArgs& a, int n_sm, cudaStream_t stream, int* n_launches);
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream);
 }  // namespace bvc

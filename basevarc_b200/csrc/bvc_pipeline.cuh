@@ -1,0 +1,567 @@
+// bvc_pipeline.cuh -- the staged B200 pipeline of the per-site `basetype` calling core.
+//
+// One tile of sites goes through five kernels instead of the reference's one-site-at-a-time loop
+// (bt_s -> bt_f -> BaseType::LRT -> EM -> WriteVcf; paths under /root/reference):
+//
+//   K1 site_hist_kernel    warp per site.  Streams the packed entries ONCE (code + qual bytes, 32-bit
+//                          coalesced loads) into a shared-memory (base, qual) histogram; compacts the
+//                          non-empty classes to a global pool; derives depth / strand tables from a
+//                          32-bin code histogram.  HBM-bound by construction.
+//                          (bt_f counting src/BaseVarC.cpp:548-602; BaseType ctor src/BaseType.cpp:5-23)
+//   K2 site_prepare_kernel thread per site.  CVG Fisher + SOR, candidate filter, first ladder step,
+//                          emits the full-model fit.  (src/BaseVarC.cpp:603-608, src/BaseType.cpp:73-90)
+//   K3 em_fit_kernel       THREAD PER FIT, flattened (pass, class) loop with dynamic refill: every lane
+//                          always has a class to process, no shuffles, no per-class state.  FP64-bound.
+//                          (EM / singleEM / delta_bylog src/Algorithm.cpp:69-130; UpdateF src/BaseType.cpp:41-71)
+//   K4 ladder_kernel       thread per site.  log-likelihood sums of the finished fits, LRT decision,
+//                          next-stage subsets or final ALT set / AF / chi-square QUAL.
+//                          (src/BaseType.cpp:93-135, combs_ :237-255, chisf src/Algorithm.cpp:3-7)
+//   K5 vcf_stats_kernel    warp per LRT-positive site.  VCF strand table Fisher/SOR and the three
+//                          Mann-Whitney tests from 256-bin histograms.  (src/BaseType.cpp:149-197)
+//
+// EM restatement used by K3/K4 (all reads of a site with equal (base, qual) share one E-step row):
+//   ml_c   = sum_j f_j L_cj = e3_q * F + f_b * (ome_q - e3_q),  F = sum_j f_j          (Algorithm.cpp:76-79)
+//   eap_j  = f_j * (sum_c cnt_c e3_q / ml_c + sum_{c: b=j} cnt_c (ome_q - e3_q) / ml_c) / n   (:80-91)
+//   delta  = sum_c cnt_c |log ml'_c - log ml_c| = sum_c cnt_c |log1p((ml_c - ml'_c) / ml'_c)|  (:103-113)
+// with ml_c recomputed from the previous pass's f (no per-class state).  log1p is an 8-term series when
+// |x| <= 2^-6; a class with |x| > 2^-6 alone contributes >= |x|/(1+|x|) > 0.015 > epsilon, so the pass
+// is "not converged" without evaluating it.  Differences from the reference are pure rounding
+// (<= a few ulp per pass); the hard thresholds are flagged when met within 1e-9 (BVC_FLAG_*).
+#pragma once
+#include <stdint.h>
+#include "../../include/bvc_gpu.h"
+#include "bvc_device_math.cuh"
+#include "bvc_kernels.h"
+#include "bvc_pipeline_args.h"
+
+namespace bvc {
+
+// ---- shared per-class arithmetic ----------------------------------------------------------------------
+__device__ __forceinline__ double sel4(int b, double v0, double v1, double v2, double v3)
+{
+    return b == 0 ? v0 : (b == 1 ? v1 : (b == 2 ? v2 : v3));
+}
+// lut_s layout: [0..128) e/3, [128..256) 1-e, [256..384) log(e/3), [384..512) log(1-e), [512..640) (1-e) - e/3
+__device__ __forceinline__ double class_ml(const double* lut_s, int q, double fb, double F)
+{
+    return fma(fb, lut_s[4 * kNQ + q], lut_s[q] * F);
+}
+
+// 1/x to <= 1 ulp for normal positive x: hardware seed + two Newton steps (no slow path)
+__device__ __forceinline__ double fast_rcp(double x)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);          // third step: safe whatever the seed's precision (>= 8 bits suffices)
+    r = fma(r, e, r);
+    return r;
+}
+
+// log1p(x) for |x| <= 2^-6: x * (1 - x/2 + x^2/3 - ... - x^7/8), truncation < 4e-16 relative
+__device__ __forceinline__ double log1p_small(double x)
+{
+    double p = -1.0 / 8.0;
+    p = fma(p, x, 1.0 / 7.0);
+    p = fma(p, x, -1.0 / 6.0);
+    p = fma(p, x, 1.0 / 5.0);
+    p = fma(p, x, -1.0 / 4.0);
+    p = fma(p, x, 1.0 / 3.0);
+    p = fma(p, x, -1.0 / 2.0);
+    p = fma(p, x, 1.0);
+    return p * x;
+}
+
+
+// =====================================================================================================
+// K1: warp per site -- stream entries, histogram, compact classes, strand tables
+// =====================================================================================================
+constexpr int kHistWarps = 8;
+
+__global__ void __launch_bounds__(kHistWarps * 32)
+site_hist_kernel(PipeArgs a)
+{
+    __shared__ uint32_t hist_s[kHistWarps][kNBins];
+    __shared__ uint32_t code_s[kHistWarps][32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t* hist = hist_s[wid];
+    uint32_t* chist = code_s[wid];
+    for (int i = lane; i < kNBins; i += 32) hist[i] = 0;
+    chist[lane] = 0;
+    __syncwarp();
+
+    const int n_warps = gridDim.x * kHistWarps;
+    for (int site = blockIdx.x * kHistWarps + wid; site < a.s.n_sites; site += n_warps) {
+        const uint32_t b0 = a.s.entry_off[site], b1 = a.s.entry_off[site + 1];
+        const int ref = a.s.ref_base[site] & 3;
+        // ---- stream: 4 entries per lane per 32-bit load, 128 B per warp-load, both arrays in flight ----
+        unsigned qmin = 127, qmax = 0;
+        const uint32_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;
+        const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
+        const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
+        for (uint32_t wbase = w0; wbase < w1; wbase += 32) {
+            const uint32_t wi = wbase + lane;
+            uint32_t cw = 0, qw = 0;
+            if (wi < w1) { cw = __ldg(code4 + wi); qw = __ldg(qual4 + wi); }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t e = wi * 4 + k;
+                const bool valid = (wi < w1) && e >= b0 && e < b1;
+                const unsigned c = (cw >> (8 * k)) & 31u;
+                const unsigned q = (qw >> (8 * k)) & (kNQ - 1);
+                // code histogram: lanes with equal codes elect one leader -> conflict-free shared atomics
+                const unsigned key = valid ? c : 32u;
+                const unsigned peers = __match_any_sync(0xffffffffu, key);
+                if (valid && (__ffs(peers) - 1) == lane) atomicAdd(&chist[c], (unsigned)__popc(peers));
+                if (valid && !(c & 16)) {
+                    atomicAdd(&hist[((c & 3) << 7) | q], 1u);
+                    qmin = min(qmin, q); qmax = max(qmax, q);
+                }
+            }
+        }
+        __syncwarp();
+        const int cnt = (int)chist[lane];          // lane = base | strand << 3 | indel << 4
+        chist[lane] = 0;
+        qmin = __reduce_min_sync(0xffffffffu, qmin);
+        qmax = __reduce_max_sync(0xffffffffu, qmax);
+
+        int depth[4], fwd[4], n_reads = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {               // src/BaseVarC.cpp:550-559
+            fwd[b] = __shfl_sync(0xffffffffu, cnt, b | 8);
+            depth[b] = __shfl_sync(0xffffffffu, cnt, b) + fwd[b];
+            n_reads += depth[b];
+        }
+        // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
+        int best = -1, bestd = -1, second = -1, secondd = -1;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            if (depth[b] > bestd) { second = best; secondd = bestd; best = b; bestd = depth[b]; }
+            else if (depth[b] > secondd) { second = b; secondd = depth[b]; }
+        }
+        const int alt = (best != ref) ? best : second;
+        // src/BaseVarC.cpp:587-602: 2x2 table over ALL entries (indel entries carry stale base/strand)
+        const int c0 = __shfl_sync(0xffffffffu, cnt, ref | 8) + __shfl_sync(0xffffffffu, cnt, ref | 24);
+        const int c1 = __shfl_sync(0xffffffffu, cnt, ref) + __shfl_sync(0xffffffffu, cnt, ref | 16);
+        const int c2 = __shfl_sync(0xffffffffu, cnt, alt | 8) + __shfl_sync(0xffffffffu, cnt, alt | 24);
+        const int c3 = __shfl_sync(0xffffffffu, cnt, alt) + __shfl_sync(0xffffffffu, cnt, alt | 16);
+
+        // ---- compact the non-empty classes into the global pool (count, allocate, write) ----------------
+        int ncls = 0;
+        const unsigned qlo = qmin & ~31u;
+        if (n_reads > 0) {
+            for (int b = 0; b < 4; ++b) {
+                if (depth[b] == 0) continue;
+                for (unsigned q0 = qlo; q0 <= qmax; q0 += 32)
+                    ncls += __popc(__ballot_sync(0xffffffffu, hist[(b << 7) + q0 + lane] != 0));
+            }
+        }
+        uint32_t off = 0;
+        if (lane == 0 && ncls) off = atomicAdd(a.cls_cursor, (uint32_t)ncls);
+        off = __shfl_sync(0xffffffffu, off, 0);
+        if (n_reads > 0) {
+            uint32_t pos = off;
+            for (int b = 0; b < 4; ++b) {
+                if (depth[b] == 0) continue;
+                for (unsigned q0 = qlo; q0 <= qmax; q0 += 32) {
+                    const unsigned bin = (b << 7) + q0 + lane;
+                    const uint32_t v = hist[bin];
+                    const unsigned m = __ballot_sync(0xffffffffu, v != 0);
+                    if (v) {
+                        a.cls[pos + __popc(m & ((1u << lane) - 1))] = (v << 9) | bin;
+                        hist[bin] = 0;
+                    }
+                    pos += __popc(m);
+                }
+            }
+        }
+        // ---- 64-byte summary: lanes 0..15 store one word each ----------------------------------------------
+        int word = 0;
+        if (lane < 4) word = depth[lane];
+        else if (lane < 8) word = fwd[lane - 4];
+        else if (lane == 8) word = c0; else if (lane == 9) word = c1; else if (lane == 10) word = c2; else if (lane == 11) word = c3;
+        else if (lane == 12) word = (int)off;
+        else if (lane == 13) word = ncls | (alt << 16) | ((n_reads > 0 && qmin == 0) ? (1 << 24) : 0);
+        else if (lane == 14) word = (int)(b1 - b0);
+        if (lane < 16) reinterpret_cast<int*>(a.sum + site)[lane] = word;
+        __syncwarp();
+    }
+}
+
+// =====================================================================================================
+// shared: queue append, finalisation of a site's LRT
+// =====================================================================================================
+__device__ __forceinline__ uint32_t warp_agg_append(uint32_t* ctr, bool pred)
+{
+    const unsigned active = __activemask();
+    const unsigned m = __ballot_sync(active, pred);
+    uint32_t base = 0;
+    if (!pred) return 0;
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    if (lane == leader) base = atomicAdd(ctr, (uint32_t)__popc(m));
+    base = __shfl_sync(m, base, leader);
+    return base + __popc(m & ((1u << lane) - 1));
+}
+
+// BaseType.cpp:111-135 + the LRT half of the output record.
+__device__ __noinline__ void finalize_site(const PipeArgs& a, int site, int ref, const int* depth, int n_reads,
+                                           const int8_t* cand, int n, const double* frq, double chi_t,
+                                           int em_fits, int em_passes, uint32_t flags)
+{
+    bvc_site_result* r = a.s.out + site;
+    int n_alt = 0; int8_t alt_bases[3] = {-1, -1, -1};
+    double af[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int t = 0; t < n; ++t) {
+        const int b = cand[t];
+        if (b != ref && n_alt < 3) { alt_bases[n_alt++] = (int8_t)b; af[b] = sel4(b, frq[0], frq[1], frq[2], frq[3]); }
+    }
+    double vq = 0.0;
+    const int ok = n_alt > 0;
+    if (ok) {
+        const double total = (double)n_reads;
+        const int b0 = cand[0];
+        const double rr = (double)(b0 == 0 ? depth[0] : b0 == 1 ? depth[1] : b0 == 2 ? depth[2] : depth[3]) / total;
+        if (n == 1 && total > 10 && rr > 0.5) vq = 5000.0;
+        else if (chi_t <= 0) vq = 0.0;
+        else {
+            const double p = dm_chisf(chi_t, 1.0);
+            vq = (p != 0) ? -10.0 * log10(p) : 10000.0;
+            if (vq == 0) vq = 0.0;
+        }
+        if (near_rel(vq, 60.0)) flags |= BVC_FLAG_QUAL60;
+    }
+    r->af_lrt[0] = af[0]; r->af_lrt[1] = af[1]; r->af_lrt[2] = af[2]; r->af_lrt[3] = af[3];
+    r->chi = chi_t; r->var_qual = vq;
+    r->em_fits = em_fits; r->em_passes = em_passes; r->flags = flags;
+    r->lrt_ok = (int8_t)ok; r->n_alt = (int8_t)n_alt;
+    r->alt_bases[0] = alt_bases[0]; r->alt_bases[1] = alt_bases[1]; r->alt_bases[2] = alt_bases[2];
+    a.state[site] = kStDone;
+    if (ok) a.vcf_list[atomicAdd(a.vcf_n, 1u)] = (uint32_t)site;
+}
+
+// =====================================================================================================
+// K2: thread per site -- CVG Fisher/SOR, candidate filter, emit the full-model fit
+// =====================================================================================================
+__global__ void __launch_bounds__(128)
+site_prepare_kernel(PipeArgs a)
+{
+    const int site = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in = site < a.s.n_sites;
+    bool emit = false;
+    if (in) {
+        const SiteSum su = a.sum[site];
+        const int ref = a.s.ref_base[site] & 3;
+        const int n_reads = su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3];
+        bvc_site_result* r = a.s.out + site;
+        if (su.has_q0) {
+            a.state[site] = kStLegacy;
+            a.legacy_list[atomicAdd(a.legacy_n, 1u)] = (uint32_t)site;
+        } else {
+            r->cvg_fs = dm_fisher(a.s.lgam, su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
+            r->cvg_sor = dm_sor(su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
+            r->vcf_fs = 0.0; r->vcf_sor = 0.0; r->ranksum[0] = 0.0; r->ranksum[1] = 0.0; r->ranksum[2] = 0.0;
+            r->n_entries = su.n_entries;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { r->depth[j] = su.depth[j]; r->cvg_strand[j] = su.cvg[j]; r->vcf_strand[j] = 0; }
+            r->cvg_alt_base = (int8_t)su.alt; r->pad[0] = 0; r->pad[1] = 0;
+            // BaseType.cpp:75-82
+            int8_t cand[4]; int n = 0; uint32_t flags = 0, full = 0;
+            const double total = (double)n_reads;
+            if (n_reads > 0) {
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const double fr = (double)su.depth[b] / total;
+                    if (near_rel(fr, a.s.min_af)) flags |= BVC_FLAG_MIN_AF;
+                    if (fr >= a.s.min_af) { cand[n++] = (int8_t)b; full |= 1u << b; }
+                }
+            }
+            if (n <= 1) {
+                // no EM needed: 0 candidates -> false; 1 candidate -> one (closed-form) fit, chi stays 0
+                const double frq[4] = {full & 1 ? 1.0 : 0.0, full & 2 ? 1.0 : 0.0, full & 4 ? 1.0 : 0.0, full & 8 ? 1.0 : 0.0};
+                finalize_site(a, site, ref, su.depth, n_reads, cand, n, frq, 0.0, n, 2 * n, flags);
+            } else {
+                Ladder L;
+                L.lr_alt = 0.0; L.frq[0] = L.frq[1] = L.frq[2] = L.frq[3] = 0.0; L.chi_t = 0.0;
+                for (int t = 0; t < 4; ++t) L.cand[t] = t < n ? cand[t] : (int8_t)-1;
+                L.n = (int8_t)n; L.k = (int8_t)n; L.nfit = 1; L.pad0 = 0;
+                L.em_fits = 0; L.em_passes = 0; L.flags = flags; L.pad1 = 0;
+                a.lad[site] = L;
+                a.fit[(size_t)site * 4].mask = full;
+                a.state[site] = kStActive;
+                emit = true;
+            }
+        }
+    }
+    const uint32_t pos = warp_agg_append(a.q_out_n, emit);
+    if (emit) a.q_out[pos] = ((uint32_t)site << 2);
+}
+
+// =====================================================================================================
+// K3: thread per fit, flattened (pass, class) loop with dynamic refill
+// =====================================================================================================
+constexpr int kEmThreads = 128;
+
+__global__ void __launch_bounds__(kEmThreads)
+em_fit_kernel(PipeArgs a)
+{
+    __shared__ double lut_e3[kNQ], lut_d[kNQ];
+    for (int i = threadIdx.x; i < kNQ; i += blockDim.x) { lut_e3[i] = a.s.lut[i]; lut_d[i] = a.s.lut[4 * kNQ + i]; }
+    __syncthreads();
+    const uint32_t nfits = *a.q_in_n;
+    const int lane = threadIdx.x & 31;
+    const double eps = a.s.eps;
+    const int max_iter = a.s.max_iter;
+
+    bool active = false, done = false, big = false;
+    const uint32_t* cp = a.cls;
+    int ncls = 0, c = 0, pass = 0;
+    uint32_t item = 0, fl = 0;
+    double f0 = 0, f1 = 0, f2 = 0, f3 = 0, p0 = 0, p1 = 0, p2 = 0, p3 = 0, F = 0, Fp = 0;
+    double accT = 0, V0 = 0, V1 = 0, V2 = 0, V3 = 0, dl = 0, inv_n = 0;
+
+    for (;;) {
+        // ---- refill: lanes without a fit take the next queue items (one atomic per warp) ---------------
+        const bool want = !active && !done;
+        const unsigned wm = __ballot_sync(0xffffffffu, want);
+        if (wm) {
+            uint32_t base = 0;
+            const int leader = __ffs(wm) - 1;
+            if (lane == leader) base = atomicAdd(a.q_in_head, (uint32_t)__popc(wm));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (want) {
+                const uint32_t idx = base + __popc(wm & ((1u << lane) - 1));
+                if (idx < nfits) {
+                    item = a.q_in[idx];
+                    const uint32_t site = item >> 2;
+                    const SiteSum su = a.sum[site];
+                    const uint32_t mask = a.fit[(size_t)site * 4 + (item & 3)].mask;
+                    int dsum = 0;                                   // BaseType.cpp:25-39
+                    if (mask & 1) dsum += su.depth[0];
+                    if (mask & 2) dsum += su.depth[1];
+                    if (mask & 4) dsum += su.depth[2];
+                    if (mask & 8) dsum += su.depth[3];
+                    const double ds = (double)dsum;
+                    f0 = (mask & 1) ? (double)su.depth[0] / ds : 0.0;
+                    f1 = (mask & 2) ? (double)su.depth[1] / ds : 0.0;
+                    f2 = (mask & 4) ? (double)su.depth[2] / ds : 0.0;
+                    f3 = (mask & 8) ? (double)su.depth[3] / ds : 0.0;
+                    F = ((f0 + f1) + f2) + f3;
+                    inv_n = 1.0 / (double)(su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3]);
+                    cp = a.cls + su.cls_off; ncls = su.ncls; c = 0; pass = 0; fl = 0;
+                    accT = V0 = V1 = V2 = V3 = dl = 0.0; big = false;
+                    active = true;
+                } else done = true;
+            }
+        }
+        if (__all_sync(0xffffffffu, done)) break;
+        if (!active) continue;
+
+        // ---- one class of the current pass ---------------------------------------------------------------
+        const uint32_t w = __ldg(cp + c);
+        const int q = w & (kNQ - 1), b = (w >> 7) & 3;
+        const double cnt = (double)(w >> 9);
+        const double e3 = lut_e3[q], d = lut_d[q];
+        const double fb = sel4(b, f0, f1, f2, f3);
+        const double ml = fma(fb, d, e3 * F);                        // Algorithm.cpp:76-79
+        const double r = fast_rcp(ml);
+        const double wgt = cnt * r;
+        accT = fma(e3, wgt, accT);                                   // :80-91, factored (see file header)
+        const double v = d * wgt;
+        if (b == 0) V0 += v; else if (b == 1) V1 += v; else if (b == 2) V2 += v; else V3 += v;
+        if (pass > 0) {                                              // :103-113, stateless
+            const double pb = sel4(b, p0, p1, p2, p3);
+            const double mlp = fma(pb, d, e3 * Fp);
+            const double x = (mlp - ml) * r;
+            const double t = fabs(log1p_small(x));
+            if (fabs(x) <= 0.015625) dl = fma(cnt, t, dl); else big = true;
+        }
+        if (++c == ncls) {
+            const double e0 = f0 * (accT + V0) * inv_n, e1 = f1 * (accT + V1) * inv_n;
+            const double e2 = f2 * (accT + V2) * inv_n, e3v = f3 * (accT + V3) * inv_n;
+            bool stop = (pass == max_iter);
+            if (pass > 0 && !big) {
+                if (near_rel(dl, eps)) fl |= BVC_FLAG_EM_DELTA;
+                if (dl < eps) stop = true;                           // :124
+            }
+            if (stop) {
+                FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
+                fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
+                fr->eap[0] = e0; fr->eap[1] = e1; fr->eap[2] = e2; fr->eap[3] = e3v;
+                fr->passes = pass + 1; fr->flags = fl;
+                active = false;
+            } else {
+                p0 = f0; p1 = f1; p2 = f2; p3 = f3; Fp = F;
+                f0 = e0; f1 = e1; f2 = e2; f3 = e3v;                 // :95-101
+                F = ((f0 + f1) + f2) + f3;
+                accT = V0 = V1 = V2 = V3 = dl = 0.0; big = false;
+                c = 0; ++pass;
+            }
+        }
+    }
+}
+
+// =====================================================================================================
+// K4: thread per site -- log-likelihoods of the finished fits, LRT decision, next stage or final call
+// =====================================================================================================
+// lr of one fit: sum_c cnt_c * log(ml_c(f))  (BaseType.cpp:57-60) with the same ml formula as K3
+__device__ __forceinline__ double fit_loglik(const PipeArgs& a, const SiteSum& su, const double* f)
+{
+    const double F = ((f[0] + f[1]) + f[2]) + f[3];
+    const uint32_t* cp = a.cls + su.cls_off;
+    double s = 0.0;
+    for (int c = 0; c < su.ncls; ++c) {
+        const uint32_t w = __ldg(cp + c);
+        const int q = w & (kNQ - 1), b = (w >> 7) & 3;
+        const double ml = fma(sel4(b, f[0], f[1], f[2], f[3]), __ldg(a.s.lut + 4 * kNQ + q), __ldg(a.s.lut + q) * F);
+        s = fma((double)(w >> 9), log(ml), s);
+    }
+    return s;
+}
+// closed form for a single-base model: f = e_b is a fixed point of EM (2 passes, delta == 0);
+// lr = sum_c cnt_c * log L_cb from the host-built (glibc) log table
+__device__ __forceinline__ double single_loglik(const PipeArgs& a, const SiteSum& su, int base)
+{
+    const uint32_t* cp = a.cls + su.cls_off;
+    double s = 0.0;
+    for (int c = 0; c < su.ncls; ++c) {
+        const uint32_t w = __ldg(cp + c);
+        const int q = w & (kNQ - 1), b = (w >> 7) & 3;
+        s = fma((double)(w >> 9), __ldg(a.s.lut + (b == base ? 3 : 2) * kNQ + q), s);
+    }
+    return s;
+}
+
+__global__ void __launch_bounds__(128)
+ladder_kernel(PipeArgs a)
+{
+    const int site = blockIdx.x * blockDim.x + threadIdx.x;
+    if (site >= a.s.n_sites || a.state[site] != kStActive) return;
+    const SiteSum su = a.sum[site];
+    Ladder L = a.lad[site];
+    const int ref = a.s.ref_base[site] & 3;
+    const int n_reads = su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3];
+    const FitRes* fr = a.fit + (size_t)site * 4;
+    int n = L.n, k = L.k;
+    bool cont = true;          // ladder still running
+
+    // ---- results of the EM stage in flight -----------------------------------------------------------------
+    if (k == n) {                                                  // the full model (BaseType.cpp:88-90)
+        L.lr_alt = fit_loglik(a, su, fr[0].f);
+        for (int j = 0; j < 4; ++j) L.frq[j] = fr[0].eap[j];
+        L.em_fits += 1; L.em_passes += fr[0].passes; L.flags |= fr[0].flags;
+    } else {                                                       // k-subsets, combs_ order (BaseType.cpp:93-110)
+        double cmin = 0.0, lr_min = 0.0; int imin = 0;
+        for (int i = 0; i < L.nfit; ++i) {
+            const double lr = fit_loglik(a, su, fr[i].f);
+            const double chi = 2.0 * (L.lr_alt - lr);
+            if (i > 0 && near_rel(chi, cmin)) L.flags |= BVC_FLAG_ARGMIN_TIE;
+            if (i == 0 || chi < cmin) { cmin = chi; lr_min = lr; imin = i; }
+            L.em_fits += 1; L.em_passes += fr[i].passes; L.flags |= fr[i].flags;
+        }
+        L.lr_alt = lr_min; L.chi_t = cmin;
+        if (near_rel(cmin, a.s.lrt_thr)) L.flags |= BVC_FLAG_LRT_CHI;
+        if (cmin < a.s.lrt_thr) {
+            const uint32_t keep = fr[imin].mask;
+            int nn = 0;
+            for (int t = 0; t < n; ++t) if (keep >> L.cand[t] & 1) L.cand[nn++] = L.cand[t];
+            n = nn;
+            for (int j = 0; j < 4; ++j) L.frq[j] = fr[imin].eap[j];
+        } else cont = false;
+    }
+    // ---- following stages: singles are closed-form (done here), larger subsets go back to K3 ---------------
+    while (cont) {
+        k = n - 1;
+        if (k < 1) break;
+        if (k >= 2) {
+            int slot = 0;
+            for (unsigned m = (1u << n) - 1; m >= 1; --m) {            // combs_ order: bit (n-1-i) <=> cand[i]
+                if (__popc(m) != k) continue;
+                uint32_t sub = 0;
+                for (int i = 0; i < n; ++i) if (m >> (n - 1 - i) & 1) sub |= 1u << L.cand[i];
+                a.fit[(size_t)site * 4 + slot].mask = sub;
+                ++slot;
+            }
+            L.n = (int8_t)n; L.k = (int8_t)k; L.nfit = (int8_t)slot;
+            a.lad[site] = L;
+            const uint32_t pos = atomicAdd(a.q_out_n, (uint32_t)slot);
+            for (int i = 0; i < slot; ++i) a.q_out[pos + i] = ((uint32_t)site << 2) | (uint32_t)i;
+            return;
+        }
+        // k == 1: n == 2 single-base models, in cand order
+        double cmin = 0.0, lr_min = 0.0; int imin = 0;
+        for (int i = 0; i < n; ++i) {
+            const double lr = single_loglik(a, su, L.cand[i]);
+            const double chi = 2.0 * (L.lr_alt - lr);
+            if (i > 0 && near_rel(chi, cmin)) L.flags |= BVC_FLAG_ARGMIN_TIE;
+            if (i == 0 || chi < cmin) { cmin = chi; lr_min = lr; imin = i; }
+            L.em_fits += 1; L.em_passes += 2;
+        }
+        L.lr_alt = lr_min; L.chi_t = cmin;
+        if (near_rel(cmin, a.s.lrt_thr)) L.flags |= BVC_FLAG_LRT_CHI;
+        if (cmin < a.s.lrt_thr) {
+            const int b = L.cand[imin];
+            L.cand[0] = (int8_t)b; n = 1;
+            for (int j = 0; j < 4; ++j) L.frq[j] = (j == b) ? 1.0 : 0.0;
+        }
+        cont = false;
+    }
+    finalize_site(a, site, ref, su.depth, n_reads, L.cand, n, L.frq, L.chi_t, L.em_fits, L.em_passes, L.flags);
+}
+
+// =====================================================================================================
+// K5: warp per LRT-positive site -- VCF strand table, Fisher/SOR, three rank-sum tests
+// =====================================================================================================
+constexpr int kVcfWarps = 4;
+
+__global__ void __launch_bounds__(kVcfWarps * 32)
+vcf_stats_kernel(PipeArgs a)
+{
+    __shared__ uint32_t H_s[kVcfWarps][6 * 256];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t* H = H_s[wid];
+    const uint32_t n_list = *a.vcf_n;
+    for (uint32_t i = blockIdx.x * kVcfWarps + wid; i < n_list; i += gridDim.x * kVcfWarps) {
+        const int site = (int)a.vcf_list[i];
+        const SiteSum su = a.sum[site];
+        bvc_site_result* r = a.s.out + site;
+        const int ref = a.s.ref_base[site] & 3;
+        unsigned altmask = 0;
+        for (int t = 0; t < r->n_alt; ++t) altmask |= 1u << r->alt_bases[t];
+        // BaseType.cpp:174-187: non-indel entries only, alt = any surviving alt base
+        int vs[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            if (b == ref) { vs[0] = su.fwd[b]; vs[1] = su.depth[b] - su.fwd[b]; }
+            else if (altmask >> b & 1) { vs[2] += su.fwd[b]; vs[3] += su.depth[b] - su.fwd[b]; }
+        }
+        const double vcf_fs = dm_fisher(a.s.lgam, vs[0], vs[1], vs[2], vs[3]);
+        const double vcf_sor = dm_sor(vs[0], vs[1], vs[2], vs[3]);
+        for (int j = lane; j < 6 * 256; j += 32) H[j] = 0;
+        __syncwarp();
+        const uint32_t b0 = a.s.entry_off[site], b1 = a.s.entry_off[site + 1];
+        for (uint32_t e = b0 + lane; e < b1; e += 32) {
+            const unsigned c = a.s.code[e];
+            if (c & 16) continue;
+            const int base = c & 7;
+            int g = -1;
+            if (base == ref) g = 0; else if (base < 4 && (altmask >> base & 1)) g = 1;
+            if (g < 0) continue;
+            atomicAdd(&H[(0 * 2 + g) * 256 + a.s.mapq[e]], 1u);
+            atomicAdd(&H[(1 * 2 + g) * 256 + a.s.qual[e]], 1u);
+            atomicAdd(&H[(2 * 2 + g) * 256 + a.s.rpr[e]], 1u);
+        }
+        __syncwarp();
+        double rs[3];
+        for (int f = 0; f < 3; ++f) rs[f] = ranksum_hist(H + f * 512, H + f * 512 + 256, lane);
+        if (lane == 0) {
+            r->vcf_fs = vcf_fs; r->vcf_sor = vcf_sor;
+            r->ranksum[0] = rs[0]; r->ranksum[1] = rs[1]; r->ranksum[2] = rs[2];
+            r->vcf_strand[0] = vs[0]; r->vcf_strand[1] = vs[1]; r->vcf_strand[2] = vs[2]; r->vcf_strand[3] = vs[3];
+        }
+        __syncwarp();
+    }
+}
+}  // namespace bvc

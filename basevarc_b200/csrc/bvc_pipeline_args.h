@@ -1,0 +1,66 @@
+// bvc_pipeline_args.h -- device-side intermediate records and the argument block of the staged pipeline
+// (shared by bvc_pipeline.cuh and the host API, which only allocates them).
+#pragma once
+#include <stdint.h>
+#include "bvc_kernels.h"
+
+namespace bvc {
+
+// ---- intermediate records (device only) ------------------------------------------------------------
+struct __align__(16) SiteSum {      // 64 B, written by K1
+    int32_t  depth[4];              // non-indel entries per base
+    int32_t  fwd[4];                // of which forward strand
+    int32_t  cvg[4];                // CVG strand table over ALL entries (ref_fwd, ref_rev, alt_fwd, alt_rev)
+    uint32_t cls_off;               // first class of this site in the pool
+    uint16_t ncls;
+    uint8_t  alt;                   // top-count non-ref base
+    uint8_t  has_q0;                // a qual-0 class exists: the site takes the IEEE-faithful legacy path
+    int32_t  n_entries;
+    int32_t  pad;
+};
+
+struct __align__(16) FitRes {       // 80 B, one per (site, slot)
+    double  f[4];                   // allele frequencies used by the LAST E-step (its ml enters lr)
+    double  eap[4];                 // M-step after it (what UpdateF reports, BaseType.cpp:61-69)
+    int32_t passes;
+    uint32_t flags;
+    uint32_t mask;                  // allele subset (bit b = base b)
+    uint32_t pad;
+};
+
+struct __align__(16) Ladder {       // 80 B per site
+    double  lr_alt;
+    double  frq[4];
+    double  chi_t;
+    int8_t  cand[4];
+    int8_t  n;                      // current number of candidate bases
+    int8_t  k;                      // size of the subsets in flight (== n: the full model)
+    int8_t  nfit;                   // fits in flight
+    int8_t  pad0;
+    int32_t em_fits, em_passes;
+    uint32_t flags;
+    int32_t pad1;
+};
+
+constexpr uint8_t kStActive = 0, kStDone = 1, kStLegacy = 2;
+
+struct PipeArgs {
+    SiteArgs s;                 // tile arrays, out, lut, lgam, thresholds
+    SiteSum*  sum;              // [n_sites]
+    uint32_t* cls;              // class pool: cnt << 9 | base << 7 | qual
+    uint32_t* cls_cursor;       // pool allocation cursor
+    Ladder*   lad;              // [n_sites]
+    FitRes*   fit;              // [n_sites][4]
+    uint8_t*  state;            // [n_sites]
+    uint32_t* q_in;             // fit queue consumed by K3 (site << 2 | slot)
+    uint32_t* q_out;            // fit queue filled by K2/K4
+    uint32_t* q_in_n;           // counts
+    uint32_t* q_out_n;
+    uint32_t* q_in_head;        // K3 refill cursor
+    uint32_t* vcf_list;         // LRT-positive sites
+    uint32_t* vcf_n;
+    uint32_t* legacy_list;      // sites for the IEEE-faithful warp-per-site kernel
+    uint32_t* legacy_n;
+};
+
+}  // namespace bvc

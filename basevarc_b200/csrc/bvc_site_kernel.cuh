@@ -48,7 +48,6 @@ struct SiteState {
     uint32_t flags;
 };
 
-__device__ __forceinline__ bool near_rel(double x, double thr) { return fabs(x - thr) <= 1e-9 * fabs(thr); }
 
 // One EM fit over the classes for the allele subset `mask` (bit b = base b).  Warp-uniform result.
 // Algorithm.cpp:115-130 with UpdateF's start vector and log-likelihood sum (BaseType.cpp:25-39,57-60).
