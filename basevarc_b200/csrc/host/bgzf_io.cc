@@ -1,0 +1,200 @@
+// bgzf_io.cc -- see bgzf_io.hpp
+#include "bgzf_io.hpp"
+
+#include <string.h>
+#include <zlib.h>
+
+namespace bvc_host {
+
+namespace {
+constexpr size_t kBlockData = 0xff00;      // uncompressed bytes per block (htslib's BGZF_BLOCK_SIZE)
+constexpr size_t kMaxBlock = 0x10000;
+
+inline uint16_t rd16(const unsigned char* p) { return (uint16_t)(p[0] | (p[1] << 8)); }
+inline uint32_t rd32(const unsigned char* p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24); }
+inline void wr16(unsigned char* p, uint16_t v) { p[0] = (unsigned char)(v & 0xff); p[1] = (unsigned char)(v >> 8); }
+inline void wr32(unsigned char* p, uint32_t v) { wr16(p, (uint16_t)(v & 0xffff)); wr16(p + 2, (uint16_t)(v >> 16)); }
+}  // namespace
+
+const unsigned char BgzfWriter::kEofBlock[28] = {0x1f, 0x8b, 0x08, 0x04, 0, 0, 0, 0, 0, 0xff, 0x06, 0x00, 0x42, 0x43,
+                                                 0x02, 0x00, 0x1b, 0x00, 0x03, 0x00, 0, 0, 0, 0, 0, 0, 0, 0};
+
+bool bgzf_is_complete(const std::string& path)
+{
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) return false;
+    unsigned char h[18], t[28];
+    bool ok = fread(h, 1, 18, f) == 18 && h[0] == 0x1f && h[1] == 0x8b && h[2] == 8 && (h[3] & 4) && h[12] == 'B' && h[13] == 'C';
+    if (ok) ok = fseek(f, -28, SEEK_END) == 0 && fread(t, 1, 28, f) == 28 && memcmp(t, BgzfWriter::kEofBlock, 28) == 0;
+    fclose(f);
+    return ok;
+}
+
+// ---- reader ------------------------------------------------------------------------------------------
+bool BgzfReader::open(const std::string& path, std::string* err)
+{
+    close();
+    f_ = fopen(path.c_str(), "rb");
+    if (!f_) { if (err) *err = "cannot open " + path; return false; }
+    setvbuf(f_, nullptr, _IOFBF, 1 << 20);
+    comp_.resize(kMaxBlock);
+    buf_.resize(kMaxBlock);
+    pos_ = len_ = 0; failed_ = eof_ = false; carry_.clear(); err_.clear();
+    return true;
+}
+
+void BgzfReader::close()
+{
+    if (f_) fclose(f_);
+    f_ = nullptr;
+}
+
+bool BgzfReader::fill()
+{
+    while (!eof_) {
+        unsigned char* h = comp_.data();
+        size_t got = fread(h, 1, 12, f_);
+        if (got == 0) { eof_ = true; return false; }
+        if (got != 12 || h[0] != 0x1f || h[1] != 0x8b || h[2] != 8 || !(h[3] & 4)) { failed_ = true; err_ = "not a BGZF block"; return false; }
+        const size_t xlen = rd16(h + 10);
+        if (12 + xlen > kMaxBlock || fread(h + 12, 1, xlen, f_) != xlen) { failed_ = true; err_ = "truncated BGZF header"; return false; }
+        size_t bsize = 0;
+        for (size_t o = 0; o + 4 <= xlen;) {
+            const unsigned char* s = h + 12 + o;
+            const size_t sl = rd16(s + 2);
+            if (s[0] == 'B' && s[1] == 'C' && sl == 2) bsize = (size_t)rd16(s + 4) + 1;
+            o += 4 + sl;
+        }
+        const size_t head = 12 + xlen;
+        if (bsize < head + 8 || bsize > kMaxBlock) { failed_ = true; err_ = "bad BGZF block size"; return false; }
+        const size_t rest = bsize - head;
+        if (fread(h + head, 1, rest, f_) != rest) { failed_ = true; err_ = "truncated BGZF block"; return false; }
+        const size_t isize = rd32(h + bsize - 4);
+        if (isize > kMaxBlock) { failed_ = true; err_ = "bad BGZF ISIZE"; return false; }
+        if (isize == 0) continue;              // empty block (EOF marker or flush point)
+        z_stream zs;
+        memset(&zs, 0, sizeof zs);
+        if (inflateInit2(&zs, -15) != Z_OK) { failed_ = true; err_ = "inflateInit2 failed"; return false; }
+        zs.next_in = h + head; zs.avail_in = (uInt)(rest - 8);
+        zs.next_out = reinterpret_cast<Bytef*>(buf_.data()); zs.avail_out = (uInt)kMaxBlock;
+        const int rc = inflate(&zs, Z_FINISH);
+        inflateEnd(&zs);
+        if (rc != Z_STREAM_END || zs.total_out != isize) { failed_ = true; err_ = "inflate failed"; return false; }
+        if ((uint32_t)crc32(crc32(0L, Z_NULL, 0), reinterpret_cast<const Bytef*>(buf_.data()), (uInt)isize) != rd32(h + bsize - 8)) {
+            failed_ = true; err_ = "BGZF CRC mismatch"; return false;
+        }
+        pos_ = 0; len_ = isize;
+        return true;
+    }
+    return false;
+}
+
+bool BgzfReader::getline_view(const char** ptr, size_t* len)
+{
+    carry_.clear();
+    bool have_carry = false;
+    for (;;) {
+        if (pos_ >= len_ && !fill()) {
+            if (have_carry && !failed_) { *ptr = carry_.data(); *len = carry_.size(); return true; }   // last line without '\n'
+            return false;
+        }
+        const char* b = buf_.data() + pos_;
+        const char* nl = static_cast<const char*>(memchr(b, '\n', len_ - pos_));
+        if (nl) {
+            const size_t n = (size_t)(nl - b);
+            pos_ += n + 1;
+            if (!have_carry) { *ptr = b; *len = n; return true; }
+            carry_.append(b, n);
+            *ptr = carry_.data(); *len = carry_.size();
+            return true;
+        }
+        carry_.append(b, len_ - pos_);
+        have_carry = true;
+        pos_ = len_;
+    }
+}
+
+bool BgzfReader::getline(std::string& line)
+{
+    const char* p; size_t n;
+    if (!getline_view(&p, &n)) return false;
+    line.assign(p, n);
+    return true;
+}
+
+// ---- writer ------------------------------------------------------------------------------------------
+bool BgzfWriter::open(const std::string& path)
+{
+    close();
+    f_ = fopen(path.c_str(), "wb");
+    if (!f_) return false;
+    setvbuf(f_, nullptr, _IOFBF, 1 << 20);
+    mem_mode_ = false; open_ = true; pend_.clear();
+    return true;
+}
+
+void BgzfWriter::open_memory()
+{
+    close();
+    mem_mode_ = true; open_ = true; mem_.clear(); pend_.clear();
+}
+
+bool BgzfWriter::sink(const void* p, size_t n)
+{
+    if (mem_mode_) { mem_.append(static_cast<const char*>(p), n); return true; }
+    return fwrite(p, 1, n, f_) == n;
+}
+
+bool BgzfWriter::flush_block(const char* data, size_t n)
+{
+    unsigned char out[kMaxBlock + 64];
+    static const unsigned char head[16] = {0x1f, 0x8b, 0x08, 0x04, 0, 0, 0, 0, 0, 0xff, 0x06, 0x00, 'B', 'C', 0x02, 0x00};
+    memcpy(out, head, 16);
+    z_stream zs;
+    memset(&zs, 0, sizeof zs);
+    int level = level_;
+    for (;;) {
+        if (deflateInit2(&zs, level, Z_DEFLATED, -15, 8, Z_DEFAULT_STRATEGY) != Z_OK) return false;
+        zs.next_in = reinterpret_cast<Bytef*>(const_cast<char*>(data)); zs.avail_in = (uInt)n;
+        zs.next_out = out + 18; zs.avail_out = (uInt)(kMaxBlock - 18 - 8);
+        const int rc = deflate(&zs, Z_FINISH);
+        deflateEnd(&zs);
+        if (rc == Z_STREAM_END) break;
+        if (level == 0) return false;          // cannot happen for n <= 0xff00 with stored blocks
+        level = 0;                             // incompressible data: fall back to stored
+    }
+    const size_t clen = zs.total_out, bsize = 18 + clen + 8;
+    wr16(out + 16, (uint16_t)(bsize - 1));
+    wr32(out + 18 + clen, (uint32_t)crc32(crc32(0L, Z_NULL, 0), reinterpret_cast<const Bytef*>(data), (uInt)n));
+    wr32(out + 18 + clen + 4, (uint32_t)n);
+    return sink(out, bsize);
+}
+
+bool BgzfWriter::write(const char* data, size_t n)
+{
+    if (!open_) return false;
+    while (n) {
+        const size_t room = kBlockData - pend_.size();
+        const size_t take = n < room ? n : room;
+        pend_.insert(pend_.end(), data, data + take);
+        data += take; n -= take;
+        if (pend_.size() == kBlockData) {
+            if (!flush_block(pend_.data(), pend_.size())) return false;
+            pend_.clear();
+        }
+    }
+    return true;
+}
+
+bool BgzfWriter::close(bool eof_marker)
+{
+    if (!open_) return true;
+    bool ok = true;
+    if (!pend_.empty()) { ok = flush_block(pend_.data(), pend_.size()); pend_.clear(); }
+    if (eof_marker) ok = sink(kEofBlock, 28) && ok;
+    if (f_) { ok = (fclose(f_) == 0) && ok; f_ = nullptr; }
+    open_ = false;
+    return ok;
+}
+
+}  // namespace bvc_host

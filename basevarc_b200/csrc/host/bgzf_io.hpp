@@ -1,0 +1,74 @@
+// bgzf_io.hpp -- minimal BGZF (blocked gzip, "BC" extra sub-field) line reader and writer on zlib.
+//
+// The reference reads its batch files and writes its .vcf.gz/.cvg.gz through htslib's bgzf_*
+// (paths under /root/reference: src/BaseVarC.cpp:223-231 validity probe, :327-338,:407 bgzf_getline,
+// :268-295 sub-file merge).  This is a from-scratch restatement of the container format only:
+// every block is an independent gzip member of <= 64 KiB with its total size in the BC field; a
+// well-formed file ends with the 28-byte empty block.
+#pragma once
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+namespace bvc_host {
+
+// true iff `path` starts with a BGZF block header and ends with the EOF marker block
+// (bgzf_compression(fp) == 2 && bgzf_check_EOF(fp) == 1, src/BaseVarC.cpp:224-227).
+bool bgzf_is_complete(const std::string& path);
+
+class BgzfReader {
+public:
+    BgzfReader() = default;
+    ~BgzfReader() { close(); }
+    BgzfReader(const BgzfReader&) = delete;
+    BgzfReader& operator=(const BgzfReader&) = delete;
+    bool open(const std::string& path, std::string* err);
+    void close();
+    // One line without its '\n' (bgzf_getline semantics); false at end of file.  On a corrupt block
+    // returns false and sets failed().
+    bool getline(std::string& line);
+    // Zero-copy variant: the line as a [ptr, ptr+len) view, valid until the next call.
+    bool getline_view(const char** ptr, size_t* len);
+    bool failed() const { return failed_; }
+    const std::string& error() const { return err_; }
+
+private:
+    bool fill();            // inflate the next non-empty block into buf_
+    FILE* f_ = nullptr;
+    std::vector<unsigned char> comp_;
+    std::vector<char> buf_;
+    size_t pos_ = 0, len_ = 0;
+    std::string carry_;     // a line that spans blocks
+    bool failed_ = false, eof_ = false;
+    std::string err_;
+};
+
+// Writes BGZF either to a file or to an in-memory byte string (take()).  close() appends the EOF block
+// unless `eof_marker` is false (used for window sub-streams that are concatenated later: BGZF blocks are
+// independent gzip members, so concatenating compressed windows equals compressing the concatenation).
+class BgzfWriter {
+public:
+    explicit BgzfWriter(int level = 6) : level_(level) {}
+    ~BgzfWriter() { close(); }
+    BgzfWriter(const BgzfWriter&) = delete;
+    BgzfWriter& operator=(const BgzfWriter&) = delete;
+    bool open(const std::string& path);        // file sink
+    void open_memory();                        // memory sink
+    bool write(const char* data, size_t n);
+    bool write(const std::string& s) { return write(s.data(), s.size()); }
+    bool close(bool eof_marker = true);
+    std::string& memory() { return mem_; }
+    static const unsigned char kEofBlock[28];
+
+private:
+    bool flush_block(const char* data, size_t n);
+    bool sink(const void* p, size_t n);
+    FILE* f_ = nullptr;
+    bool mem_mode_ = false, open_ = false;
+    std::string mem_;
+    std::vector<char> pend_;
+    int level_;
+};
+
+}  // namespace bvc_host
