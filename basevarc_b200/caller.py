@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libbvc_gpu.so")
 EXPORTS = (
     "bvc_default_params", "bvc_create", "bvc_destroy", "bvc_last_error", "bvc_enqueue", "bvc_wait",
     "bvc_fetch_groups", "bvc_host_alloc", "bvc_host_free", "bvc_resident_upload", "bvc_resident_run",
-    "bvc_resident_download", "bvc_kernel_launch_count", "bvc_measure_fp64_peak",
+    "bvc_resident_download", "bvc_kernel_launch_count", "bvc_measure_fp64_peak", "bvc_kernel_name", "bvc_transfer_bytes",
 )
 
 
@@ -57,6 +57,10 @@ def load_library():
     L.bvc_kernel_launch_count.argtypes = [C.c_void_p]
     L.bvc_kernel_launch_count.restype = C.c_int64
     L.bvc_measure_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
+    L.bvc_kernel_name.argtypes = [C.c_int]
+    L.bvc_kernel_name.restype = C.c_char_p
+    L.bvc_transfer_bytes.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    L.bvc_transfer_bytes.restype = None
     _lib = L
     return L
 
@@ -145,13 +149,21 @@ class BaseTypeCaller:
         self._check(self.lib.bvc_resident_upload(self.ctx, C.byref(ct)), "bvc_resident_upload")
         self._resident_sites = tile.n_sites
 
-    def resident_run(self, iters=1, flush_l2=True):
+    def resident_run(self, iters=1, flush_l2=True, per_kernel=False):
+        """Mean device ms per pass; with per_kernel=True also {kernel name: ms per pass} (events between launches)."""
         ms = C.c_float(0)
-        per = (C.c_float * 8)()
+        per = (C.c_float * 16)()
         nk = C.c_int(0)
-        self._check(self.lib.bvc_resident_run(self.ctx, int(iters), int(bool(flush_l2)), C.byref(ms), per, C.byref(nk)),
-                    "bvc_resident_run")
-        return ms.value, [per[i] for i in range(nk.value)]
+        self._check(self.lib.bvc_resident_run(self.ctx, int(iters), int(bool(flush_l2)), C.byref(ms),
+                                              per if per_kernel else None, C.byref(nk)), "bvc_resident_run")
+        names = [self.lib.bvc_kernel_name(i).decode() for i in range(nk.value)]
+        return ms.value, ({n: per[i] for i, n in enumerate(names)} if per_kernel else {})
+
+    @property
+    def transfer_bytes(self):
+        h, d = C.c_int64(0), C.c_int64(0)
+        self.lib.bvc_transfer_bytes(self.ctx, C.byref(h), C.byref(d))
+        return h.value, d.value
 
     def resident_download(self):
         out = np.zeros(self._resident_sites, SITE_RESULT_DTYPE)

@@ -30,6 +30,7 @@ struct Slot {
     uint8_t* d_state = nullptr;
     uint32_t *d_qa = nullptr, *d_qb = nullptr, *d_vcf_list = nullptr, *d_legacy_list = nullptr;
     uint32_t* d_ctr = nullptr;     // [16]: cls_cursor, qa_n, qb_n, q_head, vcf_n, legacy_n
+    const uint8_t *k_mapq = nullptr, *k_rpr = nullptr;   // what the kernels read: d_mapq/d_rpr or zero-copy host pointers
     uint64_t ticket = 0;       // 0 = idle
     int n_sites = 0;
     int64_t n_entries = 0;
@@ -49,6 +50,8 @@ struct bvc_ctx {
     size_t flush_bytes = 0;
     uint64_t next_ticket = 1;
     int64_t launches = 0;
+    int64_t h2d_bytes = 0, d2h_bytes = 0;   // bytes moved by cudaMemcpyAsync on the host-buffer path
+    bool zero_copy = true;         // BVC_NO_ZERO_COPY=1 forces the full mapq/rpr copy (A/B checks)
     bool legacy_only = false;      // BVC_LEGACY_KERNEL=1: the single warp-per-site kernel for every site (A/B checks)
     std::string err;
     bool resident = false;
@@ -123,34 +126,56 @@ int check_tile(bvc_ctx* ctx, const bvc_tile* t, int64_t* n_entries)
     return BVC_OK;
 }
 
-int upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R)
+// Device-visible alias of a pinned, 4-byte-aligned host array, or nullptr (pageable memory / BVC_NO_ZERO_COPY=1).
+const uint8_t* zero_copy_ptr(bvc_ctx* ctx, const uint8_t* host)
+{
+    if (!ctx->zero_copy || (reinterpret_cast<uintptr_t>(host) & 3u)) return nullptr;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, host) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (at.type != cudaMemoryTypeHost || !at.devicePointer) return nullptr;
+    return static_cast<const uint8_t*>(at.devicePointer);
+}
+
+int upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool resident)
 {
     const size_t S = (size_t)t->n_sites;
     s.n_sites = t->n_sites; s.n_entries = R;
     if (S) CK(cudaMemcpyAsync(s.d_ref, t->ref_base, S, cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.d_off, t->entry_off, (S + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
+    ctx->h2d_bytes += (int64_t)(S + (S + 1) * sizeof(uint32_t) + 2 * (size_t)R);
     if (R) {
         CK(cudaMemcpyAsync(s.d_code, t->code, (size_t)R, cudaMemcpyHostToDevice, s.stream));
         CK(cudaMemcpyAsync(s.d_qual, t->qual, (size_t)R, cudaMemcpyHostToDevice, s.stream));
-        CK(cudaMemcpyAsync(s.d_mapq, t->mapq, (size_t)R, cudaMemcpyHostToDevice, s.stream));
-        CK(cudaMemcpyAsync(s.d_rpr, t->rpr, (size_t)R, cudaMemcpyHostToDevice, s.stream));
-        if (s.d_sample && t->sample) CK(cudaMemcpyAsync(s.d_sample, t->sample, (size_t)R * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
+        // mapq / rpr are read only at LRT-positive sites (K5: ~0.3 % of a low-pass window).  When the caller's
+        // arrays are pinned (bvc_host_alloc / cudaHostRegister) the kernels read them in place over PCIe
+        // instead of paying a full H2D copy; pageable arrays are copied as before.
+        s.k_mapq = resident ? nullptr : zero_copy_ptr(ctx, t->mapq);
+        s.k_rpr = resident ? nullptr : zero_copy_ptr(ctx, t->rpr);
+        if (!s.k_mapq) { CK(cudaMemcpyAsync(s.d_mapq, t->mapq, (size_t)R, cudaMemcpyHostToDevice, s.stream)); s.k_mapq = s.d_mapq; ctx->h2d_bytes += R; }
+        if (!s.k_rpr) { CK(cudaMemcpyAsync(s.d_rpr, t->rpr, (size_t)R, cudaMemcpyHostToDevice, s.stream)); s.k_rpr = s.d_rpr; ctx->h2d_bytes += R; }
+        if (s.d_sample && t->sample) {
+            CK(cudaMemcpyAsync(s.d_sample, t->sample, (size_t)R * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
+            ctx->h2d_bytes += (int64_t)R * 4;
+        }
     }
     return BVC_OK;
 }
 
-int launch(bvc_ctx* ctx, Slot& s)
+int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullptr, int* n_out = nullptr)
 {
     if (s.n_sites == 0) return BVC_OK;
     CK(cudaMemsetAsync(s.d_counter, 0, sizeof(unsigned int), s.stream));
     bvc::SiteArgs a;
-    a.ref_base = s.d_ref; a.entry_off = s.d_off; a.code = s.d_code; a.qual = s.d_qual; a.mapq = s.d_mapq; a.rpr = s.d_rpr;
+    a.ref_base = s.d_ref; a.entry_off = s.d_off; a.code = s.d_code; a.qual = s.d_qual; a.mapq = s.k_mapq ? s.k_mapq : s.d_mapq; a.rpr = s.k_rpr ? s.k_rpr : s.d_rpr;
     a.out = s.d_out; a.counter = s.d_counter; a.lut = ctx->d_lut; a.lgam = ctx->d_lgam;
     a.n_sites = s.n_sites; a.max_iter = ctx->prm.em_max_iter;
     a.min_af = ctx->prm.min_af; a.lrt_thr = ctx->prm.lrt_threshold; a.eps = ctx->prm.em_epsilon;
     a.site_list = nullptr; a.list_n = nullptr;
     if (ctx->legacy_only) {
+        if (ev) { CK(cudaEventRecord(ev[0], s.stream)); kinds[0] = bvc::kKLegacy; }
         CK(bvc::launch_site_call(a, ctx->n_sm, s.stream));
+        if (ev) CK(cudaEventRecord(ev[1], s.stream));
+        if (n_out) *n_out = 1;
         ctx->launches += 1;
         return BVC_OK;
     }
@@ -165,7 +190,8 @@ int launch(bvc_ctx* ctx, Slot& s)
     p.vcf_list = s.d_vcf_list; p.vcf_n = s.d_ctr + 4;
     p.legacy_list = s.d_legacy_list; p.legacy_n = s.d_ctr + 5;
     int nl = 0;
-    CK(bvc::launch_pipeline(p, ctx->n_sm, s.stream, &nl));
+    CK(bvc::launch_pipeline(p, ctx->n_sm, s.stream, &nl, ev, kinds));
+    if (n_out) *n_out = nl;
     ctx->launches += nl;
     return BVC_OK;
 }
@@ -225,6 +251,7 @@ int bvc_create(bvc_ctx** out, int device, const bvc_params* prm)
     if (prop.major < 10) { ctx->err = "bvc_create: device is not sm_100 class (kernels are built for sm_100a only)"; return fail(BVC_ERR_CUDA); }
     ctx->n_sm = prop.multiProcessorCount;
     { const char* e = getenv("BVC_LEGACY_KERNEL"); ctx->legacy_only = (e && e[0] == '1'); }
+    { const char* e = getenv("BVC_NO_ZERO_COPY"); ctx->zero_copy = !(e && e[0] == '1'); }
     if (!(prm->em_epsilon <= 0.01)) { ctx->err = "bvc_create: em_epsilon must be <= 0.01 (see the delta bound in bvc_pipeline.cuh)"; return fail(BVC_ERR_ARG); }
 
     // host-built tables (glibc): per-qual likelihoods (src/BaseType.cpp:13-15) and lgamma(k)
@@ -272,9 +299,10 @@ int bvc_enqueue(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_result* out, uint64
     const uint64_t tk = ctx->next_ticket;
     Slot& s = ctx->slot[tk & 1];
     if (s.ticket) { CK(cudaStreamSynchronize(s.stream)); s.ticket = 0; }
-    if ((rc = upload(ctx, s, tile, R)) != BVC_OK) return rc;
+    if ((rc = upload(ctx, s, tile, R, false)) != BVC_OK) return rc;
     if ((rc = launch(ctx, s)) != BVC_OK) return rc;
     if (s.n_sites) CK(cudaMemcpyAsync(out, s.d_out, (size_t)s.n_sites * sizeof(bvc_site_result), cudaMemcpyDeviceToHost, s.stream));
+    ctx->d2h_bytes += (int64_t)s.n_sites * (int64_t)sizeof(bvc_site_result);
     CK(cudaEventRecord(s.done, s.stream));
     s.ticket = tk;
     ctx->next_ticket += 1;
@@ -320,7 +348,7 @@ int bvc_resident_upload(bvc_ctx* ctx, const bvc_tile* tile)
     Slot& s = ctx->slot[0];
     CK(cudaStreamSynchronize(s.stream));
     s.ticket = 0;
-    if ((rc = upload(ctx, s, tile, R)) != BVC_OK) return rc;
+    if ((rc = upload(ctx, s, tile, R, true)) != BVC_OK) return rc;
     CK(cudaStreamSynchronize(s.stream));
     ctx->resident = true;
     return BVC_OK;
@@ -335,24 +363,44 @@ int bvc_resident_run(bvc_ctx* ctx, int iters, int flush_l2, float* ms_per_launch
     if (flush_l2 && !ctx->d_flush) { ctx->flush_bytes = (size_t)256 << 20; CK(cudaMalloc(&ctx->d_flush, ctx->flush_bytes)); }
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    // per-kernel breakdown: an event before every launch (only when asked for: the records sit between kernels)
+    cudaEvent_t ev[bvc::kMaxPipeLaunches + 1];
+    int kinds[bvc::kMaxPipeLaunches];
+    double kind_ms[bvc::kNumKernelKinds];
+    for (int k = 0; k < bvc::kNumKernelKinds; ++k) kind_ms[k] = 0.0;
+    if (per_kernel_ms) for (int i = 0; i <= bvc::kMaxPipeLaunches; ++i) CK(cudaEventCreate(&ev[i]));
     double total = 0.0;
     for (int i = 0; i < iters; ++i) {
         if (flush_l2) CK(cudaMemsetAsync(ctx->d_flush, i & 0xff, ctx->flush_bytes, s.stream));
-        CK(cudaMemsetAsync(s.d_counter, 0, sizeof(unsigned int), s.stream));
         CK(cudaEventRecord(e0, s.stream));
-        int rc = launch(ctx, s);
+        int nl = 0;
+        int rc = launch(ctx, s, per_kernel_ms ? ev : nullptr, per_kernel_ms ? kinds : nullptr, &nl);
         if (rc != BVC_OK) return rc;
         CK(cudaEventRecord(e1, s.stream));
         CK(cudaEventSynchronize(e1));
         float ms = 0.f;
         CK(cudaEventElapsedTime(&ms, e0, e1));
         total += ms;
+        if (per_kernel_ms) for (int l = 0; l < nl; ++l) {
+            float k_ms = 0.f;
+            CK(cudaEventElapsedTime(&k_ms, ev[l], ev[l + 1]));
+            kind_ms[kinds[l]] += k_ms;
+        }
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (per_kernel_ms) for (int i = 0; i <= bvc::kMaxPipeLaunches; ++i) cudaEventDestroy(ev[i]);
     if (ms_per_launch) *ms_per_launch = (float)(total / iters);
-    if (per_kernel_ms) per_kernel_ms[0] = (float)(total / iters);
-    if (n_kernels_out) *n_kernels_out = 1;
+    if (per_kernel_ms) for (int k = 0; k < bvc::kNumKernelKinds; ++k) per_kernel_ms[k] = (float)(kind_ms[k] / iters);
+    if (n_kernels_out) *n_kernels_out = bvc::kNumKernelKinds;
     return BVC_OK;
+}
+
+const char* bvc_kernel_name(int kind) { return bvc::kernel_kind_name(kind); }
+
+void bvc_transfer_bytes(const bvc_ctx* ctx, int64_t* h2d, int64_t* d2h)
+{
+    if (h2d) *h2d = ctx ? ctx->h2d_bytes : 0;
+    if (d2h) *d2h = ctx ? ctx->d2h_bytes : 0;
 }
 
 int bvc_resident_download(bvc_ctx* ctx, bvc_site_result* out)

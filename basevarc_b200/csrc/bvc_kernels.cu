@@ -196,7 +196,14 @@ cudaError_t launch_site_call(const SiteArgs& a, int n_sm, cudaStream_t stream)
     return cudaGetLastError();
 }
 
-cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, int* n_launches)
+const char* kernel_kind_name(int kind)
+{
+    static const char* names[kNumKernelKinds] = {"site_hist_kernel", "site_prepare_kernel", "em_fit_kernel", "ladder_kernel",
+                                                 "vcf_stats_kernel", "site_call_kernel"};
+    return (kind >= 0 && kind < kNumKernelKinds) ? names[kind] : "?";
+}
+
+cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, int* n_launches, cudaEvent_t* ev, int* kinds)
 {
     PipeArgs a = a0;
     const int S = a.s.n_sites;
@@ -211,10 +218,13 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     }
     auto capped = [&](long long want, int per_sm) { long long g = (long long)n_sm * per_sm; if (g > want) g = want; return (unsigned)(g < 1 ? 1 : g); };
     const unsigned site_blocks = (unsigned)((S + 127) / 128);
+    // optional per-launch timing: ev[i] is recorded BEFORE launch i, ev[launches] after the last one
+    auto mark = [&](int kind) { if (ev) { cudaEventRecord(ev[launches], stream); kinds[launches] = kind; } ++launches; };
 
+    mark(kKHist);
     site_hist_kernel<<<capped((S + kHistWarps - 1) / kHistWarps, occ_hist), kHistWarps * 32, 0, stream>>>(a);
+    mark(kKPrepare);
     site_prepare_kernel<<<site_blocks, 128, 0, stream>>>(a);
-    launches += 2;
     // at most three EM stages: the full model, the (n-1)-subsets (n >= 3), the pairs of a reduced 4-candidate site
     for (int stage = 0; stage < 3; ++stage) {
         uint32_t* t;
@@ -222,16 +232,19 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
         t = a.q_in_n; a.q_in_n = a.q_out_n; a.q_out_n = t;
         cudaMemsetAsync(a.q_out_n, 0, sizeof(uint32_t), stream);
         cudaMemsetAsync(a.q_in_head, 0, sizeof(uint32_t), stream);
+        mark(kKEm);
         em_fit_kernel<<<(unsigned)(n_sm * occ_em), kEmThreads, 0, stream>>>(a);
+        mark(kKLadder);
         ladder_kernel<<<site_blocks, 128, 0, stream>>>(a);
-        launches += 2;
     }
+    mark(kKVcf);
     vcf_stats_kernel<<<capped(S, occ_vcf), kVcfWarps * 32, 0, stream>>>(a);
     // qual-0 sites: the IEEE-faithful warp-per-site kernel over the legacy list
     SiteArgs leg = a.s;
     leg.site_list = a.legacy_list; leg.list_n = a.legacy_n;
+    mark(kKLegacy);
     site_call_kernel<<<(unsigned)(n_sm * occ_leg), kWarpsPerBlock * 32, 0, stream>>>(leg);
-    launches += 2;
+    if (ev) cudaEventRecord(ev[launches], stream);
     if (n_launches) *n_launches = launches;
     return cudaGetLastError();
 }

@@ -541,17 +541,38 @@ vcf_stats_kernel(PipeArgs a)
         const double vcf_sor = dm_sor(vs[0], vs[1], vs[2], vs[3]);
         for (int j = lane; j < 6 * 256; j += 32) H[j] = 0;
         __syncwarp();
+        // 4 entries per lane per 32-bit load.  mapq / rpr may live in the caller's PINNED host memory
+        // (zero-copy over PCIe: only LRT-positive sites ever touch them, see upload() in bvc_api.cu),
+        // so they are fetched only by lanes that hold at least one ref/alt entry.
         const uint32_t b0 = a.s.entry_off[site], b1 = a.s.entry_off[site + 1];
-        for (uint32_t e = b0 + lane; e < b1; e += 32) {
-            const unsigned c = a.s.code[e];
-            if (c & 16) continue;
-            const int base = c & 7;
-            int g = -1;
-            if (base == ref) g = 0; else if (base < 4 && (altmask >> base & 1)) g = 1;
-            if (g < 0) continue;
-            atomicAdd(&H[(0 * 2 + g) * 256 + a.s.mapq[e]], 1u);
-            atomicAdd(&H[(1 * 2 + g) * 256 + a.s.qual[e]], 1u);
-            atomicAdd(&H[(2 * 2 + g) * 256 + a.s.rpr[e]], 1u);
+        const uint32_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;
+        const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
+        const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
+        const uint32_t* mapq4 = reinterpret_cast<const uint32_t*>(a.s.mapq);
+        const uint32_t* rpr4 = reinterpret_cast<const uint32_t*>(a.s.rpr);
+        for (uint32_t wi = w0 + lane; wi < w1; wi += 32) {
+            const uint32_t cw = __ldg(code4 + wi);
+            int g[4]; bool any = false;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t e = wi * 4 + k;
+                const unsigned c = (cw >> (8 * k)) & 31u;
+                const int base = c & 7;
+                g[k] = -1;
+                if (e >= b0 && e < b1 && !(c & 16)) {
+                    if (base == ref) g[k] = 0; else if (base < 4 && (altmask >> base & 1)) g[k] = 1;
+                }
+                any |= g[k] >= 0;
+            }
+            if (!any) continue;
+            const uint32_t qw = __ldg(qual4 + wi), mw = mapq4[wi], rw = rpr4[wi];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (g[k] < 0) continue;
+                atomicAdd(&H[(0 * 2 + g[k]) * 256 + ((mw >> (8 * k)) & 255u)], 1u);
+                atomicAdd(&H[(1 * 2 + g[k]) * 256 + ((qw >> (8 * k)) & 255u)], 1u);
+                atomicAdd(&H[(2 * 2 + g[k]) * 256 + ((rw >> (8 * k)) & 255u)], 1u);
+            }
         }
         __syncwarp();
         double rs[3];

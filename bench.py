@@ -201,12 +201,14 @@ def main():
         sampler.wait_started()
     barrier()
     l0 = caller.kernel_launches
-    ms, per_kernel = caller.resident_run(args.steps, flush_l2=False)
+    ms, _ = caller.resident_run(args.steps, flush_l2=False)
     barrier()
     launches = caller.kernel_launches - l0
     ms_step = max_over_ranks(ms)
     recs = caller.resident_download()
     value = world * units_per_gpu / (ms_step * 1e-3)
+    # per-kernel breakdown of the same pass (separate, untimed-for-value run: events sit between the launches)
+    _, per_kernel = caller.resident_run(max(2, min(args.steps, 5)), flush_l2=False, per_kernel=True)
 
     # ---- e2e leg: host buffers through bvc_enqueue / bvc_wait (pinned H2D + D2H inside the region) --
     nsub = max(1, min(args.subtiles, S))
@@ -222,8 +224,6 @@ def main():
             setattr(t, k, pa.array)
         subs.append(t)
     outs = [PinnedArray((t.n_sites,), B.SITE_RESULT_DTYPE) for t in subs]
-    h2d = sum(t.nbytes() for t in subs)
-    d2h = sum(o.array.nbytes for o in outs)
 
     def e2e_step():
         tks = [caller.enqueue(t, o.array) for t, o in zip(subs, outs)]
@@ -233,11 +233,18 @@ def main():
     for _ in range(args.warmup):
         e2e_step()
     barrier()
+    h2d0, d2h0 = caller.transfer_bytes
     t0 = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
     barrier()
     e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+    h2d1, d2h1 = caller.transfer_bytes
+    # copied bytes (counted by the library from the tensors it copies) + the pinned mapq/rpr words the
+    # rank-sum kernel reads in place over PCIe at LRT-positive sites (2 arrays, rounded up to 32-bit words)
+    zc = int((recs["n_entries"][recs["lrt_ok"] == 1].astype(np.int64) + 6).sum()) * 2
+    h2d = (h2d1 - h2d0) // args.steps + zc
+    d2h = (d2h1 - d2h0) // args.steps
     clocks = sampler.stop() if sampler else None
     e2e_value = world * units_per_gpu / e2e_s
     same = all(np.array_equal(np.concatenate([o.array for o in outs])[f], recs[f]) for f in ("depth", "lrt_ok", "alt_bases"))
@@ -276,6 +283,7 @@ def main():
         "fp64": {"algorithmic_tflops": f_alg / (ms * 1e-3) / 1e12, "peak_tflops_measured": fp64_peak,
                  "frac": f_alg / (ms * 1e-3) / 1e12 / fp64_peak, "algorithmic_flop_per_launch": f_alg,
                  "note": "F_alg counts the reference's per-read E/M/delta flops (SURVEY 8d); the kernel does fewer (class collapse)"},
+        "kernels_ms": {k: round(v, 4) for k, v in per_kernel.items()},
         "cpu_baseline": cpu,
         "clocks": clocks,
         "sites_lrt_positive": int(recs["lrt_ok"].sum()), "em_passes_per_site": float(recs["em_passes"].mean()),

@@ -133,11 +133,16 @@ void  bvc_host_free(void* p);
  * flushing L2 (a >126 MB memset) before each timed launch, and returns the mean device time per
  * launch in milliseconds measured with CUDA events on that stream.  per_kernel_ms (may be NULL)
  * receives [n_kernels] mean times; n_kernels is returned through *n_kernels_out. */
+/* per_kernel_ms is indexed by kernel KIND (all launches of a kind summed per run); bvc_kernel_name(kind) names it. */
 int  bvc_resident_upload(bvc_ctx* ctx, const bvc_tile* tile);
 int  bvc_resident_run(bvc_ctx* ctx, int iters, int flush_l2, float* ms_per_launch,
                       float* per_kernel_ms, int* n_kernels_out);
 int  bvc_resident_download(bvc_ctx* ctx, bvc_site_result* out);
+const char* bvc_kernel_name(int kind);                 /* kind in [0, n_kernels) */
 int64_t bvc_kernel_launch_count(const bvc_ctx* ctx);   /* kernels of ours launched so far */
+/* Cumulative bytes moved by bvc_enqueue's copies (H2D of tiles, D2H of records).  mapq / rpr arrays that live
+ * in pinned host memory are NOT copied: the kernels read them in place for LRT-positive sites only. */
+void bvc_transfer_bytes(const bvc_ctx* ctx, int64_t* h2d, int64_t* d2h);
 
 /* FP64 pipe microbenchmark (dependent-free DFMA chains on all SMs): returns TFLOP/s (2 flop/FMA). */
 int  bvc_measure_fp64_peak(int device, double* tflops);
