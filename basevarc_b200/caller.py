@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libbvc_gpu.so")
 EXPORTS = (
     "bvc_default_params", "bvc_create", "bvc_destroy", "bvc_last_error", "bvc_enqueue", "bvc_wait",
     "bvc_fetch_groups", "bvc_host_alloc", "bvc_host_free", "bvc_resident_upload", "bvc_resident_run",
-    "bvc_resident_download", "bvc_kernel_launch_count", "bvc_measure_fp64_peak", "bvc_kernel_name", "bvc_transfer_bytes",
+    "bvc_resident_download", "bvc_kernel_launch_count", "bvc_measure_fp64_peak", "bvc_kernel_name", "bvc_transfer_bytes", "bvc_work_counters",
 )
 
 
@@ -61,6 +61,7 @@ def load_library():
     L.bvc_kernel_name.restype = C.c_char_p
     L.bvc_transfer_bytes.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.bvc_transfer_bytes.restype = None
+    L.bvc_work_counters.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
     _lib = L
     return L
 
@@ -158,6 +159,11 @@ class BaseTypeCaller:
                                               per if per_kernel else None, C.byref(nk)), "bvc_resident_run")
         names = [self.lib.bvc_kernel_name(i).decode() for i in range(nk.value)]
         return ms.value, ({n: per[i] for i, n in enumerate(names)} if per_kernel else {})
+
+    def work_counters(self):
+        out = (C.c_uint64 * 4)()
+        self._check(self.lib.bvc_work_counters(self.ctx, out), "bvc_work_counters")
+        return dict(em_class_passes=out[0], em_long_class_passes=out[1], loglik_class_evals=out[2], em_fits=out[3])
 
     @property
     def transfer_bytes(self):

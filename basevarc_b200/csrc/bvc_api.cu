@@ -14,6 +14,7 @@
 namespace {
 
 thread_local std::string g_create_error;
+constexpr size_t kCtrWords = 16 + bvc::kNBins + 16;
 
 struct Slot {
     cudaStream_t stream = nullptr;
@@ -28,8 +29,8 @@ struct Slot {
     bvc::Ladder* d_lad = nullptr;
     bvc::FitRes* d_fit = nullptr;
     uint8_t* d_state = nullptr;
-    uint32_t *d_qa = nullptr, *d_qb = nullptr, *d_vcf_list = nullptr, *d_legacy_list = nullptr;
-    uint32_t* d_ctr = nullptr;     // [16]: cls_cursor, qa_n, qb_n, q_head, vcf_n, legacy_n
+    uint32_t *d_qa = nullptr, *d_qb = nullptr, *d_qs = nullptr, *d_ql = nullptr, *d_vcf_list = nullptr, *d_legacy_list = nullptr;
+    uint32_t* d_ctr = nullptr;     // [kCtrWords]: cls_cursor, qa_n, qb_n, q_head, vcf_n, legacy_n, long_n, work[4] (u64 at word 8), bins at word 16
     const uint8_t *k_mapq = nullptr, *k_rpr = nullptr;   // what the kernels read: d_mapq/d_rpr or zero-copy host pointers
     uint64_t ticket = 0;       // 0 = idle
     int n_sites = 0;
@@ -97,9 +98,11 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
     CK(cudaMalloc(&s.d_state, S + 16));
     CK(cudaMalloc(&s.d_qa, (4 * S + 16) * sizeof(uint32_t)));
     CK(cudaMalloc(&s.d_qb, (4 * S + 16) * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.d_qs, (4 * S + 16) * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.d_ql, (4 * S + 16) * sizeof(uint32_t)));
     CK(cudaMalloc(&s.d_vcf_list, (S + 16) * sizeof(uint32_t)));
     CK(cudaMalloc(&s.d_legacy_list, (S + 16) * sizeof(uint32_t)));
-    CK(cudaMalloc(&s.d_ctr, 16 * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.d_ctr, kCtrWords * sizeof(uint32_t)));
     return BVC_OK;
 }
 
@@ -108,7 +111,7 @@ void free_slot(Slot& s)
     cudaFree(s.d_ref); cudaFree(s.d_off); cudaFree(s.d_code); cudaFree(s.d_qual); cudaFree(s.d_mapq);
     cudaFree(s.d_rpr); cudaFree(s.d_sample); cudaFree(s.d_out); cudaFree(s.d_counter);
     cudaFree(s.d_sum); cudaFree(s.d_cls); cudaFree(s.d_lad); cudaFree(s.d_fit); cudaFree(s.d_state);
-    cudaFree(s.d_qa); cudaFree(s.d_qb); cudaFree(s.d_vcf_list); cudaFree(s.d_legacy_list); cudaFree(s.d_ctr);
+    cudaFree(s.d_qa); cudaFree(s.d_qb); cudaFree(s.d_qs); cudaFree(s.d_ql); cudaFree(s.d_vcf_list); cudaFree(s.d_legacy_list); cudaFree(s.d_ctr);
     if (s.done) cudaEventDestroy(s.done);
     if (s.stream) cudaStreamDestroy(s.stream);
     s = Slot();
@@ -179,7 +182,7 @@ int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullpt
         ctx->launches += 1;
         return BVC_OK;
     }
-    CK(cudaMemsetAsync(s.d_ctr, 0, 16 * sizeof(uint32_t), s.stream));
+    CK(cudaMemsetAsync(s.d_ctr, 0, kCtrWords * sizeof(uint32_t), s.stream));
     bvc::PipeArgs p;
     p.s = a;
     p.sum = s.d_sum; p.cls = s.d_cls; p.cls_cursor = s.d_ctr + 0;
@@ -189,6 +192,9 @@ int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullpt
     p.q_in_head = s.d_ctr + 3;
     p.vcf_list = s.d_vcf_list; p.vcf_n = s.d_ctr + 4;
     p.legacy_list = s.d_legacy_list; p.legacy_n = s.d_ctr + 5;
+    p.q_sorted = s.d_qs; p.q_long = s.d_ql; p.q_long_n = s.d_ctr + 6;
+    p.work = reinterpret_cast<unsigned long long*>(s.d_ctr + 8);
+    p.bins = s.d_ctr + 16;
     int nl = 0;
     CK(bvc::launch_pipeline(p, ctx->n_sm, s.stream, &nl, ev, kinds));
     if (n_out) *n_out = nl;
@@ -252,7 +258,7 @@ int bvc_create(bvc_ctx** out, int device, const bvc_params* prm)
     ctx->n_sm = prop.multiProcessorCount;
     { const char* e = getenv("BVC_LEGACY_KERNEL"); ctx->legacy_only = (e && e[0] == '1'); }
     { const char* e = getenv("BVC_NO_ZERO_COPY"); ctx->zero_copy = !(e && e[0] == '1'); }
-    if (!(prm->em_epsilon <= 0.01)) { ctx->err = "bvc_create: em_epsilon must be <= 0.01 (see the delta bound in bvc_pipeline.cuh)"; return fail(BVC_ERR_ARG); }
+    if (!(prm->em_epsilon <= 0.0019)) { ctx->err = "bvc_create: em_epsilon must be <= 0.0019 (see log1p_tiny in bvc_pipeline.cuh)"; return fail(BVC_ERR_ARG); }
 
     // host-built tables (glibc): per-qual likelihoods (src/BaseType.cpp:13-15) and lgamma(k)
     std::vector<double> lut(5 * bvc::kNQ), lgam((size_t)prm->n_samples + 3);
@@ -396,6 +402,17 @@ int bvc_resident_run(bvc_ctx* ctx, int iters, int flush_l2, float* ms_per_launch
 }
 
 const char* bvc_kernel_name(int kind) { return bvc::kernel_kind_name(kind); }
+
+int bvc_work_counters(bvc_ctx* ctx, uint64_t* out4)
+{
+    if (!ctx || !out4) return BVC_ERR_ARG;
+    if (!ctx->resident) { set_err(ctx, "bvc_work_counters: no resident tile"); return BVC_ERR_STATE; }
+    CK(cudaSetDevice(ctx->device));
+    Slot& s = ctx->slot[0];
+    CK(cudaStreamSynchronize(s.stream));
+    CK(cudaMemcpy(out4, s.d_ctr + 8, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    return BVC_OK;
+}
 
 void bvc_transfer_bytes(const bvc_ctx* ctx, int64_t* h2d, int64_t* d2h)
 {

@@ -198,8 +198,9 @@ cudaError_t launch_site_call(const SiteArgs& a, int n_sm, cudaStream_t stream)
 
 const char* kernel_kind_name(int kind)
 {
-    static const char* names[kNumKernelKinds] = {"site_hist_kernel", "site_prepare_kernel", "em_fit_kernel", "ladder_kernel",
-                                                 "vcf_stats_kernel", "site_call_kernel"};
+    static const char* names[kNumKernelKinds] = {"site_hist_kernel", "site_prepare_kernel", "queue_sort_kernels", "em_fit_kernel",
+                                                 "em_long_kernel", "fit_loglik_kernel", "ladder_kernel", "vcf_stats_kernel",
+                                                 "site_call_kernel"};
     return (kind >= 0 && kind < kNumKernelKinds) ? names[kind] : "?";
 }
 
@@ -208,8 +209,11 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     PipeArgs a = a0;
     const int S = a.s.n_sites;
     int launches = 0;
-    static int occ_hist = 0, occ_em = 0, occ_vcf = 0, occ_leg = 0;
+    static int occ_hist = 0, occ_em = 0, occ_vcf = 0, occ_leg = 0, occ_long = 0, occ_ll = 0;
     if (!occ_hist) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_long, em_long_kernel, kLongWarps * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ll, fit_loglik_kernel, kEmThreads, 0);
+        if (occ_long < 1) occ_long = 1; if (occ_ll < 1) occ_ll = 1;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist, site_hist_kernel, kHistWarps * 32, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_em, em_fit_kernel, kEmThreads, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_vcf, vcf_stats_kernel, kVcfWarps * 32, 0);
@@ -232,8 +236,20 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
         t = a.q_in_n; a.q_in_n = a.q_out_n; a.q_out_n = t;
         cudaMemsetAsync(a.q_out_n, 0, sizeof(uint32_t), stream);
         cudaMemsetAsync(a.q_in_head, 0, sizeof(uint32_t), stream);
+        cudaMemsetAsync(a.q_long_n, 0, sizeof(uint32_t), stream);
+        cudaMemsetAsync(a.bins, 0, (kNBins + 1) * sizeof(uint32_t), stream);
+        mark(kKSort);
+        queue_hist_kernel<<<(unsigned)(n_sm * 2), kSortThreads, 0, stream>>>(a);
+        mark(kKSort);
+        queue_scan_kernel<<<1, kSortThreads, 0, stream>>>(a);
+        mark(kKSort);
+        queue_scatter_kernel<<<(unsigned)(n_sm * 2), kSortThreads, 0, stream>>>(a);
         mark(kKEm);
         em_fit_kernel<<<(unsigned)(n_sm * occ_em), kEmThreads, 0, stream>>>(a);
+        mark(kKEmLong);
+        em_long_kernel<<<(unsigned)(n_sm * occ_long), kLongWarps * 32, 0, stream>>>(a);
+        mark(kKLoglik);
+        fit_loglik_kernel<<<(unsigned)(n_sm * occ_ll), kEmThreads, 0, stream>>>(a);
         mark(kKLadder);
         ladder_kernel<<<site_blocks, 128, 0, stream>>>(a);
     }

@@ -35,8 +35,8 @@ cudaError_t launch_site_call(const SiteArgs& a, int n_sm, cudaStream_t stream);
 // The staged pipeline (bvc_pipeline.cuh).  q_a/q_b + their counters ping-pong between stages.
 // ev/kinds (optional, [kMaxPipeLaunches + 1] / [kMaxPipeLaunches]): an event before every launch and one after the
 // last, plus the kernel kind of each launch, for the per-kernel breakdown of bvc_resident_run.
-enum KernelKind { kKHist = 0, kKPrepare, kKEm, kKLadder, kKVcf, kKLegacy, kNumKernelKinds };
-constexpr int kMaxPipeLaunches = 16;
+enum KernelKind { kKHist = 0, kKPrepare, kKSort, kKEm, kKEmLong, kKLoglik, kKLadder, kKVcf, kKLegacy, kNumKernelKinds };
+constexpr int kMaxPipeLaunches = 32;
 const char* kernel_kind_name(int kind);
 cudaError_t launch_pipeline(const PipeArgs& a, int n_sm, cudaStream_t stream, int* n_launches,
                             cudaEvent_t* ev = nullptr, int* kinds = nullptr);

@@ -1,6 +1,6 @@
 // bvc_pipeline.cuh -- the staged B200 pipeline of the per-site `basetype` calling core.
 //
-// One tile of sites goes through five kernels instead of the reference's one-site-at-a-time loop
+// One tile of sites goes through these kernels instead of the reference's one-site-at-a-time loop
 // (bt_s -> bt_f -> BaseType::LRT -> EM -> WriteVcf; paths under /root/reference):
 //
 //   K1 site_hist_kernel    warp per site.  Streams the packed entries ONCE (code + qual bytes, 32-bit
@@ -10,23 +10,30 @@
 //                          (bt_f counting src/BaseVarC.cpp:548-602; BaseType ctor src/BaseType.cpp:5-23)
 //   K2 site_prepare_kernel thread per site.  CVG Fisher + SOR, candidate filter, first ladder step,
 //                          emits the full-model fit.  (src/BaseVarC.cpp:603-608, src/BaseType.cpp:73-90)
-//   K3 em_fit_kernel       THREAD PER FIT, flattened (pass, class) loop with dynamic refill: every lane
-//                          always has a class to process, no shuffles, no per-class state.  FP64-bound.
-//                          (EM / singleEM / delta_bylog src/Algorithm.cpp:69-130; UpdateF src/BaseType.cpp:41-71)
-//   K4 ladder_kernel       thread per site.  log-likelihood sums of the finished fits, LRT decision,
-//                          next-stage subsets or final ALT set / AF / chi-square QUAL.
+//   Qs queue_{hist,scan,scatter}_kernel   counting sort of the stage's fit queue by descending class count.
+//   K3 em_fit_kernel       THREAD PER FIT, pass-aligned: the sorted queue gives the 32 lanes of a warp fits of
+//                          (nearly) equal class count, so the class loop has a warp-uniform trip count, every
+//                          pass ends for all lanes together and lanes refill at pass boundaries.  No shuffles,
+//                          no per-class state.  FP64-pipe-bound.  A fit that needs more than kPassBudget passes
+//                          is parked for K3b.  (EM / singleEM / delta_bylog src/Algorithm.cpp:69-130;
+//                          UpdateF / SetAlleleFreq src/BaseType.cpp:25-71)
+//   K3b em_long_kernel     warp per parked fit (classes across lanes + butterfly sums): bounds the stage's tail.
+//   K3c fit_loglik_kernel  thread per fit: lr = sum_c cnt_c log ml_c(f_last).  (src/BaseType.cpp:57-60)
+//   K4 ladder_kernel       thread per site.  LRT decision from the fits' lr, next-stage subsets (single-base
+//                          models are closed-form) or final ALT set / AF / chi-square QUAL.
 //                          (src/BaseType.cpp:93-135, combs_ :237-255, chisf src/Algorithm.cpp:3-7)
 //   K5 vcf_stats_kernel    warp per LRT-positive site.  VCF strand table Fisher/SOR and the three
 //                          Mann-Whitney tests from 256-bin histograms.  (src/BaseType.cpp:149-197)
 //
-// EM restatement used by K3/K4 (all reads of a site with equal (base, qual) share one E-step row):
+// EM restatement used by K3/K3b/K3c (all reads of a site with equal (base, qual) share one E-step row):
 //   ml_c   = sum_j f_j L_cj = e3_q * F + f_b * (ome_q - e3_q),  F = sum_j f_j          (Algorithm.cpp:76-79)
 //   eap_j  = f_j * (sum_c cnt_c e3_q / ml_c + sum_{c: b=j} cnt_c (ome_q - e3_q) / ml_c) / n   (:80-91)
 //   delta  = sum_c cnt_c |log ml'_c - log ml_c| = sum_c cnt_c |log1p((ml_c - ml'_c) / ml'_c)|  (:103-113)
-// with ml_c recomputed from the previous pass's f (no per-class state).  log1p is an 8-term series when
-// |x| <= 2^-6; a class with |x| > 2^-6 alone contributes >= |x|/(1+|x|) > 0.015 > epsilon, so the pass
-// is "not converged" without evaluating it.  Differences from the reference are pure rounding
-// (<= a few ulp per pass); the hard thresholds are flagged when met within 1e-9 (BVC_FLAG_*).
+// with ml_c recomputed from the previous pass's f (no per-class state).  delta only ever enters the test
+// delta < epsilon: log1p is a 5-term series when |x| <= 2^-9, and a class with |x| > 2^-9 alone contributes
+// more than epsilon, so that pass is "not converged" without evaluating the sum (see log1p_tiny).
+// Differences from the reference are pure rounding (<= a few ulp per pass); the hard thresholds are flagged
+// when met within 1e-9 (BVC_FLAG_*).
 #pragma once
 #include <stdint.h>
 #include "../../include/bvc_gpu.h"
@@ -41,40 +48,6 @@ __device__ __forceinline__ double sel4(int b, double v0, double v1, double v2, d
 {
     return b == 0 ? v0 : (b == 1 ? v1 : (b == 2 ? v2 : v3));
 }
-// lut_s layout: [0..128) e/3, [128..256) 1-e, [256..384) log(e/3), [384..512) log(1-e), [512..640) (1-e) - e/3
-__device__ __forceinline__ double class_ml(const double* lut_s, int q, double fb, double F)
-{
-    return fma(fb, lut_s[4 * kNQ + q], lut_s[q] * F);
-}
-
-// 1/x to <= 1 ulp for normal positive x: hardware seed + two Newton steps (no slow path)
-__device__ __forceinline__ double fast_rcp(double x)
-{
-    double r;
-    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
-    double e = fma(-x, r, 1.0);
-    r = fma(r, e, r);
-    e = fma(-x, r, 1.0);
-    r = fma(r, e, r);
-    e = fma(-x, r, 1.0);          // third step: safe whatever the seed's precision (>= 8 bits suffices)
-    r = fma(r, e, r);
-    return r;
-}
-
-// log1p(x) for |x| <= 2^-6: x * (1 - x/2 + x^2/3 - ... - x^7/8), truncation < 4e-16 relative
-__device__ __forceinline__ double log1p_small(double x)
-{
-    double p = -1.0 / 8.0;
-    p = fma(p, x, 1.0 / 7.0);
-    p = fma(p, x, -1.0 / 6.0);
-    p = fma(p, x, 1.0 / 5.0);
-    p = fma(p, x, -1.0 / 4.0);
-    p = fma(p, x, 1.0 / 3.0);
-    p = fma(p, x, -1.0 / 2.0);
-    p = fma(p, x, 1.0);
-    return p * x;
-}
-
 
 // =====================================================================================================
 // K1: warp per site -- stream entries, histogram, compact classes, strand tables
@@ -300,30 +273,190 @@ site_prepare_kernel(PipeArgs a)
 }
 
 // =====================================================================================================
-// K3: thread per fit, flattened (pass, class) loop with dynamic refill
+// Qs: counting sort of a stage's fit queue by DESCENDING class count.  Lanes of a warp then hold fits of
+// (nearly) equal length, so K3's class loop has a warp-uniform trip count and every pass ends for all
+// lanes together; long fits start first (LPT order).
+// =====================================================================================================
+constexpr int kSortThreads = 256;
+constexpr int kSortItems = 8;              // items per thread per chunk
+
+__global__ void __launch_bounds__(kSortThreads)
+queue_hist_kernel(PipeArgs a)
+{
+    __shared__ uint32_t h[kNBins + 1];
+    for (int i = threadIdx.x; i <= kNBins; i += blockDim.x) h[i] = 0;
+    __syncthreads();
+    const uint32_t n = *a.q_in_n;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        atomicAdd(&h[a.sum[a.q_in[i] >> 2].ncls], 1u);
+    __syncthreads();
+    for (int i = threadIdx.x; i <= kNBins; i += blockDim.x) if (h[i]) atomicAdd(&a.bins[i], h[i]);
+}
+
+// one block: bins[k] <- number of fits with MORE than k classes (exclusive scan in descending key order)
+__global__ void __launch_bounds__(kSortThreads)
+queue_scan_kernel(PipeArgs a)
+{
+    __shared__ uint32_t h[kNBins + 1];
+    for (int i = threadIdx.x; i <= kNBins; i += blockDim.x) h[i] = a.bins[i];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+        for (int k = kNBins; k >= 0; --k) { const uint32_t c = h[k]; h[k] = run; run += c; }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i <= kNBins; i += blockDim.x) a.bins[i] = h[i];
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+queue_scatter_kernel(PipeArgs a)
+{
+    __shared__ uint32_t h[kNBins + 1], base[kNBins + 1];
+    const uint32_t n = *a.q_in_n;
+    constexpr uint32_t kChunk = kSortThreads * kSortItems;
+    for (uint32_t c0 = blockIdx.x * kChunk; c0 < n; c0 += gridDim.x * kChunk) {
+        for (int i = threadIdx.x; i <= kNBins; i += blockDim.x) h[i] = 0;
+        __syncthreads();
+        uint32_t item[kSortItems], rank[kSortItems]; uint16_t key[kSortItems];
+#pragma unroll
+        for (int k = 0; k < kSortItems; ++k) {
+            const uint32_t i = c0 + k * kSortThreads + threadIdx.x;
+            if (i < n) {
+                item[k] = a.q_in[i];
+                key[k] = a.sum[item[k] >> 2].ncls;
+                rank[k] = atomicAdd(&h[key[k]], 1u);
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i <= kNBins; i += blockDim.x) if (h[i]) base[i] = atomicAdd(&a.bins[i], h[i]);
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < kSortItems; ++k) {
+            const uint32_t i = c0 + k * kSortThreads + threadIdx.x;
+            if (i < n) a.q_sorted[base[key[k]] + rank[k]] = item[k];
+        }
+        __syncthreads();
+    }
+}
+
+// =====================================================================================================
+// K3: thread per fit, pass-aligned within a warp
 // =====================================================================================================
 constexpr int kEmThreads = 128;
+constexpr int kPassBudget = 32;            // passes a fit may spend in K3 before it is parked for K3b
+
+// 1/x for normal positive x: MUFU.RCP64H seed (>= 20 bits) + two Newton steps -> <= ~1 ulp
+__device__ __forceinline__ double rcp_nr2(double x)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    return r;
+}
+
+// log1p(x) for |x| <= 2^-9: x * (1 - x/2 + x^2/3 - x^3/4 + x^4/5), truncation < |x|^5/6 <= 5e-15 relative.
+// A class with |x| >= 2^-9 alone contributes cnt*|log1p(x)| >= |x|/(1+|x|) > 1.9e-3 > epsilon (= 0.001,
+// enforced <= 0.0019 at bvc_create), so that pass is "not converged" without evaluating the sum exactly.
+__device__ __forceinline__ double log1p_tiny(double x)
+{
+    double p = 1.0 / 5.0;
+    p = fma(p, x, -1.0 / 4.0);
+    p = fma(p, x, 1.0 / 3.0);
+    p = fma(p, x, -1.0 / 2.0);
+    p = fma(p, x, 1.0);
+    return p * x;
+}
+
+// exact double of a 23-bit count without an I2F: 2^52 + cnt has cnt in its low mantissa bits
+__device__ __forceinline__ double cnt_to_double(uint32_t cnt)
+{
+    return __hiloint2double(0x43300000, (int)cnt) - 4503599627370496.0;
+}
+
+struct EmAcc { double accT, V0, V1, V2, V3, dl; int xmax; };   // xmax: max over classes of the high word of |x|
+constexpr int kBigXHi = 0x3f600000;       // high word of 2^-9: |x| >= 2^-9  <=>  hi(|x|) >= kBigXHi
+// a class word that contributes exactly nothing (count 0) with finite arithmetic for any valid f: (base 0, qual 30)
+constexpr uint32_t kNullClass = 30u;
+
+// Branch-free 4-way selects by the class's base bits (bit 7 / bit 8 of the class word): nvcc turns the
+// equivalent C ternaries into divergent branches, which serialises lanes whose classes differ in base.
+__device__ __forceinline__ void sel4_pair(uint32_t w, double f0, double f1, double f2, double f3, double p0, double p1,
+                                          double p2, double p3, double& fb, double& pb)
+{
+    asm("{\n\t.reg .pred o, t;\n\t.reg .f64 lo, hi;\n\t"
+        "setp.ne.u32 o, %10, 0;\n\tsetp.ne.u32 t, %11, 0;\n\t"
+        "selp.f64 lo, %3, %2, o;\n\tselp.f64 hi, %5, %4, o;\n\tselp.f64 %0, hi, lo, t;\n\t"
+        "selp.f64 lo, %7, %6, o;\n\tselp.f64 hi, %9, %8, o;\n\tselp.f64 %1, hi, lo, t;\n\t}"
+        : "=d"(fb), "=d"(pb)
+        : "d"(f0), "d"(f1), "d"(f2), "d"(f3), "d"(p0), "d"(p1), "d"(p2), "d"(p3), "r"(w & 0x80u), "r"(w & 0x100u));
+}
+// V_b += v for the class's base b: four predicated adds, no branch
+__device__ __forceinline__ void acc_by_base(uint32_t w, double v, double& V0, double& V1, double& V2, double& V3)
+{
+    asm("{\n\t.reg .pred q0, q1, q2, q3;\n\t"
+        "setp.eq.u32 q0, %5, 0;\n\tsetp.eq.u32 q1, %5, 0x80;\n\tsetp.eq.u32 q2, %5, 0x100;\n\tsetp.eq.u32 q3, %5, 0x180;\n\t"
+        "@q0 add.f64 %0, %0, %4;\n\t@q1 add.f64 %1, %1, %4;\n\t@q2 add.f64 %2, %2, %4;\n\t@q3 add.f64 %3, %3, %4;\n\t}"
+        : "+d"(V0), "+d"(V1), "+d"(V2), "+d"(V3)
+        : "d"(v), "r"(w & 0x180u));
+}
+
+// One class of one pass: Algorithm.cpp:76-91 (E and M step, factored as in the file header) and the
+// stateless delta term (:103-113) against the previous pass's frequencies p (pass 0: p == f -> x == 0).
+__device__ __forceinline__ void em_class(uint32_t w, const double2* lut2, double f0, double f1, double f2, double f3, double F,
+                                         double p0, double p1, double p2, double p3, double Fp, EmAcc& A)
+{
+    const int q = w & (kNQ - 1);
+    const double cnt = cnt_to_double(w >> 9);
+    const double2 ed = lut2[q];                                  // (e/3, (1-e) - e/3)
+    double fb, pb;
+    sel4_pair(w, f0, f1, f2, f3, p0, p1, p2, p3, fb, pb);
+    const double ml = fma(fb, ed.y, ed.x * F);
+    const double r = rcp_nr2(ml);
+    const double wgt = cnt * r;
+    A.accT = fma(ed.x, wgt, A.accT);
+    acc_by_base(w, ed.y * wgt, A.V0, A.V1, A.V2, A.V3);
+    const double mlp = fma(pb, ed.y, ed.x * Fp);
+    const double x = (mlp - ml) * r;
+    A.dl = fma(cnt, fabs(log1p_tiny(x)), A.dl);
+    // range test on the high word (integer pipe); count-0 padding classes never trip it
+    A.xmax = max(A.xmax, (w >> 9) ? (__double2hiint(x) & 0x7fffffff) : 0);
+}
+
+__device__ __forceinline__ void load_lut2(double2* lut2, const double* lut)
+{
+    for (int i = threadIdx.x; i < kNQ; i += blockDim.x) lut2[i] = make_double2(lut[i], lut[4 * kNQ + i]);
+    __syncthreads();
+}
+
+__device__ __forceinline__ void add_work(unsigned long long* ctr, unsigned long long v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(ctr, v);
+}
 
 __global__ void __launch_bounds__(kEmThreads)
 em_fit_kernel(PipeArgs a)
 {
-    __shared__ double lut_e3[kNQ], lut_d[kNQ];
-    for (int i = threadIdx.x; i < kNQ; i += blockDim.x) { lut_e3[i] = a.s.lut[i]; lut_d[i] = a.s.lut[4 * kNQ + i]; }
-    __syncthreads();
+    __shared__ double2 lut2[kNQ];
+    load_lut2(lut2, a.s.lut);
     const uint32_t nfits = *a.q_in_n;
     const int lane = threadIdx.x & 31;
     const double eps = a.s.eps;
     const int max_iter = a.s.max_iter;
 
-    bool active = false, done = false, big = false;
+    bool active = false, done = false;
     const uint32_t* cp = a.cls;
-    int ncls = 0, c = 0, pass = 0;
+    int ncls = 0, pass = 0;
     uint32_t item = 0, fl = 0;
-    double f0 = 0, f1 = 0, f2 = 0, f3 = 0, p0 = 0, p1 = 0, p2 = 0, p3 = 0, F = 0, Fp = 0;
-    double accT = 0, V0 = 0, V1 = 0, V2 = 0, V3 = 0, dl = 0, inv_n = 0;
+    double f0 = 0, f1 = 0, f2 = 0, f3 = 0, p0 = 0, p1 = 0, p2 = 0, p3 = 0, F = 0, Fp = 0, inv_n = 0;
+    unsigned long long work = 0, nfit = 0;
 
     for (;;) {
-        // ---- refill: lanes without a fit take the next queue items (one atomic per warp) ---------------
+        // ---- refill at the pass boundary: lanes without a fit take the next items (one atomic per warp) ---
         const bool want = !active && !done;
         const unsigned wm = __ballot_sync(0xffffffffu, want);
         if (wm) {
@@ -334,7 +467,7 @@ em_fit_kernel(PipeArgs a)
             if (want) {
                 const uint32_t idx = base + __popc(wm & ((1u << lane) - 1));
                 if (idx < nfits) {
-                    item = a.q_in[idx];
+                    item = a.q_sorted[idx];
                     const uint32_t site = item >> 2;
                     const SiteSum su = a.sum[site];
                     const uint32_t mask = a.fit[(size_t)site * 4 + (item & 3)].mask;
@@ -349,77 +482,169 @@ em_fit_kernel(PipeArgs a)
                     f2 = (mask & 4) ? (double)su.depth[2] / ds : 0.0;
                     f3 = (mask & 8) ? (double)su.depth[3] / ds : 0.0;
                     F = ((f0 + f1) + f2) + f3;
+                    p0 = f0; p1 = f1; p2 = f2; p3 = f3; Fp = F;       // pass 0: delta term is exactly 0
                     inv_n = 1.0 / (double)(su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3]);
-                    cp = a.cls + su.cls_off; ncls = su.ncls; c = 0; pass = 0; fl = 0;
-                    accT = V0 = V1 = V2 = V3 = dl = 0.0; big = false;
-                    active = true;
+                    cp = a.cls + su.cls_off; ncls = su.ncls; pass = 0; fl = 0;
+                    active = true; ++nfit;
                 } else done = true;
             }
         }
-        if (__all_sync(0xffffffffu, done)) break;
-        if (!active) continue;
+        if (!__any_sync(0xffffffffu, active)) break;
+        const int nmax = __reduce_max_sync(0xffffffffu, active ? ncls : 0);
 
-        // ---- one class of the current pass ---------------------------------------------------------------
-        const uint32_t w = __ldg(cp + c);
-        const int q = w & (kNQ - 1), b = (w >> 7) & 3;
-        const double cnt = (double)(w >> 9);
-        const double e3 = lut_e3[q], d = lut_d[q];
-        const double fb = sel4(b, f0, f1, f2, f3);
-        const double ml = fma(fb, d, e3 * F);                        // Algorithm.cpp:76-79
-        const double r = fast_rcp(ml);
-        const double wgt = cnt * r;
-        accT = fma(e3, wgt, accT);                                   // :80-91, factored (see file header)
-        const double v = d * wgt;
-        if (b == 0) V0 += v; else if (b == 1) V1 += v; else if (b == 2) V2 += v; else V3 += v;
-        if (pass > 0) {                                              // :103-113, stateless
-            const double pb = sel4(b, p0, p1, p2, p3);
-            const double mlp = fma(pb, d, e3 * Fp);
-            const double x = (mlp - ml) * r;
-            const double t = fabs(log1p_small(x));
-            if (fabs(x) <= 0.015625) dl = fma(cnt, t, dl); else big = true;
+        // ---- one pass: warp-uniform trip count, lanes with fewer classes idle at the end --------------------
+        // Straight-line body: a lane past its last class (or without a fit) processes a count-0 null class, so
+        // the four unrolled class bodies interleave (ILP) instead of sitting behind per-class branches.
+        EmAcc A; A.accT = A.V0 = A.V1 = A.V2 = A.V3 = A.dl = 0.0; A.xmax = 0;
+        const int nmine = active ? ncls : 0;
+#pragma unroll 4
+        for (int c = 0; c < nmax; ++c) {
+            const uint32_t w = (c < nmine) ? __ldg(cp + c) : kNullClass;
+            em_class(w, lut2, f0, f1, f2, f3, F, p0, p1, p2, p3, Fp, A);
         }
-        if (++c == ncls) {
-            const double e0 = f0 * (accT + V0) * inv_n, e1 = f1 * (accT + V1) * inv_n;
-            const double e2 = f2 * (accT + V2) * inv_n, e3v = f3 * (accT + V3) * inv_n;
+        const bool big = A.xmax >= kBigXHi;
+
+        if (active) {
+            work += (unsigned long long)ncls;
+            const double e0 = f0 * (A.accT + A.V0) * inv_n, e1 = f1 * (A.accT + A.V1) * inv_n;
+            const double e2 = f2 * (A.accT + A.V2) * inv_n, e3 = f3 * (A.accT + A.V3) * inv_n;
             bool stop = (pass == max_iter);
             if (pass > 0 && !big) {
-                if (near_rel(dl, eps)) fl |= BVC_FLAG_EM_DELTA;
-                if (dl < eps) stop = true;                           // :124
+                if (near_rel(A.dl, eps)) fl |= BVC_FLAG_EM_DELTA;
+                if (A.dl < eps) stop = true;                         // Algorithm.cpp:124
             }
+            FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
             if (stop) {
-                FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
                 fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
-                fr->eap[0] = e0; fr->eap[1] = e1; fr->eap[2] = e2; fr->eap[3] = e3v;
-                fr->passes = pass + 1; fr->flags = fl;
+                fr->eap[0] = e0; fr->eap[1] = e1; fr->eap[2] = e2; fr->eap[3] = e3;
+                fr->passes = pass + 1; fr->flags = fl; fr->unfinished = 0;
                 active = false;
             } else {
                 p0 = f0; p1 = f1; p2 = f2; p3 = f3; Fp = F;
-                f0 = e0; f1 = e1; f2 = e2; f3 = e3v;                 // :95-101
+                f0 = e0; f1 = e1; f2 = e2; f3 = e3;                  // Algorithm.cpp:95-101
                 F = ((f0 + f1) + f2) + f3;
-                accT = V0 = V1 = V2 = V3 = dl = 0.0; big = false;
-                c = 0; ++pass;
+                ++pass;
+                if (pass >= kPassBudget) {                           // park: K3b resumes at `pass` with (f, p)
+                    fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
+                    fr->eap[0] = p0; fr->eap[1] = p1; fr->eap[2] = p2; fr->eap[3] = p3;
+                    fr->passes = pass; fr->flags = fl; fr->unfinished = 1;
+                    a.q_long[atomicAdd(a.q_long_n, 1u)] = item;
+                    active = false;
+                }
             }
         }
     }
+    add_work(a.work + 0, work);
+    add_work(a.work + 3, nfit);
+}
+
+// =====================================================================================================
+// K3b: warp per parked fit -- classes across lanes, butterfly sums: ~25x lower latency per pass than a
+// single thread, so the few fits that need up to 101 passes do not set the stage's duration.
+// =====================================================================================================
+constexpr int kLongWarps = 4;
+
+__global__ void __launch_bounds__(kLongWarps * 32)
+em_long_kernel(PipeArgs a)
+{
+    __shared__ double2 lut2[kNQ];
+    load_lut2(lut2, a.s.lut);
+    const uint32_t n_long = *a.q_long_n;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const double eps = a.s.eps;
+    const int max_iter = a.s.max_iter;
+    unsigned long long work = 0;
+    for (uint32_t i = blockIdx.x * kLongWarps + wid; i < n_long; i += gridDim.x * kLongWarps) {
+        const uint32_t item = a.q_long[i];
+        const SiteSum su = a.sum[item >> 2];
+        FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
+        double f0 = fr->f[0], f1 = fr->f[1], f2 = fr->f[2], f3 = fr->f[3];
+        double p0 = fr->eap[0], p1 = fr->eap[1], p2 = fr->eap[2], p3 = fr->eap[3];
+        double F = ((f0 + f1) + f2) + f3, Fp = ((p0 + p1) + p2) + p3;
+        int pass = fr->passes;
+        uint32_t fl = fr->flags;
+        const double inv_n = 1.0 / (double)(su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3]);
+        const uint32_t* cp = a.cls + su.cls_off;
+        const int ncls = su.ncls;
+        __syncwarp();
+        for (;;) {
+            EmAcc A; A.accT = A.V0 = A.V1 = A.V2 = A.V3 = A.dl = 0.0; A.xmax = 0;
+            for (int c = lane; c < ncls; c += 32) em_class(__ldg(cp + c), lut2, f0, f1, f2, f3, F, p0, p1, p2, p3, Fp, A);
+            const double accT = warp_sum(A.accT), V0 = warp_sum(A.V0), V1 = warp_sum(A.V1), V2 = warp_sum(A.V2),
+                         V3 = warp_sum(A.V3), dl = warp_sum(A.dl);
+            const bool big = __any_sync(0xffffffffu, A.xmax >= kBigXHi);
+            if (lane == 0) work += (unsigned long long)ncls;
+            const double e0 = f0 * (accT + V0) * inv_n, e1 = f1 * (accT + V1) * inv_n;
+            const double e2 = f2 * (accT + V2) * inv_n, e3 = f3 * (accT + V3) * inv_n;
+            bool stop = (pass == max_iter);
+            if (pass > 0 && !big) {
+                if (near_rel(dl, eps)) fl |= BVC_FLAG_EM_DELTA;
+                if (dl < eps) stop = true;
+            }
+            if (stop) {
+                if (lane == 0) {
+                    fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
+                    fr->eap[0] = e0; fr->eap[1] = e1; fr->eap[2] = e2; fr->eap[3] = e3;
+                    fr->passes = pass + 1; fr->flags = fl; fr->unfinished = 0;
+                }
+                break;
+            }
+            p0 = f0; p1 = f1; p2 = f2; p3 = f3; Fp = F;
+            f0 = e0; f1 = e1; f2 = e2; f3 = e3;
+            F = ((f0 + f1) + f2) + f3;
+            ++pass;
+        }
+        __syncwarp();
+    }
+    add_work(a.work + 1, work);
+}
+
+// =====================================================================================================
+// K3c: thread per fit -- lr = sum_c cnt_c log ml_c(f) with the f of the fit's LAST E-step
+// (BaseType.cpp:57-60).  Same sorted queue, so a warp's 32 loops have (nearly) equal length.
+// =====================================================================================================
+__global__ void __launch_bounds__(kEmThreads)
+fit_loglik_kernel(PipeArgs a)
+{
+    __shared__ double2 lut2[kNQ];
+    load_lut2(lut2, a.s.lut);
+    const uint32_t nfits = *a.q_in_n;
+    unsigned long long work = 0;
+    const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u, lane = threadIdx.x & 31;
+    for (uint32_t wbase = i0; wbase < nfits; wbase += gridDim.x * blockDim.x) {
+        const uint32_t idx = wbase + lane;
+        const bool on = idx < nfits;
+        const uint32_t item = on ? a.q_sorted[idx] : 0u;
+        FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
+        double f0 = 0, f1 = 0, f2 = 0, f3 = 0;
+        const uint32_t* cp = a.cls; int ncls = 0;
+        if (on) {
+            const SiteSum su = a.sum[item >> 2];
+            f0 = fr->f[0]; f1 = fr->f[1]; f2 = fr->f[2]; f3 = fr->f[3];
+            cp = a.cls + su.cls_off; ncls = su.ncls;
+        }
+        const double F = ((f0 + f1) + f2) + f3;
+        const int nmax = __reduce_max_sync(0xffffffffu, ncls);
+        double s = 0.0;
+        for (int c = 0; c < nmax; ++c) {
+            if (c < ncls) {
+                const uint32_t w = __ldg(cp + c);
+                const int q = w & (kNQ - 1);
+                const double2 ed = lut2[q];
+                double fb, unused;
+                sel4_pair(w, f0, f1, f2, f3, f0, f1, f2, f3, fb, unused);
+                const double ml = fma(fb, ed.y, ed.x * F);
+                s = fma(cnt_to_double(w >> 9), log(ml), s);
+            }
+        }
+        if (on) { fr->lr = s; work += (unsigned long long)ncls; }
+    }
+    add_work(a.work + 2, work);
 }
 
 // =====================================================================================================
 // K4: thread per site -- log-likelihoods of the finished fits, LRT decision, next stage or final call
 // =====================================================================================================
-// lr of one fit: sum_c cnt_c * log(ml_c(f))  (BaseType.cpp:57-60) with the same ml formula as K3
-__device__ __forceinline__ double fit_loglik(const PipeArgs& a, const SiteSum& su, const double* f)
-{
-    const double F = ((f[0] + f[1]) + f[2]) + f[3];
-    const uint32_t* cp = a.cls + su.cls_off;
-    double s = 0.0;
-    for (int c = 0; c < su.ncls; ++c) {
-        const uint32_t w = __ldg(cp + c);
-        const int q = w & (kNQ - 1), b = (w >> 7) & 3;
-        const double ml = fma(sel4(b, f[0], f[1], f[2], f[3]), __ldg(a.s.lut + 4 * kNQ + q), __ldg(a.s.lut + q) * F);
-        s = fma((double)(w >> 9), log(ml), s);
-    }
-    return s;
-}
 // closed form for a single-base model: f = e_b is a fixed point of EM (2 passes, delta == 0);
 // lr = sum_c cnt_c * log L_cb from the host-built (glibc) log table
 __device__ __forceinline__ double single_loglik(const PipeArgs& a, const SiteSum& su, int base)
@@ -449,13 +674,13 @@ ladder_kernel(PipeArgs a)
 
     // ---- results of the EM stage in flight -----------------------------------------------------------------
     if (k == n) {                                                  // the full model (BaseType.cpp:88-90)
-        L.lr_alt = fit_loglik(a, su, fr[0].f);
+        L.lr_alt = fr[0].lr;
         for (int j = 0; j < 4; ++j) L.frq[j] = fr[0].eap[j];
         L.em_fits += 1; L.em_passes += fr[0].passes; L.flags |= fr[0].flags;
     } else {                                                       // k-subsets, combs_ order (BaseType.cpp:93-110)
         double cmin = 0.0, lr_min = 0.0; int imin = 0;
         for (int i = 0; i < L.nfit; ++i) {
-            const double lr = fit_loglik(a, su, fr[i].f);
+            const double lr = fr[i].lr;
             const double chi = 2.0 * (L.lr_alt - lr);
             if (i > 0 && near_rel(chi, cmin)) L.flags |= BVC_FLAG_ARGMIN_TIE;
             if (i == 0 || chi < cmin) { cmin = chi; lr_min = lr; imin = i; }

@@ -19,13 +19,15 @@ struct __align__(16) SiteSum {      // 64 B, written by K1
     int32_t  pad;
 };
 
-struct __align__(16) FitRes {       // 80 B, one per (site, slot)
+struct __align__(16) FitRes {       // 96 B, one per (site, slot)
     double  f[4];                   // allele frequencies used by the LAST E-step (its ml enters lr)
     double  eap[4];                 // M-step after it (what UpdateF reports, BaseType.cpp:61-69)
-    int32_t passes;
+                                    // (an UNFINISHED fit parks its state here: f = next f, eap = previous f)
+    double  lr;                     // sum_c cnt_c log ml_c(f)  (BaseType.cpp:57-60), written by fit_loglik_kernel
+    int32_t passes;                 // singleEM passes done (unfinished: index of the pass to resume at)
     uint32_t flags;
     uint32_t mask;                  // allele subset (bit b = base b)
-    uint32_t pad;
+    uint32_t unfinished;            // 1: pass budget hit in em_fit_kernel, em_long_kernel finishes it
 };
 
 struct __align__(16) Ladder {       // 80 B per site
@@ -52,11 +54,16 @@ struct PipeArgs {
     Ladder*   lad;              // [n_sites]
     FitRes*   fit;              // [n_sites][4]
     uint8_t*  state;            // [n_sites]
-    uint32_t* q_in;             // fit queue consumed by K3 (site << 2 | slot)
-    uint32_t* q_out;            // fit queue filled by K2/K4
+    uint32_t* q_in;             // fit queue of this stage as K2/K4 filled it (site << 2 | slot), unsorted
+    uint32_t* q_out;            // fit queue K4 fills for the next stage
     uint32_t* q_in_n;           // counts
     uint32_t* q_out_n;
     uint32_t* q_in_head;        // K3 refill cursor
+    uint32_t* q_sorted;         // q_in counting-sorted by descending class count (lanes of a warp get equal-length fits)
+    uint32_t* bins;             // [kNBins + 1] histogram of class counts, then scatter cursors
+    uint32_t* q_long;           // fits that hit the pass budget
+    uint32_t* q_long_n;
+    unsigned long long* work;   // [4] diagnostics: class-passes done by em_fit / em_long, loglik class evaluations, fits
     uint32_t* vcf_list;         // LRT-positive sites
     uint32_t* vcf_n;
     uint32_t* legacy_list;      // sites for the IEEE-faithful warp-per-site kernel

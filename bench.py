@@ -26,6 +26,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "site*samples/sec for basetype EM+LRT"
+# FP64 operations em_fit_kernel's arithmetic performs per (base, qual) class per singleEM pass, FMA = 2
+# (DESIGN.md "Kernels": E/M step 17 = count 1, ml 3, Newton reciprocal 8, weight 1, two accumulations 4;
+#  delta term 17 = ml' 3, difference + scale 2, log1p series 9, accumulate 2, range test 1)
+FLOP_PER_CLASS_PASS = 34
 UNIT = "site*samples/s"
 
 
@@ -209,6 +213,7 @@ def main():
     value = world * units_per_gpu / (ms_step * 1e-3)
     # per-kernel breakdown of the same pass (separate, untimed-for-value run: events sit between the launches)
     _, per_kernel = caller.resident_run(max(2, min(args.steps, 5)), flush_l2=False, per_kernel=True)
+    work = caller.work_counters()
 
     # ---- e2e leg: host buffers through bvc_enqueue / bvc_wait (pinned H2D + D2H inside the region) --
     nsub = max(1, min(args.subtiles, S))
@@ -249,13 +254,28 @@ def main():
     e2e_value = world * units_per_gpu / e2e_s
     same = all(np.array_equal(np.concatenate([o.array for o in outs])[f], recs[f]) for f in ("depth", "lrt_ok", "alt_bases"))
 
-    # ---- roofline of the dominant (only) kernel ---------------------------------------------------
+    # ---- rooflines (DESIGN.md "Measurement"): the dominant kernel, the streaming kernel, the whole step ----------
     peak, peak_src = _peaks()
-    alg_bytes = _alg_bytes(tile)
-    achieved = alg_bytes / (ms * 1e-3) / 1e9
-    n_reads = recs["depth"].sum(1).astype(np.float64)
-    f_alg = float((n_reads * (21.0 * recs["em_passes"] - 3.0 * recs["em_fits"])).sum())
     fp64_peak = B.measure_fp64_peak(local)
+    dom = max(per_kernel, key=per_kernel.get)
+    k_ms = per_kernel[dom]
+    alg_bytes = _alg_bytes(tile)                       # whole step, SURVEY 8(d): 4R + 8S + 192 S_out
+    hist_bytes = 2 * R + 5 * S + 64 * S                # K1: code+qual bytes, offsets+ref, 64-B site summary out
+    hist_ms = per_kernel.get("site_hist_kernel", 0.0)
+    em_flop = FLOP_PER_CLASS_PASS * work["em_class_passes"]
+    if dom == "em_fit_kernel":
+        roof = {"bound": "fp64", "achieved": em_flop / (k_ms * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
+                "peak_source": "measured here (bvc_measure_fp64_peak: dependent-free DFMA chains on all SMs)",
+                "algorithmic_flop_per_launch": em_flop, "class_passes_per_launch": int(work["em_class_passes"]),
+                "flop_per_class_pass": FLOP_PER_CLASS_PASS}
+    else:
+        kb = hist_bytes if dom == "site_hist_kernel" else alg_bytes
+        roof = {"bound": "hbm", "achieved": kb / (k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": int(kb)}
+    roof.update({"frac": roof["achieved"] / roof["peak"], "traffic": None, "kernel": dom, "kernel_ms": k_ms,
+                 "kernel_share_of_step": k_ms / max(sum(per_kernel.values()), 1e-9)})
+    n_reads = recs["depth"].sum(1).astype(np.float64)
+    f_alg = float((n_reads * (21.0 * recs["em_passes"] - 3.0 * recs["em_fits"])).sum())   # per-READ formulation, SURVEY 8(d)
 
     if rank != 0:
         if dist is not None:
@@ -277,12 +297,16 @@ def main():
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "matches_resident": bool(same)},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
-                     "kernel": "site_call_kernel", "kernel_ms": ms},
-        "fp64": {"algorithmic_tflops": f_alg / (ms * 1e-3) / 1e12, "peak_tflops_measured": fp64_peak,
-                 "frac": f_alg / (ms * 1e-3) / 1e12 / fp64_peak, "algorithmic_flop_per_launch": f_alg,
-                 "note": "F_alg counts the reference's per-read E/M/delta flops (SURVEY 8d); the kernel does fewer (class collapse)"},
+        "roofline": roof,
+        "hbm_stream": {"kernel": "site_hist_kernel", "kernel_ms": hist_ms, "algorithmic_bytes_per_launch": int(hist_bytes),
+                       "achieved": hist_bytes / max(hist_ms, 1e-9) / 1e6, "peak": peak, "unit": "GB/s",
+                       "frac": hist_bytes / max(hist_ms, 1e-9) / 1e6 / peak},
+        "step": {"algorithmic_bytes": int(alg_bytes), "hbm_floor_ms": alg_bytes / peak / 1e6,
+                 "em_flop_floor_ms": em_flop / fp64_peak / 1e9, "measured_ms": ms,
+                 "per_read_flop_survey": f_alg, "per_read_tflops_equiv": f_alg / (ms * 1e-3) / 1e12,
+                 "note": "per_read_* counts the flops of the reference's per-read EM (SURVEY 8d); the class-collapsed "
+                         "kernels do ~n_reads/n_classes fewer, so it is an equivalence figure, not pipe utilisation"},
+        "work": {k: int(v) for k, v in work.items()},
         "kernels_ms": {k: round(v, 4) for k, v in per_kernel.items()},
         "cpu_baseline": cpu,
         "clocks": clocks,

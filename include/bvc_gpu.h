@@ -139,6 +139,10 @@ int  bvc_resident_run(bvc_ctx* ctx, int iters, int flush_l2, float* ms_per_launc
                       float* per_kernel_ms, int* n_kernels_out);
 int  bvc_resident_download(bvc_ctx* ctx, bvc_site_result* out);
 const char* bvc_kernel_name(int kind);                 /* kind in [0, n_kernels) */
+/* Work done by the last bvc_resident_run pass: out4 = { class-passes in em_fit_kernel, class-passes in
+ * em_long_kernel, class evaluations in fit_loglik_kernel, EM fits }.  One class-pass = one (base, qual)
+ * class of one singleEM pass (src/Algorithm.cpp:69-93 + its delta term :103-113). */
+int  bvc_work_counters(bvc_ctx* ctx, uint64_t* out4);
 int64_t bvc_kernel_launch_count(const bvc_ctx* ctx);   /* kernels of ours launched so far */
 /* Cumulative bytes moved by bvc_enqueue's copies (H2D of tiles, D2H of records).  mapq / rpr arrays that live
  * in pinned host memory are NOT copied: the kernels read them in place for LRT-positive sites only. */
