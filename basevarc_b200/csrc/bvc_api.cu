@@ -192,7 +192,7 @@ int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullpt
     p.q_in_head = s.d_ctr + 3;
     p.vcf_list = s.d_vcf_list; p.vcf_n = s.d_ctr + 4;
     p.legacy_list = s.d_legacy_list; p.legacy_n = s.d_ctr + 5;
-    p.q_sorted = s.d_qs; p.q_long = s.d_ql; p.q_long_n = s.d_ctr + 6;
+    p.q_sorted = s.d_qs; p.q_long = s.d_ql; p.q_long_n = s.d_ctr + 6; p.q_long_head = s.d_ctr + 7;
     p.work = reinterpret_cast<unsigned long long*>(s.d_ctr + 8);
     p.bins = s.d_ctr + 16;
     int nl = 0;

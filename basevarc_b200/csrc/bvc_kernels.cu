@@ -211,7 +211,7 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     int launches = 0;
     static int occ_hist = 0, occ_em = 0, occ_vcf = 0, occ_leg = 0, occ_long = 0, occ_ll = 0;
     if (!occ_hist) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_long, em_long_kernel, kLongWarps * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_long, em_long_kernel, kLongThreads, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ll, fit_loglik_kernel, kEmThreads, 0);
         if (occ_long < 1) occ_long = 1; if (occ_ll < 1) occ_ll = 1;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist, site_hist_kernel, kHistWarps * 32, 0);
@@ -236,7 +236,7 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
         t = a.q_in_n; a.q_in_n = a.q_out_n; a.q_out_n = t;
         cudaMemsetAsync(a.q_out_n, 0, sizeof(uint32_t), stream);
         cudaMemsetAsync(a.q_in_head, 0, sizeof(uint32_t), stream);
-        cudaMemsetAsync(a.q_long_n, 0, sizeof(uint32_t), stream);
+        cudaMemsetAsync(a.q_long_n, 0, 2 * sizeof(uint32_t), stream);   // q_long_n, q_long_head
         cudaMemsetAsync(a.bins, 0, (kNBins + 1) * sizeof(uint32_t), stream);
         mark(kKSort);
         queue_hist_kernel<<<(unsigned)(n_sm * 2), kSortThreads, 0, stream>>>(a);
@@ -247,7 +247,7 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
         mark(kKEm);
         em_fit_kernel<<<(unsigned)(n_sm * occ_em), kEmThreads, 0, stream>>>(a);
         mark(kKEmLong);
-        em_long_kernel<<<(unsigned)(n_sm * occ_long), kLongWarps * 32, 0, stream>>>(a);
+        em_long_kernel<<<(unsigned)(n_sm * occ_long), kLongThreads, 0, stream>>>(a);
         mark(kKLoglik);
         fit_loglik_kernel<<<(unsigned)(n_sm * occ_ll), kEmThreads, 0, stream>>>(a);
         mark(kKLadder);

@@ -53,61 +53,95 @@ __device__ __forceinline__ double sel4(int b, double v0, double v1, double v2, d
 // K1: warp per site -- stream entries, histogram, compact classes, strand tables
 // =====================================================================================================
 constexpr int kHistWarps = 8;
+constexpr int kHistBins = 2 * kNBins;      // [strand][base][qual]
 
 __global__ void __launch_bounds__(kHistWarps * 32)
 site_hist_kernel(PipeArgs a)
 {
-    __shared__ uint32_t hist_s[kHistWarps][kNBins];
-    __shared__ uint32_t code_s[kHistWarps][32];
+    __shared__ uint32_t hist_s[kHistWarps][kHistBins];
+    __shared__ uint32_t ind_s[kHistWarps][8];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    uint32_t* hist = hist_s[wid];
-    uint32_t* chist = code_s[wid];
-    for (int i = lane; i < kNBins; i += 32) hist[i] = 0;
-    chist[lane] = 0;
+    uint32_t* hist = hist_s[wid];              // non-indel entries: strand << 9 | base << 7 | qual
+    uint32_t* ind = ind_s[wid];                // indel entries (stale base < 4): strand << 2 | base
+    for (int i = lane; i < kHistBins; i += 32) hist[i] = 0;
+    if (lane < 8) ind[lane] = 0;
     __syncwarp();
+    const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
+    const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
+    const unsigned lt = (1u << lane) - 1u;
 
     const int n_warps = gridDim.x * kHistWarps;
     for (int site = blockIdx.x * kHistWarps + wid; site < a.s.n_sites; site += n_warps) {
         const uint32_t b0 = a.s.entry_off[site], b1 = a.s.entry_off[site + 1];
         const int ref = a.s.ref_base[site] & 3;
-        // ---- stream: 4 entries per lane per 32-bit load, 128 B per warp-load, both arrays in flight ----
-        unsigned qmin = 127, qmax = 0;
+        // ---- stream: 4 entries per lane per 32-bit load, 128 B per warp-load, both arrays in flight.  One shared
+        // atomic per entry does all the counting: the bin carries strand, base and qual.  Bytes outside
+        // [b0, b1) in the first / last word are turned into code 0x14 (indel, base 4), which nothing counts.
         const uint32_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;
-        const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
-        const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
-        for (uint32_t wbase = w0; wbase < w1; wbase += 32) {
-            const uint32_t wi = wbase + lane;
-            uint32_t cw = 0, qw = 0;
-            if (wi < w1) { cw = __ldg(code4 + wi); qw = __ldg(qual4 + wi); }
+        uint32_t qor = 0;
+        bool any_ind = false;
+        for (uint32_t wi = w0 + lane; wi < w1; wi += 32) {
+            uint32_t cw = __ldg(code4 + wi);
+            const uint32_t qw = __ldg(qual4 + wi) & 0x7f7f7f7fu;
+            if (wi == w0 || wi + 1 == w1) {
+                const uint32_t e0 = wi * 4;
+                const uint32_t lo = b0 > e0 ? b0 - e0 : 0u, hi = b1 < e0 + 4 ? b1 - e0 : 4u;     // valid bytes [lo, hi)
+                const uint32_t vm = (hi >= 4 ? 0xffffffffu : ((1u << (8 * hi)) - 1u)) & ~((1u << (8 * lo)) - 1u);
+                cw = (cw & vm) | (0x14141414u & ~vm);
+            }
+            qor |= qw;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const uint32_t e = wi * 4 + k;
-                const bool valid = (wi < w1) && e >= b0 && e < b1;
-                const unsigned c = (cw >> (8 * k)) & 31u;
-                const unsigned q = (qw >> (8 * k)) & (kNQ - 1);
-                // code histogram: lanes with equal codes elect one leader -> conflict-free shared atomics
-                const unsigned key = valid ? c : 32u;
-                const unsigned peers = __match_any_sync(0xffffffffu, key);
-                if (valid && (__ffs(peers) - 1) == lane) atomicAdd(&chist[c], (unsigned)__popc(peers));
-                if (valid && !(c & 16)) {
-                    atomicAdd(&hist[((c & 3) << 7) | q], 1u);
-                    qmin = min(qmin, q); qmax = max(qmax, q);
+                const uint32_t c = cw >> (8 * k), q = (qw >> (8 * k)) & 0x7fu;
+                if (!(c & 0x14u)) atomicAdd(&hist[((c & 8u) << 6) | ((c & 3u) << 7) | q], 1u);
+            }
+            if (cw & 0x10101010u) {                 // rare: indel entries keep only (stale base, strand)
+                any_ind = true;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t c = cw >> (8 * k);
+                    if ((c & 0x14u) == 0x10u) atomicAdd(&ind[((c >> 1) & 4u) | (c & 3u)], 1u);
                 }
             }
         }
         __syncwarp();
-        const int cnt = (int)chist[lane];          // lane = base | strand << 3 | indel << 4
-        chist[lane] = 0;
-        qmin = __reduce_min_sync(0xffffffffu, qmin);
-        qmax = __reduce_max_sync(0xffffffffu, qmax);
+        // qual range actually present, from the OR of all qual bytes: scan 32, 64 or 128 quals per (base, strand)
+        qor = __reduce_or_sync(0xffffffffu, qor);
+        qor = (qor | (qor >> 8) | (qor >> 16) | (qor >> 24)) & 0x7fu;
+        const int nsteps = qor >= 64 ? 4 : (qor >= 32 ? 2 : 1);
+        any_ind = __any_sync(0xffffffffu, any_ind);
 
+        // ---- pass 1 over the bins: merged counts into registers, per-base depth / forward depth / class count --------
+        uint32_t v[4][4];
+        int dsum[4], fsum[4], ncb[4];
+        unsigned lowq = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            dsum[b] = 0; fsum[b] = 0; ncb[b] = 0;
+#pragma unroll
+            for (int st = 0; st < 4; ++st) {
+                v[b][st] = 0;
+                if (st < nsteps) {
+                    const int bin = (b << 7) + st * 32 + lane;
+                    const uint32_t h0 = hist[bin], h1 = hist[kNBins + bin];
+                    hist[bin] = 0; hist[kNBins + bin] = 0;
+                    v[b][st] = h0 + h1;
+                    dsum[b] += (int)(h0 + h1); fsum[b] += (int)h1;
+                    const unsigned m = __ballot_sync(0xffffffffu, v[b][st] != 0);
+                    ncb[b] += __popc(m);
+                    if (st == 0) lowq |= m & 3u;          // bit 0: a qual-0 class, bit 1: a qual-1 class
+                }
+            }
+        }
         int depth[4], fwd[4], n_reads = 0;
 #pragma unroll
         for (int b = 0; b < 4; ++b) {               // src/BaseVarC.cpp:550-559
-            fwd[b] = __shfl_sync(0xffffffffu, cnt, b | 8);
-            depth[b] = __shfl_sync(0xffffffffu, cnt, b) + fwd[b];
+            depth[b] = __reduce_add_sync(0xffffffffu, dsum[b]);
+            fwd[b] = __reduce_add_sync(0xffffffffu, fsum[b]);
             n_reads += depth[b];
         }
+        int icnt = 0;                               // lane = strand << 2 | base of the indel entries
+        if (any_ind) { icnt = lane < 8 ? (int)ind[lane] : 0; __syncwarp(); if (lane < 8) ind[lane] = 0; }
         // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
         int best = -1, bestd = -1, second = -1, secondd = -1;
 #pragma unroll
@@ -117,48 +151,47 @@ site_hist_kernel(PipeArgs a)
         }
         const int alt = (best != ref) ? best : second;
         // src/BaseVarC.cpp:587-602: 2x2 table over ALL entries (indel entries carry stale base/strand)
-        const int c0 = __shfl_sync(0xffffffffu, cnt, ref | 8) + __shfl_sync(0xffffffffu, cnt, ref | 24);
-        const int c1 = __shfl_sync(0xffffffffu, cnt, ref) + __shfl_sync(0xffffffffu, cnt, ref | 16);
-        const int c2 = __shfl_sync(0xffffffffu, cnt, alt | 8) + __shfl_sync(0xffffffffu, cnt, alt | 24);
-        const int c3 = __shfl_sync(0xffffffffu, cnt, alt) + __shfl_sync(0xffffffffu, cnt, alt | 16);
+        const int fr_ = ref == 0 ? fwd[0] : ref == 1 ? fwd[1] : ref == 2 ? fwd[2] : fwd[3];
+        const int dr_ = ref == 0 ? depth[0] : ref == 1 ? depth[1] : ref == 2 ? depth[2] : depth[3];
+        const int fa_ = alt == 0 ? fwd[0] : alt == 1 ? fwd[1] : alt == 2 ? fwd[2] : fwd[3];
+        const int da_ = alt == 0 ? depth[0] : alt == 1 ? depth[1] : alt == 2 ? depth[2] : depth[3];
+        const int c0 = fr_ + __shfl_sync(0xffffffffu, icnt, ref | 4);
+        const int c1 = (dr_ - fr_) + __shfl_sync(0xffffffffu, icnt, ref);
+        const int c2 = fa_ + __shfl_sync(0xffffffffu, icnt, alt | 4);
+        const int c3 = (da_ - fa_) + __shfl_sync(0xffffffffu, icnt, alt);
 
-        // ---- compact the non-empty classes into the global pool (count, allocate, write) ----------------
-        int ncls = 0;
-        const unsigned qlo = qmin & ~31u;
-        if (n_reads > 0) {
-            for (int b = 0; b < 4; ++b) {
-                if (depth[b] == 0) continue;
-                for (unsigned q0 = qlo; q0 <= qmax; q0 += 32)
-                    ncls += __popc(__ballot_sync(0xffffffffu, hist[(b << 7) + q0 + lane] != 0));
-            }
-        }
+        // ---- pass 2: write the non-empty classes to the pool.  Order: the MAJOR base (top depth, ties -> lowest
+        // code) first, then the other bases ascending; K3 runs the major segment select-free. ----------------------
+        const int ncls = ncb[0] + ncb[1] + ncb[2] + ncb[3];
+        const int n_major = best == 0 ? ncb[0] : best == 1 ? ncb[1] : best == 2 ? ncb[2] : ncb[3];
         uint32_t off = 0;
         if (lane == 0 && ncls) off = atomicAdd(a.cls_cursor, (uint32_t)ncls);
         off = __shfl_sync(0xffffffffu, off, 0);
-        if (n_reads > 0) {
-            uint32_t pos = off;
-            for (int b = 0; b < 4; ++b) {
-                if (depth[b] == 0) continue;
-                for (unsigned q0 = qlo; q0 <= qmax; q0 += 32) {
-                    const unsigned bin = (b << 7) + q0 + lane;
-                    const uint32_t v = hist[bin];
-                    const unsigned m = __ballot_sync(0xffffffffu, v != 0);
-                    if (v) {
-                        a.cls[pos + __popc(m & ((1u << lane) - 1))] = (v << 9) | bin;
-                        hist[bin] = 0;
-                    }
+        uint32_t run = off + (uint32_t)n_major;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            uint32_t pos;
+            if (b == best) pos = off; else { pos = run; run += (uint32_t)ncb[b]; }
+            if (ncb[b] == 0) continue;
+#pragma unroll
+            for (int st = 0; st < 4; ++st) {
+                if (st < nsteps) {
+                    const uint32_t x = v[b][st];
+                    const unsigned m = __ballot_sync(0xffffffffu, x != 0);
+                    if (x) a.cls[pos + __popc(m & lt)] = (x << 9) | (uint32_t)((b << 7) + st * 32 + lane);
                     pos += __popc(m);
                 }
             }
         }
         // ---- 64-byte summary: lanes 0..15 store one word each ----------------------------------------------
         int word = 0;
-        if (lane < 4) word = depth[lane];
-        else if (lane < 8) word = fwd[lane - 4];
+        if (lane == 0) word = depth[0]; else if (lane == 1) word = depth[1]; else if (lane == 2) word = depth[2]; else if (lane == 3) word = depth[3];
+        else if (lane == 4) word = fwd[0]; else if (lane == 5) word = fwd[1]; else if (lane == 6) word = fwd[2]; else if (lane == 7) word = fwd[3];
         else if (lane == 8) word = c0; else if (lane == 9) word = c1; else if (lane == 10) word = c2; else if (lane == 11) word = c3;
         else if (lane == 12) word = (int)off;
-        else if (lane == 13) word = ncls | (alt << 16) | ((n_reads > 0 && qmin == 0) ? (1 << 24) : 0);
+        else if (lane == 13) word = ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0);
         else if (lane == 14) word = (int)(b1 - b0);
+        else if (lane == 15) word = n_major | (best << 16);
         if (lane < 16) reinterpret_cast<int*>(a.sum + site)[lane] = word;
         __syncwarp();
     }
@@ -229,7 +262,7 @@ site_prepare_kernel(PipeArgs a)
         const int ref = a.s.ref_base[site] & 3;
         const int n_reads = su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3];
         bvc_site_result* r = a.s.out + site;
-        if (su.has_q0) {
+        if (su.has_q0 & 1) {
             a.state[site] = kStLegacy;
             a.legacy_list[atomicAdd(a.legacy_n, 1u)] = (uint32_t)site;
         } else {
@@ -344,6 +377,8 @@ queue_scatter_kernel(PipeArgs a)
 // =====================================================================================================
 constexpr int kEmThreads = 128;
 constexpr int kPassBudget = 32;            // passes a fit may spend in K3 before it is parked for K3b
+constexpr int kDrainMinPass = 8;           // once the queue is empty, fits at or beyond this pass move to K3b
+constexpr int kLongGroup = 8;              // lanes per fit in K3b
 
 // 1/x for normal positive x: MUFU.RCP64H seed (>= 20 bits) + two Newton steps -> <= ~1 ulp
 __device__ __forceinline__ double rcp_nr2(double x)
@@ -383,15 +418,14 @@ constexpr uint32_t kNullClass = 30u;
 
 // Branch-free 4-way selects by the class's base bits (bit 7 / bit 8 of the class word): nvcc turns the
 // equivalent C ternaries into divergent branches, which serialises lanes whose classes differ in base.
-__device__ __forceinline__ void sel4_pair(uint32_t w, double f0, double f1, double f2, double f3, double p0, double p1,
-                                          double p2, double p3, double& fb, double& pb)
+__device__ __forceinline__ double sel4_w(uint32_t w, double f0, double f1, double f2, double f3)
 {
+    double fb;
     asm("{\n\t.reg .pred o, t;\n\t.reg .f64 lo, hi;\n\t"
-        "setp.ne.u32 o, %10, 0;\n\tsetp.ne.u32 t, %11, 0;\n\t"
-        "selp.f64 lo, %3, %2, o;\n\tselp.f64 hi, %5, %4, o;\n\tselp.f64 %0, hi, lo, t;\n\t"
-        "selp.f64 lo, %7, %6, o;\n\tselp.f64 hi, %9, %8, o;\n\tselp.f64 %1, hi, lo, t;\n\t}"
-        : "=d"(fb), "=d"(pb)
-        : "d"(f0), "d"(f1), "d"(f2), "d"(f3), "d"(p0), "d"(p1), "d"(p2), "d"(p3), "r"(w & 0x80u), "r"(w & 0x100u));
+        "setp.ne.u32 o, %5, 0;\n\tsetp.ne.u32 t, %6, 0;\n\t"
+        "selp.f64 lo, %2, %1, o;\n\tselp.f64 hi, %4, %3, o;\n\tselp.f64 %0, hi, lo, t;\n\t}"
+        : "=d"(fb) : "d"(f0), "d"(f1), "d"(f2), "d"(f3), "r"(w & 0x80u), "r"(w & 0x100u));
+    return fb;
 }
 // V_b += v for the class's base b: four predicated adds, no branch
 __device__ __forceinline__ void acc_by_base(uint32_t w, double v, double& V0, double& V1, double& V2, double& V3)
@@ -403,22 +437,40 @@ __device__ __forceinline__ void acc_by_base(uint32_t w, double v, double& V0, do
         : "d"(v), "r"(w & 0x180u));
 }
 
-// One class of one pass: Algorithm.cpp:76-91 (E and M step, factored as in the file header) and the
-// stateless delta term (:103-113) against the previous pass's frequencies p (pass 0: p == f -> x == 0).
-__device__ __forceinline__ void em_class(uint32_t w, const double2* lut2, double f0, double f1, double f2, double f3, double F,
-                                         double p0, double p1, double p2, double p3, double Fp, EmAcc& A)
+// ---- K3's class bodies: E and M step only (Algorithm.cpp:76-91, factored as in the file header) ----------
+// major segment: every class has the lane's major base -> fb and the V accumulator are plain registers
+__device__ __forceinline__ void em_class_major(uint32_t w, const double2* lut2, double fb, double F, double& accT, double& Vm)
 {
-    const int q = w & (kNQ - 1);
+    const double2 ed = lut2[w & (kNQ - 1)];                     // (e/3, (1-e) - e/3)
+    const double r = rcp_nr2(fma(fb, ed.y, ed.x * F));
+    const double wgt = cnt_to_double(w >> 9) * r;
+    accT = fma(ed.x, wgt, accT);
+    Vm = fma(ed.y, wgt, Vm);
+}
+// other bases: select by the class word
+__device__ __forceinline__ void em_class_minor(uint32_t w, const double2* lut2, double f0, double f1, double f2, double f3, double F,
+                                               double& accT, double& V0, double& V1, double& V2, double& V3)
+{
+    const double2 ed = lut2[w & (kNQ - 1)];
+    const double r = rcp_nr2(fma(sel4_w(w, f0, f1, f2, f3), ed.y, ed.x * F));
+    const double wgt = cnt_to_double(w >> 9) * r;
+    accT = fma(ed.x, wgt, accT);
+    acc_by_base(w, ed.y * wgt, V0, V1, V2, V3);
+}
+
+// ---- K3b's class body: E/M step plus the exact, stateless delta term (Algorithm.cpp:103-113) against the
+// previous pass's frequencies p (pass 0: p == f -> x == 0)
+__device__ __forceinline__ void em_class_exact(uint32_t w, const double2* lut2, double f0, double f1, double f2, double f3, double F,
+                                               double p0, double p1, double p2, double p3, double Fp, EmAcc& A)
+{
     const double cnt = cnt_to_double(w >> 9);
-    const double2 ed = lut2[q];                                  // (e/3, (1-e) - e/3)
-    double fb, pb;
-    sel4_pair(w, f0, f1, f2, f3, p0, p1, p2, p3, fb, pb);
-    const double ml = fma(fb, ed.y, ed.x * F);
+    const double2 ed = lut2[w & (kNQ - 1)];
+    const double ml = fma(sel4_w(w, f0, f1, f2, f3), ed.y, ed.x * F);
     const double r = rcp_nr2(ml);
     const double wgt = cnt * r;
     A.accT = fma(ed.x, wgt, A.accT);
     acc_by_base(w, ed.y * wgt, A.V0, A.V1, A.V2, A.V3);
-    const double mlp = fma(pb, ed.y, ed.x * Fp);
+    const double mlp = fma(sel4_w(w, p0, p1, p2, p3), ed.y, ed.x * Fp);
     const double x = (mlp - ml) * r;
     A.dl = fma(cnt, fabs(log1p_tiny(x)), A.dl);
     // range test on the high word (integer pipe); count-0 padding classes never trip it
@@ -438,6 +490,21 @@ __device__ __forceinline__ void add_work(unsigned long long* ctr, unsigned long 
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(ctr, v);
 }
 
+// Convergence test of K3 without per-class work.  With x_c = (ml_c(p) - ml_c(f)) / ml_c(f) =
+// (d_c (p_b - f_b) + e3_c (Fp - F)) / ml_c(f), all classes of a base move the same way, so
+//   P = sum_b |p_b - f_b| V_b,  V_b = sum_{c in b} cnt_c d_c / ml_c(f)   (already accumulated by the M step)
+// equals sum_c cnt_c |x_c| up to the (Fp - F) ~ 1e-16 term, and delta = sum_c cnt_c |log1p(x_c)| lies in
+// [P / (1 + P), P / (1 - P)] because every |x_c| <= cnt_c |x_c| <= P.  Outside a +-0.1 % band around
+// epsilon the decision delta < epsilon (Algorithm.cpp:124) is therefore certain; inside it the fit is
+// parked and K3b repeats the pass with the exact sum.   returns 0: not converged, 1: converged, 2: ambiguous
+__device__ __forceinline__ int delta_decision(double P, double eps)
+{
+    if (!(P < 0.25)) return 0;
+    if (P > eps * (1.0 + P) * (1.0 + 1e-6)) return 0;            // P / (1 + P) > eps
+    if (P < eps * (1.0 - P) * (1.0 - 1e-6)) return 1;            // P / (1 - P) < eps
+    return 2;
+}
+
 __global__ void __launch_bounds__(kEmThreads)
 em_fit_kernel(PipeArgs a)
 {
@@ -447,12 +514,14 @@ em_fit_kernel(PipeArgs a)
     const int lane = threadIdx.x & 31;
     const double eps = a.s.eps;
     const int max_iter = a.s.max_iter;
+    // a stage with fewer fits than lanes gains nothing from thread-per-fit: park everything at pass 0 for K3b
+    const int budget = (nfits >= (uint32_t)(gridDim.x * blockDim.x)) ? kPassBudget : 0;
 
-    bool active = false, done = false;
+    bool active = false, done = false, drain = false, lowq = false;
     const uint32_t* cp = a.cls;
-    int ncls = 0, pass = 0;
-    uint32_t item = 0, fl = 0;
-    double f0 = 0, f1 = 0, f2 = 0, f3 = 0, p0 = 0, p1 = 0, p2 = 0, p3 = 0, F = 0, Fp = 0, inv_n = 0;
+    int nmaj = 0, nmin = 0, pass = 0, major = 0;
+    uint32_t item = 0;
+    double f0 = 0, f1 = 0, f2 = 0, f3 = 0, p0 = 0, p1 = 0, p2 = 0, p3 = 0, F = 0, inv_n = 0;
     unsigned long long work = 0, nfit = 0;
 
     for (;;) {
@@ -482,52 +551,82 @@ em_fit_kernel(PipeArgs a)
                     f2 = (mask & 4) ? (double)su.depth[2] / ds : 0.0;
                     f3 = (mask & 8) ? (double)su.depth[3] / ds : 0.0;
                     F = ((f0 + f1) + f2) + f3;
-                    p0 = f0; p1 = f1; p2 = f2; p3 = f3; Fp = F;       // pass 0: delta term is exactly 0
+                    p0 = f0; p1 = f1; p2 = f2; p3 = f3;
                     inv_n = 1.0 / (double)(su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3]);
-                    cp = a.cls + su.cls_off; ncls = su.ncls; pass = 0; fl = 0;
+                    cp = a.cls + su.cls_off; nmaj = su.n_major; nmin = su.ncls - su.n_major; major = su.major;
+                    pass = 0; lowq = (su.has_q0 & 2) != 0;
                     active = true; ++nfit;
                 } else done = true;
             }
         }
         if (!__any_sync(0xffffffffu, active)) break;
-        const int nmax = __reduce_max_sync(0xffffffffu, active ? ncls : 0);
+        // the queue is empty: nothing is left to overlap a long fit with, so finish what the lanes hold in K3b
+        drain = drain || __any_sync(0xffffffffu, done);
 
-        // ---- one pass: warp-uniform trip count, lanes with fewer classes idle at the end --------------------
-        // Straight-line body: a lane past its last class (or without a fit) processes a count-0 null class, so
-        // the four unrolled class bodies interleave (ILP) instead of sitting behind per-class branches.
-        EmAcc A; A.accT = A.V0 = A.V1 = A.V2 = A.V3 = A.dl = 0.0; A.xmax = 0;
-        const int nmine = active ? ncls : 0;
-#pragma unroll 4
-        for (int c = 0; c < nmax; ++c) {
-            const uint32_t w = (c < nmine) ? __ldg(cp + c) : kNullClass;
-            em_class(w, lut2, f0, f1, f2, f3, F, p0, p1, p2, p3, Fp, A);
-        }
-        const bool big = A.xmax >= kBigXHi;
-
-        if (active) {
-            work += (unsigned long long)ncls;
-            const double e0 = f0 * (A.accT + A.V0) * inv_n, e1 = f1 * (A.accT + A.V1) * inv_n;
-            const double e2 = f2 * (A.accT + A.V2) * inv_n, e3 = f3 * (A.accT + A.V3) * inv_n;
-            bool stop = (pass == max_iter);
-            if (pass > 0 && !big) {
-                if (near_rel(A.dl, eps)) fl |= BVC_FLAG_EM_DELTA;
-                if (A.dl < eps) stop = true;                         // Algorithm.cpp:124
-            }
+        // a class with qual <= 1 has (1-e) - e/3 < 0, which voids delta_decision's sign argument: exact path
+        if (active && (budget == 0 || lowq)) {
             FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
-            if (stop) {
-                fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
-                fr->eap[0] = e0; fr->eap[1] = e1; fr->eap[2] = e2; fr->eap[3] = e3;
-                fr->passes = pass + 1; fr->flags = fl; fr->unfinished = 0;
-                active = false;
-            } else {
-                p0 = f0; p1 = f1; p2 = f2; p3 = f3; Fp = F;
-                f0 = e0; f1 = e1; f2 = e2; f3 = e3;                  // Algorithm.cpp:95-101
-                F = ((f0 + f1) + f2) + f3;
-                ++pass;
-                if (pass >= kPassBudget) {                           // park: K3b resumes at `pass` with (f, p)
+            fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
+            fr->eap[0] = p0; fr->eap[1] = p1; fr->eap[2] = p2; fr->eap[3] = p3;
+            fr->passes = 0; fr->flags = 0; fr->unfinished = 1;
+            a.q_long[atomicAdd(a.q_long_n, 1u)] = item;
+            active = false;
+        }
+        if (__any_sync(0xffffffffu, active)) {
+            const int nmaj_max = __reduce_max_sync(0xffffffffu, active ? nmaj : 0);
+            const int nmin_max = __reduce_max_sync(0xffffffffu, active ? nmin : 0);
+            // ---- one pass.  Straight-line bodies: a lane past its last class (or without a fit) processes a
+            // count-0 null class, so the unrolled bodies interleave (ILP) instead of sitting behind branches.
+            double accT = 0.0, Vm = 0.0, V0 = 0.0, V1 = 0.0, V2 = 0.0, V3 = 0.0;
+            const int my_maj = active ? nmaj : 0, my_min = active ? nmin : 0;
+            const double fm = sel4(major, f0, f1, f2, f3);
+#pragma unroll 4
+            for (int c = 0; c < nmaj_max; ++c) {
+                const uint32_t w = (c < my_maj) ? __ldg(cp + c) : kNullClass;
+                em_class_major(w, lut2, fm, F, accT, Vm);
+            }
+#pragma unroll 2
+            for (int c = 0; c < nmin_max; ++c) {
+                const uint32_t w = (c < my_min) ? __ldg(cp + my_maj + c) : kNullClass;
+                em_class_minor(w, lut2, f0, f1, f2, f3, F, accT, V0, V1, V2, V3);
+            }
+            if (active) {
+                work += (unsigned long long)(nmaj + nmin);
+                if (major == 0) V0 += Vm; else if (major == 1) V1 += Vm; else if (major == 2) V2 += Vm; else V3 += Vm;
+                bool stop = (pass == max_iter), park = false;
+                if (pass > 0) {
+                    const double P = fabs(p0 - f0) * V0 + fabs(p1 - f1) * V1 + fabs(p2 - f2) * V2 + fabs(p3 - f3) * V3;
+                    const int dec = delta_decision(P, eps);
+                    if (dec == 1) stop = true;
+                    else if (dec == 2 && !stop) park = true;         // K3b repeats this pass with the exact delta
+                }
+                FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
+                if (park) {
                     fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
                     fr->eap[0] = p0; fr->eap[1] = p1; fr->eap[2] = p2; fr->eap[3] = p3;
-                    fr->passes = pass; fr->flags = fl; fr->unfinished = 1;
+                    fr->passes = pass; fr->flags = 0; fr->unfinished = 1;
+                    a.q_long[atomicAdd(a.q_long_n, 1u)] = item;
+                    active = false;
+                } else {
+                    const double e0 = f0 * (accT + V0) * inv_n, e1 = f1 * (accT + V1) * inv_n;
+                    const double e2 = f2 * (accT + V2) * inv_n, e3 = f3 * (accT + V3) * inv_n;
+                    if (stop) {
+                        fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
+                        fr->eap[0] = e0; fr->eap[1] = e1; fr->eap[2] = e2; fr->eap[3] = e3;
+                        fr->passes = pass + 1; fr->flags = 0; fr->unfinished = 0;
+                        active = false;
+                    } else {
+                        p0 = f0; p1 = f1; p2 = f2; p3 = f3;
+                        f0 = e0; f1 = e1; f2 = e2; f3 = e3;              // Algorithm.cpp:95-101
+                        F = ((f0 + f1) + f2) + f3;
+                        ++pass;
+                        park = (pass >= budget) || (drain && pass >= kDrainMinPass);
+                    }
+                }
+                if (park && active) {                                // resume point: pass `pass` with (f, p)
+                    fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
+                    fr->eap[0] = p0; fr->eap[1] = p1; fr->eap[2] = p2; fr->eap[3] = p3;
+                    fr->passes = pass; fr->flags = 0; fr->unfinished = 1;
                     a.q_long[atomicAdd(a.q_long_n, 1u)] = item;
                     active = false;
                 }
@@ -539,62 +638,103 @@ em_fit_kernel(PipeArgs a)
 }
 
 // =====================================================================================================
-// K3b: warp per parked fit -- classes across lanes, butterfly sums: ~25x lower latency per pass than a
-// single thread, so the few fits that need up to 101 passes do not set the stage's duration.
+// K3b: kLongGroup lanes per parked fit -- classes across the group's lanes, butterfly sums, exact delta.
+// A pass costs a few hundred cycles instead of ncls x (latency of the dependent FP64 chain), so the fits
+// that need up to 101 passes, the fits in flight when K3's queue drains and the fits of a small stage do
+// not set the stage's duration.  Passes are aligned across the four groups of a warp as in K3.
 // =====================================================================================================
-constexpr int kLongWarps = 4;
+constexpr int kLongThreads = 128;
 
-__global__ void __launch_bounds__(kLongWarps * 32)
+__global__ void __launch_bounds__(kLongThreads)
 em_long_kernel(PipeArgs a)
 {
     __shared__ double2 lut2[kNQ];
     load_lut2(lut2, a.s.lut);
     const uint32_t n_long = *a.q_long_n;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, g = lane & (kLongGroup - 1);
+    const unsigned gmask = ((1u << kLongGroup) - 1u) << (lane & ~(kLongGroup - 1));
+    const int gleader = lane & ~(kLongGroup - 1);
     const double eps = a.s.eps;
     const int max_iter = a.s.max_iter;
     unsigned long long work = 0;
-    for (uint32_t i = blockIdx.x * kLongWarps + wid; i < n_long; i += gridDim.x * kLongWarps) {
-        const uint32_t item = a.q_long[i];
-        const SiteSum su = a.sum[item >> 2];
-        FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
-        double f0 = fr->f[0], f1 = fr->f[1], f2 = fr->f[2], f3 = fr->f[3];
-        double p0 = fr->eap[0], p1 = fr->eap[1], p2 = fr->eap[2], p3 = fr->eap[3];
-        double F = ((f0 + f1) + f2) + f3, Fp = ((p0 + p1) + p2) + p3;
-        int pass = fr->passes;
-        uint32_t fl = fr->flags;
-        const double inv_n = 1.0 / (double)(su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3]);
-        const uint32_t* cp = a.cls + su.cls_off;
-        const int ncls = su.ncls;
-        __syncwarp();
-        for (;;) {
-            EmAcc A; A.accT = A.V0 = A.V1 = A.V2 = A.V3 = A.dl = 0.0; A.xmax = 0;
-            for (int c = lane; c < ncls; c += 32) em_class(__ldg(cp + c), lut2, f0, f1, f2, f3, F, p0, p1, p2, p3, Fp, A);
-            const double accT = warp_sum(A.accT), V0 = warp_sum(A.V0), V1 = warp_sum(A.V1), V2 = warp_sum(A.V2),
-                         V3 = warp_sum(A.V3), dl = warp_sum(A.dl);
-            const bool big = __any_sync(0xffffffffu, A.xmax >= kBigXHi);
-            if (lane == 0) work += (unsigned long long)ncls;
-            const double e0 = f0 * (accT + V0) * inv_n, e1 = f1 * (accT + V1) * inv_n;
-            const double e2 = f2 * (accT + V2) * inv_n, e3 = f3 * (accT + V3) * inv_n;
+
+    bool active = false, done = false;
+    const uint32_t* cp = a.cls;
+    int ncls = 0, pass = 0;
+    uint32_t item = 0, fl = 0;
+    double f0 = 0, f1 = 0, f2 = 0, f3 = 0, p0 = 0, p1 = 0, p2 = 0, p3 = 0, F = 0, Fp = 0, inv_n = 0;
+
+    for (;;) {
+        // ---- refill: one queue slot per idle group (claimed by its leader lane) ------------------------------
+        const bool want = !active && !done;
+        const unsigned wm = __ballot_sync(0xffffffffu, want && g == 0);
+        if (wm) {
+            uint32_t base = 0;
+            const int leader = __ffs(wm) - 1;
+            if (lane == leader) base = atomicAdd(a.q_long_head, (uint32_t)__popc(wm));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (want) {
+                const uint32_t idx = base + __popc(wm & ((1u << gleader) - 1));
+                if (idx < n_long) {
+                    item = a.q_long[idx];
+                    const SiteSum su = a.sum[item >> 2];
+                    const FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
+                    f0 = fr->f[0]; f1 = fr->f[1]; f2 = fr->f[2]; f3 = fr->f[3];
+                    p0 = fr->eap[0]; p1 = fr->eap[1]; p2 = fr->eap[2]; p3 = fr->eap[3];
+                    F = ((f0 + f1) + f2) + f3; Fp = ((p0 + p1) + p2) + p3;
+                    pass = fr->passes; fl = fr->flags;
+                    inv_n = 1.0 / (double)(su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3]);
+                    cp = a.cls + su.cls_off; ncls = su.ncls;
+                    active = true;
+                } else done = true;
+            }
+        }
+        if (!__any_sync(0xffffffffu, active)) break;
+        const int nmine = active ? ncls : 0;
+        const int trips = (__reduce_max_sync(0xffffffffu, nmine) + kLongGroup - 1) / kLongGroup;
+
+        EmAcc A; A.accT = A.V0 = A.V1 = A.V2 = A.V3 = A.dl = 0.0; A.xmax = 0;
+#pragma unroll 2
+        for (int k = 0; k < trips; ++k) {
+            const int c = k * kLongGroup + g;
+            const uint32_t w = (c < nmine) ? __ldg(cp + c) : kNullClass;
+            em_class_exact(w, lut2, f0, f1, f2, f3, F, p0, p1, p2, p3, Fp, A);
+        }
+#pragma unroll
+        for (int o = kLongGroup / 2; o > 0; o >>= 1) {               // butterfly within the group: all its lanes agree
+            A.accT += __shfl_xor_sync(0xffffffffu, A.accT, o);
+            A.V0 += __shfl_xor_sync(0xffffffffu, A.V0, o);
+            A.V1 += __shfl_xor_sync(0xffffffffu, A.V1, o);
+            A.V2 += __shfl_xor_sync(0xffffffffu, A.V2, o);
+            A.V3 += __shfl_xor_sync(0xffffffffu, A.V3, o);
+            A.dl += __shfl_xor_sync(0xffffffffu, A.dl, o);
+            A.xmax = max(A.xmax, __shfl_xor_sync(0xffffffffu, A.xmax, o));
+        }
+        if (active) {
+            if (g == 0) work += (unsigned long long)ncls;
+            const double e0 = f0 * (A.accT + A.V0) * inv_n, e1 = f1 * (A.accT + A.V1) * inv_n;
+            const double e2 = f2 * (A.accT + A.V2) * inv_n, e3 = f3 * (A.accT + A.V3) * inv_n;
             bool stop = (pass == max_iter);
-            if (pass > 0 && !big) {
-                if (near_rel(dl, eps)) fl |= BVC_FLAG_EM_DELTA;
-                if (dl < eps) stop = true;
+            if (pass > 0 && A.xmax < kBigXHi) {
+                if (near_rel(A.dl, eps)) fl |= BVC_FLAG_EM_DELTA;
+                if (A.dl < eps) stop = true;                         // Algorithm.cpp:124
             }
             if (stop) {
-                if (lane == 0) {
+                if (g == 0) {
+                    FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
                     fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
                     fr->eap[0] = e0; fr->eap[1] = e1; fr->eap[2] = e2; fr->eap[3] = e3;
                     fr->passes = pass + 1; fr->flags = fl; fr->unfinished = 0;
                 }
-                break;
+                active = false;
+            } else {
+                p0 = f0; p1 = f1; p2 = f2; p3 = f3; Fp = F;
+                f0 = e0; f1 = e1; f2 = e2; f3 = e3;                  // Algorithm.cpp:95-101
+                F = ((f0 + f1) + f2) + f3;
+                ++pass;
             }
-            p0 = f0; p1 = f1; p2 = f2; p3 = f3; Fp = F;
-            f0 = e0; f1 = e1; f2 = e2; f3 = e3;
-            F = ((f0 + f1) + f2) + f3;
-            ++pass;
         }
-        __syncwarp();
+        (void)gmask;
     }
     add_work(a.work + 1, work);
 }
@@ -631,9 +771,7 @@ fit_loglik_kernel(PipeArgs a)
                 const uint32_t w = __ldg(cp + c);
                 const int q = w & (kNQ - 1);
                 const double2 ed = lut2[q];
-                double fb, unused;
-                sel4_pair(w, f0, f1, f2, f3, f0, f1, f2, f3, fb, unused);
-                const double ml = fma(fb, ed.y, ed.x * F);
+                const double ml = fma(sel4_w(w, f0, f1, f2, f3), ed.y, ed.x * F);
                 s = fma(cnt_to_double(w >> 9), log(ml), s);
             }
         }

@@ -14,9 +14,11 @@ struct __align__(16) SiteSum {      // 64 B, written by K1
     uint32_t cls_off;               // first class of this site in the pool
     uint16_t ncls;
     uint8_t  alt;                   // top-count non-ref base
-    uint8_t  has_q0;                // a qual-0 class exists: the site takes the IEEE-faithful legacy path
+    uint8_t  has_q0;                // bit 0: a qual-0 class exists (IEEE-faithful legacy path); bit 1: a qual <= 1 class exists (exact-delta path)
     int32_t  n_entries;
-    int32_t  pad;
+    uint16_t n_major;               // classes of the major (top-depth) base: they come first in the pool
+    uint8_t  major;                 // that base
+    uint8_t  pad;
 };
 
 struct __align__(16) FitRes {       // 96 B, one per (site, slot)
@@ -63,6 +65,7 @@ struct PipeArgs {
     uint32_t* bins;             // [kNBins + 1] histogram of class counts, then scatter cursors
     uint32_t* q_long;           // fits that hit the pass budget
     uint32_t* q_long_n;
+    uint32_t* q_long_head;      // K3b refill cursor
     unsigned long long* work;   // [4] diagnostics: class-passes done by em_fit / em_long, loglik class evaluations, fits
     uint32_t* vcf_list;         // LRT-positive sites
     uint32_t* vcf_n;

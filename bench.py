@@ -27,9 +27,9 @@ sys.path.insert(0, ROOT)
 
 METRIC = "site*samples/sec for basetype EM+LRT"
 # FP64 operations em_fit_kernel's arithmetic performs per (base, qual) class per singleEM pass, FMA = 2
-# (DESIGN.md "Kernels": E/M step 17 = count 1, ml 3, Newton reciprocal 8, weight 1, two accumulations 4;
-#  delta term 17 = ml' 3, difference + scale 2, log1p series 9, accumulate 2, range test 1)
-FLOP_PER_CLASS_PASS = 34
+# (DESIGN.md "Kernels": exact count 1, ml = e3*F + f_b*d 3, Newton reciprocal 8, weight 1, two accumulations 4;
+#  the convergence test costs nothing per class: see delta_decision in bvc_pipeline.cuh)
+FLOP_PER_CLASS_PASS = 17
 UNIT = "site*samples/s"
 
 
