@@ -185,6 +185,7 @@ int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullpt
     CK(cudaMemsetAsync(s.d_ctr, 0, kCtrWords * sizeof(uint32_t), s.stream));
     bvc::PipeArgs p;
     p.s = a;
+    p.mean_entries = (int)(s.n_entries / (s.n_sites > 0 ? s.n_sites : 1));
     p.sum = s.d_sum; p.cls = s.d_cls; p.cls_cursor = s.d_ctr + 0;
     p.lad = s.d_lad; p.fit = s.d_fit; p.state = s.d_state;
     p.q_in = s.d_qb; p.q_in_n = s.d_ctr + 2;          // swapped before the first EM stage

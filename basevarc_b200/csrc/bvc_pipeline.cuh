@@ -52,96 +52,141 @@ __device__ __forceinline__ double sel4(int b, double v0, double v1, double v2, d
 // =====================================================================================================
 // K1: warp per site -- stream entries, histogram, compact classes, strand tables
 // =====================================================================================================
-constexpr int kHistWarps = 8;
-constexpr int kHistBins = 2 * kNBins;      // [strand][base][qual]
+constexpr int kHistWarps = 4;
+constexpr int kHistBins = 2 * kNBins;      // per site in flight: [base][qual][strand]
 
+// shared-memory increment without a result and without a branch around it
+__device__ __forceinline__ void red_inc_if(uint32_t* p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %1, 0;\n\t@q red.shared.add.u32 [%0], 1;\n\t}"
+                 :: "r"((uint32_t)__cvta_generic_to_shared(p)), "r"((uint32_t)pred) : "memory");
+}
+
+// Reductions over the G lanes of a group.  The *_sync reduce intrinsics with a run-time partial mask compile to a
+// ~140-instruction emulation; one full-warp REDUX per group on pre-masked values is 2 instructions.
+template <int G> __device__ __forceinline__ int group_add(int v, int gi)
+{
+    if (G == 32) return __reduce_add_sync(0xffffffffu, v);
+    int r = 0;
+#pragma unroll
+    for (int k = 0; k < 32 / G; ++k) { const int t = __reduce_add_sync(0xffffffffu, gi == k ? v : 0); if (gi == k) r = t; }
+    return r;
+}
+template <int G> __device__ __forceinline__ unsigned group_max(unsigned v, int gi)
+{
+    if (G == 32) return __reduce_max_sync(0xffffffffu, v);
+    unsigned r = 0;
+#pragma unroll
+    for (int k = 0; k < 32 / G; ++k) { const unsigned t = __reduce_max_sync(0xffffffffu, gi == k ? v : 0u); if (gi == k) r = t; }
+    return r;
+}
+template <int G> __device__ __forceinline__ unsigned group_min(unsigned v, int gi)
+{
+    if (G == 32) return __reduce_min_sync(0xffffffffu, v);
+    unsigned r = 0;
+#pragma unroll
+    for (int k = 0; k < 32 / G; ++k) { const unsigned t = __reduce_min_sync(0xffffffffu, gi == k ? v : 0xffffffffu); if (gi == k) r = t; }
+    return r;
+}
+
+// G lanes per site (32 / G sites per warp): G = 32 for deep pileups, 16 for a few hundred entries per site.
+template <int G>
 __global__ void __launch_bounds__(kHistWarps * 32)
 site_hist_kernel(PipeArgs a)
 {
-    __shared__ uint32_t hist_s[kHistWarps][kHistBins];
-    __shared__ uint32_t ind_s[kHistWarps][8];
+    constexpr int kGroups = 32 / G;
+    __shared__ __align__(8) uint32_t hist_s[kHistWarps * kGroups][kHistBins];
+    __shared__ uint32_t ind_s[kHistWarps * kGroups][8];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    uint32_t* hist = hist_s[wid];              // non-indel entries: strand << 9 | base << 7 | qual
-    uint32_t* ind = ind_s[wid];                // indel entries (stale base < 4): strand << 2 | base
-    for (int i = lane; i < kHistBins; i += 32) hist[i] = 0;
-    if (lane < 8) ind[lane] = 0;
+    const int g = lane & (G - 1), gi = lane / G;
+    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (gi * G));
+    uint32_t* hist = hist_s[wid * kGroups + gi];   // non-indel entries: base << 8 | qual << 1 | strand
+    uint32_t* ind = ind_s[wid * kGroups + gi];     // indel entries (stale base < 4): strand << 2 | base
+    for (int i = g; i < kHistBins; i += G) hist[i] = 0;
+    if (g < 8) ind[g] = 0;
     __syncwarp();
     const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
     const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
-    const unsigned lt = (1u << lane) - 1u;
+    const unsigned lt = (1u << g) - 1u;
 
-    const int n_warps = gridDim.x * kHistWarps;
-    for (int site = blockIdx.x * kHistWarps + wid; site < a.s.n_sites; site += n_warps) {
-        const uint32_t b0 = a.s.entry_off[site], b1 = a.s.entry_off[site + 1];
-        const int ref = a.s.ref_base[site] & 3;
-        // ---- stream: 4 entries per lane per 32-bit load, 128 B per warp-load, both arrays in flight.  One shared
-        // atomic per entry does all the counting: the bin carries strand, base and qual.  Bytes outside
-        // [b0, b1) in the first / last word are turned into code 0x14 (indel, base 4), which nothing counts.
+    const int n_groups = gridDim.x * kHistWarps * kGroups;
+    const int first = (blockIdx.x * kHistWarps + wid) * kGroups + gi;
+    // warp-uniform trip count: every lane runs the same number of site iterations, idle groups just predicate off
+    const int n_iter = (a.s.n_sites + n_groups - 1) / n_groups;
+    for (int it = 0; it < n_iter; ++it) {
+        const int site = first + it * n_groups;
+        const bool live = site < a.s.n_sites;
+        const uint32_t b0 = live ? a.s.entry_off[site] : 0u, b1 = live ? a.s.entry_off[site + 1] : 0u;
+        const int ref = live ? (a.s.ref_base[site] & 3) : 0;
+        // ---- stream: 4 entries per lane per 32-bit load, both arrays in flight.  One shared-memory increment per
+        // entry does all the counting: the bin carries base, qual and strand.  Bytes outside [b0, b1) in the first /
+        // last word are turned into code 0x14 (indel, base 4), which nothing counts.
         const uint32_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;
-        uint32_t qor = 0;
+        const uint32_t trips = (__reduce_max_sync(0xffffffffu, w1 - w0) + G - 1) / G;
+        uint32_t qmax = 0, qmin = 127;
         bool any_ind = false;
-        for (uint32_t wi = w0 + lane; wi < w1; wi += 32) {
-            uint32_t cw = __ldg(code4 + wi);
-            const uint32_t qw = __ldg(qual4 + wi) & 0x7f7f7f7fu;
-            if (wi == w0 || wi + 1 == w1) {
-                const uint32_t e0 = wi * 4;
-                const uint32_t lo = b0 > e0 ? b0 - e0 : 0u, hi = b1 < e0 + 4 ? b1 - e0 : 4u;     // valid bytes [lo, hi)
-                const uint32_t vm = (hi >= 4 ? 0xffffffffu : ((1u << (8 * hi)) - 1u)) & ~((1u << (8 * lo)) - 1u);
-                cw = (cw & vm) | (0x14141414u & ~vm);
-            }
-            qor |= qw;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint32_t c = cw >> (8 * k), q = (qw >> (8 * k)) & 0x7fu;
-                if (!(c & 0x14u)) atomicAdd(&hist[((c & 8u) << 6) | ((c & 3u) << 7) | q], 1u);
-            }
-            if (cw & 0x10101010u) {                 // rare: indel entries keep only (stale base, strand)
-                any_ind = true;
+        for (uint32_t t = 0; t < trips; ++t) {
+            const uint32_t wi = w0 + t * G + g;
+            if (wi < w1) {
+                uint32_t cw = __ldg(code4 + wi);
+                const uint32_t qw = __ldg(qual4 + wi) & 0x7f7f7f7fu;
+                if (wi == w0 || wi + 1 == w1) {
+                    const uint32_t e0 = wi * 4;
+                    const uint32_t lo = b0 > e0 ? b0 - e0 : 0u, hi = b1 < e0 + 4 ? b1 - e0 : 4u;     // valid bytes [lo, hi)
+                    const uint32_t vm = (hi >= 4 ? 0xffffffffu : ((1u << (8 * hi)) - 1u)) & ~((1u << (8 * lo)) - 1u);
+                    cw = (cw & vm) | (0x14141414u & ~vm);
+                }
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    const uint32_t c = cw >> (8 * k);
-                    if ((c & 0x14u) == 0x10u) atomicAdd(&ind[((c >> 1) & 4u) | (c & 3u)], 1u);
+                    const uint32_t c = cw >> (8 * k), q = (qw >> (8 * k)) & 0x7fu;
+                    const bool ok = !(c & 0x14u);
+                    qmin = min(qmin, ok ? q : 127u); qmax = max(qmax, ok ? q : 0u);
+                    red_inc_if(&hist[((c & 3u) << 8) | (q << 1) | ((c >> 3) & 1u)], ok);
+                }
+                if (cw & 0x10101010u) {                 // rare: indel entries keep only (stale base, strand)
+                    any_ind = true;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t c = cw >> (8 * k);
+                        if ((c & 0x14u) == 0x10u) atomicAdd(&ind[((c >> 1) & 4u) | (c & 3u)], 1u);
+                    }
                 }
             }
         }
         __syncwarp();
-        // qual range actually present, from the OR of all qual bytes: scan 32, 64 or 128 quals per (base, strand)
-        qor = __reduce_or_sync(0xffffffffu, qor);
-        qor = (qor | (qor >> 8) | (qor >> 16) | (qor >> 24)) & 0x7fu;
-        const int nsteps = qor >= 64 ? 4 : (qor >= 32 ? 2 : 1);
+        // qual range present in this site, scanned G quals at a time per base
+        qmax = group_max<G>(qmax, gi);
+        qmin = group_min<G>(qmin, gi);
+        const int q_lo = (int)min(qmin, qmax);
+        const int my_steps = live && b1 > b0 ? ((int)qmax - q_lo) / G + 1 : 0;
+        const int nsteps = __reduce_max_sync(0xffffffffu, my_steps);
         any_ind = __any_sync(0xffffffffu, any_ind);
 
-        // ---- pass 1 over the bins: merged counts into registers, per-base depth / forward depth / class count --------
-        uint32_t v[4][4];
+        // ---- pass 1 over the bins: merged counts, per-base depth / forward depth / class count -------------------
         int dsum[4], fsum[4], ncb[4];
         unsigned lowq = 0;
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
             dsum[b] = 0; fsum[b] = 0; ncb[b] = 0;
-#pragma unroll
-            for (int st = 0; st < 4; ++st) {
-                v[b][st] = 0;
-                if (st < nsteps) {
-                    const int bin = (b << 7) + st * 32 + lane;
-                    const uint32_t h0 = hist[bin], h1 = hist[kNBins + bin];
-                    hist[bin] = 0; hist[kNBins + bin] = 0;
-                    v[b][st] = h0 + h1;
-                    dsum[b] += (int)(h0 + h1); fsum[b] += (int)h1;
-                    const unsigned m = __ballot_sync(0xffffffffu, v[b][st] != 0);
-                    ncb[b] += __popc(m);
-                    if (st == 0) lowq |= m & 3u;          // bit 0: a qual-0 class, bit 1: a qual-1 class
-                }
+            for (int st = 0; st < nsteps; ++st) {
+                const int q = q_lo + st * G + g;
+                uint2 h = make_uint2(0u, 0u);
+                if (st < my_steps && q < kNQ) h = *reinterpret_cast<const uint2*>(&hist[(b << 8) | (q << 1)]);
+                dsum[b] += (int)(h.x + h.y); fsum[b] += (int)h.y;
+                const unsigned m = (__ballot_sync(0xffffffffu, (h.x + h.y) != 0) & gmask) >> (gi * G);
+                ncb[b] += __popc(m);
+                if (q_lo <= 1 && st == 0) lowq |= (m << q_lo) & 3u;     // bit 0: a qual-0 class, bit 1: a qual-1 class
             }
         }
         int depth[4], fwd[4], n_reads = 0;
 #pragma unroll
         for (int b = 0; b < 4; ++b) {               // src/BaseVarC.cpp:550-559
-            depth[b] = __reduce_add_sync(0xffffffffu, dsum[b]);
-            fwd[b] = __reduce_add_sync(0xffffffffu, fsum[b]);
+            depth[b] = group_add<G>(dsum[b], gi);
+            fwd[b] = group_add<G>(fsum[b], gi);
             n_reads += depth[b];
         }
-        int icnt = 0;                               // lane = strand << 2 | base of the indel entries
-        if (any_ind) { icnt = lane < 8 ? (int)ind[lane] : 0; __syncwarp(); if (lane < 8) ind[lane] = 0; }
+        int icnt = 0;                               // g = strand << 2 | base of the indel entries
+        if (any_ind) { icnt = g < 8 ? (int)ind[g] : 0; __syncwarp(); if (g < 8) ind[g] = 0; }
         // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
         int best = -1, bestd = -1, second = -1, secondd = -1;
 #pragma unroll
@@ -155,44 +200,48 @@ site_hist_kernel(PipeArgs a)
         const int dr_ = ref == 0 ? depth[0] : ref == 1 ? depth[1] : ref == 2 ? depth[2] : depth[3];
         const int fa_ = alt == 0 ? fwd[0] : alt == 1 ? fwd[1] : alt == 2 ? fwd[2] : fwd[3];
         const int da_ = alt == 0 ? depth[0] : alt == 1 ? depth[1] : alt == 2 ? depth[2] : depth[3];
-        const int c0 = fr_ + __shfl_sync(0xffffffffu, icnt, ref | 4);
-        const int c1 = (dr_ - fr_) + __shfl_sync(0xffffffffu, icnt, ref);
-        const int c2 = fa_ + __shfl_sync(0xffffffffu, icnt, alt | 4);
-        const int c3 = (da_ - fa_) + __shfl_sync(0xffffffffu, icnt, alt);
+        const int gl = gi * G;                      // first lane of my group
+        const int c0 = fr_ + __shfl_sync(0xffffffffu, icnt, gl + (ref | 4));
+        const int c1 = (dr_ - fr_) + __shfl_sync(0xffffffffu, icnt, gl + ref);
+        const int c2 = fa_ + __shfl_sync(0xffffffffu, icnt, gl + (alt | 4));
+        const int c3 = (da_ - fa_) + __shfl_sync(0xffffffffu, icnt, gl + alt);
 
-        // ---- pass 2: write the non-empty classes to the pool.  Order: the MAJOR base (top depth, ties -> lowest
-        // code) first, then the other bases ascending; K3 runs the major segment select-free. ----------------------
+        // ---- pass 2: write the non-empty classes to the pool (and clear the bins).  Order: the MAJOR base (top
+        // depth, ties -> lowest code) first, then the other bases ascending; K3 runs the major segment select-free.
         const int ncls = ncb[0] + ncb[1] + ncb[2] + ncb[3];
         const int n_major = best == 0 ? ncb[0] : best == 1 ? ncb[1] : best == 2 ? ncb[2] : ncb[3];
         uint32_t off = 0;
-        if (lane == 0 && ncls) off = atomicAdd(a.cls_cursor, (uint32_t)ncls);
-        off = __shfl_sync(0xffffffffu, off, 0);
+        if (g == 0 && ncls) off = atomicAdd(a.cls_cursor, (uint32_t)ncls);
+        off = __shfl_sync(0xffffffffu, off, gl);
         uint32_t run = off + (uint32_t)n_major;
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
             uint32_t pos;
             if (b == best) pos = off; else { pos = run; run += (uint32_t)ncb[b]; }
-            if (ncb[b] == 0) continue;
-#pragma unroll
-            for (int st = 0; st < 4; ++st) {
-                if (st < nsteps) {
-                    const uint32_t x = v[b][st];
-                    const unsigned m = __ballot_sync(0xffffffffu, x != 0);
-                    if (x) a.cls[pos + __popc(m & lt)] = (x << 9) | (uint32_t)((b << 7) + st * 32 + lane);
-                    pos += __popc(m);
+            for (int st = 0; st < nsteps; ++st) {
+                const int q = q_lo + st * G + g;
+                uint32_t x = 0;
+                if (st < my_steps && q < kNQ) {
+                    uint2* hp = reinterpret_cast<uint2*>(&hist[(b << 8) | (q << 1)]);
+                    const uint2 h = *hp;
+                    x = h.x + h.y;
+                    if (x) *hp = make_uint2(0u, 0u);
                 }
+                const unsigned m = (__ballot_sync(0xffffffffu, x != 0) & gmask) >> (gi * G);
+                if (x) a.cls[pos + __popc(m & lt)] = (x << 9) | (uint32_t)((b << 7) | q);
+                pos += __popc(m);
             }
         }
-        // ---- 64-byte summary: lanes 0..15 store one word each ----------------------------------------------
+        // ---- 64-byte summary: lanes 0..15 of the group store one word each ---------------------------------------
         int word = 0;
-        if (lane == 0) word = depth[0]; else if (lane == 1) word = depth[1]; else if (lane == 2) word = depth[2]; else if (lane == 3) word = depth[3];
-        else if (lane == 4) word = fwd[0]; else if (lane == 5) word = fwd[1]; else if (lane == 6) word = fwd[2]; else if (lane == 7) word = fwd[3];
-        else if (lane == 8) word = c0; else if (lane == 9) word = c1; else if (lane == 10) word = c2; else if (lane == 11) word = c3;
-        else if (lane == 12) word = (int)off;
-        else if (lane == 13) word = ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0);
-        else if (lane == 14) word = (int)(b1 - b0);
-        else if (lane == 15) word = n_major | (best << 16);
-        if (lane < 16) reinterpret_cast<int*>(a.sum + site)[lane] = word;
+        if (g == 0) word = depth[0]; else if (g == 1) word = depth[1]; else if (g == 2) word = depth[2]; else if (g == 3) word = depth[3];
+        else if (g == 4) word = fwd[0]; else if (g == 5) word = fwd[1]; else if (g == 6) word = fwd[2]; else if (g == 7) word = fwd[3];
+        else if (g == 8) word = c0; else if (g == 9) word = c1; else if (g == 10) word = c2; else if (g == 11) word = c3;
+        else if (g == 12) word = (int)off;
+        else if (g == 13) word = ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0);
+        else if (g == 14) word = (int)(b1 - b0);
+        else if (g == 15) word = n_major | (best << 16);
+        if (live && g < 16) reinterpret_cast<int*>(a.sum + site)[g] = word;
         __syncwarp();
     }
 }

@@ -49,6 +49,7 @@ struct __align__(16) Ladder {       // 80 B per site
 constexpr uint8_t kStActive = 0, kStDone = 1, kStLegacy = 2;
 
 struct PipeArgs {
+    int mean_entries;           // entries / sites of the tile (host side: picks K1's lanes-per-site)
     SiteArgs s;                 // tile arrays, out, lut, lgam, thresholds
     SiteSum*  sum;              // [n_sites]
     uint32_t* cls;              // class pool: cnt << 9 | base << 7 | qual
