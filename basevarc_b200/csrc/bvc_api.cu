@@ -207,6 +207,13 @@ int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullpt
 
 extern "C" {
 
+int bvc_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { set_err(nullptr, "cudaGetDeviceCount failed: no usable CUDA driver/device"); cudaGetLastError(); return 0; }
+    return n;
+}
+
 void bvc_default_params(bvc_params* p, int32_t n_samples, double maf)
 {
     memset(p, 0, sizeof(*p));

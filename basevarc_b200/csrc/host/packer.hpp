@@ -1,0 +1,48 @@
+// packer.hpp -- batch-file lines -> structure-of-arrays pileup tile (host side of include/bvc_host.h).
+//
+// Restates what the reference's window loop does with each line it reads (paths under /root/reference):
+// strtok_r on " " then on ",", std::atoi into the AlleleInfo bitfield, N-bases skipped while the sample
+// index still advances, indel tokens reusing the stale numeric fields (src/BaseVarC.cpp:393-441,
+// src/BamProcess.h:30-39).  Output layout = bvc_tile (CSR over covered entries, one byte per field).
+#pragma once
+#include <stdint.h>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../../include/bvc_gpu.h"
+
+namespace bvc_host {
+
+class Packer {
+public:
+    explicit Packer(int32_t n_samples) : n_samples_(n_samples) { entry_off_.push_back(0); }
+    void clear();
+    void begin_site(int32_t pos, uint8_t ref_base);
+    int add_line(const char* line, size_t len);
+    int32_t end_site();
+    void drop_last_site();                       // undo begin_site/end_site of a site that got no entries
+    void adopt_state(const Packer& other);       // take over the stale-token state (next tile of the same window)
+    int32_t n_sites() const { return (int32_t)ref_base_.size(); }
+    int64_t n_entries() const { return (int64_t)code_.size(); }
+    void tile(bvc_tile* out) const;
+    const int32_t* positions() const { return pos_.data(); }
+    const char* indel(int64_t entry) const;
+    const std::string& error() const { return err_; }
+    int32_t n_samples() const { return n_samples_; }
+
+private:
+    int32_t n_samples_;
+    // the reference's reused `AlleleInfo ai` (Q1): survives tokens, lines, sites and clear()
+    uint8_t st_base_ = 0, st_mapq_ = 0, st_qual_ = 0, st_rpr_ = 0, st_strand_ = 0;
+    uint32_t sample_ = 0;          // j of src/BaseVarC.cpp:404: advances on every token of the current site
+    std::vector<int32_t> pos_;
+    std::vector<uint8_t> ref_base_;
+    std::vector<uint32_t> entry_off_;
+    std::vector<uint8_t> code_, qual_, mapq_, rpr_;
+    std::vector<uint32_t> smp_;
+    std::unordered_map<int64_t, std::string> indel_;
+    std::string err_;
+};
+
+}  // namespace bvc_host

@@ -1,0 +1,499 @@
+// rerun.cc -- `BaseVarC basetype --rerun` with the compute phase on the GPU(s): bvc_basetype_main.
+//
+// What it keeps from the reference's runBaseType / bt_s (paths under /root/reference, src/BaseVarC.cpp):
+//   the command line (:129-148,797-827), N = lines of the BAM list (:186-189), the region arithmetic and the
+//   site list pv (:190-204), the batch-file names and their BGZF+EOF validity probe (:214-233), the window
+//   partition (:399-403), the headers (:65-88,364-391), the status lines on stdout/stderr, --keep_tmp (:458-462),
+//   the order of the output (windows in thread order, header from window 0 only, :268-295).
+// What it replaces: one std::thread per window calling bt_f per site (:263-266,403-454) becomes one reader /
+// tokeniser / formatter thread per window feeding tiles of sites to one dispatcher thread per GPU through the
+// C ABI of include/bvc_gpu.h (windows [g*T/G, (g+1)*T/G) -> GPU g, no collective); window outputs are
+// compressed in memory as independent BGZF blocks and concatenated, instead of re-read and re-compressed.
+// The load phase (BAM decoding, bt_r) is NOT here: it stays with the reference binary (`--load`); this
+// command needs complete batch files and says so otherwise.
+#include <getopt.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <fstream>
+#include <iostream>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "../../../include/bvc_host.h"
+#include "bgzf_io.hpp"
+#include "fasta.hpp"
+#include "format.hpp"
+#include "packer.hpp"
+
+namespace bvc_host {
+namespace {
+
+const char* kUsage =
+    "Commands: BaseVarC basetype (B200 calling core; needs batch files written by `BaseVarC basetype --load`)\n"
+    "Usage   : BaseVarC basetype --rerun [options]\n\n"
+    "Options :\n"
+    "  --input,      -i         BAM/CRAM file list, one file per row (only its line count N is used)\n"
+    "  --output,     -o         Output file prefix\n"
+    "  --reference,  -r         Reference file\n"
+    "  --region,     -s         Samtools-like region <chr:start-end>\n"
+    "  --group,      -g         Population group information <SampleID Group>\n"
+    "  --mapq,       -q <INT>   (load phase only)\n"
+    "  --thread,     -t <INT>   Number of windows the batch files were written with\n"
+    "  --batch,      -b <INT>   Number of samples each batch\n"
+    "  --maf,        -a <FLOAT> Minimum allele count frequency [min(0.001, 100/N, maf)]\n"
+    "  --rerun,                 Read previous loaded data and rerun\n"
+    "  --keep_tmp,              Don't remove tmp files when basetype finished\n"
+    "  --gpus <INT>             GPUs to use [all visible; env BVC_GPUS]\n"
+    "  --tile_sites <INT>       Sites per GPU tile [auto]\n";
+
+const char* kCvgHeader =
+    "##fileformat=CVGv1.0\n"
+    "##Group information is the depth of A:C:G:T:Indel\n"
+    "#CHROM\tPOS\tREF\tDepth\tA\tC\tG\tT\tIndels\tFS\tSOR\tStrand_Coverage(REF_FWD,REF_REV,ALT_FWD,ALT_REV)";
+
+const char* kVcfHeader =
+    "##fileformat=VCFv4.2\n"
+    "##FILTER=<ID=LowQual,Description=\"Low quality (QUAL < 60)\">\n"
+    "##FORMAT=<ID=GT,Number=1,Type=String,Description=\"Genotype\">\n"
+    "##FORMAT=<ID=AB,Number=1,Type=String,Description=\"Allele Base\">\n"
+    "##FORMAT=<ID=SO,Number=1,Type=String,Description=\"Strand orientation of the mapping base. Marked as + or -\">\n"
+    "##FORMAT=<ID=BP,Number=1,Type=String,Description=\"Base Probability which calculate by base quality\">\n"
+    "##INFO=<ID=CM_AF,Number=A,Type=Float,Description=\"An ordered, comma delimited list of allele frequencies base on LRT algorithm\">\n"
+    "##INFO=<ID=CM_CAF,Number=A,Type=Float,Description=\"An ordered, comma delimited list of allele frequencies just base on read count\">\n"
+    "##INFO=<ID=CM_AC,Number=A,Type=Integer,Description=\"An ordered, comma delimited allele depth in CMDB\">\n"
+    "##INFO=<ID=CM_DP,Number=A,Type=Integer,Description=\"Total Depth\">\n"
+    "##INFO=<ID=SB_REF,Number=A,Type=Integer,Description=\"Read number support REF: Forward,Reverse\">\n"
+    "##INFO=<ID=SB_ALT,Number=A,Type=Integer,Description=\"Read number support ALT: Forward,Reverse\">\n"
+    "##INFO=<ID=FS,Number=1,Type=Float,Description=\"Phred-scaled p-value using Fisher's exact test to detect strand bias\">\n"
+    "##INFO=<ID=BaseQRankSum,Number=1,Type=Float,Description=\"Phred-score from Wilcoxon rank sum test of Alt Vs. Ref base qualities\">\n"
+    "##INFO=<ID=SOR,Number=1,Type=Float,Description=\"Symmetric Odds Ratio of 2x2 contingency table to detect strand bias\">\n"
+    "##INFO=<ID=MQRankSum,Number=1,Type=Float,Description=\"Phred-score From Wilcoxon rank sum test of Alt vs. Ref read mapping qualities\">\n"
+    "##INFO=<ID=ReadPosRankSum,Number=1,Type=Float,Description=\"Phred-score from Wilcoxon rank sum test of Alt vs. Ref read position bias\">\n"
+    "##INFO=<ID=QD,Number=1,Type=Float,Description=\"Variant Confidence Quality by Depth\">\n";
+
+struct Options {
+    bool rerun = false, load = false, keep_tmp = false, verbose = false;
+    int mapq = 10, thread = 1, batch = 10, gpus = 0, tile_sites = 0;
+    double maf = 0.001;
+    std::string input, reference, group, region, output;
+};
+
+// src/BaseVarC.cpp:797-827 (same letters, same long names; 6/7/8 are the reference's codes for the flags)
+bool parse_options(int argc, char** argv, Options& o)
+{
+    static const option longopts[] = {
+        {"verbose", no_argument, nullptr, 'v'},       {"input", required_argument, nullptr, 'i'},
+        {"output", required_argument, nullptr, 'o'},  {"reference", required_argument, nullptr, 'r'},
+        {"posfile", required_argument, nullptr, 'p'}, {"region", required_argument, nullptr, 's'},
+        {"group", required_argument, nullptr, 'g'},   {"mapq", required_argument, nullptr, 'q'},
+        {"batch", required_argument, nullptr, 'b'},   {"thread", required_argument, nullptr, 't'},
+        {"maf", required_argument, nullptr, 'a'},     {"rerun", no_argument, nullptr, 8},
+        {"load", no_argument, nullptr, 7},            {"keep_tmp", no_argument, nullptr, 6},
+        {"gpus", required_argument, nullptr, 1},      {"tile_sites", required_argument, nullptr, 2},
+        {nullptr, 0, nullptr, 0}};
+    bool die = false;
+    optind = 1;
+    for (int c; (c = getopt_long(argc, argv, "hva:i:r:p:s:o:q:t:b:g:", longopts, nullptr)) != -1;) {
+        const char* a = optarg ? optarg : "";
+        switch (c) {
+        case 'q': o.mapq = atoi(a); break;
+        case 'b': o.batch = atoi(a); break;
+        case 't': o.thread = atoi(a); break;
+        case 'i': o.input = a; break;
+        case 'r': o.reference = a; break;
+        case 'p': break;
+        case 's': o.region = a; break;
+        case 'g': o.group = a; break;
+        case 'o': o.output = a; break;
+        case 'a': o.maf = atof(a); break;
+        case 8: o.rerun = true; break;
+        case 7: o.load = true; break;
+        case 6: o.keep_tmp = true; break;
+        case 1: o.gpus = atoi(a); break;
+        case 2: o.tile_sites = atoi(a); break;
+        case 'v': o.verbose = true; break;
+        default: die = true;
+        }
+    }
+    if (die || o.input.empty() || o.output.empty()) { std::cerr << kUsage; return false; }
+    return true;
+}
+
+// BaseVarUtils.h:59-75: "chr:S-E" -> (chr, S, E-1)
+bool split_region(const std::string& rg, std::string& chr, long long& s, long long& e)
+{
+    const size_t c = rg.find(':');
+    if (c == std::string::npos) return false;
+    const std::string rest = rg.substr(c + 1);
+    const size_t d = rest.find('-');
+    if (d == std::string::npos) return false;
+    chr = rg.substr(0, c);
+    s = atoll(rest.substr(0, d).c_str());
+    e = atoll(rest.substr(d + 1).c_str()) - 1;
+    return true;
+}
+
+inline int base_code(char c)       // BASE_INT8_TABLE, src/BaseType.h:25-42
+{
+    switch (c) { case 'A': return 0; case 'C': return 1; case 'G': return 2; case 'T': return 3; default: return -1; }
+}
+
+std::string now_string()
+{
+    time_t t = time(nullptr);
+    return std::string(ctime(&t));
+}
+
+// ---- one tile in flight: the packed sites of a window, their records, and a completion flag ----------------
+struct TileJob {
+    explicit TileJob(int32_t n_samples) : pk(n_samples) {}
+    Packer pk;
+    std::vector<bvc_site_result> rec;
+    std::vector<int32_t> group_depth;      // [n_sites][n_groups][4]
+    std::vector<double> group_af;
+    std::mutex m;
+    std::condition_variable cv;
+    bool done = false;
+    int rc = 0;
+    std::string err;
+};
+
+// ---- one dispatcher thread per GPU: owns the context (not thread-safe), keeps two tickets in flight ----------
+class GpuServer {
+public:
+    GpuServer(int device, const bvc_params& prm) : device_(device), prm_(prm) {}
+    bool start(std::string* err)
+    {
+        const int rc = bvc_create(&ctx_, device_, &prm_);
+        if (rc != BVC_OK) { *err = std::string("GPU ") + std::to_string(device_) + ": " + bvc_last_error(nullptr); return false; }
+        th_ = std::thread([this] { run(); });
+        return true;
+    }
+    void submit(TileJob* j)
+    {
+        { std::lock_guard<std::mutex> lk(m_); q_.push_back(j); }
+        cv_.notify_one();
+    }
+    void stop()
+    {
+        { std::lock_guard<std::mutex> lk(m_); stop_ = true; }
+        cv_.notify_one();
+        if (th_.joinable()) th_.join();
+        if (ctx_) { launches_ = bvc_kernel_launch_count(ctx_); bvc_destroy(ctx_); ctx_ = nullptr; }
+    }
+    long long launches() const { return launches_; }
+
+private:
+    struct Flight { TileJob* job; uint64_t ticket; };
+    void finish(const Flight& f)
+    {
+        int rc = bvc_wait(ctx_, f.ticket);
+        std::string err = rc == BVC_OK ? "" : bvc_last_error(ctx_);
+        if (rc == BVC_OK && prm_.n_groups > 0 && f.job->pk.n_sites() > 0) {
+            rc = bvc_fetch_groups(ctx_, f.ticket, f.job->group_depth.data(), f.job->group_af.data());
+            if (rc != BVC_OK) err = bvc_last_error(ctx_);
+        }
+        { std::lock_guard<std::mutex> lk(f.job->m); f.job->rc = rc; f.job->err = err; f.job->done = true; }
+        f.job->cv.notify_all();
+    }
+    void run()
+    {
+        std::deque<Flight> fly;
+        for (;;) {
+            TileJob* j = nullptr;
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                if (fly.empty()) cv_.wait(lk, [this] { return stop_ || !q_.empty(); });
+                if (!q_.empty()) { j = q_.front(); q_.pop_front(); }
+                else if (stop_ && fly.empty()) return;
+            }
+            // group outputs belong to the most recent ticket of a slot: with groups, retire before re-using a slot
+            const size_t max_fly = prm_.n_groups > 0 ? 1 : 2;
+            if (j) {
+                while (fly.size() >= max_fly) { finish(fly.front()); fly.pop_front(); }
+                bvc_tile t;
+                j->pk.tile(&t);
+                if (prm_.n_groups == 0) t.sample = nullptr;
+                uint64_t tk = 0;
+                const int rc = bvc_enqueue(ctx_, &t, j->rec.data(), &tk);
+                if (rc != BVC_OK) {
+                    { std::lock_guard<std::mutex> lk(j->m); j->rc = rc; j->err = bvc_last_error(ctx_); j->done = true; }
+                    j->cv.notify_all();
+                } else fly.push_back({j, tk});
+            } else if (!fly.empty()) { finish(fly.front()); fly.pop_front(); }
+        }
+    }
+    int device_;
+    bvc_params prm_;
+    bvc_ctx* ctx_ = nullptr;
+    std::thread th_;
+    std::mutex m_;
+    std::condition_variable cv_;
+    std::deque<TileJob*> q_;
+    bool stop_ = false;
+    long long launches_ = 0;
+};
+
+struct Shared {
+    Options opt;
+    std::string chr, refseq;
+    long long rg_s = 0;
+    std::vector<int32_t> pv;
+    int32_t N = 0, nb = 0, tile_sites = 0;
+    int64_t tile_entries = 0;
+    int n_groups = 0;
+    std::vector<std::string> group_names;
+    std::vector<const char*> group_name_ptrs;
+    std::string headvcf, headcvg;
+    std::atomic<bool> failed{false};
+    std::mutex err_m;
+    std::string err;
+    void fail(const std::string& e) { std::lock_guard<std::mutex> lk(err_m); if (!failed.exchange(true)) err = e; }
+};
+
+// ---- one thread per window: read + tokenise -> tile -> GPU -> format -> BGZF (in memory) ---------------------
+void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out, std::string* cvg_out)
+{
+    const Options& o = sh->opt;
+    const int T = o.thread;
+    std::vector<std::unique_ptr<BgzfReader>> in;
+    std::vector<std::string> names;
+    for (int j = 0; j < sh->nb; ++j) {
+        names.push_back(o.output + ".tmp.thread." + std::to_string(ithread) + "/batch." + std::to_string(j));
+        in.emplace_back(new BgzfReader());
+        std::string e;
+        if (!in.back()->open(names.back(), &e)) { sh->fail(e); return; }
+    }
+    std::string line;
+    for (auto& r : in) r->getline(line);                     // sample-name lines (header is built by the caller)
+    BgzfWriter wv, wc;
+    wv.open_memory(); wc.open_memory();
+    if (ithread == 0) { wv.write(sh->headvcf); wc.write(sh->headcvg); }
+    std::cerr << "begin to load data and run basetype" << std::endl;
+
+    const size_t P = sh->pv.size();
+    const size_t window = P % (size_t)T + P / (size_t)T;     // src/BaseVarC.cpp:399
+    size_t it = std::min(P, (size_t)ithread * window);
+    const size_t it_end = (ithread == T - 1) ? P : std::min(P, (size_t)(ithread + 1) * window);
+
+    TileJob jobs[2] = {TileJob(sh->N), TileJob(sh->N)};
+    // the two packers share ONE stale-token state in the reference (a single `ai` per window): hand it over by
+    // packing strictly in site order and copying the state forward (Packer::adopt_state)
+    int cur = 0, count = 0;
+    bool pending[2] = {false, false};
+    std::string vline, cline;
+
+    auto drain = [&](int k) -> bool {                         // wait for job k, format its sites, release it
+        TileJob& j = jobs[k];
+        { std::unique_lock<std::mutex> lk(j.m); j.cv.wait(lk, [&] { return j.done; }); }
+        pending[k] = false;
+        if (j.rc != BVC_OK) { sh->fail("GPU call failed: " + j.err); return false; }
+        bvc_tile t;
+        j.pk.tile(&t);
+        const int32_t* pos = j.pk.positions();
+        const int G = sh->n_groups;
+        for (int32_t s = 0; s < j.pk.n_sites(); ++s) {
+            const bvc_site_result* r = &j.rec[(size_t)s];
+            const int32_t* gd = G ? &j.group_depth[(size_t)s * G * 4] : nullptr;
+            const double* ga = G ? &j.group_af[(size_t)s * G * 4] : nullptr;
+            if (r->lrt_ok) {
+                format_vcf(vline, sh->chr.c_str(), pos[s], &t, s, r, sh->N, G, sh->group_name_ptrs.data(), gd, ga);
+                wv.write(vline);
+            }
+            format_cvg(cline, sh->chr.c_str(), pos[s], &t, s, r, &j.pk, G, gd);
+            wc.write(cline);
+            if (!(++count % 1000)) std::cerr << "basetype completed " << count << " sites -- thread" << ithread << std::endl;
+        }
+        return true;
+    };
+    auto flush = [&](int k) {                                 // hand job k to the GPU
+        TileJob& j = jobs[k];
+        j.rec.resize((size_t)j.pk.n_sites());
+        if (sh->n_groups) {
+            j.group_depth.assign((size_t)j.pk.n_sites() * sh->n_groups * 4, 0);
+            j.group_af.assign((size_t)j.pk.n_sites() * sh->n_groups * 4, 0.0);
+        }
+        j.done = false;
+        pending[k] = true;
+        gpu->submit(&j);
+    };
+
+    for (; it < it_end && !sh->failed; ++it) {
+        TileJob& j = jobs[cur];
+        const int32_t p = sh->pv[it];
+        const int rb = base_code(sh->refseq[(size_t)(p - sh->rg_s)]);
+        j.pk.begin_site(p, (uint8_t)rb);
+        for (auto& r : in) {
+            const char* lp; size_t ln;
+            if (r->getline_view(&lp, &ln)) {
+                if (j.pk.add_line(lp, ln) != BVC_OK) { sh->fail(j.pk.error()); return; }
+            } else if (r->failed()) { sh->fail("corrupt batch file: " + r->error()); return; }
+        }
+        if (j.pk.end_site() == 0) j.pk.drop_last_site();      // no entries: the reference prints nothing (:442)
+        if (j.pk.n_sites() >= sh->tile_sites || j.pk.n_entries() + sh->N > sh->tile_entries) {
+            flush(cur);
+            const int other = cur ^ 1;
+            if (pending[other] && !drain(other)) return;
+            jobs[other].pk.clear();
+            jobs[other].pk.adopt_state(jobs[cur].pk);
+            cur = other;
+        }
+    }
+    if (sh->failed) { for (int k = 0; k < 2; ++k) if (pending[k]) { std::unique_lock<std::mutex> lk(jobs[k].m); jobs[k].cv.wait(lk, [&] { return jobs[k].done; }); } return; }
+    if (jobs[cur].pk.n_sites() > 0) flush(cur);
+    // drain in submission order: the job submitted first is the one that is not `cur` (if still pending)
+    if (pending[cur ^ 1] && !drain(cur ^ 1)) return;
+    if (pending[cur] && !drain(cur)) return;
+    wv.close(false); wc.close(false);
+    *vcf_out = std::move(wv.memory());
+    *cvg_out = std::move(wc.memory());
+    if (!o.keep_tmp) for (auto& n : names) remove(n.c_str());  // src/BaseVarC.cpp:458-462
+}
+
+}  // namespace
+}  // namespace bvc_host
+
+// =====================================================================================================
+extern "C" int bvc_basetype_main(int argc, char** argv)
+{
+    using namespace bvc_host;
+    Shared sh;
+    Options& o = sh.opt;
+    if (!parse_options(argc, argv, o)) return EXIT_FAILURE;
+    std::string chr; long long rg_s = 0, rg_e = 0;
+    if (!split_region(o.region, chr, rg_s, rg_e)) {
+        std::cerr << "region must be feed with samtools-like format, i.e. chr:start-end" << std::endl;
+        return EXIT_FAILURE;
+    }
+    if (o.reference.empty()) { std::cerr << "reference must be feed" << std::endl; return EXIT_FAILURE; }
+    const clock_t ctb = clock();
+    std::cout << "basetype start -- " << now_string();
+    // N = number of lines of the BAM list (src/BaseVarC.cpp:186-189); the BAMs themselves are never opened here
+    {
+        std::ifstream ib(o.input);
+        if (!ib.is_open()) { std::cerr << "cannot open " << o.input << std::endl; return EXIT_FAILURE; }
+        std::string l; int32_t n = 0;
+        while (std::getline(ib, l)) ++n;
+        sh.N = n;
+    }
+    if (sh.N <= 0 || o.thread <= 0 || o.batch <= 0) { std::cerr << "empty input list or bad --thread/--batch" << std::endl; return EXIT_FAILURE; }
+    // reference bases of [S, E-1+1000) (src/BaseVarC.cpp:193-196 with both splitrg decrements) and the site list
+    Fasta fa;
+    std::string err;
+    if (!fa.open(o.reference, &err) || !fa.fetch(chr, rg_s - 1, rg_e + 998, sh.refseq, &err)) { std::cerr << "ERROR: " << err << std::endl; return EXIT_FAILURE; }
+    const long long buf = 1000;
+    if ((long long)sh.refseq.size() <= buf) { std::cerr << "ERROR: region is empty or past the end of " << chr << std::endl; return EXIT_FAILURE; }
+    for (size_t i = 0; i < sh.refseq.size() - (size_t)buf; ++i)
+        if (base_code(sh.refseq[i]) >= 0) sh.pv.push_back((int32_t)(i + rg_s));
+    sh.chr = chr; sh.rg_s = rg_s;
+    const int T = o.thread;
+    sh.nb = 1 + (sh.N - 1) / o.batch;
+    if (T > 1 && (size_t)(T - 1) * (sh.pv.size() % T + sh.pv.size() / T) > sh.pv.size()) {
+        std::cerr << "ERROR: --thread " << T << " does not partition " << sh.pv.size() << " sites (the reference reads past its site list here)" << std::endl;
+        return EXIT_FAILURE;
+    }
+    // batch files: all T x nb must be complete BGZF files (src/BaseVarC.cpp:214-233)
+    int ngz = 0;
+    for (int j = 0; j < sh.nb; ++j)
+        for (int i = 0; i < T; ++i)
+            if (bgzf_is_complete(o.output + ".tmp.thread." + std::to_string(i) + "/batch." + std::to_string(j))) ++ngz;
+    if (ngz != T * sh.nb) {
+        std::cerr << "ERROR: " << ngz << " of " << T * sh.nb << " batch files are complete under " << o.output
+                  << ".tmp.thread.*; BAM decoding stays with the reference: run `BaseVarC basetype --load` with the same -t/-b first" << std::endl;
+        return EXIT_FAILURE;
+    }
+    std::cout << "basetype loading done -- " << now_string();
+    if (o.load) return EXIT_SUCCESS;
+
+    // sample names = first line of every batch file of window 0, concatenated (src/BaseVarC.cpp:333-338)
+    std::string sams;
+    for (int j = 0; j < sh.nb; ++j) {
+        BgzfReader r; std::string l;
+        if (!r.open(o.output + ".tmp.thread.0/batch." + std::to_string(j), &err)) { std::cerr << "ERROR: " << err << std::endl; return EXIT_FAILURE; }
+        if (r.getline(l)) sams += l;
+    }
+    if (!sams.empty()) sams.pop_back();
+    // population groups (src/BaseVarC.cpp:340-370): std::map order = sorted group names
+    std::vector<int32_t> sample_group((size_t)sh.N, -1);
+    sh.headcvg = kCvgHeader; sh.headvcf = kVcfHeader;
+    if (!o.group.empty()) {
+        std::ifstream ifg(o.group);
+        std::unordered_map<std::string, std::string> popg;
+        std::string id, grp;
+        while (ifg >> id >> grp) popg.insert({id, grp});
+        std::map<std::string, std::vector<int>> idx;
+        std::istringstream iss(sams);
+        int i = -1;
+        while (std::getline(iss, id, '\t')) { ++i; auto f = popg.find(id); if (f != popg.end()) idx[f->second].push_back(i); }
+        for (auto& kv : idx) {
+            for (int s : kv.second) if (s < sh.N) sample_group[(size_t)s] = (int32_t)sh.group_names.size();
+            sh.group_names.push_back(kv.first);
+            sh.headcvg += "\t" + kv.first;
+            sh.headvcf += "##INFO=<ID=" + kv.first + "_AF,Number=A,Type=Float,Description=\"Allele frequency in the " + kv.first + " populations calculated based on LRT.[0,1]\">\n";
+        }
+        sh.n_groups = (int)sh.group_names.size();
+        for (auto& g : sh.group_names) sh.group_name_ptrs.push_back(g.c_str());
+    }
+    for (auto& c : fa.contigs()) sh.headvcf += "##contig=<ID=" + c.name + ",length=" + std::to_string(c.len) + ">\n";
+    sh.headvcf += "##reference=file://" + o.reference + "\n";
+    sh.headvcf += "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\t" + sams + "\n";
+    sh.headcvg += "\n";
+
+    // tile geometry and one dispatcher per GPU
+    int n_dev = bvc_device_count();
+    if (const char* e = getenv("BVC_GPUS")) if (o.gpus <= 0) o.gpus = atoi(e);
+    if (n_dev <= 0) { std::cerr << "ERROR: no CUDA device: the basetype calling core has no CPU path (" << bvc_last_error(nullptr) << ")" << std::endl; return EXIT_FAILURE; }
+    const int G = std::max(1, std::min(std::min(o.gpus > 0 ? o.gpus : n_dev, n_dev), T));
+    sh.tile_entries = (int64_t)32 << 20;
+    sh.tile_sites = o.tile_sites > 0 ? o.tile_sites : (int32_t)std::max<int64_t>(64, std::min<int64_t>(16384, sh.tile_entries / sh.N));
+    sh.tile_entries = std::max<int64_t>(sh.tile_entries, (int64_t)sh.tile_sites * 0 + 2 * (int64_t)sh.N);
+    bvc_params prm;
+    bvc_default_params(&prm, sh.N, o.maf);
+    prm.max_sites = sh.tile_sites;
+    prm.max_entries = sh.tile_entries;
+    prm.n_groups = sh.n_groups;
+    prm.sample_group = sh.n_groups ? sample_group.data() : nullptr;
+    std::vector<std::unique_ptr<GpuServer>> gpus;
+    for (int g = 0; g < G; ++g) {
+        gpus.emplace_back(new GpuServer(g, prm));
+        if (!gpus.back()->start(&err)) { std::cerr << "ERROR: " << err << std::endl; for (auto& s : gpus) s->stop(); return EXIT_FAILURE; }
+    }
+    // windows [g*T/G, (g+1)*T/G) -> GPU g
+    std::vector<std::string> vcf((size_t)T), cvg((size_t)T);
+    std::vector<std::thread> workers;
+    for (int i = 0; i < T; ++i) workers.emplace_back(window_worker, &sh, gpus[(size_t)((long long)i * G / T)].get(), i, &vcf[(size_t)i], &cvg[(size_t)i]);
+    for (auto& w : workers) w.join();
+    long long launches = 0;
+    for (auto& s : gpus) { s->stop(); launches += s->launches(); }
+    if (sh.failed) { std::cerr << "ERROR: " << sh.err << std::endl; return EXIT_FAILURE; }
+    // ordered concatenation of the windows' BGZF blocks + one EOF block (replaces the re-read merge of :268-295)
+    for (int k = 0; k < 2; ++k) {
+        const std::string path = o.output + (k ? ".cvg.gz" : ".vcf.gz");
+        FILE* f = fopen(path.c_str(), "wb");
+        if (!f) { std::cerr << "ERROR: cannot write " << path << std::endl; return EXIT_FAILURE; }
+        for (int i = 0; i < T; ++i) { const std::string& s = k ? cvg[(size_t)i] : vcf[(size_t)i]; fwrite(s.data(), 1, s.size(), f); }
+        fwrite(BgzfWriter::kEofBlock, 1, 28, f);
+        if (fclose(f) != 0) std::cerr << "warning: file cannot be closed" << std::endl;
+    }
+    std::cout << "merge subfiles done" << std::endl;
+    if (!o.keep_tmp) for (int i = 0; i < T; ++i) rmdir((o.output + ".tmp.thread." + std::to_string(i)).c_str());
+    std::cout << "basetype computing done -- " << now_string();
+    std::cout << "basetype elapsed cpu secs : " << double(clock() - ctb) / CLOCKS_PER_SEC << std::endl;
+    if (o.verbose) std::cout << "basetype gpu kernels launched : " << launches << " on " << G << " GPU(s)" << std::endl;
+    std::cout << "basetype done" << std::endl;
+    return EXIT_SUCCESS;
+}

@@ -59,6 +59,9 @@ typedef struct bvc_params {
     int64_t max_entries;        /* capacity of one tile (entries) */
 } bvc_params;
 
+/* Number of CUDA devices visible to this process (0 when there is no driver / device). */
+int  bvc_device_count(void);
+
 /* Fills *p with the reference's constants for a cohort of n_samples and `--maf maf`. */
 void bvc_default_params(bvc_params* p, int32_t n_samples, double maf);
 

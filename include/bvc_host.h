@@ -1,0 +1,73 @@
+/* include/bvc_host.h -- host side of the `basetype --rerun` drop-in: what sits between the reference's
+ * batch files and the GPU calling core (include/bvc_gpu.h), and between the result records and the
+ * reference's .cvg / .vcf text.  Implemented in C++ (basevarc_b200/csrc/host), exported as plain C.
+ *
+ * Reference code each entry point replaces (paths under /root/reference):
+ *   bvc_packer_*        the tokeniser / merger of the window loop          src/BaseVarC.cpp:393-441
+ *                       (AlleleInfo, AlleleInfoVector, DepM idx            src/BamProcess.h:30-39, src/BaseType.h:21)
+ *   bvc_format_cvg      the CVG line of bt_f                               src/BaseVarC.cpp:568-575,609-610,640,662
+ *   bvc_format_vcf      the text part of WriteVcf                          src/BaseType.cpp:143-163,198-233
+ *   bvc_basetype_main   runBaseType + bt_s for `--rerun` (compute phase)   src/BaseVarC.cpp:176-314,316-465
+ *
+ * None of these computes a statistic: every number printed comes from a bvc_site_result the GPU produced
+ * (or, in tests only, from the oracle).  bvc_basetype_main has no CPU calling path: without a usable
+ * sm_100 device it fails with the error of bvc_create.
+ */
+#ifndef BVC_HOST_H
+#define BVC_HOST_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "bvc_gpu.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- packer: batch-file lines -> structure-of-arrays tile --------------------------------------------------
+ * One packer per window (= per reference thread directory): it carries the reference's reused `AlleleInfo ai`
+ * across tokens, lines and sites (quirk Q1: an indel token keeps base/mapq/qual/rpr/strand of the last numeric
+ * token, src/BaseVarC.cpp:393,432-435).  Before the first numeric token those fields are uninitialised in the
+ * reference; here they are zero. */
+typedef struct bvc_packer bvc_packer;
+
+bvc_packer* bvc_packer_create(int32_t n_samples);
+void bvc_packer_destroy(bvc_packer* pk);
+/* Drop the packed sites, keep the stale-field state (call between tiles of one window). */
+void bvc_packer_clear(bvc_packer* pk);
+/* Start a site: ref_base = BASE_INT8_TABLE[refseq[p - rg_s]] (0..3), pos = 1-based position. */
+void bvc_packer_begin_site(bvc_packer* pk, int32_t pos, uint8_t ref_base);
+/* Tokens of one batch-file line (no '\n'); sample indices continue across the lines of a site.
+ * Returns 0, or BVC_ERR_ARG for a token the GPU path does not accept (non-indel base > 4, qual > 127). */
+int  bvc_packer_add_line(bvc_packer* pk, const char* line, size_t len);
+/* Close the site.  Returns the number of entries it got (0: the reference prints nothing for it). */
+int32_t bvc_packer_end_site(bvc_packer* pk);
+int32_t bvc_packer_n_sites(const bvc_packer* pk);
+int64_t bvc_packer_n_entries(const bvc_packer* pk);
+/* The tile over the packer's arrays (valid until the next packer call) and the host-only side arrays. */
+void bvc_packer_tile(const bvc_packer* pk, bvc_tile* out);
+const int32_t* bvc_packer_positions(const bvc_packer* pk);             /* [n_sites] */
+const char* bvc_packer_indel(const bvc_packer* pk, int64_t entry);     /* indel token text, or NULL */
+const char* bvc_packer_error(const bvc_packer* pk);
+
+/* ---- formatter: result record + the site's entries -> the reference's text ---------------------------------
+ * Both return the number of bytes the line needs (excluding the NUL); at most cap-1 bytes are written.
+ * group_depth / group_af: [n_groups][4] for this site as bvc_fetch_groups returns them, or NULL;
+ * group_names: n_groups names in the reference's (sorted) order. */
+size_t bvc_format_cvg(char* buf, size_t cap, const char* chr, int32_t pos, const bvc_tile* tile, int32_t site,
+                      const bvc_site_result* rec, const bvc_packer* indel_src,
+                      int32_t n_groups, const int32_t* group_depth);
+/* n_samples = N (all samples get a column, src/BaseType.cpp:152).  Returns 0 when !rec->lrt_ok. */
+size_t bvc_format_vcf(char* buf, size_t cap, const char* chr, int32_t pos, const bvc_tile* tile, int32_t site,
+                      const bvc_site_result* rec, int32_t n_samples,
+                      int32_t n_groups, const char* const* group_names, const int32_t* group_depth,
+                      const double* group_af);
+
+/* ---- the command: `BaseVarC basetype --rerun ...` with the compute phase on the GPU(s) ----------------------
+ * argv as the reference's runBaseType sees it (argv[0] = "basetype").  Returns the process exit status. */
+int bvc_basetype_main(int argc, char** argv);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BVC_HOST_H */
