@@ -213,7 +213,10 @@ __device__ __noinline__ double ranksum_hist(const uint32_t* hr, const uint32_t* 
     const double r1 = (double)twice / 2.0;
     const double expected = (double)(n1 * (n1 + n2 + 1)) / 2.0;
     const double z = (r1 - expected) / sqrt((double)(n1 * n2 * (n1 + n2 + 1)) / 12.0);
-    return dm_phred(2 * dm_normsf(fabs(z)));
+    // n1 == 0 or n2 == 0: z = 0/0.  The reference's NaN goes through fabs() and keeps a clear sign bit down to the
+    // "{:.3f}" (prints "nan"); the device's canonical NaN has the sign bit set, so clear it.
+    const double v = dm_phred(2 * dm_normsf(fabs(z)));
+    return (v != v) ? __longlong_as_double(0x7ff8000000000000LL) : v;   // abs.f64 of a NaN is unspecified in PTX
 }
 
 }  // namespace bvc
