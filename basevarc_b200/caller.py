@@ -138,6 +138,17 @@ class BaseTypeCaller:
     def wait(self, ticket):
         self._check(self.lib.bvc_wait(self.ctx, C.c_uint64(ticket)), "bvc_wait")
 
+    def call_sites_with_groups(self, tile):
+        """(records, group_depth[S][G][4], group_af[S][G][4]) -- bt_f with a --group file (src/BaseVarC.cpp:617-661)."""
+        out = np.zeros(tile.n_sites, SITE_RESULT_DTYPE)
+        G = self.params.n_groups
+        gd = np.zeros((tile.n_sites, G, 4), np.int32)
+        ga = np.zeros((tile.n_sites, G, 4), np.float64)
+        tk = self.enqueue(tile, out)
+        self.wait(tk)
+        self._check(self.lib.bvc_fetch_groups(self.ctx, C.c_uint64(tk), gd.ctypes.data, ga.ctypes.data), "bvc_fetch_groups")
+        return out, gd, ga
+
     def call_sites(self, tile, out=None):
         if out is None:
             out = np.zeros(tile.n_sites, SITE_RESULT_DTYPE)

@@ -23,6 +23,8 @@ struct Slot {
     uint32_t *d_off = nullptr, *d_sample = nullptr;
     bvc_site_result* d_out = nullptr;
     unsigned int* d_counter = nullptr;
+    int32_t* d_gdepth = nullptr;   // --group outputs [S][n_groups][4]
+    double* d_gaf = nullptr;
     // staged-pipeline intermediates (bvc_pipeline.cuh)
     bvc::SiteSum* d_sum = nullptr;
     uint32_t* d_cls = nullptr;
@@ -33,6 +35,7 @@ struct Slot {
     uint32_t* d_ctr = nullptr;     // [kCtrWords]: cls_cursor, qa_n, qb_n, q_head, vcf_n, legacy_n, long_n, work[4] (u64 at word 8), bins at word 16
     const uint8_t *k_mapq = nullptr, *k_rpr = nullptr;   // what the kernels read: d_mapq/d_rpr or zero-copy host pointers
     uint64_t ticket = 0;       // 0 = idle
+    uint64_t last_ticket = 0;  // ticket of the tile whose outputs the slot's device buffers hold
     int n_sites = 0;
     int64_t n_entries = 0;
 };
@@ -47,6 +50,7 @@ struct bvc_ctx {
     Slot slot[2];
     double* d_lut = nullptr;
     double* d_lgam = nullptr;
+    int32_t* d_sample_group = nullptr;
     void* d_flush = nullptr;
     size_t flush_bytes = 0;
     uint64_t next_ticket = 1;
@@ -87,7 +91,11 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
     CK(cudaMalloc(&s.d_qual, R + 16));
     CK(cudaMalloc(&s.d_mapq, R + 16));
     CK(cudaMalloc(&s.d_rpr, R + 16));
-    if (ctx->prm.n_groups > 0) CK(cudaMalloc(&s.d_sample, (R + 4) * sizeof(uint32_t)));
+    if (ctx->prm.n_groups > 0) {
+        CK(cudaMalloc(&s.d_sample, (R + 4) * sizeof(uint32_t)));
+        CK(cudaMalloc(&s.d_gdepth, (S + 1) * (size_t)ctx->prm.n_groups * 4 * sizeof(int32_t)));
+        CK(cudaMalloc(&s.d_gaf, (S + 1) * (size_t)ctx->prm.n_groups * 4 * sizeof(double)));
+    }
     CK(cudaMalloc(&s.d_out, (S + 1) * sizeof(bvc_site_result)));
     CK(cudaMalloc(&s.d_counter, sizeof(unsigned int)));
     size_t pool = R < S * (size_t)bvc::kNBins ? R : S * (size_t)bvc::kNBins;
@@ -109,7 +117,7 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
 void free_slot(Slot& s)
 {
     cudaFree(s.d_ref); cudaFree(s.d_off); cudaFree(s.d_code); cudaFree(s.d_qual); cudaFree(s.d_mapq);
-    cudaFree(s.d_rpr); cudaFree(s.d_sample); cudaFree(s.d_out); cudaFree(s.d_counter);
+    cudaFree(s.d_rpr); cudaFree(s.d_sample); cudaFree(s.d_gdepth); cudaFree(s.d_gaf); cudaFree(s.d_out); cudaFree(s.d_counter);
     cudaFree(s.d_sum); cudaFree(s.d_cls); cudaFree(s.d_lad); cudaFree(s.d_fit); cudaFree(s.d_state);
     cudaFree(s.d_qa); cudaFree(s.d_qb); cudaFree(s.d_qs); cudaFree(s.d_ql); cudaFree(s.d_vcf_list); cudaFree(s.d_legacy_list); cudaFree(s.d_ctr);
     if (s.done) cudaEventDestroy(s.done);
@@ -200,6 +208,10 @@ int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullpt
     CK(bvc::launch_pipeline(p, ctx->n_sm, s.stream, &nl, ev, kinds));
     if (n_out) *n_out = nl;
     ctx->launches += nl;
+    if (ctx->prm.n_groups > 0) {
+        CK(bvc::launch_groups(a, s.d_sample, ctx->d_sample_group, ctx->prm.n_groups, s.d_gdepth, s.d_gaf, ctx->n_sm, s.stream));
+        ctx->launches += 2;
+    }
     return BVC_OK;
 }
 
@@ -286,6 +298,14 @@ int bvc_create(bvc_ctx** out, int device, const bvc_params* prm)
         !ck(cudaMemcpy(ctx->d_lut, lut.data(), lut.size() * sizeof(double), cudaMemcpyHostToDevice), "copy lut") ||
         !ck(cudaMemcpy(ctx->d_lgam, lgam.data(), lgam.size() * sizeof(double), cudaMemcpyHostToDevice), "copy lgam"))
         return fail(BVC_ERR_CUDA);
+    if (prm->n_groups > 0) {
+        for (int i = 0; i < prm->n_samples; ++i)
+            if (ctx->sample_group[(size_t)i] >= prm->n_groups) { ctx->err = "bvc_create: sample_group id out of range"; return fail(BVC_ERR_ARG); }
+        if (ctx->legacy_only) { ctx->err = "bvc_create: BVC_LEGACY_KERNEL=1 does not serve the --group path"; return fail(BVC_ERR_ARG); }
+        if (!ck(cudaMalloc(&ctx->d_sample_group, (size_t)prm->n_samples * sizeof(int32_t)), "cudaMalloc sample_group") ||
+            !ck(cudaMemcpy(ctx->d_sample_group, ctx->sample_group.data(), (size_t)prm->n_samples * sizeof(int32_t), cudaMemcpyHostToDevice), "copy sample_group"))
+            return fail(BVC_ERR_CUDA);
+    }
     for (int i = 0; i < 2; ++i) { int rc = alloc_slot(ctx, ctx->slot[i]); if (rc != BVC_OK) return fail(rc); }
     *out = ctx;
     return BVC_OK;
@@ -296,7 +316,7 @@ void bvc_destroy(bvc_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     for (int i = 0; i < 2; ++i) { if (ctx->slot[i].stream) cudaStreamSynchronize(ctx->slot[i].stream); free_slot(ctx->slot[i]); }
-    cudaFree(ctx->d_lut); cudaFree(ctx->d_lgam); cudaFree(ctx->d_flush);
+    cudaFree(ctx->d_lut); cudaFree(ctx->d_lgam); cudaFree(ctx->d_flush); cudaFree(ctx->d_sample_group);
     delete ctx;
 }
 
@@ -318,7 +338,7 @@ int bvc_enqueue(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_result* out, uint64
     if (s.n_sites) CK(cudaMemcpyAsync(out, s.d_out, (size_t)s.n_sites * sizeof(bvc_site_result), cudaMemcpyDeviceToHost, s.stream));
     ctx->d2h_bytes += (int64_t)s.n_sites * (int64_t)sizeof(bvc_site_result);
     CK(cudaEventRecord(s.done, s.stream));
-    s.ticket = tk;
+    s.ticket = tk; s.last_ticket = tk;
     ctx->next_ticket += 1;
     ctx->resident = false;
     *ticket = tk;
@@ -337,11 +357,22 @@ int bvc_wait(bvc_ctx* ctx, uint64_t ticket)
     return BVC_OK;
 }
 
-int bvc_fetch_groups(bvc_ctx* ctx, uint64_t, int32_t*, double*)
+int bvc_fetch_groups(bvc_ctx* ctx, uint64_t ticket, int32_t* group_depth, double* group_af)
 {
     if (!ctx) return BVC_ERR_ARG;
-    set_err(ctx, "bvc_fetch_groups: the --group path is not built yet");
-    return BVC_ERR_STATE;
+    if (ctx->prm.n_groups <= 0 || !group_depth || !group_af) { set_err(ctx, "bvc_fetch_groups: context has no groups / NULL output"); return BVC_ERR_ARG; }
+    if (ticket == 0 || ticket >= ctx->next_ticket) { set_err(ctx, "bvc_fetch_groups: unknown ticket"); return BVC_ERR_STATE; }
+    Slot& s = ctx->slot[ticket & 1];
+    if (s.last_ticket != ticket) { set_err(ctx, "bvc_fetch_groups: the slot of this ticket was re-used by a later bvc_enqueue"); return BVC_ERR_STATE; }
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(s.stream));
+    const size_t n = (size_t)s.n_sites * (size_t)ctx->prm.n_groups * 4;
+    if (n) {
+        CK(cudaMemcpy(group_depth, s.d_gdepth, n * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(group_af, s.d_gaf, n * sizeof(double), cudaMemcpyDeviceToHost));
+        ctx->d2h_bytes += (int64_t)(n * 12);
+    }
+    return BVC_OK;
 }
 
 void* bvc_host_alloc(size_t bytes)

@@ -3,6 +3,7 @@
 #include "bvc_kernels.h"
 #include "bvc_site_kernel.cuh"
 #include "bvc_pipeline.cuh"
+#include "bvc_groups.cuh"
 
 namespace bvc {
 
@@ -268,6 +269,20 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     site_call_kernel<<<(unsigned)(n_sm * occ_leg), kWarpsPerBlock * 32, 0, stream>>>(leg);
     if (ev) cudaEventRecord(ev[launches], stream);
     if (n_launches) *n_launches = launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_groups(const SiteArgs& s, const uint32_t* sample, const int32_t* sample_group, int n_groups,
+                          int32_t* gdepth, double* gaf, int n_sm, cudaStream_t stream)
+{
+    GroupArgs g;
+    g.s = s; g.sample = sample; g.sample_group = sample_group; g.gdepth = gdepth; g.gaf = gaf; g.n_groups = n_groups;
+    const size_t n = (size_t)s.n_sites * n_groups * 4;
+    cudaMemsetAsync(gdepth, 0, n * sizeof(int32_t), stream);
+    cudaMemsetAsync(gaf, 0, n * sizeof(double), stream);
+    const unsigned grid = (unsigned)(n_sm * 8);
+    group_depth_kernel<<<grid, kGroupWarps * 32, 0, stream>>>(g);
+    group_lrt_kernel<<<grid, kGroupWarps * 32, 0, stream>>>(g);
     return cudaGetLastError();
 }
 

@@ -40,5 +40,8 @@ constexpr int kMaxPipeLaunches = 32;
 const char* kernel_kind_name(int kind);
 cudaError_t launch_pipeline(const PipeArgs& a, int n_sm, cudaStream_t stream, int* n_launches,
                             cudaEvent_t* ev = nullptr, int* kinds = nullptr);
+// --group path (bvc_groups.cuh): per-group depths of every site + the group-level LRT of the LRT-positive sites
+cudaError_t launch_groups(const SiteArgs& s, const uint32_t* sample, const int32_t* sample_group, int n_groups,
+                          int32_t* gdepth, double* gaf, int n_sm, cudaStream_t stream);
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream);
 }  // namespace bvc

@@ -73,10 +73,21 @@ def leaf_kats():
     print("leaf_kats.json:", {k: len(v) for k, v in out.items()})
 
 
-def synth_ref(name, N, S, depth, model, seed, threads, batch, indel_frac):
+def group_of(i):
+    """The fixed sample -> population assignment of the *_groups fixture (every 4th sample has no group)."""
+    return ["EAS", "AFR", "EUR", None][i % 4]
+
+
+def synth_ref(name, N, S, depth, model, seed, threads, batch, indel_frac, groups=False):
     tile = B.synth_tile(N, S, depth, model, seed=seed, first_pos=5001, indel_frac=indel_frac)
     with tempfile.TemporaryDirectory() as d:
-        cvg, vcf = refrun.run_reference(tile, d, threads=threads, batch=batch)
+        extra = []
+        if groups:
+            gf = os.path.join(d, "groups.txt")
+            with open(gf, "w") as f:
+                f.write("".join("S%d %s\n" % (i, group_of(i)) for i in range(N) if group_of(i)))
+            extra = ["-g", gf]
+        cvg, vcf = refrun.run_reference(tile, d, threads=threads, batch=batch, extra=extra)
     np.savez_compressed(os.path.join(HERE, name + ".npz"), n_samples=N, ref_base=tile.ref_base, entry_off=tile.entry_off,
                         code=tile.code, qual=tile.qual, mapq=tile.mapq, rpr=tile.rpr, sample=tile.sample, pos=tile.pos)
     for kind, text in (("cvg", cvg), ("vcf", vcf)):
@@ -91,3 +102,4 @@ if __name__ == "__main__":
     leaf_kats()
     synth_ref("synth_ref_lowpass", 120, 2500, 0.6, "lowpass", 101, 3, 16, 0.01)
     synth_ref("synth_ref_highpoly", 48, 1500, 2.0, "highpoly", 102, 2, 10, 0.03)
+    synth_ref("synth_ref_groups", 60, 1200, 3.0, "highpoly", 103, 2, 16, 0.02, groups=True)

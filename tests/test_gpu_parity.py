@@ -64,6 +64,27 @@ def test_qual_edge_cases(oracle):
     assert nbad == 0, "\n".join(lines)
 
 
+def test_group_path_parity(oracle):
+    """--group: per-group depths (exact) and the group-level LRT allele frequencies against the oracle."""
+    from test_host_cpp import group_setup
+    tile = synth_tile(60, 900, 3.0, "highpoly", seed=41, indel_frac=0.02)
+    q = tile.qual.copy(); q[::97] = 0; q[::89] = 1; tile.qual = q
+    p, sg = group_setup(tile.n_samples)
+    caller = B.BaseTypeCaller(tile.n_samples, max_sites=tile.n_sites, max_entries=tile.n_entries, sample_group=sg, n_groups=3)
+    got, gd, ga = caller.call_sites_with_groups(tile)
+    caller.close()
+    want, wd, wa = oracle.call_sites(tile, p, want_groups=True)
+    nbad, lines = compare_records(got, want)
+    assert nbad == 0, "\n".join(lines)
+    assert np.array_equal(gd, wd)
+    ok = (want["lrt_ok"] == 1) & (got["flags"] == 0)
+    assert ok.sum() > 50 and (wa[ok] != 0).any() and (wa[ok] == -1).any()
+    a, b = ga[ok], wa[ok]
+    close = (np.abs(a - b) <= 1e-9 * np.maximum(np.abs(a), np.abs(b))) | (np.isnan(a) & np.isnan(b))
+    assert close.all(), (a[~close][:5], b[~close][:5])
+    assert (ga[want["lrt_ok"] == 0] == 0).all()
+
+
 def test_double_buffered_tickets(oracle):
     tiles = [synth_tile(500, 700, 0.5, "lowpass", seed=20 + i) for i in range(5)]
     caller = B.BaseTypeCaller(500, max_sites=700, max_entries=700 * 500)

@@ -75,3 +75,15 @@ def test_rerun_is_invariant_to_tiling_and_partition(tmp_path):
     body = lambda t: [l for l in t.splitlines() if not l.startswith("#")]
     assert body(a[1]) == body(b[1]) and len(body(a[1])) > 10
     assert os.path.exists(a[2] + ".tmp.thread.0/batch.0")
+
+
+def test_rerun_group_path_matches_reference_binary_text(tmp_path):
+    import refrun
+    tile, cvg_ref, vcf_ref = refrun.load_golden_tile("synth_ref_groups")
+    names = ["EAS", "AFR", "EUR", None]
+    gf = str(tmp_path / "groups.txt")
+    with open(gf, "w") as f:
+        f.write("".join("S%d %s\n" % (i, names[i % 4]) for i in range(tile.n_samples) if names[i % 4]))
+    cvg, vcf, _ = _run_cli(tile, str(tmp_path / "w"), 2, 16, extra=["-g", gf, "--tile_sites", "250"])
+    _compare_text(cvg, vcf, cvg_ref, vcf_ref, tile.n_samples)
+    assert "##INFO=<ID=AFR_AF" in vcf and "EUR_AF=" in vcf

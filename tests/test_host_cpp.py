@@ -130,6 +130,50 @@ def test_formatter_reproduces_reference_text(oracle, name):
     assert ci == len(cvg_lines) and vi == len(vcf_lines)
 
 
+GROUP_NAMES = ["AFR", "EAS", "EUR"]          # sorted, as the reference's std::map iterates them
+
+
+def group_setup(n_samples):
+    """sample -> group id of the *_groups fixture (tests/golden/make_golden.py: group_of)."""
+    names = ["EAS", "AFR", "EUR", None]
+    sg = np.array([GROUP_NAMES.index(names[i % 4]) if names[i % 4] else -1 for i in range(n_samples)], np.int32)
+    p = B.default_params(n_samples)
+    p.n_groups = 3
+    import ctypes as C
+    p.sample_group = sg.ctypes.data_as(C.POINTER(C.c_int32))
+    return p, sg
+
+
+def test_formatter_group_path_reproduces_reference_text(oracle):
+    """--group: per-group depth columns in the CVG, <grp>_AF keys in the VCF INFO (src/BaseVarC.cpp:617-661)."""
+    import refrun
+    tile, cvg_ref, vcf_ref = refrun.load_golden_tile("synth_ref_groups")
+    pk = _pack(tile, batch=16)
+    p, sg = group_setup(tile.n_samples)
+    rec, gd, ga = oracle.call_sites(tile, p, want_groups=True)
+    ct = pk.ctile()
+    cvg_lines = [l for l in cvg_ref.splitlines() if not l.startswith("#")]
+    vcf_lines = {int(l.split("\t")[1]): l for l in vcf_ref.splitlines() if not l.startswith("#")}
+    assert cvg_ref.splitlines()[2].endswith("\tAFR\tEAS\tEUR")
+    ci = 0
+    for s in range(tile.n_sites):
+        if rec["n_entries"][s] == 0:
+            continue
+        got = host.format_cvg("chrS", int(tile.pos[s]), ct, s, rec[s], pk, gd[s])
+        g, w = _norm_indels(got[:-1]), _norm_indels(cvg_lines[ci])
+        assert len(g) == len(w) == 15 and all(_same_number_text(x, y) for x, y in zip(g, w)), (got, cvg_lines[ci])
+        ci += 1
+        if rec["lrt_ok"][s]:
+            v = host.format_vcf("chrS", int(tile.pos[s]), ct, s, rec[s], tile.n_samples, GROUP_NAMES, gd[s], ga[s])
+            gf, wf = v[:-1].split("\t"), vcf_lines[int(tile.pos[s])].split("\t")
+            gi, wi = gf[7].split(";"), wf[7].split(";")
+            assert [x.split("=")[0] for x in gi] == [x.split("=")[0] for x in wi]
+            for x, y in zip(gi, wi):
+                assert all(_same_number_text(a, b) for a, b in zip(x.split("=")[1].split(","), y.split("=")[1].split(","))), (x, y)
+            assert gf[8:] == wf[8:]
+    assert ci == len(cvg_lines) and int(rec["lrt_ok"].sum()) == len(vcf_lines)
+
+
 def test_group_columns_format():
     tile = B.synth_tile(6, 1, 5.0, "lowpass", seed=1, indel_frac=0.0)
     pk = _pack(tile, batch=3)
