@@ -21,7 +21,7 @@ BIN_PATH = os.path.join(_HERE, "bin", "BaseVarC_b200")
 HOST_EXPORTS = (
     "bvc_packer_create", "bvc_packer_destroy", "bvc_packer_clear", "bvc_packer_begin_site", "bvc_packer_add_line",
     "bvc_packer_end_site", "bvc_packer_n_sites", "bvc_packer_n_entries", "bvc_packer_tile", "bvc_packer_positions",
-    "bvc_packer_indel", "bvc_packer_error", "bvc_format_cvg", "bvc_format_vcf", "bvc_basetype_main",
+    "bvc_packer_indel", "bvc_packer_error", "bvc_format_cvg", "bvc_format_vcf", "bvc_basetype_main", "bvc_write_batch_files",
 )
 
 _hlib = None
@@ -65,6 +65,7 @@ def load_host_library():
                                  C.c_int32, C.c_int32, C.POINTER(C.c_char_p), C.c_void_p, C.c_void_p]
     L.bvc_format_vcf.restype = C.c_size_t
     L.bvc_basetype_main.argtypes = [C.c_int, C.POINTER(C.c_char_p)]
+    L.bvc_write_batch_files.argtypes = [C.POINTER(Tile), C.c_int32, C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_char_p]
     _hlib = L
     return L
 
@@ -157,3 +158,15 @@ def run_basetype(argv):
     L = load_host_library()
     arr = (C.c_char_p * (len(argv) + 1))(*[a.encode() for a in argv], None)
     return L.bvc_basetype_main(len(argv), arr)
+
+
+def write_batch_files(tile, prefix, threads, batch, level=1, indel_token="+A"):
+    """Fast (C++, one thread per window) writer of the reference's batch files; same files as
+    batchfile.write_batch_files for tiles whose indel entries all print as `indel_token`."""
+    L = load_host_library()
+    os.makedirs(os.path.dirname(os.path.abspath(prefix)), exist_ok=True)
+    ct = tile.as_ctypes(with_sample=True)
+    rc = L.bvc_write_batch_files(C.byref(ct), tile.n_samples, prefix.encode(), int(threads), int(batch), int(level),
+                                 indel_token.encode())
+    if rc != 0:
+        raise BvcError("bvc_write_batch_files failed (%d): bad (sites, threads) partition or unwritable prefix" % rc)

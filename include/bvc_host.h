@@ -63,6 +63,12 @@ size_t bvc_format_vcf(char* buf, size_t cap, const char* chr, int32_t pos, const
                       int32_t n_groups, const char* const* group_names, const int32_t* group_depth,
                       const double* group_af);
 
+/* ---- writer of the reference's `--load` batch files from a packed tile (fixtures, benchmarks, CPU-baseline runs of the
+ * reference binary): PREFIX.tmp.thread.{t}/batch.{j} as bt_r writes them (src/BaseVarC.cpp:467-534), samples named
+ * S0..S{N-1}, indel entries printed as `indel_token` (NULL = "+A").  tile->sample is required. */
+int bvc_write_batch_files(const bvc_tile* tile, int32_t n_samples, const char* prefix, int32_t threads, int32_t batch,
+                          int32_t level, const char* indel_token);
+
 /* ---- the command: `BaseVarC basetype --rerun ...` with the compute phase on the GPU(s) ----------------------
  * argv as the reference's runBaseType sees it (argv[0] = "basetype").  Returns the process exit status. */
 int bvc_basetype_main(int argc, char** argv);
