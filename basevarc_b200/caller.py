@@ -19,7 +19,11 @@ EXPORTS = (
     "bvc_device_count", "bvc_default_params", "bvc_create", "bvc_destroy", "bvc_last_error", "bvc_enqueue", "bvc_wait",
     "bvc_fetch_groups", "bvc_host_alloc", "bvc_host_free", "bvc_resident_upload", "bvc_resident_run",
     "bvc_resident_download", "bvc_kernel_launch_count", "bvc_measure_fp64_peak", "bvc_kernel_name", "bvc_transfer_bytes", "bvc_work_counters",
+    "bvc_shard_unique_id", "bvc_shard_init", "bvc_shard_call", "bvc_shard_upload", "bvc_shard_run", "bvc_shard_init_group",
+    "bvc_shard_call_group", "bvc_shard_stats", "bvc_shard_phase_name",
 )
+SHARD_ID_BYTES = 128
+SHARD_N_PHASES = 9
 
 
 class BvcError(RuntimeError):
@@ -62,6 +66,17 @@ def load_library():
     L.bvc_transfer_bytes.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.bvc_transfer_bytes.restype = None
     L.bvc_work_counters.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+    L.bvc_shard_unique_id.argtypes = [C.c_void_p]
+    L.bvc_shard_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int]
+    L.bvc_shard_call.argtypes = [C.c_void_p, C.POINTER(Tile), C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.bvc_shard_upload.argtypes = [C.c_void_p, C.POINTER(Tile)]
+    L.bvc_shard_run.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.bvc_shard_init_group.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int]
+    L.bvc_shard_call_group.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.POINTER(Tile)), C.POINTER(C.c_void_p),
+                                       C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.bvc_shard_stats.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
+    L.bvc_shard_phase_name.argtypes = [C.c_int]
+    L.bvc_shard_phase_name.restype = C.c_char_p
     _lib = L
     return L
 
@@ -190,3 +205,105 @@ class BaseTypeCaller:
     @property
     def kernel_launches(self):
         return int(self.lib.bvc_kernel_launch_count(self.ctx))
+
+
+# ---- sample-sharded mode (include/bvc_gpu.h "Sample-sharded mode") ------------------------------------
+def shard_unique_id():
+    """ncclGetUniqueId as bytes (rank 0 calls it; broadcast the bytes to the other ranks)."""
+    L = load_library()
+    buf = C.create_string_buffer(SHARD_ID_BYTES)
+    rc = L.bvc_shard_unique_id(buf)
+    if rc != 0:
+        raise BvcError("bvc_shard_unique_id failed (%d): %s" % (rc, L.bvc_last_error(None).decode()))
+    return buf.raw
+
+
+class ShardedCaller(BaseTypeCaller):
+    """Rank `rank` of `world`: holds the entries of its own sample range for every site of a tile and returns the
+    records of its site slice.  n_samples is the size of the WHOLE cohort.  Every call is collective (NCCL)."""
+
+    def __init__(self, n_samples, rank, world, unique_id, qual_lo=1, qual_hi=63, **kw):
+        super().__init__(n_samples, **kw)
+        self.rank, self.world = int(rank), int(world)
+        assert len(unique_id) == SHARD_ID_BYTES
+        self._id = C.create_string_buffer(bytes(unique_id), SHARD_ID_BYTES)
+        self._check(self.lib.bvc_shard_init(self.ctx, self.rank, self.world, self._id, int(qual_lo), int(qual_hi)), "bvc_shard_init")
+
+    def shard_call(self, tile, out=None):
+        """(first_site, records of the owned slice) through host buffers."""
+        if out is None:
+            out = np.zeros((tile.n_sites + self.world - 1) // self.world, SITE_RESULT_DTYPE)
+        ct = tile.as_ctypes(with_sample=False)
+        first, n = C.c_int32(0), C.c_int32(0)
+        self._check(self.lib.bvc_shard_call(self.ctx, C.byref(ct), out.ctypes.data, C.byref(first), C.byref(n)), "bvc_shard_call")
+        return first.value, out[:n.value]
+
+    def shard_upload(self, tile):
+        ct = tile.as_ctypes(with_sample=False)
+        self._check(self.lib.bvc_shard_upload(self.ctx, C.byref(ct)), "bvc_shard_upload")
+        self._shard_sites = tile.n_sites
+
+    def shard_run(self, out=None):
+        if out is None:
+            out = np.zeros((self._shard_sites + self.world - 1) // self.world, SITE_RESULT_DTYPE)
+        first, n = C.c_int32(0), C.c_int32(0)
+        self._check(self.lib.bvc_shard_run(self.ctx, out.ctypes.data, C.byref(first), C.byref(n)), "bvc_shard_run")
+        return first.value, out[:n.value]
+
+    def shard_stats(self):
+        return _shard_stats(self.lib, self.ctx)
+
+
+def _shard_stats(lib, ctx):
+    ms = (C.c_float * SHARD_N_PHASES)()
+    xb, npos = C.c_int64(0), C.c_int32(0)
+    rc = lib.bvc_shard_stats(ctx, ms, C.byref(xb), C.byref(npos))
+    if rc != 0:
+        raise BvcError("bvc_shard_stats failed (%d)" % rc)
+    return dict(phase_ms={lib.bvc_shard_phase_name(i).decode(): float(ms[i]) for i in range(SHARD_N_PHASES)},
+                exchange_bytes=xb.value, n_positive=npos.value)
+
+
+class ShardGroup:
+    """W contexts of THIS process on one device with the in-process exchange (no NCCL): the same kernels and phases
+    as the NCCL path, used to parity-test sample sharding on a single GPU."""
+
+    def __init__(self, n_samples, world, qual_lo=1, qual_hi=63, **kw):
+        self.world = int(world)
+        self.callers = [BaseTypeCaller(n_samples, **kw) for _ in range(self.world)]
+        self.lib = self.callers[0].lib
+        self._ctxs = (C.c_void_p * self.world)(*[c.ctx for c in self.callers])
+        rc = self.lib.bvc_shard_init_group(self._ctxs, self.world, int(qual_lo), int(qual_hi))
+        if rc != 0:
+            raise BvcError("bvc_shard_init_group failed (%d): %s" % (rc, self._errors()))
+
+    def _errors(self):
+        return " | ".join(self.lib.bvc_last_error(c.ctx).decode() for c in self.callers)
+
+    def call_sites(self, tiles):
+        """tiles[r] = rank r's local tile (same sites, its samples' entries) -> the records of ALL sites, in order."""
+        assert len(tiles) == self.world
+        S = tiles[0].n_sites
+        sr = (S + self.world - 1) // self.world
+        outs = [np.zeros(sr, SITE_RESULT_DTYPE) for _ in range(self.world)]
+        cts = [t.as_ctypes(with_sample=False) for t in tiles]
+        tp = (C.POINTER(Tile) * self.world)(*[C.pointer(ct) for ct in cts])
+        op = (C.c_void_p * self.world)(*[o.ctypes.data for o in outs])
+        first = (C.c_int32 * self.world)()
+        n = (C.c_int32 * self.world)()
+        rc = self.lib.bvc_shard_call_group(self._ctxs, self.world, tp, op, first, n)
+        if rc != 0:
+            raise BvcError("bvc_shard_call_group failed (%d): %s" % (rc, self._errors()))
+        assert [first[r] for r in range(self.world)] == [r * sr for r in range(self.world)]
+        return np.concatenate([outs[r][:n[r]] for r in range(self.world)])
+
+    def stats(self, rank=0):
+        return _shard_stats(self.lib, self.callers[rank].ctx)
+
+    @property
+    def kernel_launches(self):
+        return sum(c.kernel_launches for c in self.callers)
+
+    def close(self):
+        for c in self.callers:
+            c.close()

@@ -7,78 +7,26 @@
 #include <string>
 #include <vector>
 
-#include "../../include/bvc_gpu.h"
-#include "bvc_kernels.h"
-#include "bvc_pipeline_args.h"
+#include "bvc_ctx.h"
+
+using bvc::Slot;
+using bvc::kCtrWords;
+using bvc::set_err;
+using bvc::check_tile;
+using bvc::upload;
 
 namespace {
-
 thread_local std::string g_create_error;
-constexpr size_t kCtrWords = 16 + bvc::kNBins + 16;
+}
 
-struct Slot {
-    cudaStream_t stream = nullptr;
-    cudaEvent_t done = nullptr;
-    uint8_t *d_ref = nullptr, *d_code = nullptr, *d_qual = nullptr, *d_mapq = nullptr, *d_rpr = nullptr;
-    uint32_t *d_off = nullptr, *d_sample = nullptr;
-    bvc_site_result* d_out = nullptr;
-    unsigned int* d_counter = nullptr;
-    int32_t* d_gdepth = nullptr;   // --group outputs [S][n_groups][4]
-    double* d_gaf = nullptr;
-    // staged-pipeline intermediates (bvc_pipeline.cuh)
-    bvc::SiteSum* d_sum = nullptr;
-    uint32_t* d_cls = nullptr;
-    bvc::Ladder* d_lad = nullptr;
-    bvc::FitRes* d_fit = nullptr;
-    uint8_t* d_state = nullptr;
-    uint32_t *d_qa = nullptr, *d_qb = nullptr, *d_qs = nullptr, *d_ql = nullptr, *d_vcf_list = nullptr, *d_legacy_list = nullptr;
-    uint32_t* d_ctr = nullptr;     // [kCtrWords]: cls_cursor, qa_n, qb_n, q_head, vcf_n, legacy_n, long_n, work[4] (u64 at word 8), bins at word 16
-    const uint8_t *k_mapq = nullptr, *k_rpr = nullptr;   // what the kernels read: d_mapq/d_rpr or zero-copy host pointers
-    uint64_t ticket = 0;       // 0 = idle
-    uint64_t last_ticket = 0;  // ticket of the tile whose outputs the slot's device buffers hold
-    int n_sites = 0;
-    int64_t n_entries = 0;
-};
-
-}  // namespace
-
-struct bvc_ctx {
-    int device = 0;
-    int n_sm = 0;
-    bvc_params prm;
-    std::vector<int32_t> sample_group;
-    Slot slot[2];
-    double* d_lut = nullptr;
-    double* d_lgam = nullptr;
-    int32_t* d_sample_group = nullptr;
-    void* d_flush = nullptr;
-    size_t flush_bytes = 0;
-    uint64_t next_ticket = 1;
-    int64_t launches = 0;
-    int64_t h2d_bytes = 0, d2h_bytes = 0;   // bytes moved by cudaMemcpyAsync on the host-buffer path
-    bool zero_copy = true;         // BVC_NO_ZERO_COPY=1 forces the full mapq/rpr copy (A/B checks)
-    bool legacy_only = false;      // BVC_LEGACY_KERNEL=1: the single warp-per-site kernel for every site (A/B checks)
-    std::string err;
-    bool resident = false;
-};
-
-namespace {
-
-#define CK(call)                                                                               \
-    do {                                                                                       \
-        cudaError_t e_ = (call);                                                               \
-        if (e_ != cudaSuccess) {                                                               \
-            char b_[512];                                                                      \
-            snprintf(b_, sizeof b_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
-            set_err(ctx, b_);                                                                  \
-            return BVC_ERR_CUDA;                                                               \
-        }                                                                                      \
-    } while (0)
-
+namespace bvc {
 void set_err(bvc_ctx* ctx, const char* m)
 {
     if (ctx) ctx->err = m; else g_create_error = m;
 }
+}  // namespace bvc
+
+namespace {
 
 int alloc_slot(bvc_ctx* ctx, Slot& s)
 {
@@ -125,7 +73,9 @@ void free_slot(Slot& s)
     s = Slot();
 }
 
-int check_tile(bvc_ctx* ctx, const bvc_tile* t, int64_t* n_entries)
+}  // namespace
+
+int bvc::check_tile(bvc_ctx* ctx, const bvc_tile* t, int64_t* n_entries)
 {
     if (!t || t->n_sites < 0 || !t->entry_off || (t->n_sites > 0 && !t->ref_base)) { set_err(ctx, "bad tile: NULL array or n_sites < 0"); return BVC_ERR_ARG; }
     if (t->entry_off[0] != 0) { set_err(ctx, "bad tile: entry_off[0] != 0"); return BVC_ERR_ARG; }
@@ -137,6 +87,8 @@ int check_tile(bvc_ctx* ctx, const bvc_tile* t, int64_t* n_entries)
     return BVC_OK;
 }
 
+namespace {
+
 // Device-visible alias of a pinned, 4-byte-aligned host array, or nullptr (pageable memory / BVC_NO_ZERO_COPY=1).
 const uint8_t* zero_copy_ptr(bvc_ctx* ctx, const uint8_t* host)
 {
@@ -147,7 +99,9 @@ const uint8_t* zero_copy_ptr(bvc_ctx* ctx, const uint8_t* host)
     return static_cast<const uint8_t*>(at.devicePointer);
 }
 
-int upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool resident)
+}  // namespace
+
+int bvc::upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool resident)
 {
     const size_t S = (size_t)t->n_sites;
     s.n_sites = t->n_sites; s.n_entries = R;
@@ -172,26 +126,13 @@ int upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool resident)
     return BVC_OK;
 }
 
-int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullptr, int* n_out = nullptr)
+void bvc::fill_args(const bvc_ctx* ctx, const Slot& s, SiteArgs& a, PipeArgs& p)
 {
-    if (s.n_sites == 0) return BVC_OK;
-    CK(cudaMemsetAsync(s.d_counter, 0, sizeof(unsigned int), s.stream));
-    bvc::SiteArgs a;
     a.ref_base = s.d_ref; a.entry_off = s.d_off; a.code = s.d_code; a.qual = s.d_qual; a.mapq = s.k_mapq ? s.k_mapq : s.d_mapq; a.rpr = s.k_rpr ? s.k_rpr : s.d_rpr;
     a.out = s.d_out; a.counter = s.d_counter; a.lut = ctx->d_lut; a.lgam = ctx->d_lgam;
     a.n_sites = s.n_sites; a.max_iter = ctx->prm.em_max_iter;
     a.min_af = ctx->prm.min_af; a.lrt_thr = ctx->prm.lrt_threshold; a.eps = ctx->prm.em_epsilon;
     a.site_list = nullptr; a.list_n = nullptr;
-    if (ctx->legacy_only) {
-        if (ev) { CK(cudaEventRecord(ev[0], s.stream)); kinds[0] = bvc::kKLegacy; }
-        CK(bvc::launch_site_call(a, ctx->n_sm, s.stream));
-        if (ev) CK(cudaEventRecord(ev[1], s.stream));
-        if (n_out) *n_out = 1;
-        ctx->launches += 1;
-        return BVC_OK;
-    }
-    CK(cudaMemsetAsync(s.d_ctr, 0, kCtrWords * sizeof(uint32_t), s.stream));
-    bvc::PipeArgs p;
     p.s = a;
     p.mean_entries = (int)(s.n_entries / (s.n_sites > 0 ? s.n_sites : 1));
     p.sum = s.d_sum; p.cls = s.d_cls; p.cls_cursor = s.d_ctr + 0;
@@ -204,6 +145,26 @@ int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullpt
     p.q_sorted = s.d_qs; p.q_long = s.d_ql; p.q_long_n = s.d_ctr + 6; p.q_long_head = s.d_ctr + 7;
     p.work = reinterpret_cast<unsigned long long*>(s.d_ctr + 8);
     p.bins = s.d_ctr + 16;
+}
+
+namespace {
+
+int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullptr, int* n_out = nullptr)
+{
+    if (s.n_sites == 0) return BVC_OK;
+    CK(cudaMemsetAsync(s.d_counter, 0, sizeof(unsigned int), s.stream));
+    bvc::SiteArgs a;
+    bvc::PipeArgs p;
+    bvc::fill_args(ctx, s, a, p);
+    if (ctx->legacy_only) {
+        if (ev) { CK(cudaEventRecord(ev[0], s.stream)); kinds[0] = bvc::kKLegacy; }
+        CK(bvc::launch_site_call(a, ctx->n_sm, s.stream));
+        if (ev) CK(cudaEventRecord(ev[1], s.stream));
+        if (n_out) *n_out = 1;
+        ctx->launches += 1;
+        return BVC_OK;
+    }
+    CK(cudaMemsetAsync(s.d_ctr, 0, kCtrWords * sizeof(uint32_t), s.stream));
     int nl = 0;
     CK(bvc::launch_pipeline(p, ctx->n_sm, s.stream, &nl, ev, kinds));
     if (n_out) *n_out = nl;
@@ -316,6 +277,7 @@ void bvc_destroy(bvc_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     for (int i = 0; i < 2; ++i) { if (ctx->slot[i].stream) cudaStreamSynchronize(ctx->slot[i].stream); free_slot(ctx->slot[i]); }
+    bvc::shard_free(ctx);
     cudaFree(ctx->d_lut); cudaFree(ctx->d_lgam); cudaFree(ctx->d_flush); cudaFree(ctx->d_sample_group);
     delete ctx;
 }

@@ -1,0 +1,86 @@
+// bvc_ctx.h -- the context behind the opaque `bvc_ctx` of include/bvc_gpu.h, shared by bvc_api.cu (tile path)
+// and bvc_shard_api.cu (sample-sharded path).  Private to the library.
+#pragma once
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/bvc_gpu.h"
+#include "bvc_kernels.h"
+#include "bvc_pipeline_args.h"
+
+namespace bvc {
+
+constexpr size_t kCtrWords = 16 + kNBins + 16;
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    uint8_t *d_ref = nullptr, *d_code = nullptr, *d_qual = nullptr, *d_mapq = nullptr, *d_rpr = nullptr;
+    uint32_t *d_off = nullptr, *d_sample = nullptr;
+    bvc_site_result* d_out = nullptr;
+    unsigned int* d_counter = nullptr;
+    int32_t* d_gdepth = nullptr;   // --group outputs [S][n_groups][4]
+    double* d_gaf = nullptr;
+    // staged-pipeline intermediates (bvc_pipeline.cuh)
+    SiteSum* d_sum = nullptr;
+    uint32_t* d_cls = nullptr;
+    Ladder* d_lad = nullptr;
+    FitRes* d_fit = nullptr;
+    uint8_t* d_state = nullptr;
+    uint32_t *d_qa = nullptr, *d_qb = nullptr, *d_qs = nullptr, *d_ql = nullptr, *d_vcf_list = nullptr, *d_legacy_list = nullptr;
+    uint32_t* d_ctr = nullptr;     // [kCtrWords]: cls_cursor, qa_n, qb_n, q_head, vcf_n, legacy_n, long_n, work[4] (u64 at word 8), bins at word 16
+    const uint8_t *k_mapq = nullptr, *k_rpr = nullptr;   // what the kernels read: d_mapq/d_rpr or zero-copy host pointers
+    uint64_t ticket = 0;       // 0 = idle
+    uint64_t last_ticket = 0;  // ticket of the tile whose outputs the slot's device buffers hold
+    int n_sites = 0;
+    int64_t n_entries = 0;
+};
+
+struct ShardState;                 // bvc_shard_api.cu
+
+}  // namespace bvc
+
+struct bvc_ctx {
+    int device = 0;
+    int n_sm = 0;
+    bvc_params prm;
+    std::vector<int32_t> sample_group;
+    bvc::Slot slot[2];
+    double* d_lut = nullptr;
+    double* d_lgam = nullptr;
+    int32_t* d_sample_group = nullptr;
+    void* d_flush = nullptr;
+    size_t flush_bytes = 0;
+    uint64_t next_ticket = 1;
+    int64_t launches = 0;
+    int64_t h2d_bytes = 0, d2h_bytes = 0;   // bytes moved by cudaMemcpyAsync on the host-buffer path
+    bool zero_copy = true;         // BVC_NO_ZERO_COPY=1 forces the full mapq/rpr copy (A/B checks)
+    bool legacy_only = false;      // BVC_LEGACY_KERNEL=1: the single warp-per-site kernel for every site (A/B checks)
+    std::string err;
+    bool resident = false;
+    bvc::ShardState* shard = nullptr;   // sample-sharded mode (bvc_shard_init / bvc_shard_init_group)
+};
+
+namespace bvc {
+
+void set_err(bvc_ctx* ctx, const char* m);     // ctx == NULL: the thread's create-time error
+int  check_tile(bvc_ctx* ctx, const bvc_tile* t, int64_t* n_entries);
+// H2D copies of a tile into the slot (code, qual, offsets, ref; mapq / rpr zero-copy when pinned) on the slot's stream
+int  upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool resident);
+// the argument blocks of the kernels over the slot's buffers
+void fill_args(const bvc_ctx* ctx, const Slot& s, SiteArgs& a, PipeArgs& p);
+void shard_free(bvc_ctx* ctx);                 // called by bvc_destroy
+
+}  // namespace bvc
+
+#define CK(call)                                                                               \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess) {                                                               \
+            char b_[512];                                                                      \
+            snprintf(b_, sizeof b_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            bvc::set_err(ctx, b_);                                                             \
+            return BVC_ERR_CUDA;                                                               \
+        }                                                                                      \
+    } while (0)

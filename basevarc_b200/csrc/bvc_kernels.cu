@@ -4,6 +4,7 @@
 #include "bvc_site_kernel.cuh"
 #include "bvc_pipeline.cuh"
 #include "bvc_groups.cuh"
+#include "bvc_shard.cuh"
 
 namespace bvc {
 
@@ -205,7 +206,7 @@ const char* kernel_kind_name(int kind)
     return (kind >= 0 && kind < kNumKernelKinds) ? names[kind] : "?";
 }
 
-cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, int* n_launches, cudaEvent_t* ev, int* kinds)
+cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, int* n_launches, cudaEvent_t* ev, int* kinds, int parts)
 {
     PipeArgs a = a0;
     const int S = a.s.n_sites;
@@ -228,12 +229,15 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     // optional per-launch timing: ev[i] is recorded BEFORE launch i, ev[launches] after the last one
     auto mark = [&](int kind) { if (ev) { cudaEventRecord(ev[launches], stream); kinds[launches] = kind; } ++launches; };
 
+    if (parts & kPartHist) {
     mark(kKHist);
     // lanes per site by mean pileup depth of the tile: a full warp from 256 entries per site (measured: C2, 393 entries, 1.11 ms vs 1.23 ms), half a warp below
     if (a.mean_entries >= 256)
         site_hist_kernel<32><<<capped((S + kHistWarps - 1) / kHistWarps, occ_hist), kHistWarps * 32, 0, stream>>>(a);
     else
         site_hist_kernel<16><<<capped((S + 2 * kHistWarps - 1) / (2 * kHistWarps), occ_hist16), kHistWarps * 32, 0, stream>>>(a);
+    }
+    if (parts & kPartCore) {
     mark(kKPrepare);
     site_prepare_kernel<<<site_blocks, 128, 0, stream>>>(a);
     // at most three EM stages: the full model, the (n-1)-subsets (n >= 3), the pairs of a reduced 4-candidate site
@@ -260,6 +264,8 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
         mark(kKLadder);
         ladder_kernel<<<site_blocks, 128, 0, stream>>>(a);
     }
+    }
+    if (parts & kPartVcf) {
     mark(kKVcf);
     vcf_stats_kernel<<<capped(S, occ_vcf), kVcfWarps * 32, 0, stream>>>(a);
     // qual-0 sites: the IEEE-faithful warp-per-site kernel over the legacy list
@@ -267,6 +273,7 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     leg.site_list = a.legacy_list; leg.list_n = a.legacy_n;
     mark(kKLegacy);
     site_call_kernel<<<(unsigned)(n_sm * occ_leg), kWarpsPerBlock * 32, 0, stream>>>(leg);
+    }
     if (ev) cudaEventRecord(ev[launches], stream);
     if (n_launches) *n_launches = launches;
     return cudaGetLastError();
@@ -283,6 +290,80 @@ cudaError_t launch_groups(const SiteArgs& s, const uint32_t* sample, const int32
     const unsigned grid = (unsigned)(n_sm * 8);
     group_depth_kernel<<<grid, kGroupWarps * 32, 0, stream>>>(g);
     group_lrt_kernel<<<grid, kGroupWarps * 32, 0, stream>>>(g);
+    return cudaGetLastError();
+}
+
+// ---- sample-sharded mode ---------------------------------------------------------------------------------
+static unsigned shard_grid(long long groups_wanted, int n_sm, int per_sm)
+{
+    long long g = (long long)n_sm * (per_sm < 1 ? 1 : per_sm);
+    if (g > groups_wanted) g = groups_wanted;
+    return (unsigned)(g < 1 ? 1 : g);
+}
+
+cudaError_t launch_shard_hist(const ShardArgs& a, int n_sm, cudaStream_t stream, int* n_launches)
+{
+    static int occ32 = 0, occ16 = 0;
+    if (!occ32) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ32, shard_hist_kernel<32>, kHistWarps * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ16, shard_hist_kernel<16>, kHistWarps * 32, 0);
+        if (occ32 < 1) occ32 = 1; if (occ16 < 1) occ16 = 1;
+    }
+    const long long n_pad = (long long)a.world * a.Sr;
+    if (a.p.mean_entries >= 256)
+        shard_hist_kernel<32><<<shard_grid((n_pad + kHistWarps - 1) / kHistWarps, n_sm, occ32), kHistWarps * 32, 0, stream>>>(a);
+    else
+        shard_hist_kernel<16><<<shard_grid((n_pad + 2 * kHistWarps - 1) / (2 * kHistWarps), n_sm, occ16), kHistWarps * 32, 0, stream>>>(a);
+    if (n_launches) *n_launches = 1;
+    return cudaGetLastError();
+}
+
+// owner: merged histograms -> SiteSum + classes, then K2 / EM stages / K4 on the owned sites, then the mask bytes
+cudaError_t launch_shard_merge_and_fit(const ShardArgs& a, int n_sm, cudaStream_t stream, int* n_launches)
+{
+    static int occ = 0;
+    if (!occ) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, shard_merge_kernel<32>, kHistWarps * 32, 0); if (occ < 1) occ = 1; }
+    int n = 0;
+    if (a.n_own > 0) {
+        shard_merge_kernel<32><<<shard_grid((a.n_own + kHistWarps - 1) / kHistWarps, n_sm, occ), kHistWarps * 32, 0, stream>>>(a);
+        cudaError_t e = launch_pipeline(a.p, n_sm, stream, &n, nullptr, nullptr, kPartCore);
+        if (e != cudaSuccess) return e;
+        n += 1;
+    }
+    shard_posmask_kernel<<<(unsigned)((a.Sr + 255) / 256), 256, 0, stream>>>(a);
+    if (n_launches) *n_launches = n + 1;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_shard_poslist(const ShardArgs& a, cudaStream_t stream, int* n_launches)
+{
+    shard_poslist_kernel<<<1, 1024, 0, stream>>>(a);
+    if (n_launches) *n_launches = 1;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_shard_vcf_hist(const ShardArgs& a, int n_sm, uint32_t n_pos, cudaStream_t stream, int* n_launches)
+{
+    if (n_launches) *n_launches = 0;
+    if (!n_pos) return cudaSuccess;
+    shard_vcf_hist_kernel<<<shard_grid((n_pos + kVcfWarps - 1) / kVcfWarps, n_sm, 4), kVcfWarps * 32, 0, stream>>>(a);
+    if (n_launches) *n_launches = 1;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_shard_vcf_finish(const ShardArgs& a, int n_sm, uint32_t n_pos, cudaStream_t stream, int* n_launches)
+{
+    if (n_launches) *n_launches = 0;
+    if (!n_pos) return cudaSuccess;
+    shard_vcf_finish_kernel<<<shard_grid((n_pos + kVcfWarps - 1) / kVcfWarps, n_sm, 4), kVcfWarps * 32, 0, stream>>>(a);
+    if (n_launches) *n_launches = 1;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sum_u32(uint32_t* dst, const uint32_t* src, size_t n, int n_sm, cudaStream_t stream)
+{
+    if (!n) return cudaSuccess;
+    sum_u32_kernel<<<(unsigned)(n_sm * 8), 256, 0, stream>>>(dst, src, n);
     return cudaGetLastError();
 }
 

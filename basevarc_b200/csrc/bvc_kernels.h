@@ -38,8 +38,18 @@ cudaError_t launch_site_call(const SiteArgs& a, int n_sm, cudaStream_t stream);
 enum KernelKind { kKHist = 0, kKPrepare, kKSort, kKEm, kKEmLong, kKLoglik, kKLadder, kKVcf, kKLegacy, kNumKernelKinds };
 constexpr int kMaxPipeLaunches = 32;
 const char* kernel_kind_name(int kind);
+// parts: kPartHist = K1, kPartCore = K2 + the EM stages + K4, kPartVcf = K5 + the qual-0 legacy kernel.
+enum PipeParts { kPartHist = 1, kPartCore = 2, kPartVcf = 4, kPartAll = 7 };
 cudaError_t launch_pipeline(const PipeArgs& a, int n_sm, cudaStream_t stream, int* n_launches,
-                            cudaEvent_t* ev = nullptr, int* kinds = nullptr);
+                            cudaEvent_t* ev = nullptr, int* kinds = nullptr, int parts = kPartAll);
+// sample-sharded mode (bvc_shard.cuh): one launcher per phase; each returns the number of kernels it launched
+struct ShardArgs;
+cudaError_t launch_shard_hist(const ShardArgs& a, int n_sm, cudaStream_t stream, int* n_launches);
+cudaError_t launch_shard_merge_and_fit(const ShardArgs& a, int n_sm, cudaStream_t stream, int* n_launches);
+cudaError_t launch_shard_poslist(const ShardArgs& a, cudaStream_t stream, int* n_launches);
+cudaError_t launch_shard_vcf_hist(const ShardArgs& a, int n_sm, uint32_t n_pos, cudaStream_t stream, int* n_launches);
+cudaError_t launch_shard_vcf_finish(const ShardArgs& a, int n_sm, uint32_t n_pos, cudaStream_t stream, int* n_launches);
+cudaError_t launch_sum_u32(uint32_t* dst, const uint32_t* src, size_t n, int n_sm, cudaStream_t stream);
 // --group path (bvc_groups.cuh): per-group depths of every site + the group-level LRT of the LRT-positive sites
 cudaError_t launch_groups(const SiteArgs& s, const uint32_t* sample, const int32_t* sample_group, int n_groups,
                           int32_t* gdepth, double* gaf, int n_sm, cudaStream_t stream);

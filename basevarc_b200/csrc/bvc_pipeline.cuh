@@ -89,6 +89,149 @@ template <int G> __device__ __forceinline__ unsigned group_min(unsigned v, int g
     return r;
 }
 
+// ---- K1's two halves, shared with the sample-sharded kernels of bvc_shard.cuh --------------------------------
+// hist_stream: 4 entries per lane per 32-bit load, both arrays in flight.  One shared-memory increment per entry
+// does all the counting: the bin carries base, qual and strand.  Bytes outside [b0, b1) in the first / last word are
+// turned into code 0x14 (indel, base 4), which nothing counts.  hist: non-indel entries, base << 8 | qual << 1 | strand;
+// ind: indel entries (stale base < 4), strand << 2 | base.
+template <int G>
+__device__ __forceinline__ void hist_stream(const uint32_t* __restrict__ code4, const uint32_t* __restrict__ qual4,
+                                            uint32_t b0, uint32_t b1, int g, uint32_t* hist, uint32_t* ind,
+                                            uint32_t& qmin, uint32_t& qmax, bool& any_ind)
+{
+    const uint32_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;
+    const uint32_t trips = (__reduce_max_sync(0xffffffffu, w1 - w0) + G - 1) / G;
+    for (uint32_t t = 0; t < trips; ++t) {
+        const uint32_t wi = w0 + t * G + g;
+        if (wi < w1) {
+            uint32_t cw = __ldg(code4 + wi);
+            const uint32_t qw = __ldg(qual4 + wi) & 0x7f7f7f7fu;
+            if (wi == w0 || wi + 1 == w1) {
+                const uint32_t e0 = wi * 4;
+                const uint32_t lo = b0 > e0 ? b0 - e0 : 0u, hi = b1 < e0 + 4 ? b1 - e0 : 4u;     // valid bytes [lo, hi)
+                const uint32_t vm = (hi >= 4 ? 0xffffffffu : ((1u << (8 * hi)) - 1u)) & ~((1u << (8 * lo)) - 1u);
+                cw = (cw & vm) | (0x14141414u & ~vm);
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t c = cw >> (8 * k), q = (qw >> (8 * k)) & 0x7fu;
+                const bool ok = !(c & 0x14u);
+                qmin = min(qmin, ok ? q : 127u); qmax = max(qmax, ok ? q : 0u);
+                red_inc_if(&hist[((c & 3u) << 8) | (q << 1) | ((c >> 3) & 1u)], ok);
+            }
+            if (cw & 0x10101010u) {                 // rare: indel entries keep only (stale base, strand)
+                any_ind = true;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t c = cw >> (8 * k);
+                    if ((c & 0x14u) == 0x10u) atomicAdd(&ind[((c >> 1) & 4u) | (c & 3u)], 1u);
+                }
+            }
+        }
+    }
+    __syncwarp();
+}
+
+// hist_emit: from the group's shared-memory histogram to the 64-byte SiteSum + the site's classes in the pool
+// (major base first); clears the bins it visited.  qmin / qmax are the lane-local extremes of the quals present.
+template <int G>
+__device__ __forceinline__ void hist_emit(const PipeArgs& a, int site, bool live, int ref, int n_entries,
+                                          uint32_t qmin, uint32_t qmax, bool any_ind, uint32_t* hist, uint32_t* ind,
+                                          int g, int gi)
+{
+    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (gi * G));
+    const unsigned lt = (1u << g) - 1u;
+    // qual range present in this site, scanned G quals at a time per base
+    qmax = group_max<G>(qmax, gi);
+    qmin = group_min<G>(qmin, gi);
+    const int q_lo = (int)min(qmin, qmax);
+    const int my_steps = live && n_entries > 0 ? ((int)qmax - q_lo) / G + 1 : 0;
+    const int nsteps = __reduce_max_sync(0xffffffffu, my_steps);
+    any_ind = __any_sync(0xffffffffu, any_ind);
+
+    // ---- pass 1 over the bins: merged counts, per-base depth / forward depth / class count -------------------
+    int dsum[4], fsum[4], ncb[4];
+    unsigned lowq = 0;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        dsum[b] = 0; fsum[b] = 0; ncb[b] = 0;
+        for (int st = 0; st < nsteps; ++st) {
+            const int q = q_lo + st * G + g;
+            uint2 h = make_uint2(0u, 0u);
+            if (st < my_steps && q < kNQ) h = *reinterpret_cast<const uint2*>(&hist[(b << 8) | (q << 1)]);
+            dsum[b] += (int)(h.x + h.y); fsum[b] += (int)h.y;
+            const unsigned m = (__ballot_sync(0xffffffffu, (h.x + h.y) != 0) & gmask) >> (gi * G);
+            ncb[b] += __popc(m);
+            if (q_lo <= 1 && st == 0) lowq |= (m << q_lo) & 3u;     // bit 0: a qual-0 class, bit 1: a qual-1 class
+        }
+    }
+    int depth[4], fwd[4], n_reads = 0;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {               // src/BaseVarC.cpp:550-559
+        depth[b] = group_add<G>(dsum[b], gi);
+        fwd[b] = group_add<G>(fsum[b], gi);
+        n_reads += depth[b];
+    }
+    int icnt = 0;                               // g = strand << 2 | base of the indel entries
+    if (any_ind) { icnt = g < 8 ? (int)ind[g] : 0; __syncwarp(); if (g < 8) ind[g] = 0; }
+    // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
+    int best = -1, bestd = -1, second = -1, secondd = -1;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        if (depth[b] > bestd) { second = best; secondd = bestd; best = b; bestd = depth[b]; }
+        else if (depth[b] > secondd) { second = b; secondd = depth[b]; }
+    }
+    const int alt = (best != ref) ? best : second;
+    // src/BaseVarC.cpp:587-602: 2x2 table over ALL entries (indel entries carry stale base/strand)
+    const int fr_ = ref == 0 ? fwd[0] : ref == 1 ? fwd[1] : ref == 2 ? fwd[2] : fwd[3];
+    const int dr_ = ref == 0 ? depth[0] : ref == 1 ? depth[1] : ref == 2 ? depth[2] : depth[3];
+    const int fa_ = alt == 0 ? fwd[0] : alt == 1 ? fwd[1] : alt == 2 ? fwd[2] : fwd[3];
+    const int da_ = alt == 0 ? depth[0] : alt == 1 ? depth[1] : alt == 2 ? depth[2] : depth[3];
+    const int gl = gi * G;                      // first lane of my group
+    const int c0 = fr_ + __shfl_sync(0xffffffffu, icnt, gl + (ref | 4));
+    const int c1 = (dr_ - fr_) + __shfl_sync(0xffffffffu, icnt, gl + ref);
+    const int c2 = fa_ + __shfl_sync(0xffffffffu, icnt, gl + (alt | 4));
+    const int c3 = (da_ - fa_) + __shfl_sync(0xffffffffu, icnt, gl + alt);
+
+    // ---- pass 2: write the non-empty classes to the pool (and clear the bins).  Order: the MAJOR base (top
+    // depth, ties -> lowest code) first, then the other bases ascending; K3 runs the major segment select-free.
+    const int ncls = ncb[0] + ncb[1] + ncb[2] + ncb[3];
+    const int n_major = best == 0 ? ncb[0] : best == 1 ? ncb[1] : best == 2 ? ncb[2] : ncb[3];
+    uint32_t off = 0;
+    if (g == 0 && ncls) off = atomicAdd(a.cls_cursor, (uint32_t)ncls);
+    off = __shfl_sync(0xffffffffu, off, gl);
+    uint32_t run = off + (uint32_t)n_major;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        uint32_t pos;
+        if (b == best) pos = off; else { pos = run; run += (uint32_t)ncb[b]; }
+        for (int st = 0; st < nsteps; ++st) {
+            const int q = q_lo + st * G + g;
+            uint32_t x = 0;
+            if (st < my_steps && q < kNQ) {
+                uint2* hp = reinterpret_cast<uint2*>(&hist[(b << 8) | (q << 1)]);
+                const uint2 h = *hp;
+                x = h.x + h.y;
+                if (x) *hp = make_uint2(0u, 0u);
+            }
+            const unsigned m = (__ballot_sync(0xffffffffu, x != 0) & gmask) >> (gi * G);
+            if (x) a.cls[pos + __popc(m & lt)] = (x << 9) | (uint32_t)((b << 7) | q);
+            pos += __popc(m);
+        }
+    }
+    // ---- 64-byte summary: lanes 0..15 of the group store one word each ---------------------------------------
+    int word = 0;
+    if (g == 0) word = depth[0]; else if (g == 1) word = depth[1]; else if (g == 2) word = depth[2]; else if (g == 3) word = depth[3];
+    else if (g == 4) word = fwd[0]; else if (g == 5) word = fwd[1]; else if (g == 6) word = fwd[2]; else if (g == 7) word = fwd[3];
+    else if (g == 8) word = c0; else if (g == 9) word = c1; else if (g == 10) word = c2; else if (g == 11) word = c3;
+    else if (g == 12) word = (int)off;
+    else if (g == 13) word = ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0);
+    else if (g == 14) word = n_entries;
+    else if (g == 15) word = n_major | (best << 16);
+    if (live && g < 16) reinterpret_cast<int*>(a.sum + site)[g] = word;
+    __syncwarp();
+}
+
 // G lanes per site (32 / G sites per warp): G = 32 for deep pileups, 16 for a few hundred entries per site.
 template <int G>
 __global__ void __launch_bounds__(kHistWarps * 32)
@@ -99,15 +242,13 @@ site_hist_kernel(PipeArgs a)
     __shared__ uint32_t ind_s[kHistWarps * kGroups][8];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int g = lane & (G - 1), gi = lane / G;
-    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (gi * G));
-    uint32_t* hist = hist_s[wid * kGroups + gi];   // non-indel entries: base << 8 | qual << 1 | strand
-    uint32_t* ind = ind_s[wid * kGroups + gi];     // indel entries (stale base < 4): strand << 2 | base
+    uint32_t* hist = hist_s[wid * kGroups + gi];
+    uint32_t* ind = ind_s[wid * kGroups + gi];
     for (int i = g; i < kHistBins; i += G) hist[i] = 0;
     if (g < 8) ind[g] = 0;
     __syncwarp();
     const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
     const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
-    const unsigned lt = (1u << g) - 1u;
 
     const int n_groups = gridDim.x * kHistWarps * kGroups;
     const int first = (blockIdx.x * kHistWarps + wid) * kGroups + gi;
@@ -118,131 +259,10 @@ site_hist_kernel(PipeArgs a)
         const bool live = site < a.s.n_sites;
         const uint32_t b0 = live ? a.s.entry_off[site] : 0u, b1 = live ? a.s.entry_off[site + 1] : 0u;
         const int ref = live ? (a.s.ref_base[site] & 3) : 0;
-        // ---- stream: 4 entries per lane per 32-bit load, both arrays in flight.  One shared-memory increment per
-        // entry does all the counting: the bin carries base, qual and strand.  Bytes outside [b0, b1) in the first /
-        // last word are turned into code 0x14 (indel, base 4), which nothing counts.
-        const uint32_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;
-        const uint32_t trips = (__reduce_max_sync(0xffffffffu, w1 - w0) + G - 1) / G;
         uint32_t qmax = 0, qmin = 127;
         bool any_ind = false;
-        for (uint32_t t = 0; t < trips; ++t) {
-            const uint32_t wi = w0 + t * G + g;
-            if (wi < w1) {
-                uint32_t cw = __ldg(code4 + wi);
-                const uint32_t qw = __ldg(qual4 + wi) & 0x7f7f7f7fu;
-                if (wi == w0 || wi + 1 == w1) {
-                    const uint32_t e0 = wi * 4;
-                    const uint32_t lo = b0 > e0 ? b0 - e0 : 0u, hi = b1 < e0 + 4 ? b1 - e0 : 4u;     // valid bytes [lo, hi)
-                    const uint32_t vm = (hi >= 4 ? 0xffffffffu : ((1u << (8 * hi)) - 1u)) & ~((1u << (8 * lo)) - 1u);
-                    cw = (cw & vm) | (0x14141414u & ~vm);
-                }
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint32_t c = cw >> (8 * k), q = (qw >> (8 * k)) & 0x7fu;
-                    const bool ok = !(c & 0x14u);
-                    qmin = min(qmin, ok ? q : 127u); qmax = max(qmax, ok ? q : 0u);
-                    red_inc_if(&hist[((c & 3u) << 8) | (q << 1) | ((c >> 3) & 1u)], ok);
-                }
-                if (cw & 0x10101010u) {                 // rare: indel entries keep only (stale base, strand)
-                    any_ind = true;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint32_t c = cw >> (8 * k);
-                        if ((c & 0x14u) == 0x10u) atomicAdd(&ind[((c >> 1) & 4u) | (c & 3u)], 1u);
-                    }
-                }
-            }
-        }
-        __syncwarp();
-        // qual range present in this site, scanned G quals at a time per base
-        qmax = group_max<G>(qmax, gi);
-        qmin = group_min<G>(qmin, gi);
-        const int q_lo = (int)min(qmin, qmax);
-        const int my_steps = live && b1 > b0 ? ((int)qmax - q_lo) / G + 1 : 0;
-        const int nsteps = __reduce_max_sync(0xffffffffu, my_steps);
-        any_ind = __any_sync(0xffffffffu, any_ind);
-
-        // ---- pass 1 over the bins: merged counts, per-base depth / forward depth / class count -------------------
-        int dsum[4], fsum[4], ncb[4];
-        unsigned lowq = 0;
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            dsum[b] = 0; fsum[b] = 0; ncb[b] = 0;
-            for (int st = 0; st < nsteps; ++st) {
-                const int q = q_lo + st * G + g;
-                uint2 h = make_uint2(0u, 0u);
-                if (st < my_steps && q < kNQ) h = *reinterpret_cast<const uint2*>(&hist[(b << 8) | (q << 1)]);
-                dsum[b] += (int)(h.x + h.y); fsum[b] += (int)h.y;
-                const unsigned m = (__ballot_sync(0xffffffffu, (h.x + h.y) != 0) & gmask) >> (gi * G);
-                ncb[b] += __popc(m);
-                if (q_lo <= 1 && st == 0) lowq |= (m << q_lo) & 3u;     // bit 0: a qual-0 class, bit 1: a qual-1 class
-            }
-        }
-        int depth[4], fwd[4], n_reads = 0;
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {               // src/BaseVarC.cpp:550-559
-            depth[b] = group_add<G>(dsum[b], gi);
-            fwd[b] = group_add<G>(fsum[b], gi);
-            n_reads += depth[b];
-        }
-        int icnt = 0;                               // g = strand << 2 | base of the indel entries
-        if (any_ind) { icnt = g < 8 ? (int)ind[g] : 0; __syncwarp(); if (g < 8) ind[g] = 0; }
-        // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
-        int best = -1, bestd = -1, second = -1, secondd = -1;
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            if (depth[b] > bestd) { second = best; secondd = bestd; best = b; bestd = depth[b]; }
-            else if (depth[b] > secondd) { second = b; secondd = depth[b]; }
-        }
-        const int alt = (best != ref) ? best : second;
-        // src/BaseVarC.cpp:587-602: 2x2 table over ALL entries (indel entries carry stale base/strand)
-        const int fr_ = ref == 0 ? fwd[0] : ref == 1 ? fwd[1] : ref == 2 ? fwd[2] : fwd[3];
-        const int dr_ = ref == 0 ? depth[0] : ref == 1 ? depth[1] : ref == 2 ? depth[2] : depth[3];
-        const int fa_ = alt == 0 ? fwd[0] : alt == 1 ? fwd[1] : alt == 2 ? fwd[2] : fwd[3];
-        const int da_ = alt == 0 ? depth[0] : alt == 1 ? depth[1] : alt == 2 ? depth[2] : depth[3];
-        const int gl = gi * G;                      // first lane of my group
-        const int c0 = fr_ + __shfl_sync(0xffffffffu, icnt, gl + (ref | 4));
-        const int c1 = (dr_ - fr_) + __shfl_sync(0xffffffffu, icnt, gl + ref);
-        const int c2 = fa_ + __shfl_sync(0xffffffffu, icnt, gl + (alt | 4));
-        const int c3 = (da_ - fa_) + __shfl_sync(0xffffffffu, icnt, gl + alt);
-
-        // ---- pass 2: write the non-empty classes to the pool (and clear the bins).  Order: the MAJOR base (top
-        // depth, ties -> lowest code) first, then the other bases ascending; K3 runs the major segment select-free.
-        const int ncls = ncb[0] + ncb[1] + ncb[2] + ncb[3];
-        const int n_major = best == 0 ? ncb[0] : best == 1 ? ncb[1] : best == 2 ? ncb[2] : ncb[3];
-        uint32_t off = 0;
-        if (g == 0 && ncls) off = atomicAdd(a.cls_cursor, (uint32_t)ncls);
-        off = __shfl_sync(0xffffffffu, off, gl);
-        uint32_t run = off + (uint32_t)n_major;
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            uint32_t pos;
-            if (b == best) pos = off; else { pos = run; run += (uint32_t)ncb[b]; }
-            for (int st = 0; st < nsteps; ++st) {
-                const int q = q_lo + st * G + g;
-                uint32_t x = 0;
-                if (st < my_steps && q < kNQ) {
-                    uint2* hp = reinterpret_cast<uint2*>(&hist[(b << 8) | (q << 1)]);
-                    const uint2 h = *hp;
-                    x = h.x + h.y;
-                    if (x) *hp = make_uint2(0u, 0u);
-                }
-                const unsigned m = (__ballot_sync(0xffffffffu, x != 0) & gmask) >> (gi * G);
-                if (x) a.cls[pos + __popc(m & lt)] = (x << 9) | (uint32_t)((b << 7) | q);
-                pos += __popc(m);
-            }
-        }
-        // ---- 64-byte summary: lanes 0..15 of the group store one word each ---------------------------------------
-        int word = 0;
-        if (g == 0) word = depth[0]; else if (g == 1) word = depth[1]; else if (g == 2) word = depth[2]; else if (g == 3) word = depth[3];
-        else if (g == 4) word = fwd[0]; else if (g == 5) word = fwd[1]; else if (g == 6) word = fwd[2]; else if (g == 7) word = fwd[3];
-        else if (g == 8) word = c0; else if (g == 9) word = c1; else if (g == 10) word = c2; else if (g == 11) word = c3;
-        else if (g == 12) word = (int)off;
-        else if (g == 13) word = ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0);
-        else if (g == 14) word = (int)(b1 - b0);
-        else if (g == 15) word = n_major | (best << 16);
-        if (live && g < 16) reinterpret_cast<int*>(a.sum + site)[g] = word;
-        __syncwarp();
+        hist_stream<G>(code4, qual4, b0, b1, g, hist, ind, qmin, qmax, any_ind);
+        hist_emit<G>(a, site, live, ref, (int)(b1 - b0), qmin, qmax, any_ind, hist, ind, g, gi);
     }
 }
 

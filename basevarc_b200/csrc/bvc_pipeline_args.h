@@ -74,4 +74,24 @@ struct PipeArgs {
     uint32_t* legacy_n;
 };
 
+// ---- sample-sharded mode (bvc_shard.cuh) ---------------------------------------------------------------
+constexpr int kShardHdr = 16;              // words before the bins: ind[8], n_entries, 7 spare (64-byte header)
+constexpr int kVcfHistWords = 6 * 256;
+
+struct ShardArgs {
+    PipeArgs p;                 // p.s: the LOCAL tile (entries of this rank's samples); intermediates of the owned sites
+    uint32_t* dense;            // [world * Sr][B]
+    int B, qlo, qhi;
+    int rank, world, Sr;        // Sr = ceil(S / world) sites per rank
+    int n_tile_sites;           // S
+    int n_own;                  // owned sites: [rank * Sr, rank * Sr + n_own)
+    const uint8_t* tile_ref;    // [S] ref_base of the whole tile (p.s.ref_base points at the owned slice)
+    const uint32_t* tile_off;   // [S + 1] local CSR offsets of the whole tile
+    uint32_t* err;              // bit 0: a qual outside [qlo, qhi]
+    uint8_t*  mask_all;         // [world * Sr]
+    uint32_t* pos_list;         // ascending tile-site indices of the LRT-positive sites
+    uint32_t* pos_n;
+    uint32_t* hv;               // [P][kVcfHistWords]
+};
+
 }  // namespace bvc

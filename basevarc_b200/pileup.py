@@ -65,6 +65,24 @@ class PileupTile:
             indel_text={k - e0: v for k, v in self.indel_text.items() if e0 <= k < e1},
         )
 
+    def shard_samples(self, world):
+        """Per-rank local tiles of sample sharding: rank r keeps, for EVERY site, the entries of the samples
+        [r*N/W, (r+1)*N/W) -- what a rank reads from its own range of batch files."""
+        bounds = [(r * self.n_samples) // world for r in range(world + 1)]
+        site_of = np.repeat(np.arange(self.n_sites, dtype=np.int64), np.diff(self.entry_off.astype(np.int64)))
+        tiles = []
+        for r in range(world):
+            keep = (self.sample >= bounds[r]) & (self.sample < bounds[r + 1])
+            off = np.zeros(self.n_sites + 1, np.int64)
+            np.cumsum(np.bincount(site_of[keep], minlength=self.n_sites), out=off[1:])
+            idx = np.nonzero(keep)[0]
+            tiles.append(PileupTile(
+                n_samples=self.n_samples, ref_base=self.ref_base, entry_off=off.astype(np.uint32),
+                code=np.ascontiguousarray(self.code[idx]), qual=np.ascontiguousarray(self.qual[idx]),
+                mapq=np.ascontiguousarray(self.mapq[idx]), rpr=np.ascontiguousarray(self.rpr[idx]),
+                sample=np.ascontiguousarray(self.sample[idx]), pos=self.pos))
+        return tiles
+
     def nbytes(self):
         return sum(getattr(self, k).nbytes for k in ("ref_base", "entry_off", "code", "qual", "mapq", "rpr"))
 

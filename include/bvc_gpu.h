@@ -151,6 +151,37 @@ int64_t bvc_kernel_launch_count(const bvc_ctx* ctx);   /* kernels of ours launch
  * in pinned host memory are NOT copied: the kernels read them in place for LRT-positive sites only. */
 void bvc_transfer_bytes(const bvc_ctx* ctx, int64_t* h2d, int64_t* d2h);
 
+/* ---- Sample-sharded mode (cohorts of >= 100k samples) ------------------------------------------
+ * The reference merges the sample batches of a site on one host thread: the loop over the batch files
+ * (src/BaseVarC.cpp:405-441) appends every batch's tokens to the site's one AlleleInfoVector before bt_f runs.
+ * Here rank r of W (one rank = one context = one GPU) is given, for EVERY site of a tile, only the entries of its
+ * own sample range (its range of batch files).  Per tile the ranks exchange integer sufficient statistics once:
+ * reduce-scatter of the per-site (base, qual, strand) histograms, all-gather of one byte per site, all-reduce of
+ * the rank-sum histograms of the LRT-positive sites (NCCL over NVLink; the library dlopens libnccl.so.2).
+ * Rank r returns the records of the site slice [r*ceil(S/W), ...) of the tile.  bvc_create must have been called
+ * with n_samples = the size of the WHOLE cohort (min_af and the lgamma table depend on it) and n_groups = 0.
+ * Every collective call below must be made by all W ranks with tiles of the same n_sites / ref_base.
+ * Not served in this mode: qual 0 (qual_lo >= 1; an entry whose qual is outside [qual_lo, qual_hi] makes the call
+ * fail with BVC_ERR_ARG on every rank that holds one, after all collectives have completed) and --group. */
+#define BVC_SHARD_ID_BYTES 128      /* sizeof(ncclUniqueId) */
+#define BVC_SHARD_N_PHASES 9
+int  bvc_shard_unique_id(void* id128);                     /* rank 0: ncclGetUniqueId; the caller broadcasts the bytes */
+int  bvc_shard_init(bvc_ctx* ctx, int rank, int world, const void* id128, int qual_lo, int qual_hi);   /* collective */
+/* host buffers in, the owned slice of records out (synchronous; collective) */
+int  bvc_shard_call(bvc_ctx* ctx, const bvc_tile* local_tile, bvc_site_result* out, int32_t* first_site, int32_t* n_out);
+/* device-resident variant for timing: upload once, run many times (collective) */
+int  bvc_shard_upload(bvc_ctx* ctx, const bvc_tile* local_tile);
+int  bvc_shard_run(bvc_ctx* ctx, bvc_site_result* out, int32_t* first_site, int32_t* n_out);
+/* In-process exchange WITHOUT NCCL: W contexts of one process on one device, ctxs[r] = rank r.  Same kernels and
+ * phases; the sums are plain kernels.  This is how the sharded path is parity-tested on a single GPU. */
+int  bvc_shard_init_group(bvc_ctx** ctxs, int world, int qual_lo, int qual_hi);
+int  bvc_shard_call_group(bvc_ctx** ctxs, int world, const bvc_tile* const* local_tiles, bvc_site_result* const* outs,
+                          int32_t* first_site /* [world] */, int32_t* n_out /* [world] */);
+/* Device time of each phase of the last call in ms [BVC_SHARD_N_PHASES] (bvc_shard_phase_name(i) names them), the
+ * cumulative payload bytes this rank handed to the collectives, and the number of LRT-positive sites of the tile. */
+int  bvc_shard_stats(const bvc_ctx* ctx, float* phase_ms, int64_t* exchange_bytes, int32_t* n_positive);
+const char* bvc_shard_phase_name(int i);
+
 /* FP64 pipe microbenchmark (dependent-free DFMA chains on all SMs): returns TFLOP/s (2 flop/FMA). */
 int  bvc_measure_fp64_peak(int device, double* tflops);
 
