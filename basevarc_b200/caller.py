@@ -234,6 +234,7 @@ class ShardedCaller(BaseTypeCaller):
         if out is None:
             out = np.zeros((tile.n_sites + self.world - 1) // self.world, SITE_RESULT_DTYPE)
         ct = tile.as_ctypes(with_sample=False)
+        self._shard_sites = tile.n_sites
         first, n = C.c_int32(0), C.c_int32(0)
         self._check(self.lib.bvc_shard_call(self.ctx, C.byref(ct), out.ctypes.data, C.byref(first), C.byref(n)), "bvc_shard_call")
         return first.value, out[:n.value]

@@ -132,8 +132,12 @@ def _site_allele_model(rng, S, model):
 
 
 def synth_tile(n_samples, n_sites, depth, model="lowpass", seed=1, indel_frac=0.005,
-               first_pos=1, chunk_cells=1 << 25):
-    """Deterministic synthetic pileup (numpy default_rng(seed)), spec in SURVEY.md section 8(d)."""
+               first_pos=1, chunk_cells=1 << 25, shard=None):
+    """Deterministic synthetic pileup (numpy default_rng(seed)), spec in SURVEY.md section 8(d).
+
+    shard = (rank, world): only the entries of the samples [rank*N/world, (rank+1)*N/world) -- one rank's local tile
+    of the sample-sharded mode.  The site model (ref base, allele frequencies, coverage) comes from `seed` alone, so
+    every rank sees the same sites; the reads come from a per-rank stream."""
     rng = np.random.default_rng(seed)
     S, N = int(n_sites), int(n_samples)
     ref, af = _site_allele_model(rng, S, model)
@@ -141,12 +145,18 @@ def synth_tile(n_samples, n_sites, depth, model="lowpass", seed=1, indel_frac=0.
     site_cov = np.full(S, p_cov)
     if model == "highpoly":
         site_cov = site_cov * rng.uniform(0.1, 1.0, S)
+    n_total, sample0 = N, 0
+    if shard is not None:
+        r, w = shard
+        sample0 = (r * N) // w
+        N = ((r + 1) * N) // w - sample0
+        rng = np.random.default_rng([int(seed), 7919 + int(r), int(w)])
     cum_af = np.cumsum(af, axis=1)
     is_var = af.max(1) < 1.0
     perr_lut = np.power(10.0, -np.arange(256) / 10.0).astype(np.float32)
     counts = np.empty(S, np.int64)
     parts = []
-    rows = max(1, chunk_cells // N)
+    rows = max(1, chunk_cells // max(N, 1))
     for s0 in range(0, S, rows):
         s1 = min(S, s0 + rows)
         cov = rng.random((s1 - s0, N), dtype=np.float32) < site_cov[s0:s1, None].astype(np.float32)
@@ -169,7 +179,7 @@ def synth_tile(n_samples, n_sites, depth, model="lowpass", seed=1, indel_frac=0.
         nf = np.nonzero(flip)[0]
         obs[nf] = (true_b[nf] + rng.integers(1, 4, nf.size, dtype=np.uint8)) % 4
         indel = (rng.random(R, dtype=np.float32) < indel_frac).astype(np.uint8)
-        parts.append((obs, strand, indel, qual, mapq, rpr, samp.astype(np.uint32)))
+        parts.append((obs, strand, indel, qual, mapq, rpr, (samp + sample0).astype(np.uint32)))
     cat = lambda k: np.concatenate([p[k] for p in parts]) if parts else np.zeros(0, np.uint8)
     obs, strand, indel, qual, mapq, rpr, samp = (cat(k) for k in range(7))
     if indel.size:
@@ -183,7 +193,7 @@ def synth_tile(n_samples, n_sites, depth, model="lowpass", seed=1, indel_frac=0.
     np.cumsum(counts, out=entry_off[1:])
     assert entry_off[-1] < 2 ** 32, "tile too large for uint32 CSR offsets"
     return PileupTile(
-        n_samples=N, ref_base=ref, entry_off=entry_off.astype(np.uint32),
+        n_samples=n_total, ref_base=ref, entry_off=entry_off.astype(np.uint32),
         code=make_code(obs, strand, indel), qual=qual, mapq=mapq, rpr=rpr, sample=samp.astype(np.uint32),
         pos=(np.arange(S, dtype=np.int32) + np.int32(first_pos)),
     )

@@ -31,6 +31,7 @@ METRIC = "site*samples/sec for basetype EM+LRT"
 #  the convergence test costs nothing per class: see delta_decision in bvc_pipeline.cuh)
 FLOP_PER_CLASS_PASS = 17
 UNIT = "site*samples/s"
+B_CONFIG_SAMPLES = {"C2": 1000, "C3": 10000, "C4": 100000, "C5": 2000}
 
 
 def _peaks():
@@ -185,7 +186,8 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    per_thread = args.ref_sites_per_thread
+    # the sample is sized in site*samples: --ref-sites-per-thread is quoted for 1,000 samples (C2)
+    per_thread = max(1, args.ref_sites_per_thread * 1000 // B_CONFIG_SAMPLES[args.workload])
     cfg, tile = _workload(args.workload, per_thread * cores, 0)
     value, S, dt, kind = cpu_reference_baseline(tile, per_thread, cores, steps=args.steps, warmup=args.warmup)
     what = ("unmodified reference binary `BaseVarC basetype --rerun -t %d` (compute phase: inflate, tokenise, bt_f, format, merge)" % cores
@@ -200,6 +202,145 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
+def run_sharded(args):
+    """--workload C4: the SAMPLE-SHARDED path.  Every rank holds its own sample range of the same
+    window; per tile one reduce-scatter of integer histograms + all-gather + all-reduce over NCCL.  Total work is
+    fixed (100,000 samples), so scaling is "strong"."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    import torch
+    import torch.distributed as dist
+    import basevarc_b200 as B
+    from basevarc_b200.caller import PinnedArray
+    torch.cuda.set_device(local)
+    own_pg = not dist.is_initialized()
+    if own_pg:
+        if world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        else:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29555")
+            dist.init_process_group("nccl", rank=0, world_size=1, device_id=torch.device("cuda", local))
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    cfg = B.CONFIGS[args.workload]
+    N = cfg["n_samples"]
+    S = args.sites or 16384
+    tile = B.synth_tile(N, S, cfg["depth"], cfg["model"], seed=int(args.workload[1:]), shard=(rank, world))
+    R = tile.n_entries
+    uid = [B.shard_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    qlo, qhi = args.qual_window
+    caller = B.ShardedCaller(N, rank, world, uid[0], qual_lo=qlo, qual_hi=qhi, device=local, max_sites=S, max_entries=max(R, 1))
+    units = S * N                                   # whole job: every rank works on the same S sites x N samples
+
+    # ---- resident leg: local entries already in HBM; device events per phase (max over ranks of the step time) ----
+    caller.shard_upload(tile)
+    for _ in range(args.warmup):
+        caller.shard_run()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.wait_started()
+    barrier()
+    l0 = caller.kernel_launches
+    t0 = time.perf_counter()
+    phases = {}
+    for _ in range(args.steps):
+        first, recs = caller.shard_run()
+        st = caller.shard_stats()
+        for k, v in st["phase_ms"].items():
+            phases[k] = phases.get(k, 0.0) + v / args.steps
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    launches = caller.kernel_launches - l0
+    dev_ms = sum(v for k, v in phases.items() if k not in ("h2d", "d2h"))
+    ms_step = max_over_ranks(dev_ms)
+    value = units / (ms_step * 1e-3)
+    phases = {k: max_over_ranks(v) for k, v in phases.items()}
+
+    # ---- e2e leg: pinned host buffers through bvc_shard_call (H2D + collectives + D2H inside the region) --------
+    pins = {}
+    for k in ("ref_base", "entry_off", "code", "qual", "mapq", "rpr"):
+        src = getattr(tile, k)
+        pins[k] = PinnedArray(src.shape, src.dtype)
+        pins[k].array[...] = src
+        setattr(tile, k, pins[k].array)
+    out = PinnedArray(((S + world - 1) // world,), B.SITE_RESULT_DTYPE)
+    for _ in range(args.warmup):
+        caller.shard_call(tile, out.array)
+    barrier()
+    h2d0, d2h0 = caller.transfer_bytes
+    x0 = caller.shard_stats()["exchange_bytes"]
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        first2, recs2 = caller.shard_call(tile, out.array)
+    barrier()
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+    h2d1, d2h1 = caller.transfer_bytes
+    st = caller.shard_stats()
+    clocks = sampler.stop() if sampler else None
+    same = recs2.tobytes() == recs.tobytes()
+    h2d = sum_over_ranks((h2d1 - h2d0) // args.steps)
+    d2h = sum_over_ranks((d2h1 - d2h0) // args.steps)
+    xbytes = sum_over_ranks((st["exchange_bytes"] - x0) // args.steps)
+    n_pos = st["n_positive"]
+    R_all = sum_over_ranks(R)
+
+    peak, peak_src = _peaks()
+    B_words = 16 + 8 * (qhi - qlo + 1)
+    n_pad = world * ((S + world - 1) // world)
+    hist_bytes = 2 * R + 5 * S + 4 * B_words * n_pad      # per rank: code + qual in, offsets + ref, dense records out
+    roof = {"bound": "hbm", "kernel": "shard_hist_kernel", "kernel_ms": phases["shard_hist"],
+            "achieved": hist_bytes / (phases["shard_hist"] * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": int(hist_bytes), "traffic": None,
+            "kernel_share_of_step": phases["shard_hist"] / max(ms_step, 1e-9)}
+    roof["frac"] = roof["achieved"] / roof["peak"]
+    if rank != 0:
+        caller.close()
+        if own_pg:
+            dist.destroy_process_group()
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        v, s_cpu, dt, kind = cpu_reference_baseline(tile, max(1, args.ref_sites_per_thread * 1000 // N), cores)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+               "sample": "first %d sites x %d samples of the same window, %.1f s (%s)" % (
+                   s_cpu, N, dt, "unmodified reference binary, basetype --rerun -t %d" % cores if kind == "reference" else "oracle C restatement, per-read")}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "%s: synthetic %d samples x %d sites at %.1fx depth, sample-sharded over %d GPU(s)" % (args.workload, N, S, cfg["depth"], world),
+                   "sites": S, "n_samples": N, "entries_all_ranks": int(R_all), "qual_window": [qlo, qhi],
+                   "parallelism": "sample-sharded x%d: reduce-scatter of per-site histograms + all-gather + all-reduce (NCCL)" % world,
+                   "l2": "inputs (%.0f MB per rank) exceed the 126 MB L2; no flush needed" % (tile.nbytes() / 1e6) if tile.nbytes() > 126e6
+                         else "inputs (%.0f MB per rank) fit the L2: use --sites to grow the tile" % (tile.nbytes() / 1e6)},
+        "e2e": {"value": units / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": e2e_s * 1e3, "matches_resident": bool(same)},
+        "gpu_launches": int(launches),
+        "roofline": roof,
+        "phases_ms": {k: round(v, 4) for k, v in phases.items()},
+        "exchange_bytes_per_step": int(xbytes), "wall_ms_per_step": wall_ms,
+        "cpu_baseline": cpu, "clocks": clocks, "sites_lrt_positive": int(n_pos),
+    }
+    print(json.dumps(line))
+    caller.close()
+    if own_pg:
+        dist.destroy_process_group()
+
 
 def main():
     ap = argparse.ArgumentParser()
@@ -212,9 +353,12 @@ def main():
     ap.add_argument("--subtiles", type=int, default=8, help="sub-tiles per step on the host-buffer (e2e) path")
     ap.add_argument("--ref-sites-per-thread", type=int, default=6000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--qual-window", type=int, nargs=2, default=[1, 63], help="exchange window of the sample-sharded mode (C4)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "C4":
+        return run_sharded(args)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -333,7 +477,7 @@ def main():
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
-        v, s_cpu, dt, kind = cpu_reference_baseline(tile, args.ref_sites_per_thread, cores)
+        v, s_cpu, dt, kind = cpu_reference_baseline(tile, max(1, args.ref_sites_per_thread * 1000 // N), cores)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                "sample": "first %d sites x %d samples of the same window, %.1f s (%s)" % (
                    s_cpu, N, dt, "unmodified reference binary, basetype --rerun -t %d" % cores if kind == "reference"
