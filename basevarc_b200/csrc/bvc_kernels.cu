@@ -211,11 +211,13 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     PipeArgs a = a0;
     const int S = a.s.n_sites;
     int launches = 0;
-    static int occ_hist = 0, occ_hist16 = 0, occ_em = 0, occ_vcf = 0, occ_leg = 0, occ_long = 0, occ_ll = 0;
+    static int occ_hist4 = 0, occ_hist = 0, occ_hist16 = 0, occ_em = 0, occ_vcf = 0, occ_leg = 0, occ_long = 0, occ_ll = 0;
     if (!occ_hist) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_long, em_long_kernel, kLongThreads, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ll, fit_loglik_kernel, kEmThreads, 0);
         if (occ_long < 1) occ_long = 1; if (occ_ll < 1) occ_ll = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist4, site_hist4_kernel, kHistWarps * 32, 0);
+        if (occ_hist4 < 1) occ_hist4 = 1;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist, site_hist_kernel<32>, kHistWarps * 32, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist16, site_hist_kernel<16>, kHistWarps * 32, 0);
         if (occ_hist16 < 1) occ_hist16 = 1;
@@ -232,7 +234,9 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     if (parts & kPartHist) {
     mark(kKHist);
     // lanes per site by mean pileup depth of the tile: a full warp from 256 entries per site (measured: C2, 393 entries, 1.11 ms vs 1.23 ms), half a warp below
-    if (a.mean_entries >= 256)
+    if (a.packed_hist)
+        site_hist4_kernel<<<capped((S + kHistWarps * kH4Sites - 1) / (kHistWarps * kH4Sites), occ_hist4), kHistWarps * 32, 0, stream>>>(a);
+    else if (a.mean_entries >= 256)
         site_hist_kernel<32><<<capped((S + kHistWarps - 1) / kHistWarps, occ_hist), kHistWarps * 32, 0, stream>>>(a);
     else
         site_hist_kernel<16><<<capped((S + 2 * kHistWarps - 1) / (2 * kHistWarps), occ_hist16), kHistWarps * 32, 0, stream>>>(a);
@@ -262,7 +266,7 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
         mark(kKLoglik);
         fit_loglik_kernel<<<(unsigned)(n_sm * occ_ll), kEmThreads, 0, stream>>>(a);
         mark(kKLadder);
-        ladder_kernel<<<site_blocks, 128, 0, stream>>>(a);
+        ladder_kernel<<<(unsigned)(n_sm * 8), 128, 0, stream>>>(a);
     }
     }
     if (parts & kPartVcf) {

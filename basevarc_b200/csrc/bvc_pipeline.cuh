@@ -14,7 +14,7 @@
 //   K3 em_fit_kernel       THREAD PER FIT, pass-aligned: the sorted queue gives the 32 lanes of a warp fits of
 //                          (nearly) equal class count, so the class loop has a warp-uniform trip count, every
 //                          pass ends for all lanes together and lanes refill at pass boundaries.  No shuffles,
-//                          no per-class state.  FP64-pipe-bound.  A fit that needs more than kPassBudget passes
+//                          no per-class state.  FP64-pipe-bound.  A fit that needs more than pass_budget passes
 //                          is parked for K3b.  (EM / singleEM / delta_bylog src/Algorithm.cpp:69-130;
 //                          UpdateF / SetAlleleFreq src/BaseType.cpp:25-71)
 //   K3b em_long_kernel     warp per parked fit (classes across lanes + butterfly sums): bounds the stage's tail.
@@ -54,6 +54,7 @@ __device__ __forceinline__ double sel4(int b, double v0, double v1, double v2, d
 // =====================================================================================================
 constexpr int kHistWarps = 4;
 constexpr int kHistBins = 2 * kNBins;      // per site in flight: [base][qual][strand]
+constexpr int kHistWords = kHistBins + 8;  // + the 8 indel bins (strand << 2 | stale base) right behind them
 
 // shared-memory increment without a result and without a branch around it
 __device__ __forceinline__ void red_inc_if(uint32_t* p, bool pred)
@@ -93,11 +94,11 @@ template <int G> __device__ __forceinline__ unsigned group_min(unsigned v, int g
 // hist_stream: 4 entries per lane per 32-bit load, both arrays in flight.  One shared-memory increment per entry
 // does all the counting: the bin carries base, qual and strand.  Bytes outside [b0, b1) in the first / last word are
 // turned into code 0x14 (indel, base 4), which nothing counts.  hist: non-indel entries, base << 8 | qual << 1 | strand;
-// ind: indel entries (stale base < 4), strand << 2 | base.
+// hist[kHistBins + (strand << 2 | base)]: indel entries (stale base < 4).
 template <int G>
 __device__ __forceinline__ void hist_stream(const uint32_t* __restrict__ code4, const uint32_t* __restrict__ qual4,
-                                            uint32_t b0, uint32_t b1, int g, uint32_t* hist, uint32_t* ind,
-                                            uint32_t& qmin, uint32_t& qmax, bool& any_ind)
+                                            uint32_t b0, uint32_t b1, int g, uint32_t* hist,
+                                            uint32_t& qmin, uint32_t& qmax)
 {
     const uint32_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;
     const uint32_t trips = (__reduce_max_sync(0xffffffffu, w1 - w0) + G - 1) / G;
@@ -117,15 +118,11 @@ __device__ __forceinline__ void hist_stream(const uint32_t* __restrict__ code4, 
                 const uint32_t c = cw >> (8 * k), q = (qw >> (8 * k)) & 0x7fu;
                 const bool ok = !(c & 0x14u);
                 qmin = min(qmin, ok ? q : 127u); qmax = max(qmax, ok ? q : 0u);
-                red_inc_if(&hist[((c & 3u) << 8) | (q << 1) | ((c >> 3) & 1u)], ok);
-            }
-            if (cw & 0x10101010u) {                 // rare: indel entries keep only (stale base, strand)
-                any_ind = true;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint32_t c = cw >> (8 * k);
-                    if ((c & 0x14u) == 0x10u) atomicAdd(&ind[((c >> 1) & 4u) | (c & 3u)], 1u);
-                }
+                // one increment per entry with a base < 4: a (base, qual, strand) bin, or for an indel entry (which
+                // keeps only its stale base / strand) one of the 8 bins behind the histogram -- no branch for the ~0.5 %
+                const uint32_t bin = (c & 0x10u) ? (uint32_t)kHistBins + (((c >> 1) & 4u) | (c & 3u))
+                                                 : (((c & 3u) << 8) | (q << 1) | ((c >> 3) & 1u));
+                red_inc_if(&hist[bin], !(c & 4u));
             }
         }
     }
@@ -136,8 +133,7 @@ __device__ __forceinline__ void hist_stream(const uint32_t* __restrict__ code4, 
 // (major base first); clears the bins it visited.  qmin / qmax are the lane-local extremes of the quals present.
 template <int G>
 __device__ __forceinline__ void hist_emit(const PipeArgs& a, int site, bool live, int ref, int n_entries,
-                                          uint32_t qmin, uint32_t qmax, bool any_ind, uint32_t* hist, uint32_t* ind,
-                                          int g, int gi)
+                                          uint32_t qmin, uint32_t qmax, uint32_t* hist, int g, int gi)
 {
     const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (gi * G));
     const unsigned lt = (1u << g) - 1u;
@@ -147,7 +143,6 @@ __device__ __forceinline__ void hist_emit(const PipeArgs& a, int site, bool live
     const int q_lo = (int)min(qmin, qmax);
     const int my_steps = live && n_entries > 0 ? ((int)qmax - q_lo) / G + 1 : 0;
     const int nsteps = __reduce_max_sync(0xffffffffu, my_steps);
-    any_ind = __any_sync(0xffffffffu, any_ind);
 
     // ---- pass 1 over the bins: merged counts, per-base depth / forward depth / class count -------------------
     int dsum[4], fsum[4], ncb[4];
@@ -162,7 +157,13 @@ __device__ __forceinline__ void hist_emit(const PipeArgs& a, int site, bool live
             dsum[b] += (int)(h.x + h.y); fsum[b] += (int)h.y;
             const unsigned m = (__ballot_sync(0xffffffffu, (h.x + h.y) != 0) & gmask) >> (gi * G);
             ncb[b] += __popc(m);
-            if (q_lo <= 1 && st == 0) lowq |= (m << q_lo) & 3u;     // bit 0: a qual-0 class, bit 1: a qual-1 class
+        }
+    }
+    if (__any_sync(0xffffffffu, q_lo <= 1 && my_steps > 0)) {          // rare: bit 0 = a qual-0 class, bit 1 = a qual-1 class
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const uint4 h = *reinterpret_cast<const uint4*>(&hist[b << 8]);     // quals 0 and 1 of base b, both strands
+            lowq |= ((h.x + h.y) ? 1u : 0u) | ((h.z + h.w) ? 2u : 0u);
         }
     }
     int depth[4], fwd[4], n_reads = 0;
@@ -172,8 +173,8 @@ __device__ __forceinline__ void hist_emit(const PipeArgs& a, int site, bool live
         fwd[b] = group_add<G>(fsum[b], gi);
         n_reads += depth[b];
     }
-    int icnt = 0;                               // g = strand << 2 | base of the indel entries
-    if (any_ind) { icnt = g < 8 ? (int)ind[g] : 0; __syncwarp(); if (g < 8) ind[g] = 0; }
+    const int icnt = g < 8 ? (int)hist[kHistBins + g] : 0;      // g = strand << 2 | base of the indel entries
+    if (icnt) hist[kHistBins + g] = 0;
     // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
     int best = -1, bestd = -1, second = -1, secondd = -1;
 #pragma unroll
@@ -219,16 +220,14 @@ __device__ __forceinline__ void hist_emit(const PipeArgs& a, int site, bool live
             pos += __popc(m);
         }
     }
-    // ---- 64-byte summary: lanes 0..15 of the group store one word each ---------------------------------------
-    int word = 0;
-    if (g == 0) word = depth[0]; else if (g == 1) word = depth[1]; else if (g == 2) word = depth[2]; else if (g == 3) word = depth[3];
-    else if (g == 4) word = fwd[0]; else if (g == 5) word = fwd[1]; else if (g == 6) word = fwd[2]; else if (g == 7) word = fwd[3];
-    else if (g == 8) word = c0; else if (g == 9) word = c1; else if (g == 10) word = c2; else if (g == 11) word = c3;
-    else if (g == 12) word = (int)off;
-    else if (g == 13) word = ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0);
-    else if (g == 14) word = n_entries;
-    else if (g == 15) word = n_major | (best << 16);
-    if (live && g < 16) reinterpret_cast<int*>(a.sum + site)[g] = word;
+    // ---- 64-byte summary: lanes 0..3 of the group store 16 bytes each (every lane holds all the values) ------------
+    uint4 v;
+    if (g == 0) v = make_uint4((uint32_t)depth[0], (uint32_t)depth[1], (uint32_t)depth[2], (uint32_t)depth[3]);
+    else if (g == 1) v = make_uint4((uint32_t)fwd[0], (uint32_t)fwd[1], (uint32_t)fwd[2], (uint32_t)fwd[3]);
+    else if (g == 2) v = make_uint4((uint32_t)c0, (uint32_t)c1, (uint32_t)c2, (uint32_t)c3);
+    else v = make_uint4(off, (uint32_t)(ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0)),
+                        (uint32_t)n_entries, (uint32_t)(n_major | (best << 16)));
+    if (live && g < 4) reinterpret_cast<uint4*>(a.sum + site)[g] = v;
     __syncwarp();
 }
 
@@ -238,14 +237,11 @@ __global__ void __launch_bounds__(kHistWarps * 32)
 site_hist_kernel(PipeArgs a)
 {
     constexpr int kGroups = 32 / G;
-    __shared__ __align__(8) uint32_t hist_s[kHistWarps * kGroups][kHistBins];
-    __shared__ uint32_t ind_s[kHistWarps * kGroups][8];
+    __shared__ __align__(16) uint32_t hist_s[kHistWarps * kGroups][kHistWords];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int g = lane & (G - 1), gi = lane / G;
     uint32_t* hist = hist_s[wid * kGroups + gi];
-    uint32_t* ind = ind_s[wid * kGroups + gi];
-    for (int i = g; i < kHistBins; i += G) hist[i] = 0;
-    if (g < 8) ind[g] = 0;
+    for (int i = g; i < kHistWords; i += G) hist[i] = 0;
     __syncwarp();
     const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
     const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
@@ -260,9 +256,174 @@ site_hist_kernel(PipeArgs a)
         const uint32_t b0 = live ? a.s.entry_off[site] : 0u, b1 = live ? a.s.entry_off[site + 1] : 0u;
         const int ref = live ? (a.s.ref_base[site] & 3) : 0;
         uint32_t qmax = 0, qmin = 127;
-        bool any_ind = false;
-        hist_stream<G>(code4, qual4, b0, b1, g, hist, ind, qmin, qmax, any_ind);
-        hist_emit<G>(a, site, live, ref, (int)(b1 - b0), qmin, qmax, any_ind, hist, ind, g, gi);
+        hist_stream<G>(code4, qual4, b0, b1, g, hist, qmin, qmax);
+        hist_emit<G>(a, site, live, ref, (int)(b1 - b0), qmin, qmax, hist, g, gi);
+    }
+}
+
+// =====================================================================================================
+// K1 (packed form, cohorts of < 65,536 samples): a warp takes FOUR consecutive sites at a time.
+//  * Their entries are one contiguous range of the CSR arrays, streamed by all 32 lanes as ONE range (no
+//    per-site partial trips); an entry finds its site by comparing its index with the three inner offsets.
+//  * A bin is ONE 32-bit word per (base, qual): forward count in the high half, reverse count in the low half
+//    (a site has at most n_samples < 2^16 entries), so a site's histogram is 2 KB + 8 indel words and four
+//    sites per warp fit the shared memory of six 4-warp blocks per SM.
+//  * The four sites are then emitted side by side, 8 lanes each: the per-site scalar work (argsort, strand
+//    table, pool allocation, summary) costs a quarter of the one-site-per-warp form.
+// =====================================================================================================
+constexpr int kH4Sites = 4;
+constexpr int kH4Words = kNBins + 8;       // (base << 7 | qual) words + the 8 indel bins (strand << 2 | stale base)
+
+__device__ __forceinline__ void red_add_if(uint32_t* p, uint32_t v, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q red.shared.add.u32 [%0], %1;\n\t}"
+                 :: "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v), "r"((uint32_t)pred) : "memory");
+}
+__device__ __forceinline__ int bfly8(int v)
+{
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    return v;
+}
+
+__global__ void __launch_bounds__(kHistWarps * 32)
+site_hist4_kernel(PipeArgs a)
+{
+    __shared__ __align__(16) uint32_t hist_s[kHistWarps][kH4Sites * kH4Words];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int g = lane & 7, gi = lane >> 3;
+    uint32_t* hw = hist_s[wid];
+    for (int i = lane; i < kH4Sites * kH4Words; i += 32) hw[i] = 0;
+    __syncwarp();
+    uint32_t* hist = hw + gi * kH4Words;                        // my group's site during the emit
+    const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
+    const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
+    const int S = a.s.n_sites;
+    const int n_batches = (S + kH4Sites - 1) / kH4Sites;
+    const unsigned lt = (1u << g) - 1u;
+
+    for (int batch = blockIdx.x * kHistWarps + wid; batch < n_batches; batch += gridDim.x * kHistWarps) {
+        const int s0 = batch * kH4Sites;
+        uint32_t ov = 0;
+        if (lane <= kH4Sites) ov = a.s.entry_off[min(s0 + lane, S)];
+        const uint32_t o0 = __shfl_sync(0xffffffffu, ov, 0), o1 = __shfl_sync(0xffffffffu, ov, 1), o2 = __shfl_sync(0xffffffffu, ov, 2),
+                       o3 = __shfl_sync(0xffffffffu, ov, 3), o4 = __shfl_sync(0xffffffffu, ov, 4);
+        // ---- stream [o0, o4): 4 entries per lane per 32-bit load -------------------------------------------------
+        uint32_t qmax = 0, qmin = 127;
+        const uint32_t w0 = o0 >> 2, w1 = (o4 + 3) >> 2;
+#pragma unroll 2
+        for (uint32_t wi = w0 + lane; wi < w1; wi += 32) {
+            uint32_t cw = __ldg(code4 + wi);
+            const uint32_t qw = __ldg(qual4 + wi) & 0x7f7f7f7fu;
+            const uint32_t e0 = wi * 4;
+            if (e0 < o0 || e0 + 4 > o4) {                       // first / last word of the range: bytes outside -> code 0x14
+                const uint32_t lo = o0 > e0 ? o0 - e0 : 0u, hi = o4 < e0 + 4 ? o4 - e0 : 4u;
+                const uint32_t vm = (hi >= 4 ? 0xffffffffu : ((1u << (8 * hi)) - 1u)) & ~((1u << (8 * lo)) - 1u);
+                cw = (cw & vm) | (0x14141414u & ~vm);
+            }
+            const uint32_t kf = (uint32_t)(e0 >= o1) + (uint32_t)(e0 >= o2) + (uint32_t)(e0 >= o3);
+            const uint32_t kl = (uint32_t)(e0 + 3 >= o1) + (uint32_t)(e0 + 3 >= o2) + (uint32_t)(e0 + 3 >= o3);
+            const bool straddle = kf != kl;                     // the word spans a site boundary (<= 3 words per batch)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t c = cw >> (8 * k), q = (qw >> (8 * k)) & 0x7fu;
+                const bool ok = !(c & 0x14u);
+                qmin = min(qmin, ok ? q : 127u); qmax = max(qmax, ok ? q : 0u);
+                uint32_t ks = kf;
+                if (straddle) { const uint32_t e = e0 + k; ks = (uint32_t)(e >= o1) + (uint32_t)(e >= o2) + (uint32_t)(e >= o3); }
+                const uint32_t bin = (c & 0x10u) ? (uint32_t)kNBins + (((c >> 1) & 4u) | (c & 3u)) : (((c & 3u) << 7) | q);
+                const uint32_t inc = (c & 0x10u) ? 1u : (1u << ((c & 8u) << 1));      // forward strand counts in the high half
+                red_add_if(&hw[ks * kH4Words + bin], inc, !(c & 4u));
+            }
+        }
+        __syncwarp();
+        // one qual range for the whole batch (a superset for each of its sites)
+        qmax = __reduce_max_sync(0xffffffffu, qmax);
+        qmin = __reduce_min_sync(0xffffffffu, qmin);
+        const int q_lo = (int)min(qmin, qmax);
+        const int nsteps = o4 > o0 ? ((int)qmax - q_lo) / 8 + 1 : 0;
+
+        // ---- emit: group gi <-> site s0 + gi ---------------------------------------------------------------------
+        const int site = s0 + gi;
+        const bool live = site < S;
+        const int ref = live ? (a.s.ref_base[site] & 3) : 0;
+        const int n_entries = (int)(gi == 0 ? o1 - o0 : gi == 1 ? o2 - o1 : gi == 2 ? o3 - o2 : o4 - o3);
+        int dsum[4], fsum[4], ncb[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            dsum[b] = 0; fsum[b] = 0; ncb[b] = 0;
+            for (int st = 0; st < nsteps; ++st) {
+                const int q = q_lo + st * 8 + g;
+                const uint32_t h = q < kNQ ? hist[(b << 7) | q] : 0u;
+                const uint32_t x = (h & 0xffffu) + (h >> 16);
+                dsum[b] += (int)x; fsum[b] += (int)(h >> 16);
+                ncb[b] += __popc((__ballot_sync(0xffffffffu, x != 0) >> (gi * 8)) & 0xffu);
+            }
+        }
+        unsigned lowq = 0;
+        if (q_lo <= 1 && nsteps > 0) {                          // rare: bit 0 = a qual-0 class, bit 1 = a qual-1 class
+#pragma unroll
+            for (int b = 0; b < 4; ++b) lowq |= (hist[b << 7] ? 1u : 0u) | (hist[(b << 7) | 1] ? 2u : 0u);
+        }
+        int depth[4], fwd[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) { depth[b] = bfly8(dsum[b]); fwd[b] = bfly8(fsum[b]); }   // src/BaseVarC.cpp:550-559
+        const int icnt = (int)hist[kNBins + g];                 // g = strand << 2 | base of the indel entries
+        if (icnt) hist[kNBins + g] = 0;
+        // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
+        int best = -1, bestd = -1, second = -1, secondd = -1;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            if (depth[b] > bestd) { second = best; secondd = bestd; best = b; bestd = depth[b]; }
+            else if (depth[b] > secondd) { second = b; secondd = depth[b]; }
+        }
+        const int alt = (best != ref) ? best : second;
+        // src/BaseVarC.cpp:587-602: 2x2 table over ALL entries (indel entries carry stale base/strand)
+        const int fr_ = ref == 0 ? fwd[0] : ref == 1 ? fwd[1] : ref == 2 ? fwd[2] : fwd[3];
+        const int dr_ = ref == 0 ? depth[0] : ref == 1 ? depth[1] : ref == 2 ? depth[2] : depth[3];
+        const int fa_ = alt == 0 ? fwd[0] : alt == 1 ? fwd[1] : alt == 2 ? fwd[2] : fwd[3];
+        const int da_ = alt == 0 ? depth[0] : alt == 1 ? depth[1] : alt == 2 ? depth[2] : depth[3];
+        const int gl = gi * 8;
+        const int c0 = fr_ + __shfl_sync(0xffffffffu, icnt, gl + (ref | 4));
+        const int c1 = (dr_ - fr_) + __shfl_sync(0xffffffffu, icnt, gl + ref);
+        const int c2 = fa_ + __shfl_sync(0xffffffffu, icnt, gl + (alt | 4));
+        const int c3 = (da_ - fa_) + __shfl_sync(0xffffffffu, icnt, gl + alt);
+        // pool space for the four sites with one atomic
+        const int ncls = ncb[0] + ncb[1] + ncb[2] + ncb[3];
+        const int n_major = best == 0 ? ncb[0] : best == 1 ? ncb[1] : best == 2 ? ncb[2] : ncb[3];
+        const int n0 = __shfl_sync(0xffffffffu, ncls, 0), n1 = __shfl_sync(0xffffffffu, ncls, 8),
+                  n2 = __shfl_sync(0xffffffffu, ncls, 16), n3 = __shfl_sync(0xffffffffu, ncls, 24);
+        uint32_t off = 0;
+        if (lane == 0 && n0 + n1 + n2 + n3) off = atomicAdd(a.cls_cursor, (uint32_t)(n0 + n1 + n2 + n3));
+        off = __shfl_sync(0xffffffffu, off, 0) + (uint32_t)(gi > 0 ? n0 : 0) + (uint32_t)(gi > 1 ? n1 : 0) + (uint32_t)(gi > 2 ? n2 : 0);
+        // classes to the pool, the MAJOR base first (K3 runs that segment select-free); clears the bins
+        uint32_t run = off + (uint32_t)n_major;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            uint32_t pos;
+            if (b == best) pos = off; else { pos = run; run += (uint32_t)ncb[b]; }
+            for (int st = 0; st < nsteps; ++st) {
+                const int q = q_lo + st * 8 + g;
+                uint32_t x = 0;
+                if (q < kNQ) {
+                    const uint32_t h = hist[(b << 7) | q];
+                    x = (h & 0xffffu) + (h >> 16);
+                    if (x) hist[(b << 7) | q] = 0;
+                }
+                const unsigned m = (__ballot_sync(0xffffffffu, x != 0) >> (gi * 8)) & 0xffu;
+                if (x) a.cls[pos + __popc(m & lt)] = (x << 9) | (uint32_t)((b << 7) | q);
+                pos += __popc(m);
+            }
+        }
+        uint4 v;
+        if (g == 0) v = make_uint4((uint32_t)depth[0], (uint32_t)depth[1], (uint32_t)depth[2], (uint32_t)depth[3]);
+        else if (g == 1) v = make_uint4((uint32_t)fwd[0], (uint32_t)fwd[1], (uint32_t)fwd[2], (uint32_t)fwd[3]);
+        else if (g == 2) v = make_uint4((uint32_t)c0, (uint32_t)c1, (uint32_t)c2, (uint32_t)c3);
+        else v = make_uint4(off, (uint32_t)(ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0)),
+                            (uint32_t)n_entries, (uint32_t)(n_major | (best << 16)));
+        if (live && g < 4) reinterpret_cast<uint4*>(a.sum + site)[g] = v;
+        __syncwarp();
     }
 }
 
@@ -281,17 +442,35 @@ __device__ __forceinline__ uint32_t warp_agg_append(uint32_t* ctr, bool pred)
     return base + __popc(m & ((1u << lane) - 1));
 }
 
-// BaseType.cpp:111-135 + the LRT half of the output record.
-__device__ __noinline__ void finalize_site(const PipeArgs& a, int site, int ref, const int* depth, int n_reads,
+// The 176-byte record as eleven 16-byte stores (offsets: include/bvc_gpu.h; a record is 16-byte aligned in d_out).
+__device__ __forceinline__ void st_dd(bvc_site_result* r, int off, double x, double y)
+{
+    *reinterpret_cast<double2*>(reinterpret_cast<char*>(r) + off) = make_double2(x, y);
+}
+__device__ __forceinline__ void st_iiii(bvc_site_result* r, int off, int x, int y, int z, int w)
+{
+    *reinterpret_cast<int4*>(reinterpret_cast<char*>(r) + off) = make_int4(x, y, z, w);
+}
+
+// BaseType.cpp:111-135; writes the WHOLE record of the site once (K5 later fills the VCF statistics of the
+// LRT-positive sites).  su / cvg_fs / cvg_sor: the CVG half computed by K1 / K2.
+__device__ __noinline__ void finalize_site(const PipeArgs& a, int site, int ref, const SiteSum& su, double cvg_fs, double cvg_sor,
                                            const int8_t* cand, int n, const double* frq, double chi_t,
                                            int em_fits, int em_passes, uint32_t flags)
 {
     bvc_site_result* r = a.s.out + site;
-    int n_alt = 0; int8_t alt_bases[3] = {-1, -1, -1};
+    const int* depth = su.depth;
+    const int n_reads = depth[0] + depth[1] + depth[2] + depth[3];
+    int n_alt = 0; int alt_bases[3] = {-1, -1, -1};
     double af[4] = {0.0, 0.0, 0.0, 0.0};
     for (int t = 0; t < n; ++t) {
         const int b = cand[t];
-        if (b != ref && n_alt < 3) { alt_bases[n_alt++] = (int8_t)b; af[b] = sel4(b, frq[0], frq[1], frq[2], frq[3]); }
+        if (b != ref && n_alt < 3) {
+            const double fv = sel4(b, frq[0], frq[1], frq[2], frq[3]);
+            if (n_alt == 0) alt_bases[0] = b; else if (n_alt == 1) alt_bases[1] = b; else alt_bases[2] = b;
+            ++n_alt;
+            if (b == 0) af[0] = fv; else if (b == 1) af[1] = fv; else if (b == 2) af[2] = fv; else af[3] = fv;
+        }
     }
     double vq = 0.0;
     const int ok = n_alt > 0;
@@ -308,11 +487,19 @@ __device__ __noinline__ void finalize_site(const PipeArgs& a, int site, int ref,
         }
         if (near_rel(vq, 60.0)) flags |= BVC_FLAG_QUAL60;
     }
-    r->af_lrt[0] = af[0]; r->af_lrt[1] = af[1]; r->af_lrt[2] = af[2]; r->af_lrt[3] = af[3];
-    r->chi = chi_t; r->var_qual = vq;
-    r->em_fits = em_fits; r->em_passes = em_passes; r->flags = flags;
-    r->lrt_ok = (int8_t)ok; r->n_alt = (int8_t)n_alt;
-    r->alt_bases[0] = alt_bases[0]; r->alt_bases[1] = alt_bases[1]; r->alt_bases[2] = alt_bases[2];
+    st_dd(r, 0, cvg_fs, cvg_sor);
+    st_dd(r, 16, af[0], af[1]);
+    st_dd(r, 32, af[2], af[3]);
+    st_dd(r, 48, chi_t, vq);
+    st_dd(r, 64, 0.0, 0.0);                                   // vcf_fs, vcf_sor
+    st_dd(r, 80, 0.0, 0.0);                                   // ranksum[0..1]
+    st_iiii(r, 96, 0, 0, su.n_entries, depth[0]);             // ranksum[2] = 0.0
+    st_iiii(r, 112, depth[1], depth[2], depth[3], su.cvg[0]);
+    st_iiii(r, 128, su.cvg[1], su.cvg[2], su.cvg[3], 0);
+    st_iiii(r, 144, 0, 0, 0, em_fits);
+    st_iiii(r, 160, em_passes, (int)flags,
+            (int)((uint32_t)su.alt | ((uint32_t)ok << 8) | ((uint32_t)n_alt << 16) | (((uint32_t)alt_bases[0] & 0xffu) << 24)),
+            (int)(((uint32_t)alt_bases[1] & 0xffu) | (((uint32_t)alt_bases[2] & 0xffu) << 8)));
     a.state[site] = kStDone;
     if (ok) a.vcf_list[atomicAdd(a.vcf_n, 1u)] = (uint32_t)site;
 }
@@ -330,18 +517,12 @@ site_prepare_kernel(PipeArgs a)
         const SiteSum su = a.sum[site];
         const int ref = a.s.ref_base[site] & 3;
         const int n_reads = su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3];
-        bvc_site_result* r = a.s.out + site;
         if (su.has_q0 & 1) {
             a.state[site] = kStLegacy;
             a.legacy_list[atomicAdd(a.legacy_n, 1u)] = (uint32_t)site;
         } else {
-            r->cvg_fs = dm_fisher(a.s.lgam, su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
-            r->cvg_sor = dm_sor(su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
-            r->vcf_fs = 0.0; r->vcf_sor = 0.0; r->ranksum[0] = 0.0; r->ranksum[1] = 0.0; r->ranksum[2] = 0.0;
-            r->n_entries = su.n_entries;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) { r->depth[j] = su.depth[j]; r->cvg_strand[j] = su.cvg[j]; r->vcf_strand[j] = 0; }
-            r->cvg_alt_base = (int8_t)su.alt; r->pad[0] = 0; r->pad[1] = 0;
+            const double cvg_fs = dm_fisher(a.s.lgam, su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
+            const double cvg_sor = dm_sor(su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
             // BaseType.cpp:75-82
             int8_t cand[4]; int n = 0; uint32_t flags = 0, full = 0;
             const double total = (double)n_reads;
@@ -356,10 +537,11 @@ site_prepare_kernel(PipeArgs a)
             if (n <= 1) {
                 // no EM needed: 0 candidates -> false; 1 candidate -> one (closed-form) fit, chi stays 0
                 const double frq[4] = {full & 1 ? 1.0 : 0.0, full & 2 ? 1.0 : 0.0, full & 4 ? 1.0 : 0.0, full & 8 ? 1.0 : 0.0};
-                finalize_site(a, site, ref, su.depth, n_reads, cand, n, frq, 0.0, n, 2 * n, flags);
+                finalize_site(a, site, ref, su, cvg_fs, cvg_sor, cand, n, frq, 0.0, n, 2 * n, flags);
             } else {
                 Ladder L;
                 L.lr_alt = 0.0; L.frq[0] = L.frq[1] = L.frq[2] = L.frq[3] = 0.0; L.chi_t = 0.0;
+                L.cvg_fs = cvg_fs; L.cvg_sor = cvg_sor;
                 for (int t = 0; t < 4; ++t) L.cand[t] = t < n ? cand[t] : (int8_t)-1;
                 L.n = (int8_t)n; L.k = (int8_t)n; L.nfit = 1; L.pad0 = 0;
                 L.em_fits = 0; L.em_passes = 0; L.flags = flags; L.pad1 = 0;
@@ -445,20 +627,19 @@ queue_scatter_kernel(PipeArgs a)
 // K3: thread per fit, pass-aligned within a warp
 // =====================================================================================================
 constexpr int kEmThreads = 128;
-constexpr int kPassBudget = 32;            // passes a fit may spend in K3 before it is parked for K3b
-constexpr int kDrainMinPass = 8;           // once the queue is empty, fits at or beyond this pass move to K3b
+// hand-over to K3b: PipeArgs::pass_budget (passes a fit may spend in K3) and PipeArgs::drain_min_pass (once the queue
+// is empty, fits at or beyond this pass move to K3b); defaults in bvc_ctx.h
 constexpr int kLongGroup = 8;              // lanes per fit in K3b
 
-// 1/x for normal positive x: MUFU.RCP64H seed (>= 20 bits) + two Newton steps -> <= ~1 ulp
+// 1/x for normal positive x: MUFU.RCP64H seed (relative error e <= 2^-23, PTX rcp.approx.ftz.f64) + ONE cubic step
+// r (1 + e + e^2), e = 1 - x r: remaining error e^3 <= 2^-69, i.e. correctly rounded up to the last fma (<= 1 ulp)
 __device__ __forceinline__ double rcp_nr2(double x)
 {
     double r;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
-    double e = fma(-x, r, 1.0);
-    r = fma(r, e, r);
-    e = fma(-x, r, 1.0);
-    r = fma(r, e, r);
-    return r;
+    const double e = fma(-x, r, 1.0);
+    const double t = fma(e, e, e);
+    return fma(r, t, r);
 }
 
 // log1p(x) for |x| <= 2^-9: x * (1 - x/2 + x^2/3 - x^3/4 + x^4/5), truncation < |x|^5/6 <= 5e-15 relative.
@@ -584,7 +765,7 @@ em_fit_kernel(PipeArgs a)
     const double eps = a.s.eps;
     const int max_iter = a.s.max_iter;
     // a stage with fewer fits than lanes gains nothing from thread-per-fit: park everything at pass 0 for K3b
-    const int budget = (nfits >= (uint32_t)(gridDim.x * blockDim.x)) ? kPassBudget : 0;
+    const int budget = (nfits >= (uint32_t)(gridDim.x * blockDim.x)) ? a.pass_budget : 0;
 
     bool active = false, done = false, drain = false, lowq = false;
     const uint32_t* cp = a.cls;
@@ -689,7 +870,7 @@ em_fit_kernel(PipeArgs a)
                         f0 = e0; f1 = e1; f2 = e2; f3 = e3;              // Algorithm.cpp:95-101
                         F = ((f0 + f1) + f2) + f3;
                         ++pass;
-                        park = (pass >= budget) || (drain && pass >= kDrainMinPass);
+                        park = (pass >= budget) || (drain && pass >= a.drain_min_pass);
                     }
                 }
                 if (park && active) {                                // resume point: pass `pass` with (f, p)
@@ -816,6 +997,8 @@ __global__ void __launch_bounds__(kEmThreads)
 fit_loglik_kernel(PipeArgs a)
 {
     __shared__ double2 lut2[kNQ];
+    __shared__ double2 lutlog[kNQ];                     // (log(e/3), log(1-e)): glibc values from the host table
+    for (int i = threadIdx.x; i < kNQ; i += blockDim.x) lutlog[i] = make_double2(a.s.lut[2 * kNQ + i], a.s.lut[3 * kNQ + i]);
     load_lut2(lut2, a.s.lut);
     const uint32_t nfits = *a.q_in_n;
     unsigned long long work = 0;
@@ -827,24 +1010,36 @@ fit_loglik_kernel(PipeArgs a)
         FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
         double f0 = 0, f1 = 0, f2 = 0, f3 = 0;
         const uint32_t* cp = a.cls; int ncls = 0;
+        uint32_t mask = 0;
         if (on) {
             const SiteSum su = a.sum[item >> 2];
             f0 = fr->f[0]; f1 = fr->f[1]; f2 = fr->f[2]; f3 = fr->f[3];
-            cp = a.cls + su.cls_off; ncls = su.ncls;
+            cp = a.cls + su.cls_off; ncls = su.ncls; mask = fr->mask;
         }
+        // a two-allele model is followed by the two single-base models of its alleles (BaseType.cpp:93-110 at k = 1):
+        // closed form, lr = sum_c cnt_c log L_c,b -- accumulated here, in the same class loop (see ladder_site)
+        const bool pair = __popc(mask) == 2;
+        const uint32_t bl = (uint32_t)(__ffs(mask) - 1) << 7, bh = (uint32_t)(31 - __clz(mask | 1u)) << 7;
         const double F = ((f0 + f1) + f2) + f3;
         const int nmax = __reduce_max_sync(0xffffffffu, ncls);
-        double s = 0.0;
+        double s = 0.0, sl = 0.0, sh = 0.0;
         for (int c = 0; c < nmax; ++c) {
             if (c < ncls) {
                 const uint32_t w = __ldg(cp + c);
                 const int q = w & (kNQ - 1);
                 const double2 ed = lut2[q];
+                const double2 lg = lutlog[q];
+                const double cnt = cnt_to_double(w >> 9);
                 const double ml = fma(sel4_w(w, f0, f1, f2, f3), ed.y, ed.x * F);
-                s = fma(cnt_to_double(w >> 9), log(ml), s);
+                s = fma(cnt, log(ml), s);
+                sl = fma(cnt, (w & 0x180u) == bl ? lg.y : lg.x, sl);
+                sh = fma(cnt, (w & 0x180u) == bh ? lg.y : lg.x, sh);
             }
         }
-        if (on) { fr->lr = s; work += (unsigned long long)ncls; }
+        if (on) {
+            fr->lr = s; work += (unsigned long long)ncls;
+            if (pair) { fr->f[0] = sl; fr->f[1] = sh; }     // f is dead once lr is known: it now carries the singles' lr
+        }
     }
     add_work(a.work + 2, work);
 }
@@ -866,22 +1061,22 @@ __device__ __forceinline__ double single_loglik(const PipeArgs& a, const SiteSum
     return s;
 }
 
-__global__ void __launch_bounds__(128)
-ladder_kernel(PipeArgs a)
+__device__ __forceinline__ void ladder_site(const PipeArgs& a, uint32_t item)
 {
-    const int site = blockIdx.x * blockDim.x + threadIdx.x;
-    if (site >= a.s.n_sites || a.state[site] != kStActive) return;
+    if (item & 3u) return;
+    const int site = (int)(item >> 2);
     const SiteSum su = a.sum[site];
     Ladder L = a.lad[site];
     const int ref = a.s.ref_base[site] & 3;
-    const int n_reads = su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3];
     const FitRes* fr = a.fit + (size_t)site * 4;
     int n = L.n, k = L.k;
     bool cont = true;          // ladder still running
+    const FitRes* src = nullptr;   // the two-allele fit that the current candidate pair came from
 
     // ---- results of the EM stage in flight -----------------------------------------------------------------
     if (k == n) {                                                  // the full model (BaseType.cpp:88-90)
         L.lr_alt = fr[0].lr;
+        if (n == 2) src = fr;
         for (int j = 0; j < 4; ++j) L.frq[j] = fr[0].eap[j];
         L.em_fits += 1; L.em_passes += fr[0].passes; L.flags |= fr[0].flags;
     } else {                                                       // k-subsets, combs_ order (BaseType.cpp:93-110)
@@ -897,6 +1092,7 @@ ladder_kernel(PipeArgs a)
         if (near_rel(cmin, a.s.lrt_thr)) L.flags |= BVC_FLAG_LRT_CHI;
         if (cmin < a.s.lrt_thr) {
             const uint32_t keep = fr[imin].mask;
+            if (__popc(keep) == 2) src = fr + imin;
             int nn = 0;
             for (int t = 0; t < n; ++t) if (keep >> L.cand[t] & 1) L.cand[nn++] = L.cand[t];
             n = nn;
@@ -922,10 +1118,10 @@ ladder_kernel(PipeArgs a)
             for (int i = 0; i < slot; ++i) a.q_out[pos + i] = ((uint32_t)site << 2) | (uint32_t)i;
             return;
         }
-        // k == 1: n == 2 single-base models, in cand order
+        // k == 1: n == 2 single-base models, in cand order; fit_loglik_kernel left their lr in the pair fit's f[0..1]
         double cmin = 0.0, lr_min = 0.0; int imin = 0;
         for (int i = 0; i < n; ++i) {
-            const double lr = single_loglik(a, su, L.cand[i]);
+            const double lr = (src && n == 2) ? src->f[i] : single_loglik(a, su, L.cand[i]);
             const double chi = 2.0 * (L.lr_alt - lr);
             if (i > 0 && near_rel(chi, cmin)) L.flags |= BVC_FLAG_ARGMIN_TIE;
             if (i == 0 || chi < cmin) { cmin = chi; lr_min = lr; imin = i; }
@@ -940,8 +1136,18 @@ ladder_kernel(PipeArgs a)
         }
         cont = false;
     }
-    finalize_site(a, site, ref, su.depth, n_reads, L.cand, n, L.frq, L.chi_t, L.em_fits, L.em_passes, L.flags);
+    finalize_site(a, site, ref, su, L.cvg_fs, L.cvg_sor, L.cand, n, L.frq, L.chi_t, L.em_fits, L.em_passes, L.flags);
 }
+
+__global__ void __launch_bounds__(128)
+ladder_kernel(PipeArgs a)
+{
+    // the sites with fits in flight are exactly the slot-0 items of this stage's (unsorted) queue
+    const uint32_t n_items = *a.q_in_n;
+    for (uint32_t it = blockIdx.x * blockDim.x + threadIdx.x; it < n_items; it += gridDim.x * blockDim.x)
+        ladder_site(a, a.q_in[it]);
+}
+
 
 // =====================================================================================================
 // K5: warp per LRT-positive site -- VCF strand table, Fisher/SOR, three rank-sum tests

@@ -32,10 +32,11 @@ struct __align__(16) FitRes {       // 96 B, one per (site, slot)
     uint32_t unfinished;            // 1: pass budget hit in em_fit_kernel, em_long_kernel finishes it
 };
 
-struct __align__(16) Ladder {       // 80 B per site
+struct __align__(16) Ladder {       // 96 B per site
     double  lr_alt;
     double  frq[4];
     double  chi_t;
+    double  cvg_fs, cvg_sor;        // K2's CVG Fisher / SOR, carried to the one full-record store in K4
     int8_t  cand[4];
     int8_t  n;                      // current number of candidate bases
     int8_t  k;                      // size of the subsets in flight (== n: the full model)
@@ -50,6 +51,9 @@ constexpr uint8_t kStActive = 0, kStDone = 1, kStLegacy = 2;
 
 struct PipeArgs {
     int mean_entries;           // entries / sites of the tile (host side: picks K1's lanes-per-site)
+    int packed_hist;            // 1: K1 in its packed four-sites-per-warp form (every site has < 65,536 entries)
+    int pass_budget;            // passes a fit may spend in em_fit_kernel before it is parked for em_long_kernel
+    int drain_min_pass;         // once the queue is empty, fits at or beyond this pass move to em_long_kernel
     SiteArgs s;                 // tile arrays, out, lut, lgam, thresholds
     SiteSum*  sum;              // [n_sites]
     uint32_t* cls;              // class pool: cnt << 9 | base << 7 | qual

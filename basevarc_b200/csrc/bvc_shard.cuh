@@ -34,14 +34,12 @@ __global__ void __launch_bounds__(kHistWarps * 32)
 shard_hist_kernel(ShardArgs a)
 {
     constexpr int kGroups = 32 / G;
-    __shared__ __align__(8) uint32_t hist_s[kHistWarps * kGroups][kHistBins];
-    __shared__ uint32_t ind_s[kHistWarps * kGroups][8];
+    __shared__ __align__(16) uint32_t hist_s[kHistWarps * kGroups][kHistWords];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int g = lane & (G - 1), gi = lane / G;
     uint32_t* hist = hist_s[wid * kGroups + gi];
-    uint32_t* ind = ind_s[wid * kGroups + gi];
-    for (int i = g; i < kHistBins; i += G) hist[i] = 0;
-    if (g < 8) ind[g] = 0;
+    uint32_t* ind = hist + kHistBins;
+    for (int i = g; i < kHistWords; i += G) hist[i] = 0;
     __syncwarp();
     const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.p.s.code);
     const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.p.s.qual);
@@ -56,8 +54,7 @@ shard_hist_kernel(ShardArgs a)
         const bool live = site < a.n_tile_sites;
         const uint32_t b0 = live ? a.tile_off[site] : 0u, b1 = live ? a.tile_off[site + 1] : 0u;
         uint32_t qmax = 0, qmin = 127;
-        bool any_ind = false;
-        hist_stream<G>(code4, qual4, b0, b1, g, hist, ind, qmin, qmax, any_ind);
+        hist_stream<G>(code4, qual4, b0, b1, g, hist, qmin, qmax);
         qmax = group_max<G>(qmax, gi);
         qmin = group_min<G>(qmin, gi);
         const bool bad = qmin <= qmax && ((int)qmin < a.qlo || (int)qmax > a.qhi);   // a non-indel qual outside the window
@@ -92,14 +89,12 @@ __global__ void __launch_bounds__(kHistWarps * 32)
 shard_merge_kernel(ShardArgs a)
 {
     constexpr int kGroups = 32 / G;
-    __shared__ __align__(8) uint32_t hist_s[kHistWarps * kGroups][kHistBins];
-    __shared__ uint32_t ind_s[kHistWarps * kGroups][8];
+    __shared__ __align__(16) uint32_t hist_s[kHistWarps * kGroups][kHistWords];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int g = lane & (G - 1), gi = lane / G;
     uint32_t* hist = hist_s[wid * kGroups + gi];
-    uint32_t* ind = ind_s[wid * kGroups + gi];
-    for (int i = g; i < kHistBins; i += G) hist[i] = 0;
-    if (g < 8) ind[g] = 0;
+    uint32_t* ind = hist + kHistBins;
+    for (int i = g; i < kHistWords; i += G) hist[i] = 0;
     __syncwarp();
     const int span = 2 * (a.qhi - a.qlo + 1);
 
@@ -114,7 +109,6 @@ shard_merge_kernel(ShardArgs a)
         uint32_t qmax = 0, qmin = 127, hdr = 0;
         if (live && g < kShardHdr) hdr = __ldg(src + g);
         if (live && g < 8) ind[g] = hdr;
-        const bool any_ind = live && g < 8 && hdr != 0;
         const int n_entries = (int)__shfl_sync(0xffffffffu, hdr, gi * G + 8);
         if (live) {
 #pragma unroll
@@ -128,7 +122,7 @@ shard_merge_kernel(ShardArgs a)
             }
         }
         __syncwarp();
-        hist_emit<G>(a.p, s, live, ref, n_entries, qmin, qmax, any_ind, hist, ind, g, gi);
+        hist_emit<G>(a.p, s, live, ref, n_entries, qmin, qmax, hist, g, gi);
     }
 }
 
