@@ -46,7 +46,8 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
     }
     CK(cudaMalloc(&s.d_out, (S + 1) * sizeof(bvc_site_result)));
     CK(cudaMalloc(&s.d_counter, sizeof(unsigned int)));
-    size_t pool = R < S * (size_t)bvc::kNBins ? R : S * (size_t)bvc::kNBins;
+    // class pool: one word per (base, qual) class + up to 6 alignment / padding words per site (pad4 layout)
+    size_t pool = (R < S * (size_t)bvc::kNBins ? R : S * (size_t)bvc::kNBins) + 8 * S;
     CK(cudaMalloc(&s.d_sum, (S + 1) * sizeof(bvc::SiteSum)));
     CK(cudaMalloc(&s.d_cls, (pool + 64) * sizeof(uint32_t)));
     CK(cudaMalloc(&s.d_lad, (S + 1) * sizeof(bvc::Ladder)));

@@ -53,6 +53,11 @@ __device__ __forceinline__ double sel4(int b, double v0, double v1, double v2, d
 // K1: warp per site -- stream entries, histogram, compact classes, strand tables
 // =====================================================================================================
 constexpr int kHistWarps = 4;
+// a class word that contributes exactly nothing (count 0) with finite arithmetic for any valid f: (base 0, qual 30)
+constexpr uint32_t kNullClass = 30u;
+// Pool layout of a site: [major-base classes, padded with null classes to a multiple of 4][other classes]; the site's
+// first word is 16-byte aligned, so K3 / K3b / K3c read the major segment as uint4 (one L1 request per 4 classes).
+__host__ __device__ __forceinline__ int pad4(int n) { return (n + 3) & ~3; }
 constexpr int kHistBins = 2 * kNBins;      // per site in flight: [base][qual][strand]
 constexpr int kHistWords = kHistBins + 8;  // + the 8 indel bins (strand << 2 | stale base) right behind them
 
@@ -199,9 +204,10 @@ __device__ __forceinline__ void hist_emit(const PipeArgs& a, int site, bool live
     const int ncls = ncb[0] + ncb[1] + ncb[2] + ncb[3];
     const int n_major = best == 0 ? ncb[0] : best == 1 ? ncb[1] : best == 2 ? ncb[2] : ncb[3];
     uint32_t off = 0;
-    if (g == 0 && ncls) off = atomicAdd(a.cls_cursor, (uint32_t)ncls);
+    if (g == 0 && ncls) off = atomicAdd(a.cls_cursor, (uint32_t)pad4(pad4(n_major) + ncls - n_major));
     off = __shfl_sync(0xffffffffu, off, gl);
-    uint32_t run = off + (uint32_t)n_major;
+    if (g < 4 && n_major + g < pad4(n_major)) a.cls[off + n_major + g] = kNullClass;
+    uint32_t run = off + (uint32_t)pad4(n_major);
 #pragma unroll
     for (int b = 0; b < 4; ++b) {
         uint32_t pos;
@@ -279,6 +285,18 @@ __device__ __forceinline__ void red_add_if(uint32_t* p, uint32_t v, bool pred)
     asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q red.shared.add.u32 [%0], %1;\n\t}"
                  :: "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v), "r"((uint32_t)pred) : "memory");
 }
+__device__ __forceinline__ void red_add_s(uint32_t saddr, uint32_t v, bool pred)      // saddr: shared-window byte address
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q red.shared.add.u32 [%0], %1;\n\t}"
+                 :: "r"(saddr), "r"(v), "r"((uint32_t)pred) : "memory");
+}
+// code bytes of the word at entry e0 that lie outside [lo_e, hi_e) become 0x14 (indel, base 4): nothing counts them
+__device__ __forceinline__ uint32_t mask_outside(uint32_t cw, uint32_t e0, uint32_t lo_e, uint32_t hi_e)
+{
+    const uint32_t lo = lo_e > e0 ? min(lo_e - e0, 4u) : 0u, hi = hi_e < e0 + 4 ? (hi_e > e0 ? hi_e - e0 : 0u) : 4u;
+    const uint32_t vm = (hi >= 4 ? 0xffffffffu : ((1u << (8 * hi)) - 1u)) & ~(lo >= 4 ? 0xffffffffu : ((1u << (8 * lo)) - 1u));
+    return (cw & vm) | (0x14141414u & ~vm);
+}
 __device__ __forceinline__ int bfly8(int v)
 {
     v += __shfl_xor_sync(0xffffffffu, v, 1);
@@ -297,47 +315,86 @@ site_hist4_kernel(PipeArgs a)
     for (int i = lane; i < kH4Sites * kH4Words; i += 32) hw[i] = 0;
     __syncwarp();
     uint32_t* hist = hw + gi * kH4Words;                        // my group's site during the emit
+    const uint32_t hw_s = (uint32_t)__cvta_generic_to_shared(hw);
     const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
     const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
     const int S = a.s.n_sites;
     const int n_batches = (S + kH4Sites - 1) / kH4Sites;
     const unsigned lt = (1u << g) - 1u;
 
-    for (int batch = blockIdx.x * kHistWarps + wid; batch < n_batches; batch += gridDim.x * kHistWarps) {
+    const int stride = gridDim.x * kHistWarps;
+    int batch = blockIdx.x * kHistWarps + wid;
+    uint32_t ov = 0;
+    if (batch < n_batches && lane <= kH4Sites) ov = a.s.entry_off[min(batch * kH4Sites + lane, S)];
+    for (; batch < n_batches; batch += stride) {
         const int s0 = batch * kH4Sites;
-        uint32_t ov = 0;
-        if (lane <= kH4Sites) ov = a.s.entry_off[min(s0 + lane, S)];
+        // the offsets of this warp's NEXT batch: loaded now, used (a) before the emit to pull that batch's bytes into L2
+        // while this one is emitted, (b) as the next iteration's offsets -- no dependent load at the top of a batch
+        uint32_t nov = 0;
+        if (batch + stride < n_batches && lane <= kH4Sites) nov = a.s.entry_off[min((batch + stride) * kH4Sites + lane, S)];
         const uint32_t o0 = __shfl_sync(0xffffffffu, ov, 0), o1 = __shfl_sync(0xffffffffu, ov, 1), o2 = __shfl_sync(0xffffffffu, ov, 2),
                        o3 = __shfl_sync(0xffffffffu, ov, 3), o4 = __shfl_sync(0xffffffffu, ov, 4);
-        // ---- stream [o0, o4): 4 entries per lane per 32-bit load -------------------------------------------------
+        // ---- stream [o0, o4): 4 entries per lane per 32-bit load.  A word goes to the site of its FIRST entry; the
+        // <= 3 words that straddle a site boundary are corrected afterwards.  Bin byte offsets (base << 9 | qual << 2)
+        // are formed two entries at a time in 16-bit lanes; qmin / qmax run over every byte of the range's words
+        // (pad and indel bytes carry real quals of neighbouring entries: a superset range is all the emit needs).
         uint32_t qmax = 0, qmin = 127;
         const uint32_t w0 = o0 >> 2, w1 = (o4 + 3) >> 2;
-#pragma unroll 2
+        const uint32_t A1 = (o1 + 3) >> 2, A2 = (o2 + 3) >> 2, A3 = (o3 + 3) >> 2;     // first word wholly behind boundary k
+#pragma unroll 4
         for (uint32_t wi = w0 + lane; wi < w1; wi += 32) {
             uint32_t cw = __ldg(code4 + wi);
             const uint32_t qw = __ldg(qual4 + wi) & 0x7f7f7f7fu;
-            const uint32_t e0 = wi * 4;
-            if (e0 < o0 || e0 + 4 > o4) {                       // first / last word of the range: bytes outside -> code 0x14
-                const uint32_t lo = o0 > e0 ? o0 - e0 : 0u, hi = o4 < e0 + 4 ? o4 - e0 : 4u;
-                const uint32_t vm = (hi >= 4 ? 0xffffffffu : ((1u << (8 * hi)) - 1u)) & ~((1u << (8 * lo)) - 1u);
-                cw = (cw & vm) | (0x14141414u & ~vm);
-            }
-            const uint32_t kf = (uint32_t)(e0 >= o1) + (uint32_t)(e0 >= o2) + (uint32_t)(e0 >= o3);
-            const uint32_t kl = (uint32_t)(e0 + 3 >= o1) + (uint32_t)(e0 + 3 >= o2) + (uint32_t)(e0 + 3 >= o3);
-            const bool straddle = kf != kl;                     // the word spans a site boundary (<= 3 words per batch)
+            if (wi == w0 || wi + 1 == w1) cw = mask_outside(cw, wi * 4, o0, o4);
+            const uint32_t kf = (uint32_t)(wi >= A1) + (uint32_t)(wi >= A2) + (uint32_t)(wi >= A3);
+            const uint32_t hb = hw_s + kf * (uint32_t)(kH4Words * 4);
+            const uint32_t ce = cw & 0x00ff00ffu, co = (cw >> 8) & 0x00ff00ffu;
+            const uint32_t qe = qw & 0x00ff00ffu, qo = (qw >> 8) & 0x00ff00ffu;
+            const uint32_t be = ((ce & 0x00030003u) << 9) | (qe << 2), bo = ((co & 0x00030003u) << 9) | (qo << 2);
+            const uint32_t sw = (cw >> 3) & 0x01010101u;                              // strand bits: forward counts in the high half
+            qmin = min(qmin, min(min(qe & 0xffffu, qe >> 16), min(qo & 0xffffu, qo >> 16)));
+            qmax = max(qmax, max(max(qe & 0xffffu, qe >> 16), max(qo & 0xffffu, qo >> 16)));
+            red_add_s(hb + (be & 0xffffu), (sw & 1u) * 0xffffu + 1u, !(cw & 0x00000014u));
+            red_add_s(hb + (bo & 0xffffu), ((sw >> 8) & 1u) * 0xffffu + 1u, !(cw & 0x00001400u));
+            red_add_s(hb + (be >> 16), ((sw >> 16) & 1u) * 0xffffu + 1u, !(cw & 0x00140000u));
+            red_add_s(hb + (bo >> 16), (sw >> 24) * 0xffffu + 1u, !(cw & 0x14000000u));
+            if (cw & 0x10101010u) {                                                   // indel entries keep only (stale base, strand)
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint32_t c = cw >> (8 * k), q = (qw >> (8 * k)) & 0x7fu;
-                const bool ok = !(c & 0x14u);
-                qmin = min(qmin, ok ? q : 127u); qmax = max(qmax, ok ? q : 0u);
-                uint32_t ks = kf;
-                if (straddle) { const uint32_t e = e0 + k; ks = (uint32_t)(e >= o1) + (uint32_t)(e >= o2) + (uint32_t)(e >= o3); }
-                const uint32_t bin = (c & 0x10u) ? (uint32_t)kNBins + (((c >> 1) & 4u) | (c & 3u)) : (((c & 3u) << 7) | q);
-                const uint32_t inc = (c & 0x10u) ? 1u : (1u << ((c & 8u) << 1));      // forward strand counts in the high half
-                red_add_if(&hw[ks * kH4Words + bin], inc, !(c & 4u));
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t c = cw >> (8 * k);
+                    red_add_s(hb + 4u * ((uint32_t)kNBins + (((c >> 1) & 4u) | (c & 3u))), 1u, (c & 0x14u) == 0x10u);
+                }
+            }
+        }
+        // straddling words: lane k-1 <-> boundary k; one lane per distinct straddling word moves the entries behind the
+        // boundary from the site the word was credited to to their own sites (atomic adds commute: no ordering needed)
+        if (lane < 3) {
+            const uint32_t ok_ = lane == 0 ? o1 : lane == 1 ? o2 : o3, op_ = lane == 0 ? o0 : lane == 1 ? o1 : o2;
+            const bool dup = lane > 0 && (op_ & 3u) && (op_ >> 2) == (ok_ >> 2);      // the previous boundary's lane has this word
+            if ((ok_ & 3u) && ok_ < o4 && !dup) {
+                const uint32_t wi = ok_ >> 2, e0 = wi * 4;
+                const uint32_t cw = mask_outside(__ldg(code4 + wi), e0, o0, o4), qw = __ldg(qual4 + wi) & 0x7f7f7f7fu;
+                const uint32_t kf = (uint32_t)(wi >= A1) + (uint32_t)(wi >= A2) + (uint32_t)(wi >= A3);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t c = cw >> (8 * k), q = (qw >> (8 * k)) & 0x7fu, e = e0 + k;
+                    const uint32_t ks = (uint32_t)(e >= o1) + (uint32_t)(e >= o2) + (uint32_t)(e >= o3);
+                    const uint32_t bin = (c & 0x10u) ? (uint32_t)kNBins + (((c >> 1) & 4u) | (c & 3u)) : (((c & 3u) << 7) | q);
+                    const uint32_t inc = (c & 0x10u) ? 1u : (1u << ((c & 8u) << 1));
+                    const bool mv = !(c & 4u) && ks != kf;
+                    red_add_s(hw_s + 4u * (kf * kH4Words + bin), 0u - inc, mv);
+                    red_add_s(hw_s + 4u * (ks * kH4Words + bin), inc, mv);
+                }
             }
         }
         __syncwarp();
+        {
+            const uint32_t p0 = __shfl_sync(0xffffffffu, nov, 0) & ~127u, p4 = __shfl_sync(0xffffffffu, nov, kH4Sites);
+            for (uint32_t pa = p0 + (uint32_t)lane * 128u; pa < p4; pa += 32u * 128u) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(a.s.code + pa));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(a.s.qual + pa));
+            }
+        }
         // one qual range for the whole batch (a superset for each of its sites)
         qmax = __reduce_max_sync(0xffffffffu, qmax);
         qmin = __reduce_min_sync(0xffffffffu, qmin);
@@ -392,13 +449,15 @@ site_hist4_kernel(PipeArgs a)
         // pool space for the four sites with one atomic
         const int ncls = ncb[0] + ncb[1] + ncb[2] + ncb[3];
         const int n_major = best == 0 ? ncb[0] : best == 1 ? ncb[1] : best == 2 ? ncb[2] : ncb[3];
-        const int n0 = __shfl_sync(0xffffffffu, ncls, 0), n1 = __shfl_sync(0xffffffffu, ncls, 8),
-                  n2 = __shfl_sync(0xffffffffu, ncls, 16), n3 = __shfl_sync(0xffffffffu, ncls, 24);
+        const int nalloc = ncls ? pad4(pad4(n_major) + ncls - n_major) : 0;
+        const int n0 = __shfl_sync(0xffffffffu, nalloc, 0), n1 = __shfl_sync(0xffffffffu, nalloc, 8),
+                  n2 = __shfl_sync(0xffffffffu, nalloc, 16), n3 = __shfl_sync(0xffffffffu, nalloc, 24);
         uint32_t off = 0;
         if (lane == 0 && n0 + n1 + n2 + n3) off = atomicAdd(a.cls_cursor, (uint32_t)(n0 + n1 + n2 + n3));
         off = __shfl_sync(0xffffffffu, off, 0) + (uint32_t)(gi > 0 ? n0 : 0) + (uint32_t)(gi > 1 ? n1 : 0) + (uint32_t)(gi > 2 ? n2 : 0);
         // classes to the pool, the MAJOR base first (K3 runs that segment select-free); clears the bins
-        uint32_t run = off + (uint32_t)n_major;
+        if (g < 4 && n_major + g < pad4(n_major)) a.cls[off + n_major + g] = kNullClass;
+        uint32_t run = off + (uint32_t)pad4(n_major);
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
             uint32_t pos;
@@ -423,6 +482,7 @@ site_hist4_kernel(PipeArgs a)
         else v = make_uint4(off, (uint32_t)(ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0)),
                             (uint32_t)n_entries, (uint32_t)(n_major | (best << 16)));
         if (live && g < 4) reinterpret_cast<uint4*>(a.sum + site)[g] = v;
+        ov = nov;
         __syncwarp();
     }
 }
@@ -663,8 +723,6 @@ __device__ __forceinline__ double cnt_to_double(uint32_t cnt)
 
 struct EmAcc { double accT, V0, V1, V2, V3, dl; int xmax; };   // xmax: max over classes of the high word of |x|
 constexpr int kBigXHi = 0x3f600000;       // high word of 2^-9: |x| >= 2^-9  <=>  hi(|x|) >= kBigXHi
-// a class word that contributes exactly nothing (count 0) with finite arithmetic for any valid f: (base 0, qual 30)
-constexpr uint32_t kNullClass = 30u;
 
 // Branch-free 4-way selects by the class's base bits (bit 7 / bit 8 of the class word): nvcc turns the
 // equivalent C ternaries into divergent branches, which serialises lanes whose classes differ in base.
@@ -823,21 +881,26 @@ em_fit_kernel(PipeArgs a)
             active = false;
         }
         if (__any_sync(0xffffffffu, active)) {
-            const int nmaj_max = __reduce_max_sync(0xffffffffu, active ? nmaj : 0);
-            const int nmin_max = __reduce_max_sync(0xffffffffu, active ? nmin : 0);
-            // ---- one pass.  Straight-line bodies: a lane past its last class (or without a fit) processes a
-            // count-0 null class, so the unrolled bodies interleave (ILP) instead of sitting behind branches.
+            const int my_maj4 = active ? (nmaj + 3) >> 2 : 0, my_min = active ? nmin : 0;
+            const int nmaj4_max = __reduce_max_sync(0xffffffffu, my_maj4);
+            const int nmin_max = __reduce_max_sync(0xffffffffu, my_min);
+            // ---- one pass.  Straight-line bodies: a lane past its last class (or without a fit) processes
+            // count-0 null classes, so the unrolled bodies interleave (ILP) instead of sitting behind branches.
+            // The major segment is read four classes per load (16-byte aligned, null-padded by K1).
             double accT = 0.0, Vm = 0.0, V0 = 0.0, V1 = 0.0, V2 = 0.0, V3 = 0.0;
-            const int my_maj = active ? nmaj : 0, my_min = active ? nmin : 0;
             const double fm = sel4(major, f0, f1, f2, f3);
-#pragma unroll 4
-            for (int c = 0; c < nmaj_max; ++c) {
-                const uint32_t w = (c < my_maj) ? __ldg(cp + c) : kNullClass;
-                em_class_major(w, lut2, fm, F, accT, Vm);
+            const uint4* cp4 = reinterpret_cast<const uint4*>(cp);
+            const uint32_t* cmin = cp + 4 * my_maj4;
+            for (int c = 0; c < nmaj4_max; ++c) {
+                const uint4 w = (c < my_maj4) ? __ldg(cp4 + c) : make_uint4(kNullClass, kNullClass, kNullClass, kNullClass);
+                em_class_major(w.x, lut2, fm, F, accT, Vm);
+                em_class_major(w.y, lut2, fm, F, accT, Vm);
+                em_class_major(w.z, lut2, fm, F, accT, Vm);
+                em_class_major(w.w, lut2, fm, F, accT, Vm);
             }
 #pragma unroll 2
             for (int c = 0; c < nmin_max; ++c) {
-                const uint32_t w = (c < my_min) ? __ldg(cp + my_maj + c) : kNullClass;
+                const uint32_t w = (c < my_min) ? __ldg(cmin + c) : kNullClass;
                 em_class_minor(w, lut2, f0, f1, f2, f3, F, accT, V0, V1, V2, V3);
             }
             if (active) {
@@ -910,7 +973,7 @@ em_long_kernel(PipeArgs a)
 
     bool active = false, done = false;
     const uint32_t* cp = a.cls;
-    int ncls = 0, pass = 0;
+    int ncls = 0, nmaj = 0, pass = 0;
     uint32_t item = 0, fl = 0;
     double f0 = 0, f1 = 0, f2 = 0, f3 = 0, p0 = 0, p1 = 0, p2 = 0, p3 = 0, F = 0, Fp = 0, inv_n = 0;
 
@@ -934,7 +997,7 @@ em_long_kernel(PipeArgs a)
                     F = ((f0 + f1) + f2) + f3; Fp = ((p0 + p1) + p2) + p3;
                     pass = fr->passes; fl = fr->flags;
                     inv_n = 1.0 / (double)(su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3]);
-                    cp = a.cls + su.cls_off; ncls = su.ncls;
+                    cp = a.cls + su.cls_off; ncls = su.ncls; nmaj = su.n_major;
                     active = true;
                 } else done = true;
             }
@@ -946,8 +1009,8 @@ em_long_kernel(PipeArgs a)
         EmAcc A; A.accT = A.V0 = A.V1 = A.V2 = A.V3 = A.dl = 0.0; A.xmax = 0;
 #pragma unroll 2
         for (int k = 0; k < trips; ++k) {
-            const int c = k * kLongGroup + g;
-            const uint32_t w = (c < nmine) ? __ldg(cp + c) : kNullClass;
+            const int c = k * kLongGroup + g;               // class index -> pool word: the minor classes start behind the padding
+            const uint32_t w = (c < nmine) ? __ldg(cp + (c < nmaj ? c : c + (pad4(nmaj) - nmaj))) : kNullClass;
             em_class_exact(w, lut2, f0, f1, f2, f3, F, p0, p1, p2, p3, Fp, A);
         }
 #pragma unroll
@@ -1014,7 +1077,7 @@ fit_loglik_kernel(PipeArgs a)
         if (on) {
             const SiteSum su = a.sum[item >> 2];
             f0 = fr->f[0]; f1 = fr->f[1]; f2 = fr->f[2]; f3 = fr->f[3];
-            cp = a.cls + su.cls_off; ncls = su.ncls; mask = fr->mask;
+            cp = a.cls + su.cls_off; ncls = pad4(su.n_major) + (su.ncls - su.n_major); mask = fr->mask;
         }
         // a two-allele model is followed by the two single-base models of its alleles (BaseType.cpp:93-110 at k = 1):
         // closed form, lr = sum_c cnt_c log L_c,b -- accumulated here, in the same class loop (see ladder_site)
@@ -1053,7 +1116,8 @@ __device__ __forceinline__ double single_loglik(const PipeArgs& a, const SiteSum
 {
     const uint32_t* cp = a.cls + su.cls_off;
     double s = 0.0;
-    for (int c = 0; c < su.ncls; ++c) {
+    const int n = pad4(su.n_major) + (su.ncls - su.n_major);
+    for (int c = 0; c < n; ++c) {
         const uint32_t w = __ldg(cp + c);
         const int q = w & (kNQ - 1), b = (w >> 7) & 3;
         s = fma((double)(w >> 9), __ldg(a.s.lut + (b == base ? 3 : 2) * kNQ + q), s);

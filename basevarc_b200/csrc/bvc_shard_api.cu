@@ -117,8 +117,8 @@ static int shard_alloc(bvc_ctx* ctx, int rank, int world, int qlo, int qhi, bool
     // the class pool must hold every (base, qual) class of the owned sites, whatever the local entry capacity
     Slot& s = ctx->slot[0];
     const size_t S = (size_t)ctx->prm.max_sites, R = (size_t)ctx->prm.max_entries;
-    const size_t have = R < S * (size_t)kNBins ? R : S * (size_t)kNBins;
-    const size_t need = (size_t)st->sr_cap * 4 * (size_t)(qhi - qlo + 1);
+    const size_t have = (R < S * (size_t)kNBins ? R : S * (size_t)kNBins) + 8 * S;
+    const size_t need = (size_t)st->sr_cap * (4 * (size_t)(qhi - qlo + 1) + 8);
     if (need > have) {
         CK(cudaFree(s.d_cls)); s.d_cls = nullptr;
         CK(cudaMalloc(&s.d_cls, (need + 64) * sizeof(uint32_t)));
