@@ -185,4 +185,81 @@ __device__ __forceinline__ long long warp_sum_ll(long long v)
     return v;
 }
 
+// ---- warp-cooperative Fisher exact test -------------------------------------------------------------------------
+// kt_fisher_exact's recurrence (kfunc.c:218-241) is re-anchored with lgamma whenever n11 % 11 == 0, so the chain of
+// table probabilities falls into independent SEGMENTS of <= 11 terms: a direct (lgamma) value followed by incremental
+// products.  Each lane takes one segment per round and produces bit-for-bit the p values of the serial walk; only the
+// order in which the tail sums are added differs (per-lane partial sums + a butterfly), i.e. rounding in the last
+// place.  The serial loop of kfunc.c:258-270 adds terms until the first one with p >= 0.99999999 q (index T, or the
+// end of the range) and then adds p(T) iff p(T) < 1.00000001 q; that is what tail() returns.
+struct FisherTail {
+    const double* lgam; int n1_, n_1, n, lo, hi; double q;
+
+    // the terms of segment `seg` of the walk starting at `lo` going up (dir = +1) or at `hi` going down (dir = -1)
+    __device__ __forceinline__ void segment(int dir, int seg, double& sum, bool& stop, double& pstop) const
+    {
+        sum = 0.0; stop = false; pstop = 0.0;
+        int first, last;                                          // inclusive, in walk order
+        if (dir > 0) {
+            first = seg == 0 ? lo : (lo - lo % 11) + 11 * seg;
+            last = (first - first % 11) + 10;
+            if (last > hi) last = hi;
+            if (first > hi) return;
+        } else {
+            const int top = hi % 11 == 0 ? hi : hi - hi % 11 + 11;   // the first direct point is hi itself
+            first = seg == 0 ? hi : top - 11 * seg;
+            if (first < lo) return;
+            last = first % 11 == 0 ? first - 10 : first - first % 11 + 1;
+            if (last < lo) last = lo;
+        }
+        double p = dm_hypergeo(lgam, first, n1_, n_1, n);
+        const double c = 0.99999999 * q;
+        for (int i = first;; i += dir) {
+            if (!(p < c)) { stop = true; pstop = p; return; }
+            sum += p;
+            if (i == last) return;
+            const int nx = i + dir;
+            const int n22 = nx + n - n1_ - n_1;
+            if (dir > 0) p *= (double)(n1_ - i) / nx * (n_1 - i) / n22;                    // kfunc.c:224-225
+            else         p *= (double)i / (n1_ - nx) * (i + n - n1_ - n_1) / (n_1 - nx);   // kfunc.c:230-231
+        }
+    }
+
+    __device__ __forceinline__ double tail(int dir, int lane) const
+    {
+        double total = 0.0;
+        const int n_seg = (hi - lo) / 11 + 2;
+        for (int s0 = 0; s0 < n_seg; s0 += 32) {
+            double sum, pstop; bool stop;
+            segment(dir, s0 + lane, sum, stop, pstop);
+            const unsigned m = __ballot_sync(0xffffffffu, stop);
+            const int firststop = m ? __ffs(m) - 1 : 32;
+            total += warp_sum(lane <= firststop ? sum : 0.0);
+            if (m) {
+                const double pT = __shfl_sync(0xffffffffu, pstop, firststop);
+                if (pT < 1.00000001 * q) total += pT;
+                return total;
+            }
+        }
+        return total;                                             // ran off the range: every term was below q
+    }
+};
+
+// same value on every lane; all 32 lanes must call it with the same table
+__device__ __noinline__ double dm_fisher_warp(const double* __restrict__ lgam, int n11, int n12, int n21, int n22, int lane)
+{
+    FisherTail t;
+    t.lgam = lgam; t.n1_ = n11 + n12; t.n_1 = n11 + n21; t.n = n11 + n12 + n21 + n22;
+    t.hi = t.n_1 < t.n1_ ? t.n_1 : t.n1_;
+    t.lo = t.n1_ + t.n_1 - t.n;
+    if (t.lo < 0) t.lo = 0;
+    double two = 1.;
+    if (t.lo != t.hi) {
+        t.q = dm_hypergeo(lgam, n11, t.n1_, t.n_1, t.n);
+        two = t.tail(+1, lane) + t.tail(-1, lane);
+        if (two > 1.) two = 1.;
+    }
+    return dm_phred(two);
+}
+
 }  // namespace bvc

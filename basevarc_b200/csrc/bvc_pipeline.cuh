@@ -1239,7 +1239,7 @@ vcf_stats_kernel(PipeArgs a)
             if (b == ref) { vs[0] = su.fwd[b]; vs[1] = su.depth[b] - su.fwd[b]; }
             else if (altmask >> b & 1) { vs[2] += su.fwd[b]; vs[3] += su.depth[b] - su.fwd[b]; }
         }
-        const double vcf_fs = dm_fisher(a.s.lgam, vs[0], vs[1], vs[2], vs[3]);
+        const double vcf_fs = dm_fisher_warp(a.s.lgam, vs[0], vs[1], vs[2], vs[3], lane);
         const double vcf_sor = dm_sor(vs[0], vs[1], vs[2], vs[3]);
         for (int j = lane; j < 6 * 256; j += 32) H[j] = 0;
         __syncwarp();

@@ -238,7 +238,7 @@ shard_vcf_finish_kernel(ShardArgs a)
             if (b == ref) { vs[0] = su.fwd[b]; vs[1] = su.depth[b] - su.fwd[b]; }
             else if (altmask >> b & 1) { vs[2] += su.fwd[b]; vs[3] += su.depth[b] - su.fwd[b]; }
         }
-        const double vcf_fs = dm_fisher(a.p.s.lgam, vs[0], vs[1], vs[2], vs[3]);
+        const double vcf_fs = dm_fisher_warp(a.p.s.lgam, vs[0], vs[1], vs[2], vs[3], lane);
         const double vcf_sor = dm_sor(vs[0], vs[1], vs[2], vs[3]);
         const uint32_t* H = a.hv + (size_t)i * kVcfHistWords;
         double rs[3];
