@@ -146,6 +146,7 @@ void bvc::fill_args(const bvc_ctx* ctx, const Slot& s, SiteArgs& a, PipeArgs& p)
     p.vcf_list = s.d_vcf_list; p.vcf_n = s.d_ctr + 4;
     p.legacy_list = s.d_legacy_list; p.legacy_n = s.d_ctr + 5;
     p.q_sorted = s.d_qs; p.q_long = s.d_ql; p.q_long_n = s.d_ctr + 6; p.q_long_head = s.d_ctr + 7;
+    p.deep_list = s.d_ql; p.deep_n = s.d_ctr + 16 + bvc::kNBins + 8;
     p.work = reinterpret_cast<unsigned long long*>(s.d_ctr + 8);
     p.bins = s.d_ctr + 16;
 }

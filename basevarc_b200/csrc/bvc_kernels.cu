@@ -244,6 +244,8 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     if (parts & kPartCore) {
     mark(kKPrepare);
     site_prepare_kernel<<<site_blocks, 128, 0, stream>>>(a);
+    mark(kKPrepare);
+    cvg_fisher_deep_kernel<<<(unsigned)(n_sm * 4), 128, 0, stream>>>(a);
     // at most three EM stages: the full model, the (n-1)-subsets (n >= 3), the pairs of a reduced 4-candidate site
     for (int stage = 0; stage < 3; ++stage) {
         uint32_t* t;

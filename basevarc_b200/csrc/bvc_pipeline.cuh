@@ -567,6 +567,31 @@ __device__ __noinline__ void finalize_site(const PipeArgs& a, int site, int ref,
 // =====================================================================================================
 // K2: thread per site -- CVG Fisher/SOR, candidate filter, emit the full-model fit
 // =====================================================================================================
+constexpr int kDeepFisher = 48;            // tables with more terms than this are evaluated by a whole warp
+__device__ __forceinline__ int fisher_range(int n11, int n12, int n21, int n22)
+{
+    const int n1_ = n11 + n12, n_1 = n11 + n21, n = n1_ + n21 + n22;
+    const int hi = n_1 < n1_ ? n_1 : n1_, lo = n1_ + n_1 - n;
+    return hi - (lo < 0 ? 0 : lo);
+}
+
+// warp per listed site: the CVG Fisher test K2 skipped.  The value lands where K2 would have put it: in the record of
+// a site K2 already finalised, else in the site's Ladder (K4 stores the record).
+__global__ void __launch_bounds__(128)
+cvg_fisher_deep_kernel(PipeArgs a)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t n = *a.deep_n;
+    for (uint32_t i = blockIdx.x * 4 + (threadIdx.x >> 5); i < n; i += gridDim.x * 4) {
+        const int site = (int)a.deep_list[i];
+        const SiteSum su = a.sum[site];
+        const double fs = dm_fisher_warp(a.s.lgam, su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3], lane);
+        if (lane == 0) {
+            if (a.state[site] == kStDone) a.s.out[site].cvg_fs = fs; else a.lad[site].cvg_fs = fs;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(128)
 site_prepare_kernel(PipeArgs a)
 {
@@ -581,7 +606,11 @@ site_prepare_kernel(PipeArgs a)
             a.state[site] = kStLegacy;
             a.legacy_list[atomicAdd(a.legacy_n, 1u)] = (uint32_t)site;
         } else {
-            const double cvg_fs = dm_fisher(a.s.lgam, su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
+            // kt_fisher_exact walks up to (max n11 - min n11) terms: a deep table would make this thread the kernel's
+            // tail (C4: thousands of terms at a common variant), so it goes to cvg_fisher_deep_kernel (warp per site)
+            double cvg_fs = 0.0;
+            if (fisher_range(su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]) > kDeepFisher) a.deep_list[atomicAdd(a.deep_n, 1u)] = (uint32_t)site;
+            else cvg_fs = dm_fisher(a.s.lgam, su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
             const double cvg_sor = dm_sor(su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
             // BaseType.cpp:75-82
             int8_t cand[4]; int n = 0; uint32_t flags = 0, full = 0;

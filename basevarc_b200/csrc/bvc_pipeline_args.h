@@ -76,6 +76,8 @@ struct PipeArgs {
     uint32_t* vcf_n;
     uint32_t* legacy_list;      // sites for the IEEE-faithful warp-per-site kernel
     uint32_t* legacy_n;
+    uint32_t* deep_list;        // sites whose CVG Fisher table is deep: K2 leaves them to the warp-cooperative kernel
+    uint32_t* deep_n;           //   (aliases q_long: that queue is idle until the first EM stage)
 };
 
 // ---- sample-sharded mode (bvc_shard.cuh) ---------------------------------------------------------------

@@ -24,8 +24,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# NCCL_DEBUG=VERSION (this image's default) prints a banner on stdout: the contract is ONE JSON line there
-os.environ["NCCL_DEBUG"] = os.environ.get("BVC_NCCL_DEBUG", "WARN")
+# NCCL prints its version banner on STDOUT at the VERSION and WARN debug levels: the contract is ONE JSON line there
+os.environ["NCCL_DEBUG"] = os.environ.get("BVC_NCCL_DEBUG", "NONE")
 
 METRIC = "site*samples/sec for basetype EM+LRT"
 # FP64 operations em_fit_kernel's arithmetic performs per (base, qual) class per singleEM pass, FMA = 2
