@@ -158,12 +158,51 @@ class ReferenceRun:
             raise RuntimeError("reference binary failed: %s" % r.stderr[-500:])
         return self.tile.n_sites * self.tile.n_samples / dt, dt
 
+    def dropin(self):
+        """This repo's drop-in (basevarc_b200/bin/BaseVarC_b200, same command line) on the same batch files: wall time of
+        the whole command (CUDA context creation included) and whether its .cvg / .vcf text equals the reference's."""
+        import gzip
+        ours = os.path.join(ROOT, "basevarc_b200", "bin", "BaseVarC_b200")
+        if not os.path.exists(ours):
+            return None
+        ref_txt = {}
+        for ext in ("cvg", "vcf"):
+            with gzip.open(self.prefix + "." + ext + ".gz", "rb") as f:
+                ref_txt[ext] = f.read()
+            os.rename(self.prefix + "." + ext + ".gz", self.prefix + ".ref." + ext + ".gz")
+        best = None
+        for _ in range(2):                                   # second run: page cache and driver warm, as for the reference
+            t0 = time.perf_counter()
+            r = subprocess.run([ours] + self.cmd[1:], cwd=self.dir, capture_output=True, text=True)
+            dt = time.perf_counter() - t0
+            if r.returncode != 0:
+                return {"error": (r.stderr or r.stdout)[-300:]}
+            best = dt if best is None else min(best, dt)
+        out = {"seconds": best, "value": self.tile.n_sites * self.tile.n_samples / best, "unit": UNIT}
+        for ext in ("cvg", "vcf"):
+            with gzip.open(self.prefix + "." + ext + ".gz", "rb") as f:
+                mine = f.read()
+            a, b = mine.split(b"\n"), ref_txt[ext].split(b"\n")
+            body = lambda ls: [l for l in ls if not l.startswith(b"##")]      # header lines carry the command / date
+            a, b = body(a), body(b)
+            if ext == "cvg":
+                # column 9 (Indels) comes out in the reference's hash-map iteration order (SURVEY Q10): compared as a multiset
+                def norm(l):
+                    f = l.split(b"\t")
+                    if len(f) > 8:
+                        f[8] = b",".join(sorted(f[8].split(b",")))
+                    return b"\t".join(f)
+                a, b = [norm(l) for l in a], [norm(l) for l in b]
+            out[ext + "_lines"] = len(b)
+            out[ext + "_lines_differing"] = sum(1 for x, y in zip(a, b) if x != y) + abs(len(a) - len(b))
+        return out
+
     def close(self):
         import shutil
         shutil.rmtree(self.dir, ignore_errors=True)
 
 
-def cpu_reference_baseline(tile, sites_per_thread, cores, steps=1, warmup=0):
+def cpu_reference_baseline(tile, sites_per_thread, cores, steps=1, warmup=0, dropin=None):
     """(value, sites, seconds per step, kind): the reference binary when it was built, else the oracle port."""
     S = min(tile.n_sites, sites_per_thread * cores)
     if os.path.exists(REF_BIN):
@@ -173,6 +212,9 @@ def cpu_reference_baseline(tile, sites_per_thread, cores, steps=1, warmup=0):
             for _ in range(warmup):
                 run.step()
             res = [run.step() for _ in range(max(steps, 1))]
+            if dropin is not None:
+                dropin["ref_seconds"] = float(np.mean([d for _, d in res]))
+                dropin.update(run.dropin() or {"error": "BaseVarC_b200 not built"})
         finally:
             run.close()
         return float(np.mean([v for v, _ in res])), S, float(np.mean([d for _, d in res])), "reference"
@@ -479,11 +521,15 @@ def main():
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
-        v, s_cpu, dt, kind = cpu_reference_baseline(tile, max(1, args.ref_sites_per_thread * 1000 // N), cores)
+        dropin = {}
+        v, s_cpu, dt, kind = cpu_reference_baseline(tile, max(1, args.ref_sites_per_thread * 1000 // N), cores, dropin=dropin)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                "sample": "first %d sites x %d samples of the same window, %.1f s (%s)" % (
                    s_cpu, N, dt, "unmodified reference binary, basetype --rerun -t %d" % cores if kind == "reference"
                    else "oracle C restatement, per-read")}
+        if dropin:
+            # the whole command line as a drop-in: same batch files, same -t; host inflate / tokenise / format included
+            cpu["rerun_cli"] = dropin
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
