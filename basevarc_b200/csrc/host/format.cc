@@ -4,10 +4,11 @@
 // (src/BaseType.cpp:143-163,198-233) under /root/reference.  No statistic is computed here: every number
 // comes from the bvc_site_result; the only arithmetic is what the reference itself does while printing
 // (1 - exp(MLN10TO10 * qual) per sample column, depth / depth_total, var_qual / sum of ALT depths).
-// fmt's {:.Nf} is printf's %.Nf (correctly rounded, "nan"/"inf" with the sign bit's '-').
+// fmt's {:.Nf} is printf's %.Nf ("nan"/"inf" with the sign bit's '-') except for tiny values: see put_fixed.
 #include "format.hpp"
 
 #include <math.h>
+#include <stdint.h>
 #include <stdio.h>
 #include <string.h>
 #include <algorithm>
@@ -21,9 +22,90 @@ const char kBase2Char[8] = {'A', 'C', 'G', 'T', 'N', 'N', 'N', 'N'};   // the re
 const char kStrand[2] = {'-', '+'};
 const double kMLN10TO10 = -0.23025850929940458;                        // src/BaseType.h:10
 
+// ---- the reference's "{:.Nf}" ----------------------------------------------------------------------------------
+// The reference prints through the fmt 5.3.1 it vendors (fmt/include/fmt/format-inl.h).  For ordinary values its fixed
+// format equals printf's %.Nf.  For a TINY non-zero value -- all N requested decimals are leading zeros -- that version
+// stops in fixed_handler::on_start (format-inl.h:591-605) with ONE digit, '1' or '0' by the rounding direction of the
+// Grisu-scaled value against its own leading power of ten, and grisu_prettify (format.h:1092-1105) then prints that digit
+// BEHIND the N zeros: 9.6e-5 -> "0.0001", 4.9e-5 -> "0.0000" (printf: "0.000").  FS / SOR / rank-sum values of that size
+// occur at ~0.4 % of low-pass sites, so the drop-in restates the arithmetic: Grisu's normalised 64-bit product with the
+// cached power of ten (computed exactly here and rounded half-up like fmt's table), its digit count, and the same three
+// comparisons.  Anything else falls through to printf, as fmt does.
+struct CachedPow10 { uint64_t f; int e; };
+
+CachedPow10 pow10_normalized(int K)          // 10^K = f * 2^e with the top bit of f set; K >= 0
+{
+    uint32_t w[48] = {1};
+    int n = 1;
+    for (int i = 0; i < K; ++i) {
+        uint64_t carry = 0;
+        for (int j = 0; j < n; ++j) { const uint64_t x = (uint64_t)w[j] * 10u + carry; w[j] = (uint32_t)x; carry = x >> 32; }
+        if (carry) w[n++] = (uint32_t)carry;
+    }
+    const int bl = 32 * (n - 1) + (32 - __builtin_clz(w[n - 1]));
+    auto bit = [&](int i) -> uint64_t { return (i < 0 || i >= 32 * n) ? 0u : (w[i >> 5] >> (i & 31)) & 1u; };
+    CachedPow10 c; c.f = 0; c.e = bl - 64;
+    for (int i = 0; i < 64; ++i) c.f |= bit(bl - 64 + i) << i;
+    if (bit(bl - 65)) { if (++c.f == 0) { c.f = 1ull << 63; ++c.e; } }
+    return c;
+}
+
+// true: `v` (> 0, finite) takes fmt's one-digit path; *digit is the character printed behind *zeros zeros
+bool fmt_tiny_fixed(double v, int precision, char* digit, int* zeros)
+{
+    uint64_t u; memcpy(&u, &v, 8);
+    uint64_t f = u & ((1ull << 52) - 1);
+    int biased = (int)((u >> 52) & 0x7ff);
+    if (biased) f += 1ull << 52; else biased = 1;
+    int e = biased - 1075;
+    while (!(f & (1ull << 52))) { f <<= 1; --e; }               // fp::normalize
+    f <<= 11; e -= 11;
+    const int min_exponent = -60 - (e + 64);                    // get_cached_power (format-inl.h:452-463)
+    int index = (int)ceil((min_exponent + 63) * 0.30102999566398114);
+    index = (index + 348 - 1) / 8 + 1;
+    const int K = -348 + index * 8;
+    if (K <= 0 || K > 340) return false;                        // not a tiny value
+    static CachedPow10 cache[44]; static bool have[44];
+    const int ci = K / 8;                                       // K = 4, 12, ...
+    CachedPow10 c;
+    if (have[ci]) c = cache[ci]; else { c = pow10_normalized(K); cache[ci] = c; have[ci] = true; }   // idempotent: benign if raced
+    const unsigned __int128 prod = (unsigned __int128)f * c.f;  // fp operator* (round half up on bit 63)
+    uint64_t vf = (uint64_t)(prod >> 64);
+    if ((uint64_t)prod & (1ull << 63)) ++vf;
+    const int ve = e + c.e + 64;
+    if (ve < -60 || ve > -32) return false;
+    const uint32_t integral = (uint32_t)(vf >> -ve);
+    if (integral == 0) return false;
+    int kappa = 1;
+    for (uint32_t x = integral; x >= 10; x /= 10) ++kappa;
+    if (precision + kappa - K > 0) return false;                // digits are needed: the ordinary path (= printf)
+    static const uint64_t p10[10] = {1ull, 10ull, 100ull, 1000ull, 10000ull, 100000ull, 1000000ull, 10000000ull, 100000000ull, 1000000000ull};
+    const uint64_t divisor = p10[kappa - 1] << -ve, remainder = vf / 10, error = 10;
+    bool up;                                                    // get_round_direction (format-inl.h:469-483)
+    if (remainder <= divisor - remainder && error * 2 <= divisor - remainder * 2) up = false;
+    else if (remainder >= error && remainder - error >= divisor - (remainder - error)) up = true;
+    else return false;                                          // undecidable: fmt falls back to sprintf
+    const int full_exp = 1 + kappa - K;
+    if (full_exp > 0) return false;
+    *digit = up ? '1' : '0';
+    *zeros = -full_exp < precision ? -full_exp : precision;
+    return true;
+}
+
 inline void put_fixed(std::string& s, double v, int digits)
 {
     char b[64];
+    if (v != 0 && v == v && fabs(v) < 1.0 && fabs(v) <= 1.7e308) {
+        char d; int z;
+        if (fmt_tiny_fixed(fabs(v), digits, &d, &z)) {
+            if (signbit(v)) s += '-';
+            if (digits == 0 && d == '0') { s += '0'; return; }     // precision 0: no trailing zeros (format.h:2787-2788)
+            s += "0.";
+            s.append((size_t)z, '0');
+            s += d;
+            return;
+        }
+    }
     const int n = snprintf(b, sizeof b, "%.*f", digits, v);
     s.append(b, (size_t)n);
 }
@@ -34,6 +116,8 @@ inline void put_int(std::string& s, long long v)
     s.append(b, (size_t)n);
 }
 }  // namespace
+
+void format_fixed(std::string& out, double v, int digits) { put_fixed(out, v, digits); }
 
 void format_cvg(std::string& out, const char* chr, int32_t pos, const bvc_tile* t, int32_t site, const bvc_site_result* r,
                 const Packer* indel_src, int32_t n_groups, const int32_t* group_depth)

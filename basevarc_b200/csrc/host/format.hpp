@@ -14,4 +14,7 @@ void format_vcf(std::string& out, const char* chr, int32_t pos, const bvc_tile* 
                 int32_t n_samples, int32_t n_groups, const char* const* group_names, const int32_t* group_depth,
                 const double* group_af);
 
+// the reference's "{:.Nf}" (fmt 5.3.1, including its one-digit output for tiny values)
+void format_fixed(std::string& out, double v, int digits);
+
 }  // namespace bvc_host

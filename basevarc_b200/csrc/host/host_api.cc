@@ -52,4 +52,11 @@ size_t bvc_format_vcf(char* buf, size_t cap, const char* chr, int32_t pos, const
     return emit(s, buf, cap);
 }
 
+size_t bvc_format_fixed(char* buf, size_t cap, double v, int32_t digits)
+{
+    std::string s;
+    bvc_host::format_fixed(s, v, digits);
+    return emit(s, buf, cap);
+}
+
 }  // extern "C"

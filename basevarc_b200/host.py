@@ -21,7 +21,7 @@ BIN_PATH = os.path.join(_HERE, "bin", "BaseVarC_b200")
 HOST_EXPORTS = (
     "bvc_packer_create", "bvc_packer_destroy", "bvc_packer_clear", "bvc_packer_begin_site", "bvc_packer_add_line",
     "bvc_packer_end_site", "bvc_packer_n_sites", "bvc_packer_n_entries", "bvc_packer_tile", "bvc_packer_positions",
-    "bvc_packer_indel", "bvc_packer_error", "bvc_format_cvg", "bvc_format_vcf", "bvc_basetype_main", "bvc_write_batch_files",
+    "bvc_packer_indel", "bvc_packer_error", "bvc_format_cvg", "bvc_format_vcf", "bvc_format_fixed", "bvc_basetype_main", "bvc_write_batch_files",
 )
 
 _hlib = None
@@ -64,6 +64,8 @@ def load_host_library():
     L.bvc_format_vcf.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.c_int32, C.POINTER(Tile), C.c_int32, C.c_void_p,
                                  C.c_int32, C.c_int32, C.POINTER(C.c_char_p), C.c_void_p, C.c_void_p]
     L.bvc_format_vcf.restype = C.c_size_t
+    L.bvc_format_fixed.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.c_int32]
+    L.bvc_format_fixed.restype = C.c_size_t
     L.bvc_basetype_main.argtypes = [C.c_int, C.POINTER(C.c_char_p)]
     L.bvc_write_batch_files.argtypes = [C.POINTER(Tile), C.c_int32, C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_char_p]
     _hlib = L
@@ -131,6 +133,14 @@ def _fmt(call):
         buf = C.create_string_buffer(n + 1)
         call(buf, len(buf))
     return buf.value.decode()
+
+
+def format_fixed(v, digits):
+    """`v` as the reference's "{:.Nf}" prints it (fmt 5.3.1, tiny-value quirk included)."""
+    L = load_host_library()
+    b = C.create_string_buffer(96)
+    n = L.bvc_format_fixed(b, 96, float(v), int(digits))
+    return b.raw[:n].decode()
 
 
 def format_cvg(chrom, pos, ctile, site, rec, packer=None, group_depth=None):

@@ -194,7 +194,10 @@ class ReferenceRun:
                     return b"\t".join(f)
                 a, b = [norm(l) for l in a], [norm(l) for l in b]
             out[ext + "_lines"] = len(b)
-            out[ext + "_lines_differing"] = sum(1 for x, y in zip(a, b) if x != y) + abs(len(a) - len(b))
+            diff = [(x, y) for x, y in zip(a, b) if x != y]
+            out[ext + "_lines_differing"] = len(diff) + abs(len(a) - len(b))
+            if diff:
+                out[ext + "_diff_sample"] = [[x.decode()[:160], y.decode()[:160]] for x, y in diff[:3]]
         return out
 
     def close(self):

@@ -63,6 +63,11 @@ size_t bvc_format_vcf(char* buf, size_t cap, const char* chr, int32_t pos, const
                       int32_t n_groups, const char* const* group_names, const int32_t* group_depth,
                       const double* group_af);
 
+/* One number as the reference prints it with "{:.Nf}" (src/BaseType.cpp:208-229, src/BaseVarC.cpp:609): printf's %.Nf,
+ * except that the fmt 5.3.1 vendored by the reference prints ONE extra digit for tiny non-zero values
+ * (fmt/include/fmt/format-inl.h:591-605, format.h:1092-1105), e.g. 9.6e-5 -> "0.0001" with N = 3. */
+size_t bvc_format_fixed(char* buf, size_t cap, double v, int32_t digits);
+
 /* ---- writer of the reference's `--load` batch files from a packed tile (fixtures, benchmarks, CPU-baseline runs of the
  * reference binary): PREFIX.tmp.thread.{t}/batch.{j} as bt_r writes them (src/BaseVarC.cpp:467-534), samples named
  * S0..S{N-1}, indel entries printed as `indel_token` (NULL = "+A").  tile->sample is required. */

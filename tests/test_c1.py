@@ -47,7 +47,7 @@ def _sites():
 
 
 def test_c1_packer_oracle_formatter_reproduce_reference_text(oracle):
-    from test_host_cpp import _norm_indels, _same_number_text
+    from test_host_cpp import _norm_indels
     pv = _sites()
     window = len(pv) % T + len(pv) // T                       # S2: src/BaseVarC.cpp:399-403
     cvg_got, vcf_got = [], []
@@ -74,16 +74,12 @@ def test_c1_packer_oracle_formatter_reproduce_reference_text(oracle):
     cvg_ref = [l for l in _ref_text("cvg").splitlines() if not l.startswith("#")]
     vcf_ref = [l for l in _ref_text("vcf").splitlines() if not l.startswith("#")]
     assert len(cvg_got) == len(cvg_ref) == 66613 and len(vcf_got) == len(vcf_ref) == 76 and n_indel == 57
+    # the oracle's doubles are the reference's doubles and the formatter restates its fmt: the text is IDENTICAL
+    # (only the Indels column, a hash-map iteration order in the reference, is compared as a multiset: SURVEY Q10)
     for g, w in zip(cvg_got, cvg_ref):
-        gf, wf = _norm_indels(g), _norm_indels(w)
-        assert len(gf) == len(wf) and all(_same_number_text(x, y) for x, y in zip(gf, wf)), (g, w)
+        assert _norm_indels(g) == _norm_indels(w), (g, w)
     for g, w in zip(vcf_got, vcf_ref):
-        gf, wf = g.split("\t"), w.split("\t")
-        assert gf[:5] == wf[:5] and gf[6] == wf[6] and gf[8:] == wf[8:], (gf[:9], wf[:9])
-        assert _same_number_text(gf[5], wf[5])
-        for x, y in zip(gf[7].split(";"), wf[7].split(";")):
-            assert x.split("=")[0] == y.split("=")[0]
-            assert all(_same_number_text(p, q) for p, q in zip(x.split("=")[1].split(","), y.split("=")[1].split(","))), (x, y)
+        assert g == w, (g[:300], w[:300])
 
 
 @pytest.mark.gpu
