@@ -305,6 +305,17 @@ __device__ __forceinline__ int bfly8(int v)
     return v;
 }
 
+// the words of the first two trips of the range [o0, o4) (lane's word, lane's word + 32), loaded ahead of their use
+__device__ __forceinline__ void first_trips(const uint32_t* __restrict__ code4, const uint32_t* __restrict__ qual4, uint32_t o0, uint32_t o4,
+                                            int lane, uint32_t& c0, uint32_t& q0, uint32_t& c1, uint32_t& q1)
+{
+    const uint32_t w1 = (o4 + 3) >> 2;
+    uint32_t wi = (o0 >> 2) + (uint32_t)lane;
+    if (wi < w1) { c0 = __ldg(code4 + wi); q0 = __ldg(qual4 + wi); }
+    wi += 32;
+    if (wi < w1) { c1 = __ldg(code4 + wi); q1 = __ldg(qual4 + wi); }
+}
+
 __global__ void __launch_bounds__(kHistWarps * 32)
 site_hist4_kernel(PipeArgs a)
 {
@@ -326,6 +337,8 @@ site_hist4_kernel(PipeArgs a)
     int batch = blockIdx.x * kHistWarps + wid;
     uint32_t ov = 0;
     if (batch < n_batches && lane <= kH4Sites) ov = a.s.entry_off[min(batch * kH4Sites + lane, S)];
+    uint32_t pc0 = 0, pq0 = 0, pc1 = 0, pq1 = 0;
+    first_trips(code4, qual4, __shfl_sync(0xffffffffu, ov, 0), __shfl_sync(0xffffffffu, ov, kH4Sites), lane, pc0, pq0, pc1, pq1);
     for (; batch < n_batches; batch += stride) {
         const int s0 = batch * kH4Sites;
         // the offsets of this warp's NEXT batch: loaded now, used (a) before the emit to pull that batch's bytes into L2
@@ -341,10 +354,8 @@ site_hist4_kernel(PipeArgs a)
         uint32_t qmax = 0, qmin = 127;
         const uint32_t w0 = o0 >> 2, w1 = (o4 + 3) >> 2;
         const uint32_t A1 = (o1 + 3) >> 2, A2 = (o2 + 3) >> 2, A3 = (o3 + 3) >> 2;     // first word wholly behind boundary k
-#pragma unroll 4
-        for (uint32_t wi = w0 + lane; wi < w1; wi += 32) {
-            uint32_t cw = __ldg(code4 + wi);
-            const uint32_t qw = __ldg(qual4 + wi) & 0x7f7f7f7fu;
+        auto proc = [&](uint32_t wi, uint32_t cw, uint32_t qw) {
+            qw &= 0x7f7f7f7fu;
             if (wi == w0 || wi + 1 == w1) cw = mask_outside(cw, wi * 4, o0, o4);
             const uint32_t kf = (uint32_t)(wi >= A1) + (uint32_t)(wi >= A2) + (uint32_t)(wi >= A3);
             const uint32_t hb = hw_s + kf * (uint32_t)(kH4Words * 4);
@@ -365,7 +376,14 @@ site_hist4_kernel(PipeArgs a)
                     red_add_s(hb + 4u * ((uint32_t)kNBins + (((c >> 1) & 4u) | (c & 3u))), 1u, (c & 0x14u) == 0x10u);
                 }
             }
-        }
+        };
+        // the first two trips were loaded while the previous batch was being emitted (pc / pq registers)
+        uint32_t wi = w0 + lane;
+        if (wi < w1) proc(wi, pc0, pq0);
+        wi += 32;
+        if (wi < w1) proc(wi, pc1, pq1);
+#pragma unroll 4
+        for (wi += 32; wi < w1; wi += 32) proc(wi, __ldg(code4 + wi), __ldg(qual4 + wi));
         // straddling words: lane k-1 <-> boundary k; one lane per distinct straddling word moves the entries behind the
         // boundary from the site the word was credited to to their own sites (atomic adds commute: no ordering needed)
         if (lane < 3) {
@@ -389,8 +407,9 @@ site_hist4_kernel(PipeArgs a)
         }
         __syncwarp();
         {
-            const uint32_t p0 = __shfl_sync(0xffffffffu, nov, 0) & ~127u, p4 = __shfl_sync(0xffffffffu, nov, kH4Sites);
-            for (uint32_t pa = p0 + (uint32_t)lane * 128u; pa < p4; pa += 32u * 128u) {
+            const uint32_t n0 = __shfl_sync(0xffffffffu, nov, 0), n4 = __shfl_sync(0xffffffffu, nov, kH4Sites);
+            first_trips(code4, qual4, n0, n4, lane, pc0, pq0, pc1, pq1);      // land while this batch is emitted
+            for (uint32_t pa = (n0 & ~127u) + 256u + (uint32_t)lane * 128u; pa < n4; pa += 32u * 128u) {    // the rest: into L2
                 asm volatile("prefetch.global.L2 [%0];" :: "l"(a.s.code + pa));
                 asm volatile("prefetch.global.L2 [%0];" :: "l"(a.s.qual + pa));
             }
