@@ -918,6 +918,9 @@ em_fit_kernel(PipeArgs a)
         if (!__any_sync(0xffffffffu, active)) break;
         // the queue is empty: nothing is left to overlap a long fit with, so finish what the lanes hold in K3b
         drain = drain || __any_sync(0xffffffffu, done);
+        // ... but only once this warp has thinned out: while most of its lanes still hold a fit, thread-per-fit is the
+        // cheaper way to run their passes (C3: 1.6 fits per lane, the queue is empty after the first refill)
+        const bool thin = drain && __popc(__ballot_sync(0xffffffffu, active)) <= a.drain_lanes;
 
         // a class with qual <= 1 has (1-e) - e/3 < 0, which voids delta_decision's sign argument: exact path
         if (active && (budget == 0 || lowq)) {
@@ -981,7 +984,7 @@ em_fit_kernel(PipeArgs a)
                         f0 = e0; f1 = e1; f2 = e2; f3 = e3;              // Algorithm.cpp:95-101
                         F = ((f0 + f1) + f2) + f3;
                         ++pass;
-                        park = (pass >= budget) || (drain && pass >= a.drain_min_pass);
+                        park = (pass >= budget) || (thin && pass >= a.drain_min_pass);
                     }
                 }
                 if (park && active) {                                // resume point: pass `pass` with (f, p)

@@ -53,7 +53,8 @@ struct PipeArgs {
     int mean_entries;           // entries / sites of the tile (host side: picks K1's lanes-per-site)
     int packed_hist;            // 1: K1 in its packed four-sites-per-warp form (every site has < 65,536 entries)
     int pass_budget;            // passes a fit may spend in em_fit_kernel before it is parked for em_long_kernel
-    int drain_min_pass;         // once the queue is empty, fits at or beyond this pass move to em_long_kernel
+    int drain_min_pass;         // once the queue is empty, fits at or beyond this pass move to em_long_kernel ...
+    int drain_lanes;            // ... provided at most this many lanes of the warp still hold a fit
     SiteArgs s;                 // tile arrays, out, lut, lgam, thresholds
     SiteSum*  sum;              // [n_sites]
     uint32_t* cls;              // class pool: cnt << 9 | base << 7 | qual
