@@ -512,7 +512,13 @@ def main():
         kb = hist_bytes if dom == "site_hist_kernel" else alg_bytes
         roof = {"bound": "hbm", "achieved": kb / (k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": int(kb)}
-    roof.update({"frac": roof["achieved"] / roof["peak"], "traffic": None, "kernel": dom, "kernel_ms": k_ms,
+    traffic = None
+    try:                    # DRAM bytes of that kernel per launch, from the committed ncu --set full capture of this workload
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            traffic = json.load(f).get("%s:%d" % (args.workload, S), {}).get(dom)
+    except OSError:
+        pass
+    roof.update({"frac": roof["achieved"] / roof["peak"], "traffic": traffic, "kernel": dom, "kernel_ms": k_ms,
                  "kernel_share_of_step": k_ms / max(sum(per_kernel.values()), 1e-9)})
     n_reads = recs["depth"].sum(1).astype(np.float64)
     f_alg = float((n_reads * (21.0 * recs["em_passes"] - 3.0 * recs["em_fits"])).sum())   # per-READ formulation, SURVEY 8(d)
