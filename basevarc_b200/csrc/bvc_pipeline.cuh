@@ -793,25 +793,34 @@ __device__ __forceinline__ void acc_by_base(uint32_t w, double v, double& V0, do
         : "d"(v), "r"(w & 0x180u));
 }
 
-// ---- K3's class bodies: E and M step only (Algorithm.cpp:76-91, factored as in the file header) ----------
-// major segment: every class has the lane's major base -> fb and the V accumulator are plain registers
-__device__ __forceinline__ void em_class_major(uint32_t w, const double2* lut2, double fb, double F, double& accT, double& Vm)
+// ---- K3's class bodies: E and M step only (Algorithm.cpp:76-91) in RATIO form.  With d = (1-e) - e/3 > 0 (qual >= 2;
+// fits with a qual <= 1 class run in K3b) and t = (e/3) / d, a class's marginal is ml = d (f_b + t F), so
+//   w = cnt / (f_b + t F)   gives   d cnt / ml = w   (the class's share of V_b)   and   (e/3) cnt / ml = t w   (of accT):
+// one 8-byte table word and 7 FP64 instructions per class instead of a 16-byte word and 10.
+// 1/x: MUFU.RCP64H seed (relative error <= 2^-23, PTX rcp.approx.ftz.f64) + one Newton step -> <= 2^-46 (1.4e-14): five
+// orders below the parity tolerance; decisions within that distance of epsilon are K3b's (delta_decision's band).
+__device__ __forceinline__ double rcp_nr1(double x)
 {
-    const double2 ed = lut2[w & (kNQ - 1)];                     // (e/3, (1-e) - e/3)
-    const double r = rcp_nr2(fma(fb, ed.y, ed.x * F));
-    const double wgt = cnt_to_double(w >> 9) * r;
-    accT = fma(ed.x, wgt, accT);
-    Vm = fma(ed.y, wgt, Vm);
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    return fma(r, fma(-x, r, 1.0), r);
+}
+// major segment: every class has the lane's major base -> fb and the V accumulator are plain registers
+__device__ __forceinline__ void em_class_major(uint32_t w, const double* lutT, double fb, double F, double& accT, double& Vm)
+{
+    const double t = lutT[w & (kNQ - 1)];
+    const double wgt = cnt_to_double(w >> 9) * rcp_nr1(fma(t, F, fb));
+    Vm += wgt;
+    accT = fma(t, wgt, accT);
 }
 // other bases: select by the class word
-__device__ __forceinline__ void em_class_minor(uint32_t w, const double2* lut2, double f0, double f1, double f2, double f3, double F,
+__device__ __forceinline__ void em_class_minor(uint32_t w, const double* lutT, double f0, double f1, double f2, double f3, double F,
                                                double& accT, double& V0, double& V1, double& V2, double& V3)
 {
-    const double2 ed = lut2[w & (kNQ - 1)];
-    const double r = rcp_nr2(fma(sel4_w(w, f0, f1, f2, f3), ed.y, ed.x * F));
-    const double wgt = cnt_to_double(w >> 9) * r;
-    accT = fma(ed.x, wgt, accT);
-    acc_by_base(w, ed.y * wgt, V0, V1, V2, V3);
+    const double t = lutT[w & (kNQ - 1)];
+    const double wgt = cnt_to_double(w >> 9) * rcp_nr1(fma(t, F, sel4_w(w, f0, f1, f2, f3)));
+    accT = fma(t, wgt, accT);
+    acc_by_base(w, wgt, V0, V1, V2, V3);
 }
 
 // ---- K3b's class body: E/M step plus the exact, stateless delta term (Algorithm.cpp:103-113) against the
@@ -864,8 +873,9 @@ __device__ __forceinline__ int delta_decision(double P, double eps)
 __global__ void __launch_bounds__(kEmThreads)
 em_fit_kernel(PipeArgs a)
 {
-    __shared__ double2 lut2[kNQ];
-    load_lut2(lut2, a.s.lut);
+    __shared__ double lutT[kNQ];                                  // t(q) = (e/3) / ((1-e) - e/3)
+    for (int i = threadIdx.x; i < kNQ; i += blockDim.x) lutT[i] = a.s.lut[i] / a.s.lut[4 * kNQ + i];
+    __syncthreads();
     const uint32_t nfits = *a.q_in_n;
     const int lane = threadIdx.x & 31;
     const double eps = a.s.eps;
@@ -942,17 +952,23 @@ em_fit_kernel(PipeArgs a)
             const double fm = sel4(major, f0, f1, f2, f3);
             const uint4* cp4 = reinterpret_cast<const uint4*>(cp);
             const uint32_t* cmin = cp + 4 * my_maj4;
+            // class words are loaded one trip ahead of their use (a lane's list is its own: the loads do not coalesce and
+            // 1 in 5 misses L1, so an unprefetched load is a long-scoreboard stall at the first use of the word)
+            const uint4 null4 = make_uint4(kNullClass, kNullClass, kNullClass, kNullClass);
+            uint4 wn = (0 < my_maj4) ? __ldg(cp4) : null4;
+            uint32_t mn = (0 < my_min) ? __ldg(cmin) : kNullClass;
             for (int c = 0; c < nmaj4_max; ++c) {
-                const uint4 w = (c < my_maj4) ? __ldg(cp4 + c) : make_uint4(kNullClass, kNullClass, kNullClass, kNullClass);
-                em_class_major(w.x, lut2, fm, F, accT, Vm);
-                em_class_major(w.y, lut2, fm, F, accT, Vm);
-                em_class_major(w.z, lut2, fm, F, accT, Vm);
-                em_class_major(w.w, lut2, fm, F, accT, Vm);
+                const uint4 w = wn;
+                wn = (c + 1 < my_maj4) ? __ldg(cp4 + c + 1) : null4;
+                em_class_major(w.x, lutT, fm, F, accT, Vm);
+                em_class_major(w.y, lutT, fm, F, accT, Vm);
+                em_class_major(w.z, lutT, fm, F, accT, Vm);
+                em_class_major(w.w, lutT, fm, F, accT, Vm);
             }
-#pragma unroll 2
             for (int c = 0; c < nmin_max; ++c) {
-                const uint32_t w = (c < my_min) ? __ldg(cmin + c) : kNullClass;
-                em_class_minor(w, lut2, f0, f1, f2, f3, F, accT, V0, V1, V2, V3);
+                const uint32_t w = mn;
+                mn = (c + 1 < my_min) ? __ldg(cmin + c + 1) : kNullClass;
+                em_class_minor(w, lutT, f0, f1, f2, f3, F, accT, V0, V1, V2, V3);
             }
             if (active) {
                 work += (unsigned long long)(nmaj + nmin);
