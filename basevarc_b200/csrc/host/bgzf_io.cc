@@ -47,6 +47,7 @@ void BgzfReader::close()
 {
     if (f_) fclose(f_);
     f_ = nullptr;
+    if (zs_) { inflateEnd(static_cast<z_stream*>(zs_)); delete static_cast<z_stream*>(zs_); zs_ = nullptr; }
 }
 
 bool BgzfReader::fill()
@@ -72,13 +73,16 @@ bool BgzfReader::fill()
         const size_t isize = rd32(h + bsize - 4);
         if (isize > kMaxBlock) { failed_ = true; err_ = "bad BGZF ISIZE"; return false; }
         if (isize == 0) continue;              // empty block (EOF marker or flush point)
-        z_stream zs;
-        memset(&zs, 0, sizeof zs);
-        if (inflateInit2(&zs, -15) != Z_OK) { failed_ = true; err_ = "inflateInit2 failed"; return false; }
+        if (!zs_) {
+            z_stream* z = new z_stream;
+            memset(z, 0, sizeof *z);
+            if (inflateInit2(z, -15) != Z_OK) { delete z; failed_ = true; err_ = "inflateInit2 failed"; return false; }
+            zs_ = z;
+        } else if (inflateReset(static_cast<z_stream*>(zs_)) != Z_OK) { failed_ = true; err_ = "inflateReset failed"; return false; }
+        z_stream& zs = *static_cast<z_stream*>(zs_);
         zs.next_in = h + head; zs.avail_in = (uInt)(rest - 8);
         zs.next_out = reinterpret_cast<Bytef*>(buf_.data()); zs.avail_out = (uInt)kMaxBlock;
         const int rc = inflate(&zs, Z_FINISH);
-        inflateEnd(&zs);
         if (rc != Z_STREAM_END || zs.total_out != isize) { failed_ = true; err_ = "inflate failed"; return false; }
         if ((uint32_t)crc32(crc32(0L, Z_NULL, 0), reinterpret_cast<const Bytef*>(buf_.data()), (uInt)isize) != rd32(h + bsize - 8)) {
             failed_ = true; err_ = "BGZF CRC mismatch"; return false;

@@ -42,6 +42,7 @@ private:
     std::string carry_;     // a line that spans blocks
     bool failed_ = false, eof_ = false;
     std::string err_;
+    void* zs_ = nullptr;    // z_stream kept across blocks (inflateReset instead of init / end per block)
 };
 
 // Writes BGZF either to a file or to an in-memory byte string (take()).  close() appends the EOF block

@@ -21,9 +21,18 @@ inline int field_atoi(const char* p, const char* end)
 void Packer::clear()
 {
     pos_.clear(); ref_base_.clear(); entry_off_.assign(1, 0u);
-    code_.clear(); qual_.clear(); mapq_.clear(); rpr_.clear(); smp_.clear();
+    n_ = 0;
     indel_.clear(); err_.clear();
     sample_ = 0;
+}
+
+void Packer::reserve_entries(size_t need)
+{
+    if (need <= cap_) return;
+    size_t c = cap_ ? cap_ : 4096;
+    while (c < need) c *= 2;
+    code_.resize(c); qual_.resize(c); mapq_.resize(c); rpr_.resize(c); smp_.resize(c);
+    cap_ = c;
 }
 
 void Packer::begin_site(int32_t pos, uint8_t ref_base)
@@ -33,60 +42,107 @@ void Packer::begin_site(int32_t pos, uint8_t ref_base)
     sample_ = 0;
 }
 
+// One token through the reference's general grammar: strtok_r on ",", std::atoi per field (whitespace, sign, digits),
+// empty fields skipped, fewer than five fields leave the rest stale (src/BaseVarC.cpp:410-438).
+int Packer::add_token_slow(const char* tok, const char* tend)
+{
+    const char c0 = tok[0];
+    if (c0 != '+' && c0 != '-' && c0 != 'N' && c0 != '.') {
+        const char* f = tok;
+        for (int i = 0; i < 5; ++i) {
+            while (f < tend && *f == ',') ++f;
+            if (f >= tend) break;
+            const char* fe = f;
+            while (fe < tend && *fe != ',') ++fe;
+            const int v = field_atoi(f, fe);
+            switch (i) {
+            case 0: st_base_ = (uint8_t)(v & 7); break;
+            case 1: st_mapq_ = (uint8_t)(v & 255); break;
+            case 2: st_qual_ = (uint8_t)(v & 255); break;
+            case 3: st_rpr_ = (uint8_t)(v & 255); break;
+            case 4: st_strand_ = (uint8_t)(v & 1); break;
+            }
+            f = fe;
+        }
+        if (st_base_ != 4) {                             // N base: skipped, the sample index still advances
+            if (st_base_ > 4 || st_qual_ > 127) {
+                err_ = "token with base > 4 or qual > 127 at site " + std::to_string(pos_.empty() ? 0 : pos_.back());
+                return BVC_ERR_ARG;
+            }
+            code_[n_] = BVC_MAKE_CODE(st_base_, st_strand_, 0);
+            qual_[n_] = st_qual_; mapq_[n_] = st_mapq_; rpr_[n_] = st_rpr_; smp_[n_] = sample_;
+            ++n_;
+        }
+    } else if (c0 != '.') {
+        // indel token: only is_indel and the text change; every other field keeps its stale value (Q1)
+        indel_.emplace((int64_t)n_, std::string(tok, (size_t)(tend - tok)));
+        code_[n_] = BVC_MAKE_CODE(st_base_, st_strand_, 1);
+        qual_[n_] = st_qual_ > 127 ? (uint8_t)127 : st_qual_; mapq_[n_] = st_mapq_; rpr_[n_] = st_rpr_; smp_[n_] = sample_;
+        ++n_;
+    }
+    return BVC_OK;
+}
+
+// Two fast paths cover what the reference's writer emits (src/BaseVarC.cpp:513-521): ". " for an uncovered sample and
+// "b,m..,q..,r..,s " with b, s one digit and 1-3 digit numbers.  Anything else takes add_token_slow.
 int Packer::add_line(const char* line, size_t len)
 {
+    reserve_entries(n_ + len / 2 + 2);                       // a token and its delimiter are >= 2 bytes
     const char* p = line;
     const char* const end = line + len;
+    uint8_t* const code = code_.data(); uint8_t* const qual = qual_.data();
+    uint8_t* const mapq = mapq_.data(); uint8_t* const rpr = rpr_.data();
+    uint32_t* const smp = smp_.data();
+    size_t n = n_;
+    uint32_t sample = sample_;
+    auto digit = [](char c) { return (unsigned)(c - '0') <= 9u; };
     while (p < end) {
-        while (p < end && *p == ' ') ++p;                    // strtok_r(buf, " "): runs of delimiters are skipped
-        if (p >= end) break;
+        if (*p == ' ') { ++p; continue; }                    // strtok_r(buf, " "): runs of delimiters are skipped
+        if (*p == '.' && (p + 1 == end || p[1] == ' ')) { p += 2; ++sample; continue; }
+        if (end - p >= 16 && digit(p[0]) && p[1] == ',') {
+            const char* q = p + 2;
+            unsigned v[3];
+            bool ok = true;
+            for (int i = 0; i < 3 && ok; ++i) {
+                if (!digit(*q)) { ok = false; break; }
+                unsigned x = (unsigned)(*q++ - '0');
+                if (digit(*q)) { x = x * 10u + (unsigned)(*q++ - '0'); if (digit(*q)) x = x * 10u + (unsigned)(*q++ - '0'); }
+                if (*q != ',') { ok = false; break; }
+                ++q;
+                v[i] = x;
+            }
+            if (ok && digit(q[0]) && q[1] == ' ') {
+                const unsigned b = (unsigned)(p[0] - '0') & 7u;
+                const unsigned q8 = v[1] & 255u;
+                if (b <= 4 && (b == 4 || q8 <= 127)) {       // errors are reported by the slow path
+                    st_base_ = (uint8_t)b; st_mapq_ = (uint8_t)(v[0] & 255u); st_qual_ = (uint8_t)q8;
+                    st_rpr_ = (uint8_t)(v[2] & 255u); st_strand_ = (uint8_t)((unsigned)(q[0] - '0') & 1u);
+                    if (b != 4) {
+                        code[n] = BVC_MAKE_CODE(st_base_, st_strand_, 0);
+                        qual[n] = st_qual_; mapq[n] = st_mapq_; rpr[n] = st_rpr_; smp[n] = sample;
+                        ++n;
+                    }
+                    p = q + 2; ++sample;
+                    continue;
+                }
+            }
+        }
         const char* tok = p;
         while (p < end && *p != ' ') ++p;
-        const char* tend = p;
-        const char c0 = tok[0];
-        if (c0 != '+' && c0 != '-' && c0 != 'N' && c0 != '.') {
-            // "base,mapq,qual,rpr,strand": up to five non-empty comma fields, each through atoi into the bitfield
-            const char* f = tok;
-            for (int i = 0; i < 5; ++i) {
-                while (f < tend && *f == ',') ++f;
-                if (f >= tend) break;
-                const char* fe = f;
-                while (fe < tend && *fe != ',') ++fe;
-                const int v = field_atoi(f, fe);
-                switch (i) {
-                case 0: st_base_ = (uint8_t)(v & 7); break;
-                case 1: st_mapq_ = (uint8_t)(v & 255); break;
-                case 2: st_qual_ = (uint8_t)(v & 255); break;
-                case 3: st_rpr_ = (uint8_t)(v & 255); break;
-                case 4: st_strand_ = (uint8_t)(v & 1); break;
-                }
-                f = fe;
-            }
-            if (st_base_ != 4) {                             // N base: skipped, the sample index still advances
-                if (st_base_ > 4 || st_qual_ > 127) {
-                    err_ = "token with base > 4 or qual > 127 at site " + std::to_string(pos_.empty() ? 0 : pos_.back());
-                    return BVC_ERR_ARG;
-                }
-                code_.push_back(BVC_MAKE_CODE(st_base_, st_strand_, 0));
-                qual_.push_back(st_qual_); mapq_.push_back(st_mapq_); rpr_.push_back(st_rpr_);
-                smp_.push_back(sample_);
-            }
-        } else if (c0 != '.') {
-            // indel token: only is_indel and the text change; every other field keeps its stale value (Q1)
-            indel_.emplace((int64_t)code_.size(), std::string(tok, (size_t)(tend - tok)));
-            code_.push_back(BVC_MAKE_CODE(st_base_, st_strand_, 1));
-            qual_.push_back(st_qual_ > 127 ? (uint8_t)127 : st_qual_); mapq_.push_back(st_mapq_); rpr_.push_back(st_rpr_);
-            smp_.push_back(sample_);
-        }
-        ++sample_;
+        n_ = n; sample_ = sample;
+        const int rc = add_token_slow(tok, p);
+        if (rc != BVC_OK) return rc;
+        n = n_;
+        ++sample;
     }
+    n_ = n; sample_ = sample;
     return BVC_OK;
 }
 
 int32_t Packer::end_site()
 {
-    const uint32_t n = (uint32_t)code_.size() - entry_off_.back();
-    entry_off_.push_back((uint32_t)code_.size());
+    const uint32_t n = (uint32_t)n_ - entry_off_.back();
+    entry_off_.push_back((uint32_t)n_);
     return (int32_t)n;
 }
 

@@ -24,7 +24,7 @@ public:
     void drop_last_site();                       // undo begin_site/end_site of a site that got no entries
     void adopt_state(const Packer& other);       // take over the stale-token state (next tile of the same window)
     int32_t n_sites() const { return (int32_t)ref_base_.size(); }
-    int64_t n_entries() const { return (int64_t)code_.size(); }
+    int64_t n_entries() const { return (int64_t)n_; }
     void tile(bvc_tile* out) const;
     const int32_t* positions() const { return pos_.data(); }
     const char* indel(int64_t entry) const;
@@ -39,8 +39,12 @@ private:
     std::vector<int32_t> pos_;
     std::vector<uint8_t> ref_base_;
     std::vector<uint32_t> entry_off_;
+    // per-entry arrays: raw buffers of capacity cap_ with n_ entries in use (add_line writes through pointers)
     std::vector<uint8_t> code_, qual_, mapq_, rpr_;
     std::vector<uint32_t> smp_;
+    size_t n_ = 0, cap_ = 0;
+    void reserve_entries(size_t need);
+    int add_token_slow(const char* tok, const char* tend);
     std::unordered_map<int64_t, std::string> indel_;
     std::string err_;
 };

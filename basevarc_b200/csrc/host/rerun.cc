@@ -20,9 +20,11 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <deque>
 #include <fstream>
+#include <future>
 #include <iostream>
 #include <map>
 #include <memory>
@@ -176,13 +178,10 @@ struct TileJob {
 class GpuServer {
 public:
     GpuServer(int device, const bvc_params& prm) : device_(device), prm_(prm) {}
-    bool start(std::string* err)
-    {
-        const int rc = bvc_create(&ctx_, device_, &prm_);
-        if (rc != BVC_OK) { *err = std::string("GPU ") + std::to_string(device_) + ": " + bvc_last_error(nullptr); return false; }
-        th_ = std::thread([this] { run(); });
-        return true;
-    }
+    // the context is created by the dispatcher thread itself, so that CUDA start-up (a few hundred ms) overlaps the
+    // window workers' first inflate / tokenise trips; a failure fails every job submitted to this GPU
+    void start() { th_ = std::thread([this] { run(); }); }
+    const std::string& init_error() const { return init_err_; }
     void submit(TileJob* j)
     {
         { std::lock_guard<std::mutex> lk(m_); q_.push_back(j); }
@@ -212,6 +211,21 @@ private:
     }
     void run()
     {
+        const int rc0 = bvc_create(&ctx_, device_, &prm_);
+        if (rc0 != BVC_OK) {
+            init_err_ = std::string("GPU ") + std::to_string(device_) + ": " + bvc_last_error(nullptr);
+            for (;;) {                                         // fail whatever is submitted until stop()
+                TileJob* j = nullptr;
+                {
+                    std::unique_lock<std::mutex> lk(m_);
+                    cv_.wait(lk, [this] { return stop_ || !q_.empty(); });
+                    if (q_.empty()) return;
+                    j = q_.front(); q_.pop_front();
+                }
+                { std::lock_guard<std::mutex> lk(j->m); j->rc = rc0; j->err = init_err_; j->done = true; }
+                j->cv.notify_all();
+            }
+        }
         std::deque<Flight> fly;
         for (;;) {
             TileJob* j = nullptr;
@@ -246,6 +260,7 @@ private:
     std::deque<TileJob*> q_;
     bool stop_ = false;
     long long launches_ = 0;
+    std::string init_err_;
 };
 
 struct Shared {
@@ -263,7 +278,14 @@ struct Shared {
     std::mutex err_m;
     std::string err;
     void fail(const std::string& e) { std::lock_guard<std::mutex> lk(err_m); if (!failed.exchange(true)) err = e; }
+    // --verbose: thread-time per host phase, summed over the window workers (ns)
+    std::atomic<long long> ns_read{0}, ns_pack{0}, ns_wait{0}, ns_format{0}, ns_write{0};
 };
+
+inline long long now_ns()
+{
+    return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 // ---- one thread per window: read + tokenise -> tile -> GPU -> format -> BGZF (in memory) ---------------------
 void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out, std::string* cvg_out)
@@ -294,12 +316,15 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
     // the two packers share ONE stale-token state in the reference (a single `ai` per window): hand it over by
     // packing strictly in site order and copying the state forward (Packer::adopt_state)
     int cur = 0, count = 0;
+    long long t_read = 0, t_pack = 0, t_wait = 0, t_format = 0, t_write = 0;
     bool pending[2] = {false, false};
     std::string vline, cline;
 
     auto drain = [&](int k) -> bool {                         // wait for job k, format its sites, release it
         TileJob& j = jobs[k];
+        const long long tw = now_ns();
         { std::unique_lock<std::mutex> lk(j.m); j.cv.wait(lk, [&] { return j.done; }); }
+        t_wait += now_ns() - tw;
         pending[k] = false;
         if (j.rc != BVC_OK) { sh->fail("GPU call failed: " + j.err); return false; }
         bvc_tile t;
@@ -310,12 +335,13 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
             const bvc_site_result* r = &j.rec[(size_t)s];
             const int32_t* gd = G ? &j.group_depth[(size_t)s * G * 4] : nullptr;
             const double* ga = G ? &j.group_af[(size_t)s * G * 4] : nullptr;
-            if (r->lrt_ok) {
-                format_vcf(vline, sh->chr.c_str(), pos[s], &t, s, r, sh->N, G, sh->group_name_ptrs.data(), gd, ga);
-                wv.write(vline);
-            }
+            const long long t0 = now_ns();
+            if (r->lrt_ok) format_vcf(vline, sh->chr.c_str(), pos[s], &t, s, r, sh->N, G, sh->group_name_ptrs.data(), gd, ga);
             format_cvg(cline, sh->chr.c_str(), pos[s], &t, s, r, &j.pk, G, gd);
+            const long long t1 = now_ns();
+            if (r->lrt_ok) wv.write(vline);
             wc.write(cline);
+            t_format += t1 - t0; t_write += now_ns() - t1;
             if (!(++count % 1000)) std::cerr << "basetype completed " << count << " sites -- thread" << ithread << std::endl;
         }
         return true;
@@ -339,8 +365,13 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
         j.pk.begin_site(p, (uint8_t)rb);
         for (auto& r : in) {
             const char* lp; size_t ln;
-            if (r->getline_view(&lp, &ln)) {
+            const long long t0 = now_ns();
+            const bool got = r->getline_view(&lp, &ln);
+            const long long t1 = now_ns();
+            t_read += t1 - t0;
+            if (got) {
                 if (j.pk.add_line(lp, ln) != BVC_OK) { sh->fail(j.pk.error()); return; }
+                t_pack += now_ns() - t1;
             } else if (r->failed()) { sh->fail("corrupt batch file: " + r->error()); return; }
         }
         if (j.pk.end_site() == 0) j.pk.drop_last_site();      // no entries: the reference prints nothing (:442)
@@ -358,7 +389,8 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
     // drain in submission order: the job submitted first is the one that is not `cur` (if still pending)
     if (pending[cur ^ 1] && !drain(cur ^ 1)) return;
     if (pending[cur] && !drain(cur)) return;
-    wv.close(false); wc.close(false);
+    { const long long t0 = now_ns(); wv.close(false); wc.close(false); t_write += now_ns() - t0; }
+    sh->ns_read += t_read; sh->ns_pack += t_pack; sh->ns_wait += t_wait; sh->ns_format += t_format; sh->ns_write += t_write;
     *vcf_out = std::move(wv.memory());
     *cvg_out = std::move(wc.memory());
     if (!o.keep_tmp) for (auto& n : names) remove(n.c_str());  // src/BaseVarC.cpp:458-462
@@ -382,6 +414,12 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     if (o.reference.empty()) { std::cerr << "reference must be feed" << std::endl; return EXIT_FAILURE; }
     const clock_t ctb = clock();
     std::cout << "basetype start -- " << now_string();
+    // CUDA start-up runs beside the file checks below (driver initialisation alone is ~0.1-0.2 s)
+    const long long t_init0 = now_ns();
+    auto devices = std::async(std::launch::async, [] {
+        const int n = bvc_device_count();
+        return std::make_pair(n, std::string(n > 0 ? "" : bvc_last_error(nullptr)));
+    });
     // N = number of lines of the BAM list (src/BaseVarC.cpp:186-189); the BAMs themselves are never opened here
     {
         std::ifstream ib(o.input);
@@ -454,9 +492,10 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     sh.headcvg += "\n";
 
     // tile geometry and one dispatcher per GPU
-    int n_dev = bvc_device_count();
+    const auto dev = devices.get();
+    const int n_dev = dev.first;
     if (const char* e = getenv("BVC_GPUS")) if (o.gpus <= 0) o.gpus = atoi(e);
-    if (n_dev <= 0) { std::cerr << "ERROR: no CUDA device: the basetype calling core has no CPU path (" << bvc_last_error(nullptr) << ")" << std::endl; return EXIT_FAILURE; }
+    if (n_dev <= 0) { std::cerr << "ERROR: no CUDA device: the basetype calling core has no CPU path (" << dev.second << ")" << std::endl; return EXIT_FAILURE; }
     const int G = std::max(1, std::min(std::min(o.gpus > 0 ? o.gpus : n_dev, n_dev), T));
     sh.tile_entries = (int64_t)32 << 20;
     sh.tile_sites = o.tile_sites > 0 ? o.tile_sites : (int32_t)std::max<int64_t>(64, std::min<int64_t>(16384, sh.tile_entries / sh.N));
@@ -468,17 +507,18 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     prm.n_groups = sh.n_groups;
     prm.sample_group = sh.n_groups ? sample_group.data() : nullptr;
     std::vector<std::unique_ptr<GpuServer>> gpus;
-    for (int g = 0; g < G; ++g) {
-        gpus.emplace_back(new GpuServer(g, prm));
-        if (!gpus.back()->start(&err)) { std::cerr << "ERROR: " << err << std::endl; for (auto& s : gpus) s->stop(); return EXIT_FAILURE; }
-    }
+    for (int g = 0; g < G; ++g) { gpus.emplace_back(new GpuServer(g, prm)); gpus.back()->start(); }
+    const long long t_init1 = now_ns();
     // windows [g*T/G, (g+1)*T/G) -> GPU g
     std::vector<std::string> vcf((size_t)T), cvg((size_t)T);
     std::vector<std::thread> workers;
     for (int i = 0; i < T; ++i) workers.emplace_back(window_worker, &sh, gpus[(size_t)((long long)i * G / T)].get(), i, &vcf[(size_t)i], &cvg[(size_t)i]);
     for (auto& w : workers) w.join();
+    const long long t_work1 = now_ns();
     long long launches = 0;
     for (auto& s : gpus) { s->stop(); launches += s->launches(); }
+    const long long t_stop1 = now_ns();
+    for (auto& s : gpus) if (!s->init_error().empty()) { std::cerr << "ERROR: " << s->init_error() << std::endl; return EXIT_FAILURE; }
     if (sh.failed) { std::cerr << "ERROR: " << sh.err << std::endl; return EXIT_FAILURE; }
     // ordered concatenation of the windows' BGZF blocks + one EOF block (replaces the re-read merge of :268-295)
     for (int k = 0; k < 2; ++k) {
@@ -493,7 +533,16 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     if (!o.keep_tmp) for (int i = 0; i < T; ++i) rmdir((o.output + ".tmp.thread." + std::to_string(i)).c_str());
     std::cout << "basetype computing done -- " << now_string();
     std::cout << "basetype elapsed cpu secs : " << double(clock() - ctb) / CLOCKS_PER_SEC << std::endl;
-    if (o.verbose) std::cout << "basetype gpu kernels launched : " << launches << " on " << G << " GPU(s)" << std::endl;
+    if (o.verbose) {
+        std::cout << "basetype gpu kernels launched : " << launches << " on " << G << " GPU(s)" << std::endl;
+        char b[512];
+        snprintf(b, sizeof b, "basetype host phases : checks beside CUDA start-up %.3f s, windows (context creation inside) %.3f s wall on %d threads, "
+                 "context teardown %.3f s, output files %.3f s; thread-seconds: inflate+getline %.3f, "
+                 "tokenise+pack %.3f, wait for gpu %.3f, format %.3f, bgzf deflate %.3f",
+                 (t_init1 - t_init0) * 1e-9, (t_work1 - t_init1) * 1e-9, T, (t_stop1 - t_work1) * 1e-9, (now_ns() - t_stop1) * 1e-9, sh.ns_read * 1e-9, sh.ns_pack * 1e-9, sh.ns_wait * 1e-9,
+                 sh.ns_format * 1e-9, sh.ns_write * 1e-9);
+        std::cout << b << std::endl;
+    }
     std::cout << "basetype done" << std::endl;
     return EXIT_SUCCESS;
 }

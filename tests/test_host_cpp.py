@@ -75,6 +75,60 @@ def test_packer_token_grammar_quirks():
         pk.add_site(12, 0, [b"0,30,200,1,1 "])                                   # qual > 127 is rejected loudly
 
 
+def _ref_tokenise(lines, state):
+    """Plain restatement of src/BaseVarC.cpp:410-438 for one site: strtok on " ", then strtok on "," + atoi per field."""
+    import re
+    out, sample = [], 0
+    for line in lines:
+        for tok in [t for t in line.decode().split(" ") if t]:
+            if tok[0] not in "+-N.":
+                fields = [f for f in tok.split(",") if f][:5]
+                for i, f in enumerate(fields):
+                    m = re.match(r"\s*([+-]?)(\d*)", f)
+                    v = int(m.group(2) or 0) * (-1 if m.group(1) == "-" else 1)
+                    state[i] = v & (7, 255, 255, 255, 1)[i]
+                if state[0] != 4:
+                    out.append((sample, state[0], state[4], 0, state[2], state[1], state[3]))
+            elif tok[0] != ".":
+                out.append((sample, state[0], state[4], 1, state[2], state[1], state[3]))
+            sample += 1
+    return out
+
+
+def test_packer_fast_paths_equal_the_general_grammar():
+    """The tokeniser's fast paths (". " and canonical five-field tokens) against the general strtok / atoi grammar on
+    random lines that mix canonical tokens with odd ones (short tokens, empty fields, leading zeros, 4-digit numbers,
+    trailing junk, runs of spaces), long enough for the 16-byte look-ahead to be in play."""
+    rng = np.random.default_rng(11)
+    odd = [b"1,5", b"2,,30,,20,7,1", b"03,040,035,012,01", b"0,1000,30,5,1", b"3,40,35,12,1x", b"2,60,33,1,0,9", b"+ACG", b"-T",
+           b"N", b".x", b"0,300,99,256,3", b"1, 20,30,4,1"[:4], b"4,20,11,3,0"]
+    pk = host.Packer(4096)
+    state = [0, 0, 0, 0, 0]
+    want_all = []
+    for site in range(40):
+        lines = []
+        for _ in range(3):
+            toks = []
+            for _ in range(int(rng.integers(1, 60))):
+                r = rng.random()
+                if r < 0.4:
+                    toks.append(b".")
+                elif r < 0.85:
+                    toks.append(b"%d,%d,%d,%d,%d" % (rng.integers(0, 4), rng.integers(0, 61), rng.integers(1, 94), rng.integers(0, 256), rng.integers(0, 2)))
+                else:
+                    toks.append(odd[int(rng.integers(0, len(odd)))])
+            sep = b"  " if rng.random() < 0.2 else b" "
+            lines.append(sep.join(toks) + (b" " if rng.random() < 0.8 else b""))
+        want = _ref_tokenise(lines, state)
+        n = pk.add_site(100 + site, 0, lines)
+        assert n == len(want)
+        want_all += want
+    t = pk.to_tile()
+    got = [(int(t.sample[i]), int(t.code[i] & 7), int(t.code[i] >> 3 & 1), int(t.code[i] >> 4 & 1), int(t.qual[i]), int(t.mapq[i]),
+            int(t.rpr[i])) for i in range(t.n_entries)]
+    assert got == want_all
+
+
 def _norm_indels(line):
     f = line.split("\t")
     f[8] = ",".join(sorted(f[8].split(",")))         # SURVEY Q10: the reference's order is a hash-map iteration order
