@@ -425,26 +425,67 @@ site_hist4_kernel(PipeArgs a)
         const bool live = site < S;
         const int ref = live ? (a.s.ref_base[site] & 3) : 0;
         const int n_entries = (int)(gi == 0 ? o1 - o0 : gi == 1 ? o2 - o1 : gi == 2 ? o3 - o2 : o4 - o3);
-        int dsum[4], fsum[4], ncb[4];
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            dsum[b] = 0; fsum[b] = 0; ncb[b] = 0;
-            for (int st = 0; st < nsteps; ++st) {
-                const int q = q_lo + st * 8 + g;
-                const uint32_t h = q < kNQ ? hist[(b << 7) | q] : 0u;
-                const uint32_t x = (h & 0xffffu) + (h >> 16);
-                dsum[b] += (int)x; fsum[b] += (int)(h >> 16);
-                ncb[b] += __popc((__ballot_sync(0xffffffffu, x != 0) >> (gi * 8)) & 0xffu);
-            }
-        }
+        // Fast form (the batch's quals span <= 32 values from a 4-aligned start -- any real base-quality scale): lane g of
+        // a group owns quals q0 + 4g .. q0 + 4g + 3 of every base, read as ONE 16-byte word per base; depths and class
+        // counts travel packed (two 16-bit depths / four 8-bit counts per word) through 3-step group butterflies / scans.
+        const int q0 = min(q_lo & ~3, kNQ - 32);
+        const bool fast = o4 > o0 && (int)qmax < q0 + 32;       // warp-uniform
+        int depth[4], fwd[4], ncb[4];
+        uint32_t pre = 0;                                       // fast form: classes of base b in the group's lower lanes, 8 bits per base
         unsigned lowq = 0;
         if (q_lo <= 1 && nsteps > 0) {                          // rare: bit 0 = a qual-0 class, bit 1 = a qual-1 class
 #pragma unroll
             for (int b = 0; b < 4; ++b) lowq |= (hist[b << 7] ? 1u : 0u) | (hist[(b << 7) | 1] ? 2u : 0u);
         }
-        int depth[4], fwd[4];
+        if (fast) {
+            uint32_t dpk[2] = {0, 0}, fpk[2] = {0, 0}, cpk = 0;
 #pragma unroll
-        for (int b = 0; b < 4; ++b) { depth[b] = bfly8(dsum[b]); fwd[b] = bfly8(fsum[b]); }   // src/BaseVarC.cpp:550-559
+            for (int b = 0; b < 4; ++b) {
+                const uint4 hv = *reinterpret_cast<const uint4*>(hist + (b << 7) + q0 + 4 * g);
+                const uint32_t hx[4] = {hv.x, hv.y, hv.z, hv.w};
+                uint32_t ds = 0, fs = 0, c = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t x = (hx[k] & 0xffffu) + (hx[k] >> 16);
+                    ds += x; fs += hx[k] >> 16; c += (x != 0);
+                }
+                dpk[b >> 1] |= ds << (16 * (b & 1)); fpk[b >> 1] |= fs << (16 * (b & 1)); cpk |= c << (8 * b);
+            }
+#pragma unroll
+            for (int o = 1; o < 8; o <<= 1) {                   // a site has < 65,536 entries: the 16-bit halves never carry
+                dpk[0] += __shfl_xor_sync(0xffffffffu, dpk[0], o); dpk[1] += __shfl_xor_sync(0xffffffffu, dpk[1], o);
+                fpk[0] += __shfl_xor_sync(0xffffffffu, fpk[0], o); fpk[1] += __shfl_xor_sync(0xffffffffu, fpk[1], o);
+            }
+            uint32_t inc = cpk;                                 // inclusive scan over the group's lanes (<= 32 classes per base)
+#pragma unroll
+            for (int o = 1; o < 8; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (g >= o) inc += t;
+            }
+            pre = inc - cpk;
+            const uint32_t tot = __shfl_sync(0xffffffffu, inc, gi * 8 + 7);
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                depth[b] = (int)((dpk[b >> 1] >> (16 * (b & 1))) & 0xffffu);
+                fwd[b] = (int)((fpk[b >> 1] >> (16 * (b & 1))) & 0xffffu);
+                ncb[b] = (int)((tot >> (8 * b)) & 0xffu);
+            }
+        } else {
+            int dsum[4], fsum[4];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                dsum[b] = 0; fsum[b] = 0; ncb[b] = 0;
+                for (int st = 0; st < nsteps; ++st) {
+                    const int q = q_lo + st * 8 + g;
+                    const uint32_t h = q < kNQ ? hist[(b << 7) | q] : 0u;
+                    const uint32_t x = (h & 0xffffu) + (h >> 16);
+                    dsum[b] += (int)x; fsum[b] += (int)(h >> 16);
+                    ncb[b] += __popc((__ballot_sync(0xffffffffu, x != 0) >> (gi * 8)) & 0xffu);
+                }
+            }
+#pragma unroll
+            for (int b = 0; b < 4; ++b) { depth[b] = bfly8(dsum[b]); fwd[b] = bfly8(fsum[b]); }   // src/BaseVarC.cpp:550-559
+        }
         const int icnt = (int)hist[kNBins + g];                 // g = strand << 2 | base of the indel entries
         if (icnt) hist[kNBins + g] = 0;
         // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
@@ -481,6 +522,19 @@ site_hist4_kernel(PipeArgs a)
         for (int b = 0; b < 4; ++b) {
             uint32_t pos;
             if (b == best) pos = off; else { pos = run; run += (uint32_t)ncb[b]; }
+            if (fast) {
+                uint4* hp = reinterpret_cast<uint4*>(hist + (b << 7) + q0 + 4 * g);
+                const uint4 hv = *hp;
+                const uint32_t hx[4] = {hv.x, hv.y, hv.z, hv.w};
+                pos += (pre >> (8 * b)) & 0xffu;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t x = (hx[k] & 0xffffu) + (hx[k] >> 16);
+                    if (x) a.cls[pos++] = (x << 9) | (uint32_t)((b << 7) | (q0 + 4 * g + k));
+                }
+                *hp = make_uint4(0u, 0u, 0u, 0u);
+                continue;
+            }
             for (int st = 0; st < nsteps; ++st) {
                 const int q = q_lo + st * 8 + g;
                 uint32_t x = 0;

@@ -160,6 +160,11 @@ std::string now_string()
     return std::string(ctime(&t));
 }
 
+inline long long now_ns()
+{
+    return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 // ---- one tile in flight: the packed sites of a window, their records, and a completion flag ----------------
 struct TileJob {
     explicit TileJob(int32_t n_samples) : pk(n_samples) {}
@@ -195,23 +200,30 @@ public:
         if (ctx_) { launches_ = bvc_kernel_launch_count(ctx_); bvc_destroy(ctx_); ctx_ = nullptr; }
     }
     long long launches() const { return launches_; }
+    long long create_ns() const { return create_ns_; }
+    long long busy_ns() const { return busy_ns_; }
+    int tiles() const { return tiles_; }
 
 private:
     struct Flight { TileJob* job; uint64_t ticket; };
     void finish(const Flight& f)
     {
+        const long long tb = now_ns();
         int rc = bvc_wait(ctx_, f.ticket);
         std::string err = rc == BVC_OK ? "" : bvc_last_error(ctx_);
         if (rc == BVC_OK && prm_.n_groups > 0 && f.job->pk.n_sites() > 0) {
             rc = bvc_fetch_groups(ctx_, f.ticket, f.job->group_depth.data(), f.job->group_af.data());
             if (rc != BVC_OK) err = bvc_last_error(ctx_);
         }
+        busy_ns_ += now_ns() - tb; ++tiles_;
         { std::lock_guard<std::mutex> lk(f.job->m); f.job->rc = rc; f.job->err = err; f.job->done = true; }
         f.job->cv.notify_all();
     }
     void run()
     {
+        const long long tc0 = now_ns();
         const int rc0 = bvc_create(&ctx_, device_, &prm_);
+        create_ns_ = now_ns() - tc0;
         if (rc0 != BVC_OK) {
             init_err_ = std::string("GPU ") + std::to_string(device_) + ": " + bvc_last_error(nullptr);
             for (;;) {                                         // fail whatever is submitted until stop()
@@ -243,7 +255,9 @@ private:
                 j->pk.tile(&t);
                 if (prm_.n_groups == 0) t.sample = nullptr;
                 uint64_t tk = 0;
+                const long long tb = now_ns();
                 const int rc = bvc_enqueue(ctx_, &t, j->rec.data(), &tk);
+                busy_ns_ += now_ns() - tb;
                 if (rc != BVC_OK) {
                     { std::lock_guard<std::mutex> lk(j->m); j->rc = rc; j->err = bvc_last_error(ctx_); j->done = true; }
                     j->cv.notify_all();
@@ -261,6 +275,8 @@ private:
     bool stop_ = false;
     long long launches_ = 0;
     std::string init_err_;
+    long long create_ns_ = 0, busy_ns_ = 0;          // context creation; time inside bvc_enqueue / bvc_wait / bvc_fetch_groups
+    int tiles_ = 0;
 };
 
 struct Shared {
@@ -282,10 +298,7 @@ struct Shared {
     std::atomic<long long> ns_read{0}, ns_pack{0}, ns_wait{0}, ns_format{0}, ns_write{0};
 };
 
-inline long long now_ns()
-{
-    return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
-}
+
 
 // ---- one thread per window: read + tokenise -> tile -> GPU -> format -> BGZF (in memory) ---------------------
 void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out, std::string* cvg_out)
@@ -497,9 +510,11 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     if (const char* e = getenv("BVC_GPUS")) if (o.gpus <= 0) o.gpus = atoi(e);
     if (n_dev <= 0) { std::cerr << "ERROR: no CUDA device: the basetype calling core has no CPU path (" << dev.second << ")" << std::endl; return EXIT_FAILURE; }
     const int G = std::max(1, std::min(std::min(o.gpus > 0 ? o.gpus : n_dev, n_dev), T));
-    sh.tile_entries = (int64_t)32 << 20;
-    sh.tile_sites = o.tile_sites > 0 ? o.tile_sites : (int32_t)std::max<int64_t>(64, std::min<int64_t>(16384, sh.tile_entries / sh.N));
-    sh.tile_entries = std::max<int64_t>(sh.tile_entries, (int64_t)sh.tile_sites * 0 + 2 * (int64_t)sh.N);
+    // Tiles of ~2,048 sites (fewer for wide cohorts: <= 8 M entries): with one worker per window feeding it, the GPU is
+    // never the bottleneck, so small tiles cost nothing there and let packing, kernels and formatting overlap inside a
+    // window; the context's buffers (sized by max_entries) stay small, which keeps its creation short.
+    sh.tile_sites = o.tile_sites > 0 ? o.tile_sites : (int32_t)std::max<int64_t>(64, std::min<int64_t>(2048, ((int64_t)8 << 20) / sh.N));
+    sh.tile_entries = std::max<int64_t>((int64_t)sh.tile_sites * sh.N, 2 * (int64_t)sh.N);
     bvc_params prm;
     bvc_default_params(&prm, sh.N, o.maf);
     prm.max_sites = sh.tile_sites;
@@ -516,7 +531,8 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     for (auto& w : workers) w.join();
     const long long t_work1 = now_ns();
     long long launches = 0;
-    for (auto& s : gpus) { s->stop(); launches += s->launches(); }
+    long long create_ns = 0, busy_ns = 0; int n_tiles = 0;
+    for (auto& s : gpus) { s->stop(); launches += s->launches(); create_ns = std::max(create_ns, s->create_ns()); busy_ns += s->busy_ns(); n_tiles += s->tiles(); }
     const long long t_stop1 = now_ns();
     for (auto& s : gpus) if (!s->init_error().empty()) { std::cerr << "ERROR: " << s->init_error() << std::endl; return EXIT_FAILURE; }
     if (sh.failed) { std::cerr << "ERROR: " << sh.err << std::endl; return EXIT_FAILURE; }
@@ -537,9 +553,9 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
         std::cout << "basetype gpu kernels launched : " << launches << " on " << G << " GPU(s)" << std::endl;
         char b[512];
         snprintf(b, sizeof b, "basetype host phases : checks beside CUDA start-up %.3f s, windows (context creation inside) %.3f s wall on %d threads, "
-                 "context teardown %.3f s, output files %.3f s; thread-seconds: inflate+getline %.3f, "
+                 "context teardown %.3f s, output files %.3f s; context creation %.3f s, %d tiles, %.3f s inside enqueue / wait; thread-seconds: inflate+getline %.3f, "
                  "tokenise+pack %.3f, wait for gpu %.3f, format %.3f, bgzf deflate %.3f",
-                 (t_init1 - t_init0) * 1e-9, (t_work1 - t_init1) * 1e-9, T, (t_stop1 - t_work1) * 1e-9, (now_ns() - t_stop1) * 1e-9, sh.ns_read * 1e-9, sh.ns_pack * 1e-9, sh.ns_wait * 1e-9,
+                 (t_init1 - t_init0) * 1e-9, (t_work1 - t_init1) * 1e-9, T, (t_stop1 - t_work1) * 1e-9, (now_ns() - t_stop1) * 1e-9, create_ns * 1e-9, n_tiles, busy_ns * 1e-9, sh.ns_read * 1e-9, sh.ns_pack * 1e-9, sh.ns_wait * 1e-9,
                  sh.ns_format * 1e-9, sh.ns_write * 1e-9);
         std::cout << b << std::endl;
     }
