@@ -64,6 +64,19 @@ def test_qual_edge_cases(oracle):
     assert nbad == 0, "\n".join(lines)
 
 
+@pytest.mark.parametrize("lo,hi", [(100, 127), (2, 93), (28, 59), (31, 62), (64, 66), (5, 5)])
+def test_qual_windows(oracle, lo, hi):
+    """K1's emit has a 16-byte form for batches whose quals span <= 32 values from a 4-aligned start (clamped to 96 at the top
+    of the scale) and a general form: windows on both sides of each boundary, same records as the oracle."""
+    rng = np.random.default_rng(lo * 131 + hi)
+    tile = synth_tile(300, 900, 0.8, "highpoly", seed=lo + hi, indel_frac=0.02)
+    tile.qual = rng.integers(lo, hi + 1, tile.qual.size).astype(np.uint8)
+    got, want = _run_both(tile, oracle)
+    nbad, lines = compare_records(got, want)
+    assert nbad == 0, "\n".join(lines)
+    assert want["lrt_ok"].sum() > 0
+
+
 def test_group_path_parity(oracle):
     """--group: per-group depths (exact) and the group-level LRT allele frequencies against the oracle."""
     from test_host_cpp import group_setup
