@@ -587,29 +587,35 @@ __device__ __forceinline__ void st_iiii(bvc_site_result* r, int off, int x, int 
 
 // BaseType.cpp:111-135; writes the WHOLE record of the site once (K5 later fills the VCF statistics of the
 // LRT-positive sites).  su / cvg_fs / cvg_sor: the CVG half computed by K1 / K2.
-__device__ __noinline__ void finalize_site(const PipeArgs& a, int site, int ref, const SiteSum& su, double cvg_fs, double cvg_sor,
-                                           const int8_t* cand, int n, const double* frq, double chi_t,
-                                           int em_fits, int em_passes, uint32_t flags)
+// Everything arrives by value and no array is indexed with a run-time subscript: the function inlines into K2 / K4 without
+// a stack frame (as a call taking pointers it cost those kernels ~0.5 KB of local-memory traffic per site -- more DRAM
+// write traffic than the records themselves).
+__device__ __forceinline__ int cand_at(uint32_t cand4, int t) { return (int)((cand4 >> (8 * t)) & 0xffu); }
+
+__device__ __forceinline__ void finalize_site(const PipeArgs& a, int site, int ref, const SiteSum& su, double cvg_fs, double cvg_sor,
+                                              uint32_t cand4, int n, double frq0, double frq1, double frq2, double frq3, double chi_t,
+                                              int em_fits, int em_passes, uint32_t flags)
 {
     bvc_site_result* r = a.s.out + site;
     const int* depth = su.depth;
     const int n_reads = depth[0] + depth[1] + depth[2] + depth[3];
-    int n_alt = 0; int alt_bases[3] = {-1, -1, -1};
-    double af[4] = {0.0, 0.0, 0.0, 0.0};
-    for (int t = 0; t < n; ++t) {
-        const int b = cand[t];
-        if (b != ref && n_alt < 3) {
-            const double fv = sel4(b, frq[0], frq[1], frq[2], frq[3]);
-            if (n_alt == 0) alt_bases[0] = b; else if (n_alt == 1) alt_bases[1] = b; else alt_bases[2] = b;
+    int n_alt = 0, alt0 = -1, alt1 = -1, alt2 = -1;
+    double af0 = 0.0, af1 = 0.0, af2 = 0.0, af3 = 0.0;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int b = cand_at(cand4, t);
+        if (t < n && b != ref && n_alt < 3) {
+            const double fv = sel4(b, frq0, frq1, frq2, frq3);
+            if (n_alt == 0) alt0 = b; else if (n_alt == 1) alt1 = b; else alt2 = b;
             ++n_alt;
-            if (b == 0) af[0] = fv; else if (b == 1) af[1] = fv; else if (b == 2) af[2] = fv; else af[3] = fv;
+            if (b == 0) af0 = fv; else if (b == 1) af1 = fv; else if (b == 2) af2 = fv; else af3 = fv;
         }
     }
     double vq = 0.0;
     const int ok = n_alt > 0;
     if (ok) {
         const double total = (double)n_reads;
-        const int b0 = cand[0];
+        const int b0 = cand_at(cand4, 0);
         const double rr = (double)(b0 == 0 ? depth[0] : b0 == 1 ? depth[1] : b0 == 2 ? depth[2] : depth[3]) / total;
         if (n == 1 && total > 10 && rr > 0.5) vq = 5000.0;
         else if (chi_t <= 0) vq = 0.0;
@@ -621,8 +627,8 @@ __device__ __noinline__ void finalize_site(const PipeArgs& a, int site, int ref,
         if (near_rel(vq, 60.0)) flags |= BVC_FLAG_QUAL60;
     }
     st_dd(r, 0, cvg_fs, cvg_sor);
-    st_dd(r, 16, af[0], af[1]);
-    st_dd(r, 32, af[2], af[3]);
+    st_dd(r, 16, af0, af1);
+    st_dd(r, 32, af2, af3);
     st_dd(r, 48, chi_t, vq);
     st_dd(r, 64, 0.0, 0.0);                                   // vcf_fs, vcf_sor
     st_dd(r, 80, 0.0, 0.0);                                   // ranksum[0..1]
@@ -631,8 +637,8 @@ __device__ __noinline__ void finalize_site(const PipeArgs& a, int site, int ref,
     st_iiii(r, 128, su.cvg[1], su.cvg[2], su.cvg[3], 0);
     st_iiii(r, 144, 0, 0, 0, em_fits);
     st_iiii(r, 160, em_passes, (int)flags,
-            (int)((uint32_t)su.alt | ((uint32_t)ok << 8) | ((uint32_t)n_alt << 16) | (((uint32_t)alt_bases[0] & 0xffu) << 24)),
-            (int)(((uint32_t)alt_bases[1] & 0xffu) | (((uint32_t)alt_bases[2] & 0xffu) << 8)));
+            (int)((uint32_t)su.alt | ((uint32_t)ok << 8) | ((uint32_t)n_alt << 16) | (((uint32_t)alt0 & 0xffu) << 24)),
+            (int)(((uint32_t)alt1 & 0xffu) | (((uint32_t)alt2 & 0xffu) << 8)));
     a.state[site] = kStDone;
     if (ok) a.vcf_list[atomicAdd(a.vcf_n, 1u)] = (uint32_t)site;
 }
@@ -686,25 +692,25 @@ site_prepare_kernel(PipeArgs a)
             else cvg_fs = dm_fisher(a.s.lgam, su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
             const double cvg_sor = dm_sor(su.cvg[0], su.cvg[1], su.cvg[2], su.cvg[3]);
             // BaseType.cpp:75-82
-            int8_t cand[4]; int n = 0; uint32_t flags = 0, full = 0;
+            uint32_t cand4 = 0xffffffffu; int n = 0; uint32_t flags = 0, full = 0;
             const double total = (double)n_reads;
             if (n_reads > 0) {
 #pragma unroll
                 for (int b = 0; b < 4; ++b) {
                     const double fr = (double)su.depth[b] / total;
                     if (near_rel(fr, a.s.min_af)) flags |= BVC_FLAG_MIN_AF;
-                    if (fr >= a.s.min_af) { cand[n++] = (int8_t)b; full |= 1u << b; }
+                    if (fr >= a.s.min_af) { cand4 = (cand4 & ~(0xffu << (8 * n))) | ((uint32_t)b << (8 * n)); ++n; full |= 1u << b; }
                 }
             }
             if (n <= 1) {
                 // no EM needed: 0 candidates -> false; 1 candidate -> one (closed-form) fit, chi stays 0
-                const double frq[4] = {full & 1 ? 1.0 : 0.0, full & 2 ? 1.0 : 0.0, full & 4 ? 1.0 : 0.0, full & 8 ? 1.0 : 0.0};
-                finalize_site(a, site, ref, su, cvg_fs, cvg_sor, cand, n, frq, 0.0, n, 2 * n, flags);
+                finalize_site(a, site, ref, su, cvg_fs, cvg_sor, cand4, n, full & 1 ? 1.0 : 0.0, full & 2 ? 1.0 : 0.0, full & 4 ? 1.0 : 0.0,
+                              full & 8 ? 1.0 : 0.0, 0.0, n, 2 * n, flags);
             } else {
                 Ladder L;
                 L.lr_alt = 0.0; L.frq[0] = L.frq[1] = L.frq[2] = L.frq[3] = 0.0; L.chi_t = 0.0;
                 L.cvg_fs = cvg_fs; L.cvg_sor = cvg_sor;
-                for (int t = 0; t < 4; ++t) L.cand[t] = t < n ? cand[t] : (int8_t)-1;
+                L.cand4 = cand4;
                 L.n = (int8_t)n; L.k = (int8_t)n; L.nfit = 1; L.pad0 = 0;
                 L.em_fits = 0; L.em_passes = 0; L.flags = flags; L.pad1 = 0;
                 a.lad[site] = L;
@@ -1262,6 +1268,7 @@ __device__ __forceinline__ void ladder_site(const PipeArgs& a, uint32_t item)
     if (k == n) {                                                  // the full model (BaseType.cpp:88-90)
         L.lr_alt = fr[0].lr;
         if (n == 2) src = fr;
+#pragma unroll
         for (int j = 0; j < 4; ++j) L.frq[j] = fr[0].eap[j];
         L.em_fits += 1; L.em_passes += fr[0].passes; L.flags |= fr[0].flags;
     } else {                                                       // k-subsets, combs_ order (BaseType.cpp:93-110)
@@ -1279,8 +1286,14 @@ __device__ __forceinline__ void ladder_site(const PipeArgs& a, uint32_t item)
             const uint32_t keep = fr[imin].mask;
             if (__popc(keep) == 2) src = fr + imin;
             int nn = 0;
-            for (int t = 0; t < n; ++t) if (keep >> L.cand[t] & 1) L.cand[nn++] = L.cand[t];
-            n = nn;
+            uint32_t c4 = 0xffffffffu;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int b = cand_at(L.cand4, t);
+                if (t < n && (keep >> b & 1)) { c4 = (c4 & ~(0xffu << (8 * nn))) | ((uint32_t)b << (8 * nn)); ++nn; }
+            }
+            L.cand4 = c4; n = nn;
+#pragma unroll
             for (int j = 0; j < 4; ++j) L.frq[j] = fr[imin].eap[j];
         } else cont = false;
     }
@@ -1293,7 +1306,8 @@ __device__ __forceinline__ void ladder_site(const PipeArgs& a, uint32_t item)
             for (unsigned m = (1u << n) - 1; m >= 1; --m) {            // combs_ order: bit (n-1-i) <=> cand[i]
                 if (__popc(m) != k) continue;
                 uint32_t sub = 0;
-                for (int i = 0; i < n; ++i) if (m >> (n - 1 - i) & 1) sub |= 1u << L.cand[i];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) if (i < n && (m >> (n - 1 - i) & 1)) sub |= 1u << cand_at(L.cand4, i);
                 a.fit[(size_t)site * 4 + slot].mask = sub;
                 ++slot;
             }
@@ -1306,7 +1320,7 @@ __device__ __forceinline__ void ladder_site(const PipeArgs& a, uint32_t item)
         // k == 1: n == 2 single-base models, in cand order; fit_loglik_kernel left their lr in the pair fit's f[0..1]
         double cmin = 0.0, lr_min = 0.0; int imin = 0;
         for (int i = 0; i < n; ++i) {
-            const double lr = (src && n == 2) ? src->f[i] : single_loglik(a, su, L.cand[i]);
+            const double lr = (src && n == 2) ? src->f[i] : single_loglik(a, su, cand_at(L.cand4, i));
             const double chi = 2.0 * (L.lr_alt - lr);
             if (i > 0 && near_rel(chi, cmin)) L.flags |= BVC_FLAG_ARGMIN_TIE;
             if (i == 0 || chi < cmin) { cmin = chi; lr_min = lr; imin = i; }
@@ -1315,13 +1329,14 @@ __device__ __forceinline__ void ladder_site(const PipeArgs& a, uint32_t item)
         L.lr_alt = lr_min; L.chi_t = cmin;
         if (near_rel(cmin, a.s.lrt_thr)) L.flags |= BVC_FLAG_LRT_CHI;
         if (cmin < a.s.lrt_thr) {
-            const int b = L.cand[imin];
-            L.cand[0] = (int8_t)b; n = 1;
+            const int b = cand_at(L.cand4, imin);
+            L.cand4 = 0xffffff00u | (uint32_t)b; n = 1;
+#pragma unroll
             for (int j = 0; j < 4; ++j) L.frq[j] = (j == b) ? 1.0 : 0.0;
         }
         cont = false;
     }
-    finalize_site(a, site, ref, su, L.cvg_fs, L.cvg_sor, L.cand, n, L.frq, L.chi_t, L.em_fits, L.em_passes, L.flags);
+    finalize_site(a, site, ref, su, L.cvg_fs, L.cvg_sor, L.cand4, n, L.frq[0], L.frq[1], L.frq[2], L.frq[3], L.chi_t, L.em_fits, L.em_passes, L.flags);
 }
 
 __global__ void __launch_bounds__(128)

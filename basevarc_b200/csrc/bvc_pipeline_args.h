@@ -37,7 +37,7 @@ struct __align__(16) Ladder {       // 96 B per site
     double  frq[4];
     double  chi_t;
     double  cvg_fs, cvg_sor;        // K2's CVG Fisher / SOR, carried to the one full-record store in K4
-    int8_t  cand[4];
+    uint32_t cand4;                 // candidate bases, one per byte in ladder order (byte t = candidate t; 0xff = none)
     int8_t  n;                      // current number of candidate bases
     int8_t  k;                      // size of the subsets in flight (== n: the full model)
     int8_t  nfit;                   // fits in flight
