@@ -55,6 +55,7 @@ struct PipeArgs {
     int pass_budget;            // passes a fit may spend in em_fit_kernel before it is parked for em_long_kernel
     int drain_min_pass;         // once the queue is empty, fits at or beyond this pass move to em_long_kernel ...
     int drain_lanes;            // ... provided at most this many lanes of the warp still hold a fit
+    int em_min_fits;            // a stage with fewer fits than this skips em_fit_kernel (every fit starts in em_long_kernel)
     SiteArgs s;                 // tile arrays, out, lut, lgam, thresholds
     SiteSum*  sum;              // [n_sites]
     uint32_t* cls;              // class pool: cnt << 9 | base << 7 | qual
