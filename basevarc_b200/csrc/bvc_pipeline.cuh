@@ -290,6 +290,10 @@ __device__ __forceinline__ void red_add_s(uint32_t saddr, uint32_t v, bool pred)
     asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q red.shared.add.u32 [%0], %1;\n\t}"
                  :: "r"(saddr), "r"(v), "r"((uint32_t)pred) : "memory");
 }
+__device__ __forceinline__ void red_s(uint32_t saddr, uint32_t v)
+{
+    asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(saddr), "r"(v) : "memory");
+}
 // code bytes of the word at entry e0 that lie outside [lo_e, hi_e) become 0x14 (indel, base 4): nothing counts them
 __device__ __forceinline__ uint32_t mask_outside(uint32_t cw, uint32_t e0, uint32_t lo_e, uint32_t hi_e)
 {
@@ -319,7 +323,9 @@ __device__ __forceinline__ void first_trips(const uint32_t* __restrict__ code4, 
 __global__ void __launch_bounds__(kHistWarps * 32)
 site_hist4_kernel(PipeArgs a)
 {
-    __shared__ __align__(16) uint32_t hist_s[kHistWarps][kH4Sites * kH4Words];
+    // + one dump word per warp: entries that count nowhere (indel / N-base codes, bytes outside the range) are added THERE,
+    // so the four adds of a word are unconditional (ptxas turns a predicated red into a branch region: 3 more instructions)
+    __shared__ __align__(16) uint32_t hist_s[kHistWarps][kH4Sites * kH4Words + 4];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int g = lane & 7, gi = lane >> 3;
     uint32_t* hw = hist_s[wid];
@@ -327,6 +333,7 @@ site_hist4_kernel(PipeArgs a)
     __syncwarp();
     uint32_t* hist = hw + gi * kH4Words;                        // my group's site during the emit
     const uint32_t hw_s = (uint32_t)__cvta_generic_to_shared(hw);
+    const uint32_t dump_s = hw_s + (uint32_t)(kH4Sites * kH4Words * 4);
     const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
     const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
     const int S = a.s.n_sites;
@@ -351,7 +358,7 @@ site_hist4_kernel(PipeArgs a)
         // <= 3 words that straddle a site boundary are corrected afterwards.  Bin byte offsets (base << 9 | qual << 2)
         // are formed two entries at a time in 16-bit lanes; qmin / qmax run over every byte of the range's words
         // (pad and indel bytes carry real quals of neighbouring entries: a superset range is all the emit needs).
-        uint32_t qmax = 0, qmin = 127;
+        uint32_t qmx2 = 0, qmn2 = 0x007f007fu;                  // packed 16-bit halves (one VIMNMX3.U16x2 per word each)
         const uint32_t w0 = o0 >> 2, w1 = (o4 + 3) >> 2;
         const uint32_t A1 = (o1 + 3) >> 2, A2 = (o2 + 3) >> 2, A3 = (o3 + 3) >> 2;     // first word wholly behind boundary k
         auto proc = [&](uint32_t wi, uint32_t cw, uint32_t qw) {
@@ -362,18 +369,17 @@ site_hist4_kernel(PipeArgs a)
             const uint32_t ce = cw & 0x00ff00ffu, co = (cw >> 8) & 0x00ff00ffu;
             const uint32_t qe = qw & 0x00ff00ffu, qo = (qw >> 8) & 0x00ff00ffu;
             const uint32_t be = ((ce & 0x00030003u) << 9) | (qe << 2), bo = ((co & 0x00030003u) << 9) | (qo << 2);
-            const uint32_t sw = (cw >> 3) & 0x01010101u;                              // strand bits: forward counts in the high half
-            qmin = min(qmin, min(min(qe & 0xffffu, qe >> 16), min(qo & 0xffffu, qo >> 16)));
-            qmax = max(qmax, max(max(qe & 0xffffu, qe >> 16), max(qo & 0xffffu, qo >> 16)));
-            red_add_s(hb + (be & 0xffffu), (sw & 1u) * 0xffffu + 1u, !(cw & 0x00000014u));
-            red_add_s(hb + (bo & 0xffffu), ((sw >> 8) & 1u) * 0xffffu + 1u, !(cw & 0x00001400u));
-            red_add_s(hb + (be >> 16), ((sw >> 16) & 1u) * 0xffffu + 1u, !(cw & 0x00140000u));
-            red_add_s(hb + (bo >> 16), (sw >> 24) * 0xffffu + 1u, !(cw & 0x14000000u));
+            qmn2 = __vminu2(qmn2, __vminu2(qe, qo));
+            qmx2 = __vmaxu2(qmx2, __vmaxu2(qe, qo));
+            red_s((cw & 0x00000014u) ? dump_s : hb + (be & 0xffffu), (cw & 0x00000008u) ? 0x10000u : 1u);
+            red_s((cw & 0x00001400u) ? dump_s : hb + (bo & 0xffffu), (cw & 0x00000800u) ? 0x10000u : 1u);
+            red_s((cw & 0x00140000u) ? dump_s : hb + (be >> 16), (cw & 0x00080000u) ? 0x10000u : 1u);
+            red_s((cw & 0x14000000u) ? dump_s : hb + (bo >> 16), (cw & 0x08000000u) ? 0x10000u : 1u);
             if (cw & 0x10101010u) {                                                   // indel entries keep only (stale base, strand)
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const uint32_t c = cw >> (8 * k);
-                    red_add_s(hb + 4u * ((uint32_t)kNBins + (((c >> 1) & 4u) | (c & 3u))), 1u, (c & 0x14u) == 0x10u);
+                    red_s((c & 0x14u) == 0x10u ? hb + 4u * ((uint32_t)kNBins + (((c >> 1) & 4u) | (c & 3u))) : dump_s, 1u);
                 }
             }
         };
@@ -415,8 +421,8 @@ site_hist4_kernel(PipeArgs a)
             }
         }
         // one qual range for the whole batch (a superset for each of its sites)
-        qmax = __reduce_max_sync(0xffffffffu, qmax);
-        qmin = __reduce_min_sync(0xffffffffu, qmin);
+        const uint32_t qmax = __reduce_max_sync(0xffffffffu, max(qmx2 & 0xffffu, qmx2 >> 16));
+        const uint32_t qmin = __reduce_min_sync(0xffffffffu, min(qmn2 & 0xffffu, qmn2 >> 16));
         const int q_lo = (int)min(qmin, qmax);
         const int nsteps = o4 > o0 ? ((int)qmax - q_lo) / 8 + 1 : 0;
 
