@@ -334,6 +334,7 @@ site_hist4_kernel(PipeArgs a)
     uint32_t* hist = hw + gi * kH4Words;                        // my group's site during the emit
     const uint32_t hw_s = (uint32_t)__cvta_generic_to_shared(hw);
     const uint32_t dump_s = hw_s + (uint32_t)(kH4Sites * kH4Words * 4);
+    const uint32_t hs1 = hw_s + (uint32_t)(kH4Words * 4), hs2 = hs1 + (uint32_t)(kH4Words * 4), hs3 = hs2 + (uint32_t)(kH4Words * 4);
     const uint32_t* code4 = reinterpret_cast<const uint32_t*>(a.s.code);
     const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
     const int S = a.s.n_sites;
@@ -364,8 +365,7 @@ site_hist4_kernel(PipeArgs a)
         auto proc = [&](uint32_t wi, uint32_t cw, uint32_t qw) {
             qw &= 0x7f7f7f7fu;
             if (wi == w0 || wi + 1 == w1) cw = mask_outside(cw, wi * 4, o0, o4);
-            const uint32_t kf = (uint32_t)(wi >= A1) + (uint32_t)(wi >= A2) + (uint32_t)(wi >= A3);
-            const uint32_t hb = hw_s + kf * (uint32_t)(kH4Words * 4);
+            const uint32_t hb = wi >= A2 ? (wi >= A3 ? hs3 : hs2) : (wi >= A1 ? hs1 : hw_s);    // A1 <= A2 <= A3
             const uint32_t ce = cw & 0x00ff00ffu, co = (cw >> 8) & 0x00ff00ffu;
             const uint32_t qe = qw & 0x00ff00ffu, qo = (qw >> 8) & 0x00ff00ffu;
             const uint32_t be = ((ce & 0x00030003u) << 9) | (qe << 2), bo = ((co & 0x00030003u) << 9) | (qo << 2);
@@ -375,12 +375,11 @@ site_hist4_kernel(PipeArgs a)
             red_s((cw & 0x00001400u) ? dump_s : hb + (bo & 0xffffu), (cw & 0x00000800u) ? 0x10000u : 1u);
             red_s((cw & 0x00140000u) ? dump_s : hb + (be >> 16), (cw & 0x00080000u) ? 0x10000u : 1u);
             red_s((cw & 0x14000000u) ? dump_s : hb + (bo >> 16), (cw & 0x08000000u) ? 0x10000u : 1u);
-            if (cw & 0x10101010u) {                                                   // indel entries keep only (stale base, strand)
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint32_t c = cw >> (8 * k);
-                    red_s((c & 0x14u) == 0x10u ? hb + 4u * ((uint32_t)kNBins + (((c >> 1) & 4u) | (c & 3u))) : dump_s, 1u);
-                }
+            // indel entries (0.5 % of a pile-up) keep only (stale base, strand): a loop over the set indel bits of the word, so
+            // a trip costs the warp its lanes' MAXIMUM number of indel entries (almost always 0 or 1) instead of four bodies
+            for (uint32_t m = cw & 0x10101010u & ~((cw & 0x04040404u) << 2); m; m &= m - 1) {
+                const uint32_t c = cw >> (__ffs((int)m) - 5);
+                red_s(hb + 4u * ((uint32_t)kNBins + (((c >> 1) & 4u) | (c & 3u))), 1u);
             }
         };
         // the first two trips were loaded while the previous batch was being emitted (pc / pq registers)
@@ -388,8 +387,20 @@ site_hist4_kernel(PipeArgs a)
         if (wi < w1) proc(wi, pc0, pq0);
         wi += 32;
         if (wi < w1) proc(wi, pc1, pq1);
-#pragma unroll 4
-        for (wi += 32; wi < w1; wi += 32) proc(wi, __ldg(code4 + wi), __ldg(qual4 + wi));
+        // the rest in groups of four trips, the next group's words loaded before the current group is processed
+        wi += 32;
+        uint32_t gc[4] = {0, 0, 0, 0}, gq[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (wi + 32 * k < w1) { gc[k] = __ldg(code4 + wi + 32 * k); gq[k] = __ldg(qual4 + wi + 32 * k); }
+        for (; wi < w1; wi += 128) {
+            uint32_t nc[4] = {0, 0, 0, 0}, nq[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (wi + 128 + 32 * k < w1) { nc[k] = __ldg(code4 + wi + 128 + 32 * k); nq[k] = __ldg(qual4 + wi + 128 + 32 * k); }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (wi + 32 * k < w1) proc(wi + 32 * k, gc[k], gq[k]);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { gc[k] = nc[k]; gq[k] = nq[k]; }
+        }
         // straddling words: lane k-1 <-> boundary k; one lane per distinct straddling word moves the entries behind the
         // boundary from the site the word was credited to to their own sites (atomic adds commute: no ordering needed)
         if (lane < 3) {
