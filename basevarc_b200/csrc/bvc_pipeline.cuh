@@ -1232,18 +1232,19 @@ fit_loglik_kernel(PipeArgs a)
         const double F = ((f0 + f1) + f2) + f3;
         const int nmax = __reduce_max_sync(0xffffffffu, ncls);
         double s = 0.0, sl = 0.0, sh = 0.0;
+        // straight-line bodies: a lane past its last class (or without a fit: ml == 0, result unused) evaluates count-0 null
+        // classes, so the unrolled log evaluations interleave instead of sitting behind a divergent branch each
+#pragma unroll 4
         for (int c = 0; c < nmax; ++c) {
-            if (c < ncls) {
-                const uint32_t w = __ldg(cp + c);
-                const int q = w & (kNQ - 1);
-                const double2 ed = lut2[q];
-                const double2 lg = lutlog[q];
-                const double cnt = cnt_to_double(w >> 9);
-                const double ml = fma(sel4_w(w, f0, f1, f2, f3), ed.y, ed.x * F);
-                s = fma(cnt, log(ml), s);
-                sl = fma(cnt, (w & 0x180u) == bl ? lg.y : lg.x, sl);
-                sh = fma(cnt, (w & 0x180u) == bh ? lg.y : lg.x, sh);
-            }
+            const uint32_t w = (c < ncls) ? __ldg(cp + c) : kNullClass;
+            const int q = w & (kNQ - 1);
+            const double2 ed = lut2[q];
+            const double2 lg = lutlog[q];
+            const double cnt = cnt_to_double(w >> 9);
+            const double ml = fma(sel4_w(w, f0, f1, f2, f3), ed.y, ed.x * F);
+            s = fma(cnt, log(ml), s);
+            sl = fma(cnt, (w & 0x180u) == bl ? lg.y : lg.x, sl);
+            sh = fma(cnt, (w & 0x180u) == bh ? lg.y : lg.x, sh);
         }
         if (on) {
             fr->lr = s; work += (unsigned long long)ncls;
