@@ -7,7 +7,7 @@ import ctypes as C
 
 import numpy as np
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 OK, ERR_ARG, ERR_CUDA, ERR_CAPACITY, ERR_STATE = 0, -1, -2, -3, -4
 
@@ -47,6 +47,10 @@ class Tile(C.Structure):
         ("mapq", C.c_void_p),
         ("rpr", C.c_void_p),
         ("sample", C.c_void_p),
+        ("packed8", C.c_void_p),
+        ("qual_dict", C.c_void_p),
+        ("n_qual_dict", C.c_int32),
+        ("reserved1", C.c_int32),
     ]
 
 

@@ -145,7 +145,7 @@ class BaseTypeCaller:
 
     # -- reference-facing call: host buffers in, host records out ------------------------------------
     def enqueue(self, tile, out):
-        ct = tile.as_ctypes(with_sample=self.params.n_groups > 0)
+        ct = tile.as_ctypes(with_sample=self.params.n_groups > 0, drop_code_qual=True)
         tk = C.c_uint64(0)
         self._check(self.lib.bvc_enqueue(self.ctx, C.byref(ct), out.ctypes.data, C.byref(tk)), "bvc_enqueue")
         return tk.value
@@ -172,7 +172,7 @@ class BaseTypeCaller:
 
     # -- device-resident path (kernel-only timing) ---------------------------------------------------
     def resident_upload(self, tile):
-        ct = tile.as_ctypes(with_sample=self.params.n_groups > 0)
+        ct = tile.as_ctypes(with_sample=self.params.n_groups > 0, drop_code_qual=True)
         self._check(self.lib.bvc_resident_upload(self.ctx, C.byref(ct)), "bvc_resident_upload")
         self._resident_sites = tile.n_sites
 
@@ -233,14 +233,14 @@ class ShardedCaller(BaseTypeCaller):
         """(first_site, records of the owned slice) through host buffers."""
         if out is None:
             out = np.zeros((tile.n_sites + self.world - 1) // self.world, SITE_RESULT_DTYPE)
-        ct = tile.as_ctypes(with_sample=False)
+        ct = tile.as_ctypes(with_sample=False, drop_code_qual=True)
         self._shard_sites = tile.n_sites
         first, n = C.c_int32(0), C.c_int32(0)
         self._check(self.lib.bvc_shard_call(self.ctx, C.byref(ct), out.ctypes.data, C.byref(first), C.byref(n)), "bvc_shard_call")
         return first.value, out[:n.value]
 
     def shard_upload(self, tile):
-        ct = tile.as_ctypes(with_sample=False)
+        ct = tile.as_ctypes(with_sample=False, drop_code_qual=True)
         self._check(self.lib.bvc_shard_upload(self.ctx, C.byref(ct)), "bvc_shard_upload")
         self._shard_sites = tile.n_sites
 
@@ -287,7 +287,7 @@ class ShardGroup:
         S = tiles[0].n_sites
         sr = (S + self.world - 1) // self.world
         outs = [np.zeros(sr, SITE_RESULT_DTYPE) for _ in range(self.world)]
-        cts = [t.as_ctypes(with_sample=False) for t in tiles]
+        cts = [t.as_ctypes(with_sample=False, drop_code_qual=True) for t in tiles]
         tp = (C.POINTER(Tile) * self.world)(*[C.pointer(ct) for ct in cts])
         op = (C.c_void_p * self.world)(*[o.ctypes.data for o in outs])
         first = (C.c_int32 * self.world)()

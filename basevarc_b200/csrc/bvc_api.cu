@@ -39,6 +39,7 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
     CK(cudaMalloc(&s.d_qual, R + 16));
     CK(cudaMalloc(&s.d_mapq, R + 16));
     CK(cudaMalloc(&s.d_rpr, R + 16));
+    CK(cudaMalloc(&s.d_pk8, R + 16));
     if (ctx->prm.n_groups > 0) {
         CK(cudaMalloc(&s.d_sample, (R + 4) * sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_gdepth, (S + 1) * (size_t)ctx->prm.n_groups * 4 * sizeof(int32_t)));
@@ -66,7 +67,7 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
 void free_slot(Slot& s)
 {
     cudaFree(s.d_ref); cudaFree(s.d_off); cudaFree(s.d_code); cudaFree(s.d_qual); cudaFree(s.d_mapq);
-    cudaFree(s.d_rpr); cudaFree(s.d_sample); cudaFree(s.d_gdepth); cudaFree(s.d_gaf); cudaFree(s.d_out); cudaFree(s.d_counter);
+    cudaFree(s.d_rpr); cudaFree(s.d_pk8); cudaFree(s.d_sample); cudaFree(s.d_gdepth); cudaFree(s.d_gaf); cudaFree(s.d_out); cudaFree(s.d_counter);
     cudaFree(s.d_sum); cudaFree(s.d_cls); cudaFree(s.d_lad); cudaFree(s.d_fit); cudaFree(s.d_state);
     cudaFree(s.d_qa); cudaFree(s.d_qb); cudaFree(s.d_qs); cudaFree(s.d_ql); cudaFree(s.d_vcf_list); cudaFree(s.d_legacy_list); cudaFree(s.d_ctr);
     if (s.done) cudaEventDestroy(s.done);
@@ -81,7 +82,8 @@ int bvc::check_tile(bvc_ctx* ctx, const bvc_tile* t, int64_t* n_entries)
     if (!t || t->n_sites < 0 || !t->entry_off || (t->n_sites > 0 && !t->ref_base)) { set_err(ctx, "bad tile: NULL array or n_sites < 0"); return BVC_ERR_ARG; }
     if (t->entry_off[0] != 0) { set_err(ctx, "bad tile: entry_off[0] != 0"); return BVC_ERR_ARG; }
     const int64_t R = t->entry_off[t->n_sites];
-    if (R > 0 && (!t->code || !t->qual || !t->mapq || !t->rpr)) { set_err(ctx, "bad tile: NULL entry array"); return BVC_ERR_ARG; }
+    if (R > 0 && (!t->mapq || !t->rpr || (!t->packed8 && (!t->code || !t->qual)))) { set_err(ctx, "bad tile: NULL entry array"); return BVC_ERR_ARG; }
+    if (R > 0 && t->packed8 && (!t->qual_dict || t->n_qual_dict < 1 || t->n_qual_dict > BVC_PACK8_MAX_QUALS)) { set_err(ctx, "bad tile: packed8 needs qual_dict with 1..30 entries"); return BVC_ERR_ARG; }
     if (ctx->prm.n_groups > 0 && R > 0 && !t->sample) { set_err(ctx, "bad tile: groups need the sample array"); return BVC_ERR_ARG; }
     if (t->n_sites > ctx->prm.max_sites || R > ctx->prm.max_entries) { set_err(ctx, "tile exceeds the capacity given at bvc_create"); return BVC_ERR_CAPACITY; }
     *n_entries = R;
@@ -108,10 +110,21 @@ int bvc::upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool reside
     s.n_sites = t->n_sites; s.n_entries = R;
     if (S) CK(cudaMemcpyAsync(s.d_ref, t->ref_base, S, cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.d_off, t->entry_off, (S + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
-    ctx->h2d_bytes += (int64_t)(S + (S + 1) * sizeof(uint32_t) + 2 * (size_t)R);
+    ctx->h2d_bytes += (int64_t)(S + (S + 1) * sizeof(uint32_t));
     if (R) {
-        CK(cudaMemcpyAsync(s.d_code, t->code, (size_t)R, cudaMemcpyHostToDevice, s.stream));
-        CK(cudaMemcpyAsync(s.d_qual, t->qual, (size_t)R, cudaMemcpyHostToDevice, s.stream));
+        if (t->packed8) {
+            // compact wire form: R bytes over PCIe instead of 2R, expanded into the arrays the kernels read
+            bvc::QualDict d;
+            for (int i = 0; i < 32; ++i) d.q[i] = i < t->n_qual_dict ? t->qual_dict[i] : (uint8_t)0;
+            CK(cudaMemcpyAsync(s.d_pk8, t->packed8, (size_t)R, cudaMemcpyHostToDevice, s.stream));
+            CK(bvc::launch_expand8(s.d_pk8, s.d_code, s.d_qual, R, d, ctx->n_sm, s.stream));
+            ctx->launches += 1;
+            ctx->h2d_bytes += R;
+        } else {
+            CK(cudaMemcpyAsync(s.d_code, t->code, (size_t)R, cudaMemcpyHostToDevice, s.stream));
+            CK(cudaMemcpyAsync(s.d_qual, t->qual, (size_t)R, cudaMemcpyHostToDevice, s.stream));
+            ctx->h2d_bytes += 2 * R;
+        }
         // mapq / rpr are read only at LRT-positive sites (K5: ~0.3 % of a low-pass window).  When the caller's
         // arrays are pinned (bvc_host_alloc / cudaHostRegister) the kernels read them in place over PCIe
         // instead of paying a full H2D copy; pageable arrays are copied as before.

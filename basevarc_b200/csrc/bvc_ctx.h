@@ -17,6 +17,7 @@ struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
     uint8_t *d_ref = nullptr, *d_code = nullptr, *d_qual = nullptr, *d_mapq = nullptr, *d_rpr = nullptr;
+    uint8_t *d_pk8 = nullptr;      // landing buffer of a tile's packed8 form (expanded into d_code / d_qual on the device)
     uint32_t *d_off = nullptr, *d_sample = nullptr;
     bvc_site_result* d_out = nullptr;
     unsigned int* d_counter = nullptr;

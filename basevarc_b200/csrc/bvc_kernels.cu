@@ -373,6 +373,43 @@ cudaError_t launch_sum_u32(uint32_t* dst, const uint32_t* src, size_t n, int n_s
     return cudaGetLastError();
 }
 
+// ---- packed8 expansion: 16 entries per thread (one 16-byte load, two 16-byte stores) -------------------------------------
+__global__ void __launch_bounds__(256)
+expand8_kernel(const uint4* __restrict__ pk, uint4* __restrict__ code, uint4* __restrict__ qual, int64_t n16, QualDict dict)
+{
+    __shared__ uint8_t code_lut[256], qual_lut[256];
+    {
+        const unsigned b = threadIdx.x, qi = b >> 3, strand = (b >> 2) & 1u, base = b & 3u;
+        code_lut[b] = qi < 30u ? (uint8_t)(base | (strand << 3)) : qi == 31u ? (uint8_t)(base | (strand << 3) | 0x10u) : (uint8_t)(4u | (strand << 3) | 0x10u);
+        qual_lut[b] = dict.q[qi < 30u ? qi : 0u];
+    }
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint4 v = __ldg(pk + i);
+        const uint32_t in[4] = {v.x, v.y, v.z, v.w};
+        uint32_t c[4], q[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t w = in[k];
+            c[k] = (uint32_t)code_lut[w & 0xffu] | ((uint32_t)code_lut[(w >> 8) & 0xffu] << 8) | ((uint32_t)code_lut[(w >> 16) & 0xffu] << 16) | ((uint32_t)code_lut[w >> 24] << 24);
+            q[k] = (uint32_t)qual_lut[w & 0xffu] | ((uint32_t)qual_lut[(w >> 8) & 0xffu] << 8) | ((uint32_t)qual_lut[(w >> 16) & 0xffu] << 16) | ((uint32_t)qual_lut[w >> 24] << 24);
+        }
+        code[i] = make_uint4(c[0], c[1], c[2], c[3]);
+        qual[i] = make_uint4(q[0], q[1], q[2], q[3]);
+    }
+}
+
+cudaError_t launch_expand8(const uint8_t* pk8, uint8_t* code, uint8_t* qual, int64_t n, const QualDict& dict, int n_sm, cudaStream_t stream)
+{
+    const int64_t n16 = (n + 15) / 16;
+    if (n16 <= 0) return cudaSuccess;
+    long long blocks = (n16 + 255) / 256;
+    if (blocks > (long long)n_sm * 8) blocks = (long long)n_sm * 8;
+    expand8_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<const uint4*>(pk8), reinterpret_cast<uint4*>(code),
+                                                         reinterpret_cast<uint4*>(qual), n16, dict);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream)
 {
     fp64_peak_kernel<<<blocks, threads, 0, stream>>>(out, iters);

@@ -24,6 +24,8 @@ void Packer::clear()
     n_ = 0;
     indel_.clear(); err_.clear();
     sample_ = 0;
+    for (auto& q : qidx_) q = -1;
+    ndict_ = 0; pk8_ok_ = true;
 }
 
 void Packer::reserve_entries(size_t need)
@@ -31,7 +33,7 @@ void Packer::reserve_entries(size_t need)
     if (need <= cap_) return;
     size_t c = cap_ ? cap_ : 4096;
     while (c < need) c *= 2;
-    code_.resize(c); qual_.resize(c); mapq_.resize(c); rpr_.resize(c); smp_.resize(c);
+    code_.resize(c); qual_.resize(c); mapq_.resize(c); rpr_.resize(c); smp_.resize(c); pk8_.resize(c);
     cap_ = c;
 }
 
@@ -71,6 +73,7 @@ int Packer::add_token_slow(const char* tok, const char* tend)
             }
             code_[n_] = BVC_MAKE_CODE(st_base_, st_strand_, 0);
             qual_[n_] = st_qual_; mapq_[n_] = st_mapq_; rpr_[n_] = st_rpr_; smp_[n_] = sample_;
+            pk8_[n_] = pack_counted(st_base_, st_strand_, st_qual_);
             ++n_;
         }
     } else if (c0 != '.') {
@@ -78,6 +81,8 @@ int Packer::add_token_slow(const char* tok, const char* tend)
         indel_.emplace((int64_t)n_, std::string(tok, (size_t)(tend - tok)));
         code_[n_] = BVC_MAKE_CODE(st_base_, st_strand_, 1);
         qual_[n_] = st_qual_ > 127 ? (uint8_t)127 : st_qual_; mapq_[n_] = st_mapq_; rpr_[n_] = st_rpr_; smp_[n_] = sample_;
+        if (st_base_ > 4) pk8_ok_ = false;               // stale base 5..7: not representable (and nothing the writer emits)
+        pk8_[n_] = BVC_PACK8(st_base_ == 4 ? BVC_PACK8_INDEL_N : BVC_PACK8_INDEL, st_strand_, st_base_);
         ++n_;
     }
     return BVC_OK;
@@ -93,6 +98,7 @@ int Packer::add_line(const char* line, size_t len)
     uint8_t* const code = code_.data(); uint8_t* const qual = qual_.data();
     uint8_t* const mapq = mapq_.data(); uint8_t* const rpr = rpr_.data();
     uint32_t* const smp = smp_.data();
+    uint8_t* const pk8 = pk8_.data();
     size_t n = n_;
     uint32_t sample = sample_;
     auto digit = [](char c) { return (unsigned)(c - '0') <= 9u; };
@@ -120,6 +126,7 @@ int Packer::add_line(const char* line, size_t len)
                     if (b != 4) {
                         code[n] = BVC_MAKE_CODE(st_base_, st_strand_, 0);
                         qual[n] = st_qual_; mapq[n] = st_mapq_; rpr[n] = st_rpr_; smp[n] = sample;
+                        pk8[n] = pack_counted(st_base_, st_strand_, st_qual_);
                         ++n;
                     }
                     p = q + 2; ++sample;
@@ -165,6 +172,7 @@ void Packer::tile(bvc_tile* out) const
     out->entry_off = entry_off_.data();
     out->code = code_.data(); out->qual = qual_.data(); out->mapq = mapq_.data(); out->rpr = rpr_.data();
     out->sample = smp_.data();
+    if (pk8_ok_ && n_ > 0 && ndict_ > 0) { out->packed8 = pk8_.data(); out->qual_dict = dict_; out->n_qual_dict = ndict_; }
 }
 
 const char* Packer::indel(int64_t entry) const

@@ -16,7 +16,7 @@ namespace bvc_host {
 
 class Packer {
 public:
-    explicit Packer(int32_t n_samples) : n_samples_(n_samples) { entry_off_.push_back(0); }
+    explicit Packer(int32_t n_samples) : n_samples_(n_samples) { entry_off_.push_back(0); for (auto& q : qidx_) q = -1; }
     void clear();
     void begin_site(int32_t pos, uint8_t ref_base);
     int add_line(const char* line, size_t len);
@@ -43,6 +43,21 @@ private:
     std::vector<uint8_t> code_, qual_, mapq_, rpr_;
     std::vector<uint32_t> smp_;
     size_t n_ = 0, cap_ = 0;
+    // compact wire form of (code, qual) built alongside (include/bvc_gpu.h BVC_PACK8): valid while the tile has <= 30 quals
+    std::vector<uint8_t> pk8_;
+    uint8_t dict_[32] = {0};
+    int8_t qidx_[128];
+    int ndict_ = 0;
+    bool pk8_ok_ = true;
+    inline uint8_t pack_counted(uint8_t base, uint8_t strand, uint8_t qual)
+    {
+        int qi = qidx_[qual];
+        if (qi < 0) {
+            if (ndict_ == BVC_PACK8_MAX_QUALS) { pk8_ok_ = false; return 0; }
+            qi = ndict_; qidx_[qual] = (int8_t)qi; dict_[ndict_++] = qual;
+        }
+        return BVC_PACK8((unsigned)qi, strand, base);
+    }
     void reserve_entries(size_t need);
     int add_token_slow(const char* tok, const char* tend);
     std::unordered_map<int64_t, std::string> indel_;

@@ -119,6 +119,9 @@ class Packer:
         tile = PileupTile(self.n_samples, arr(t.ref_base, S, np.uint8), arr(t.entry_off, S + 1, np.uint32),
                           arr(t.code, R, np.uint8), arr(t.qual, R, np.uint8), arr(t.mapq, R, np.uint8),
                           arr(t.rpr, R, np.uint8), arr(t.sample, R, np.uint32), pos)
+        if t.packed8:
+            tile.packed8 = arr(t.packed8, R, np.uint8)
+            tile.qual_dict = arr(t.qual_dict, t.n_qual_dict, np.uint8)
         for e in np.nonzero((tile.code >> 4) & 1)[0]:
             s = self.lib.bvc_packer_indel(self.h, int(e))
             if s is not None:

@@ -32,6 +32,8 @@ class PileupTile:
     sample: np.ndarray        # [R] uint32
     pos: np.ndarray = None    # [S] int32 1-based positions (host only)
     indel_text: dict = field(default_factory=dict)   # entry index -> indel token (host only)
+    packed8: np.ndarray = None     # [R] uint8 compact wire form of (code, qual), see pack8()
+    qual_dict: np.ndarray = None   # [<= 30] uint8
 
     @property
     def n_sites(self):
@@ -41,7 +43,7 @@ class PileupTile:
     def n_entries(self):
         return int(self.code.shape[0])
 
-    def as_ctypes(self, with_sample=True):
+    def as_ctypes(self, with_sample=True, drop_code_qual=False):
         """The bvc_tile struct over these arrays (which must outlive the call)."""
         t = Tile()
         t.n_sites = self.n_sites
@@ -50,7 +52,36 @@ class PileupTile:
             assert a.flags["C_CONTIGUOUS"]
             setattr(t, name, a.ctypes.data)
         t.sample = self.sample.ctypes.data if (with_sample and self.sample is not None) else None
+        if self.packed8 is not None:
+            assert self.packed8.flags["C_CONTIGUOUS"] and self.packed8.shape[0] == self.n_entries
+            t.packed8 = self.packed8.ctypes.data
+            t.qual_dict = self.qual_dict.ctypes.data
+            t.n_qual_dict = int(self.qual_dict.shape[0])
+            if drop_code_qual:
+                t.code = None
+                t.qual = None
         return t
+
+    def pack8(self):
+        """Adds the compact wire form (include/bvc_gpu.h BVC_PACK8: qi:5 | strand:1 | base:2 + a dictionary of the tile's
+        distinct quals) when the tile qualifies: <= 30 distinct quals among the counted entries and no non-indel entry with
+        a base code > 3.  Returns True if packed8 / qual_dict were set."""
+        base, strand, indel = self.code & 7, (self.code >> 3) & 1, (self.code >> 4) & 1
+        counted = indel == 0
+        if (base[counted] > 3).any() or (base[indel == 1] > 4).any():
+            return False
+        quals = np.unique(self.qual[counted])
+        if quals.size > 30:
+            return False
+        if quals.size == 0:
+            quals = np.array([0], np.uint8)
+        lut = np.zeros(256, np.uint8)
+        lut[quals] = np.arange(quals.size, dtype=np.uint8)
+        qi = lut[self.qual].astype(np.uint8)
+        qi[indel == 1] = np.where(base[indel == 1] == 4, 30, 31).astype(np.uint8)
+        self.packed8 = np.ascontiguousarray((qi << 3) | (strand << 2) | (base & 3)).astype(np.uint8)
+        self.qual_dict = np.ascontiguousarray(quals.astype(np.uint8))
+        return True
 
     def slice_sites(self, s0, s1):
         e0, e1 = int(self.entry_off[s0]), int(self.entry_off[s1])

@@ -323,7 +323,8 @@ def run_sharded(args):
 
     # ---- e2e leg: pinned host buffers through bvc_shard_call (H2D + collectives + D2H inside the region) --------
     pins = {}
-    for k in ("ref_base", "entry_off", "code", "qual", "mapq", "rpr"):
+    packed = args.wire == "packed8" and tile.pack8()
+    for k in ("ref_base", "entry_off", "mapq", "rpr") + (("packed8",) if packed else ("code", "qual")):
         src = getattr(tile, k)
         pins[k] = PinnedArray(src.shape, src.dtype)
         pins[k].array[...] = src
@@ -379,7 +380,7 @@ def run_sharded(args):
                    "l2": "inputs (%.0f MB per rank) exceed the 126 MB L2; no flush needed" % (tile.nbytes() / 1e6) if tile.nbytes() > 126e6
                          else "inputs (%.0f MB per rank) fit the L2: use --sites to grow the tile" % (tile.nbytes() / 1e6)},
         "e2e": {"value": units / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": e2e_s * 1e3, "matches_resident": bool(same)},
+                "ms_per_step": e2e_s * 1e3, "wire": "packed8" if packed else "plain", "matches_resident": bool(same)},
         "gpu_launches": int(launches),
         "roofline": roof,
         "phases_ms": {k: round(v, 4) for k, v in phases.items()},
@@ -400,7 +401,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C4", "C5"])
     ap.add_argument("--sites", type=int, default=0, help="sites per GPU (default: the configuration's full window, C2 = 1e6)")
-    ap.add_argument("--subtiles", type=int, default=8, help="sub-tiles per step on the host-buffer (e2e) path")
+    ap.add_argument("--subtiles", type=int, default=4, help="sub-tiles per step on the host-buffer (e2e) path (measured: 2-6 within 5 %, 8 +14 %, 16 +38 %)")
+    ap.add_argument("--wire", default="packed8", choices=["packed8", "plain"],
+                    help="host-buffer form of (code, qual) on the e2e path: one byte per entry + qual dictionary, or the two arrays")
     ap.add_argument("--ref-sites-per-thread", type=int, default=6000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--qual-window", type=int, nargs=2, default=[1, 63], help="exchange window of the sample-sharded mode (C4)")
@@ -464,7 +467,11 @@ def main():
     subs, pins = [], []
     for i in range(nsub):
         t = tile.slice_sites(int(bounds[i]), int(bounds[i + 1]))
-        for k in ("ref_base", "entry_off", "code", "qual", "mapq", "rpr"):
+        # the compact wire form (one byte per entry + qual dictionary; what the host packer emits for a tile with <= 30
+        # distinct quals) unless --wire plain: the e2e path is PCIe-bound, this halves the bytes of the two big arrays
+        packed = args.wire == "packed8" and t.pack8()
+        wire = "packed8" if packed else "plain"
+        for k in ("ref_base", "entry_off", "mapq", "rpr") + (("packed8",) if packed else ("code", "qual")):
             src = getattr(t, k)
             pa = PinnedArray(src.shape, src.dtype)
             pa.array[...] = src
@@ -550,7 +557,7 @@ def main():
                    "sites_per_gpu": S, "n_samples": N, "entries_per_gpu": R, "parallelism": "window-sharded x%d, no collective" % world,
                    "l2": "inputs (%.0f MB per launch) exceed the 126 MB L2; no flush needed" % (tile.nbytes() / 1e6)},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "matches_resident": bool(same)},
+                "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "wire": wire, "matches_resident": bool(same)},
         "gpu_launches": int(launches),
         "roofline": roof,
         "hbm_stream": {"kernel": "site_hist_kernel", "kernel_ms": hist_ms, "algorithmic_bytes_per_launch": int(hist_bytes),

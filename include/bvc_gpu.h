@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define BVC_ABI_VERSION 1
+#define BVC_ABI_VERSION 2
 
 /* error codes (negative); 0 = success */
 #define BVC_OK             0
@@ -77,7 +77,24 @@ typedef struct bvc_tile {
     const uint8_t*  mapq;       /* [R] */
     const uint8_t*  rpr;        /* [R] read position + 1, truncated to 8 bits as the bitfield does */
     const uint32_t* sample;     /* [R] global sample index; may be NULL when n_groups == 0 */
+    /* Optional compact wire form of (code, qual): ONE byte per entry plus a dictionary of the tile's distinct quals.
+     * When packed8 != NULL the library copies it instead of code / qual (half the host->device bytes of the two arrays;
+     * the path is PCIe-bound end to end) and expands it on the device; code and qual may then be NULL.
+     * mapq / rpr are unchanged.  The host packer (bvc_packer_tile) fills it whenever a tile has <= BVC_PACK8_MAX_QUALS
+     * distinct quals. */
+    const uint8_t*  packed8;    /* [R] BVC_PACK8(qi, strand, base) */
+    const uint8_t*  qual_dict;  /* [n_qual_dict] qual value of dictionary index qi */
+    int32_t n_qual_dict;        /* 1..BVC_PACK8_MAX_QUALS */
+    int32_t reserved1;
 } bvc_tile;
+
+/* packed8 byte: qi:5 | strand:1 | base:2.  qi < 30: a counted entry of base 0..3 with qual qual_dict[qi].
+ * qi == 31: an indel entry with stale base 0..3 / strand (its stale qual is not used by the calling core).
+ * qi == 30: an indel entry whose stale base is 4 (N): it counts nowhere; only strand is kept. */
+#define BVC_PACK8_MAX_QUALS 30
+#define BVC_PACK8_INDEL     31u
+#define BVC_PACK8_INDEL_N   30u
+#define BVC_PACK8(qi, strand, base) ((uint8_t)((((qi) & 31u) << 3) | (((strand) & 1u) << 2) | ((base) & 3u)))
 
 /* boundary-flag bits: a hard FP64 threshold of the reference was met within a 1e-9 relative margin
  * at this site, so a differently-ordered summation may legitimately land on the other side. */

@@ -29,7 +29,7 @@ def test_exports_match_header():
 
 def test_struct_layouts():
     assert _abi.SITE_RESULT_DTYPE.itemsize == 176
-    assert C.sizeof(_abi.Tile) == 8 + 7 * 8
+    assert C.sizeof(_abi.Tile) == 8 + 7 * 8 + 2 * 8 + 8        # + packed8, qual_dict, n_qual_dict + reserved (ABI 2)
     assert C.sizeof(_abi.Params) == 8 + 8 * 3 + 8 + 8 + 8 + 8
     lib = B.load_library()
     p = _abi.Params()

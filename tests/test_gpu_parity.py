@@ -77,6 +77,27 @@ def test_qual_windows(oracle, lo, hi):
     assert want["lrt_ok"].sum() > 0
 
 
+@pytest.mark.parametrize("N,S,depth,model,indel", [(1000, 2000, 0.5, "lowpass", 0.005), (200, 1500, 3.0, "highpoly", 0.05)])
+def test_packed8_wire_form_same_records(oracle, N, S, depth, model, indel):
+    """The compact wire form (include/bvc_gpu.h BVC_PACK8: one byte per entry + qual dictionary, expanded on the device)
+    gives byte-identical records to the two-array form, through bvc_enqueue and as a resident tile."""
+    tile = synth_tile(N, S, depth, model, seed=21, indel_frac=indel)
+    caller = B.BaseTypeCaller(N, max_sites=S, max_entries=tile.n_entries)
+    plain = caller.call_sites(tile).copy()
+    l0 = caller.kernel_launches
+    assert tile.pack8()
+    packed = caller.call_sites(tile).copy()
+    assert caller.kernel_launches - l0 > 0
+    assert packed.tobytes() == plain.tobytes()
+    caller.resident_upload(tile)
+    caller.resident_run(1, flush_l2=False)
+    assert caller.resident_download().tobytes() == plain.tobytes()
+    caller.close()
+    want = oracle.call_sites(tile, B.default_params(N))
+    nbad, lines = compare_records(packed, want)
+    assert nbad == 0, "\n".join(lines)
+
+
 def test_group_path_parity(oracle):
     """--group: per-group depths (exact) and the group-level LRT allele frequencies against the oracle."""
     from test_host_cpp import group_setup

@@ -75,6 +75,37 @@ def test_packer_token_grammar_quirks():
         pk.add_site(12, 0, [b"0,30,200,1,1 "])                                   # qual > 127 is rejected loudly
 
 
+def _unpack8(tile):
+    """(code, qual) from the compact wire form, the way the device expands it (basevarc_b200/csrc/bvc_kernels.cu expand8_kernel)."""
+    p = tile.packed8
+    qi, strand, base = p >> 3, (p >> 2) & 1, p & 3
+    code = np.where(qi < 30, base | (strand << 3), np.where(qi == 31, base | (strand << 3) | 0x10, 4 | (strand << 3) | 0x10)).astype(np.uint8)
+    qual = tile.qual_dict[np.where(qi < 30, qi, 0)]
+    return code, qual
+
+
+@pytest.mark.parametrize("indel", [0.0, 0.05])
+def test_packed8_wire_form(indel):
+    """include/bvc_gpu.h BVC_PACK8: the packer's compact form and pileup.pack8() expand to the same (code, qual) for every
+    counted entry and the same code for indel entries (whose stale qual the calling core never reads)."""
+    tile = B.synth_tile(64, 700, 1.2, "highpoly", seed=5, indel_frac=indel, first_pos=100)
+    tile.indel_text = {int(e): "+A" for e in np.nonzero((tile.code >> 4) & 1)[0]}
+    got = _pack(tile, batch=9).to_tile()
+    assert got.packed8 is not None and 1 <= got.qual_dict.size <= 30
+    counted = ((got.code >> 4) & 1) == 0
+    for t in (got, tile):
+        if t is tile:
+            assert t.pack8()
+        code, qual = _unpack8(t)
+        assert np.array_equal(code, t.code)
+        assert np.array_equal(qual[counted], t.qual[counted])
+    # more than 30 distinct quals: neither producer offers the compact form
+    wide = B.synth_tile(64, 300, 1.2, "highpoly", seed=6)
+    wide.qual = (np.arange(wide.qual.size) % 40 + 2).astype(np.uint8)
+    assert not wide.pack8() and wide.packed8 is None
+    assert _pack(wide, batch=9).to_tile().packed8 is None
+
+
 def _ref_tokenise(lines, state):
     """Plain restatement of src/BaseVarC.cpp:410-438 for one site: strtok on " ", then strtok on "," + atoi per field."""
     import re
