@@ -81,6 +81,27 @@ SITE_RESULT_DTYPE = np.dtype(
 )
 assert SITE_RESULT_DTYPE.itemsize == 176, SITE_RESULT_DTYPE.itemsize
 
+# bvc_site_core (include/bvc_gpu.h): the 72-byte part of a record every site has -- bvc_enqueue_split
+SITE_CORE_DTYPE = np.dtype(
+    [
+        ("cvg_fs", "<f8"),
+        ("cvg_sor", "<f8"),
+        ("n_entries", "<i4"),
+        ("depth", "<i4", (4,)),
+        ("cvg_strand", "<i4", (4,)),
+        ("em_fits", "<i4"),
+        ("em_passes", "<i4"),
+        ("flags", "<u4"),
+        ("cvg_alt_base", "i1"),
+        ("lrt_ok", "i1"),
+        ("n_alt", "i1"),
+        ("reserved", "i1"),
+        ("vcf_index", "<i4"),
+    ],
+    align=False,
+)
+assert SITE_CORE_DTYPE.itemsize == 72, SITE_CORE_DTYPE.itemsize
+
 # integer / index fields that must be bit-exact against the reference, and the FP64 fields held to 1e-9
 EXACT_FIELDS = ("n_entries", "depth", "cvg_strand", "cvg_alt_base", "lrt_ok", "n_alt", "alt_bases")
 EXACT_FIELDS_IF_OK = ("vcf_strand",)

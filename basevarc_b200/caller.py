@@ -10,13 +10,14 @@ import os
 
 import numpy as np
 
-from ._abi import SITE_RESULT_DTYPE, Params, Tile, default_params
+from ._abi import SITE_CORE_DTYPE, SITE_RESULT_DTYPE, Params, Tile, default_params
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbvc_gpu.so")
 
 EXPORTS = (
     "bvc_device_count", "bvc_default_params", "bvc_create", "bvc_destroy", "bvc_last_error", "bvc_enqueue", "bvc_wait",
+    "bvc_enqueue_split", "bvc_wait_split",
     "bvc_fetch_groups", "bvc_host_alloc", "bvc_host_free", "bvc_resident_upload", "bvc_resident_run",
     "bvc_resident_download", "bvc_kernel_launch_count", "bvc_measure_fp64_peak", "bvc_kernel_name", "bvc_transfer_bytes", "bvc_work_counters",
     "bvc_shard_unique_id", "bvc_shard_init", "bvc_shard_call", "bvc_shard_upload", "bvc_shard_run", "bvc_shard_init_group",
@@ -50,6 +51,8 @@ def load_library():
     L.bvc_last_error.restype = C.c_char_p
     L.bvc_enqueue.argtypes = [C.c_void_p, C.POINTER(Tile), C.c_void_p, C.POINTER(C.c_uint64)]
     L.bvc_wait.argtypes = [C.c_void_p, C.c_uint64]
+    L.bvc_enqueue_split.argtypes = [C.c_void_p, C.POINTER(Tile), C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_uint64)]
+    L.bvc_wait_split.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_int32)]
     L.bvc_fetch_groups.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
     L.bvc_host_alloc.argtypes = [C.c_size_t]
     L.bvc_host_alloc.restype = C.c_void_p
@@ -152,6 +155,27 @@ class BaseTypeCaller:
 
     def wait(self, ticket):
         self._check(self.lib.bvc_wait(self.ctx, C.c_uint64(ticket)), "bvc_wait")
+
+    def enqueue_split(self, tile, core, vcf):
+        """bvc_enqueue_split: `core` [n_sites] SITE_CORE_DTYPE, `vcf` [cap] SITE_RESULT_DTYPE (both must outlive wait_split)."""
+        ct = tile.as_ctypes(with_sample=self.params.n_groups > 0, drop_code_qual=True)
+        tk = C.c_uint64(0)
+        self._check(self.lib.bvc_enqueue_split(self.ctx, C.byref(ct), core.ctypes.data, vcf.ctypes.data if vcf.shape[0] else None,
+                                               int(vcf.shape[0]), C.byref(tk)), "bvc_enqueue_split")
+        return tk.value
+
+    def wait_split(self, ticket):
+        """Number of LRT-positive sites of the tile = valid entries of the vcf array handed to enqueue_split."""
+        n = C.c_int32(0)
+        self._check(self.lib.bvc_wait_split(self.ctx, C.c_uint64(ticket), C.byref(n)), "bvc_wait_split")
+        return n.value
+
+    def call_sites_split(self, tile, vcf_cap=None):
+        """(core records, full records of the LRT-positive sites indexed by core['vcf_index'])."""
+        core = np.zeros(tile.n_sites, SITE_CORE_DTYPE)
+        vcf = np.zeros(tile.n_sites if vcf_cap is None else vcf_cap, SITE_RESULT_DTYPE)
+        n = self.wait_split(self.enqueue_split(tile, core, vcf))
+        return core, vcf[:n]
 
     def call_sites_with_groups(self, tile):
         """(records, group_depth[S][G][4], group_af[S][G][4]) -- bt_f with a --group file (src/BaseVarC.cpp:617-661)."""

@@ -67,7 +67,8 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
 void free_slot(Slot& s)
 {
     cudaFree(s.d_ref); cudaFree(s.d_off); cudaFree(s.d_code); cudaFree(s.d_qual); cudaFree(s.d_mapq);
-    cudaFree(s.d_rpr); cudaFree(s.d_pk8); cudaFree(s.d_sample); cudaFree(s.d_gdepth); cudaFree(s.d_gaf); cudaFree(s.d_out); cudaFree(s.d_counter);
+    cudaFree(s.d_rpr); cudaFree(s.d_pk8); cudaFree(s.d_sample); cudaFree(s.d_core); cudaFree(s.d_vcfc); cudaFree(s.d_vcfc_n);
+    if (s.h_vcfc_n) cudaFreeHost(s.h_vcfc_n); cudaFree(s.d_gdepth); cudaFree(s.d_gaf); cudaFree(s.d_out); cudaFree(s.d_counter);
     cudaFree(s.d_sum); cudaFree(s.d_cls); cudaFree(s.d_lad); cudaFree(s.d_fit); cudaFree(s.d_state);
     cudaFree(s.d_qa); cudaFree(s.d_qb); cudaFree(s.d_qs); cudaFree(s.d_ql); cudaFree(s.d_vcf_list); cudaFree(s.d_legacy_list); cudaFree(s.d_ctr);
     if (s.done) cudaEventDestroy(s.done);
@@ -306,6 +307,26 @@ void bvc_destroy(bvc_ctx* ctx)
 
 const char* bvc_last_error(const bvc_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
+// Completes the slot's in-flight ticket before the slot is re-used or waited for: a plain ticket only needs the stream
+// drained; a split ticket still has to fetch its compacted records (their number is known only now).
+static int retire_slot(bvc_ctx* ctx, bvc::Slot& s)
+{
+    if (!s.ticket) return BVC_OK;
+    CK(cudaStreamSynchronize(s.stream));
+    if (s.is_split) {
+        const int32_t n = (int32_t)*s.h_vcfc_n;
+        s.retired_ticket = s.ticket; s.retired_n = n; s.retired_rc = BVC_OK;
+        if (n > s.split_cap) s.retired_rc = BVC_ERR_CAPACITY;
+        else if (n > 0) {
+            CK(cudaMemcpyAsync(s.split_vcf, s.d_vcfc, (size_t)n * sizeof(bvc_site_result), cudaMemcpyDeviceToHost, s.stream));
+            CK(cudaStreamSynchronize(s.stream));
+            ctx->d2h_bytes += (int64_t)n * (int64_t)sizeof(bvc_site_result);
+        }
+    }
+    s.ticket = 0;
+    return BVC_OK;
+}
+
 int bvc_enqueue(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_result* out, uint64_t* ticket)
 {
     if (!ctx) return BVC_ERR_ARG;
@@ -316,17 +337,68 @@ int bvc_enqueue(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_result* out, uint64
     CK(cudaSetDevice(ctx->device));
     const uint64_t tk = ctx->next_ticket;
     Slot& s = ctx->slot[tk & 1];
-    if (s.ticket) { CK(cudaStreamSynchronize(s.stream)); s.ticket = 0; }
+    if ((rc = retire_slot(ctx, s)) != BVC_OK) return rc;
     if ((rc = upload(ctx, s, tile, R, false)) != BVC_OK) return rc;
     if ((rc = launch(ctx, s)) != BVC_OK) return rc;
     if (s.n_sites) CK(cudaMemcpyAsync(out, s.d_out, (size_t)s.n_sites * sizeof(bvc_site_result), cudaMemcpyDeviceToHost, s.stream));
     ctx->d2h_bytes += (int64_t)s.n_sites * (int64_t)sizeof(bvc_site_result);
     CK(cudaEventRecord(s.done, s.stream));
+    s.ticket = tk; s.last_ticket = tk; s.is_split = false;
+    ctx->next_ticket += 1;
+    ctx->resident = false;
+    *ticket = tk;
+    return BVC_OK;
+}
+
+int bvc_enqueue_split(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_core* core, bvc_site_result* vcf, int32_t vcf_cap, uint64_t* ticket)
+{
+    if (!ctx) return BVC_ERR_ARG;
+    if (!core || !ticket || vcf_cap < 0 || (vcf_cap > 0 && !vcf)) { set_err(ctx, "bvc_enqueue_split: NULL core/ticket/vcf"); return BVC_ERR_ARG; }
+    int64_t R = 0;
+    int rc = check_tile(ctx, tile, &R);
+    if (rc != BVC_OK) return rc;
+    CK(cudaSetDevice(ctx->device));
+    const uint64_t tk = ctx->next_ticket;
+    Slot& s = ctx->slot[tk & 1];
+    if ((rc = retire_slot(ctx, s)) != BVC_OK) return rc;
+    if (!s.d_core) {                                   // first split call on this slot
+        const size_t S = (size_t)ctx->prm.max_sites;
+        CK(cudaMalloc(&s.d_core, (S + 1) * sizeof(bvc_site_core)));
+        CK(cudaMalloc(&s.d_vcfc, (S + 1) * sizeof(bvc_site_result)));
+        CK(cudaMalloc(&s.d_vcfc_n, sizeof(uint32_t)));
+        CK(cudaHostAlloc(&s.h_vcfc_n, sizeof(uint32_t), cudaHostAllocDefault));
+    }
+    if ((rc = upload(ctx, s, tile, R, false)) != BVC_OK) return rc;
+    if ((rc = launch(ctx, s)) != BVC_OK) return rc;
+    CK(bvc::launch_split_result(s.d_out, s.n_sites, s.d_core, s.d_vcfc, s.d_vcfc_n, s.stream));
+    ctx->launches += s.n_sites > 0 ? 1 : 0;
+    if (s.n_sites) CK(cudaMemcpyAsync(core, s.d_core, (size_t)s.n_sites * sizeof(bvc_site_core), cudaMemcpyDeviceToHost, s.stream));
+    CK(cudaMemcpyAsync(s.h_vcfc_n, s.d_vcfc_n, sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+    ctx->d2h_bytes += (int64_t)s.n_sites * (int64_t)sizeof(bvc_site_core) + 4;
+    CK(cudaEventRecord(s.done, s.stream));
+    s.split_vcf = vcf; s.split_cap = vcf_cap; s.is_split = true;
     s.ticket = tk; s.last_ticket = tk;
     ctx->next_ticket += 1;
     ctx->resident = false;
     *ticket = tk;
     return BVC_OK;
+}
+
+int bvc_wait_split(bvc_ctx* ctx, uint64_t ticket, int32_t* n_vcf)
+{
+    if (!ctx || !n_vcf) return BVC_ERR_ARG;
+    Slot& s = ctx->slot[ticket & 1];
+    if (ticket == 0 || ticket >= ctx->next_ticket) { set_err(ctx, "bvc_wait_split: unknown ticket"); return BVC_ERR_STATE; }
+    CK(cudaSetDevice(ctx->device));
+    if (s.ticket == ticket) {
+        if (!s.is_split) { set_err(ctx, "bvc_wait_split: not a split ticket"); return BVC_ERR_STATE; }
+        const int rc = retire_slot(ctx, s);
+        if (rc != BVC_OK) return rc;
+    }
+    if (s.retired_ticket != ticket) { set_err(ctx, "bvc_wait_split: not a split ticket, or an older one than the slot remembers"); return BVC_ERR_STATE; }
+    *n_vcf = s.retired_n;
+    if (s.retired_rc == BVC_ERR_CAPACITY) set_err(ctx, "bvc_wait_split: more LRT-positive sites than vcf_cap");
+    return s.retired_rc;
 }
 
 int bvc_wait(bvc_ctx* ctx, uint64_t ticket)
@@ -336,9 +408,7 @@ int bvc_wait(bvc_ctx* ctx, uint64_t ticket)
     if (ticket == 0 || ticket >= ctx->next_ticket) { set_err(ctx, "bvc_wait: unknown ticket"); return BVC_ERR_STATE; }
     if (s.ticket != ticket) return BVC_OK;      // already retired by a later enqueue on the same slot
     CK(cudaSetDevice(ctx->device));
-    CK(cudaStreamSynchronize(s.stream));
-    s.ticket = 0;
-    return BVC_OK;
+    return retire_slot(ctx, s);                 // a split ticket also fetches its records (count: bvc_wait_split)
 }
 
 int bvc_fetch_groups(bvc_ctx* ctx, uint64_t ticket, int32_t* group_depth, double* group_af)
@@ -375,8 +445,8 @@ int bvc_resident_upload(bvc_ctx* ctx, const bvc_tile* tile)
     if (rc != BVC_OK) return rc;
     CK(cudaSetDevice(ctx->device));
     Slot& s = ctx->slot[0];
+    if ((rc = retire_slot(ctx, s)) != BVC_OK) return rc;
     CK(cudaStreamSynchronize(s.stream));
-    s.ticket = 0;
     if ((rc = upload(ctx, s, tile, R, true)) != BVC_OK) return rc;
     CK(cudaStreamSynchronize(s.stream));
     ctx->resident = true;

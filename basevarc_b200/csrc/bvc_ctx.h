@@ -32,6 +32,17 @@ struct Slot {
     uint32_t *d_qa = nullptr, *d_qb = nullptr, *d_qs = nullptr, *d_ql = nullptr, *d_vcf_list = nullptr, *d_legacy_list = nullptr;
     uint32_t* d_ctr = nullptr;     // [kCtrWords]: cls_cursor, qa_n, qb_n, q_head, vcf_n, legacy_n, long_n, work[4] (u64 at word 8), bins at word 16
     const uint8_t *k_mapq = nullptr, *k_rpr = nullptr;   // what the kernels read: d_mapq/d_rpr or zero-copy host pointers
+    // split result (bvc_enqueue_split): device core records, compacted full records, their count; host side of the ticket
+    bvc_site_core* d_core = nullptr;
+    bvc_site_result* d_vcfc = nullptr;
+    uint32_t* d_vcfc_n = nullptr;
+    uint32_t* h_vcfc_n = nullptr;          // pinned
+    bvc_site_result* split_vcf = nullptr;  // caller's vcf[] of the ticket in flight (nullptr: not a split ticket)
+    int32_t split_cap = 0;
+    bool is_split = false;                 // the slot's last ticket came from bvc_enqueue_split
+    uint64_t retired_ticket = 0;           // last split ticket completed on this slot, its count and status
+    int32_t retired_n = 0;
+    int retired_rc = 0;
     uint64_t ticket = 0;       // 0 = idle
     uint64_t last_ticket = 0;  // ticket of the tile whose outputs the slot's device buffers hold
     int n_sites = 0;

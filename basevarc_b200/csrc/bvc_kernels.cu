@@ -373,6 +373,37 @@ cudaError_t launch_sum_u32(uint32_t* dst, const uint32_t* src, size_t n, int n_s
     return cudaGetLastError();
 }
 
+// ---- split result: thread per site ------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+split_result_kernel(const bvc_site_result* __restrict__ rec, int n_sites, bvc_site_core* __restrict__ core,
+                    bvc_site_result* __restrict__ vcf, uint32_t* vcf_n)
+{
+    const int site = blockIdx.x * blockDim.x + threadIdx.x;
+    if (site >= n_sites) return;
+    const bvc_site_result r = rec[site];
+    bvc_site_core c;
+    c.cvg_fs = r.cvg_fs; c.cvg_sor = r.cvg_sor; c.n_entries = r.n_entries;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) { c.depth[b] = r.depth[b]; c.cvg_strand[b] = r.cvg_strand[b]; }
+    c.em_fits = r.em_fits; c.em_passes = r.em_passes; c.flags = r.flags;
+    c.cvg_alt_base = r.cvg_alt_base; c.lrt_ok = r.lrt_ok; c.n_alt = r.n_alt; c.reserved = 0;
+    c.vcf_index = -1;
+    if (r.lrt_ok) {
+        const uint32_t i = atomicAdd(vcf_n, 1u);
+        vcf[i] = r;
+        c.vcf_index = (int32_t)i;
+    }
+    core[site] = c;
+}
+
+cudaError_t launch_split_result(const bvc_site_result* rec, int n_sites, bvc_site_core* core, bvc_site_result* vcf, uint32_t* vcf_n,
+                                cudaStream_t stream)
+{
+    cudaMemsetAsync(vcf_n, 0, sizeof(uint32_t), stream);
+    if (n_sites > 0) split_result_kernel<<<(unsigned)((n_sites + 255) / 256), 256, 0, stream>>>(rec, n_sites, core, vcf, vcf_n);
+    return cudaGetLastError();
+}
+
 // ---- packed8 expansion: 16 entries per thread (one 16-byte load, two 16-byte stores) -------------------------------------
 __global__ void __launch_bounds__(256)
 expand8_kernel(const uint4* __restrict__ pk, uint4* __restrict__ code, uint4* __restrict__ qual, int64_t n16, QualDict dict)

@@ -54,6 +54,9 @@ cudaError_t launch_sum_u32(uint32_t* dst, const uint32_t* src, size_t n, int n_s
 cudaError_t launch_groups(const SiteArgs& s, const uint32_t* sample, const int32_t* sample_group, int n_groups,
                           int32_t* gdepth, double* gaf, int n_sm, cudaStream_t stream);
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream);
+// records -> 72-byte cores + compacted full records of the LRT-positive sites (bvc_enqueue_split)
+cudaError_t launch_split_result(const bvc_site_result* rec, int n_sites, bvc_site_core* core, bvc_site_result* vcf, uint32_t* vcf_n,
+                                cudaStream_t stream);
 // packed8 -> (code, qual): include/bvc_gpu.h BVC_PACK8; n is rounded up to whole 16-byte words (the buffers are padded)
 struct QualDict { uint8_t q[32]; };
 cudaError_t launch_expand8(const uint8_t* pk8, uint8_t* code, uint8_t* qual, int64_t n, const QualDict& dict, int n_sm, cudaStream_t stream);

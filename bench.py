@@ -402,6 +402,8 @@ def main():
     ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C4", "C5"])
     ap.add_argument("--sites", type=int, default=0, help="sites per GPU (default: the configuration's full window, C2 = 1e6)")
     ap.add_argument("--subtiles", type=int, default=4, help="sub-tiles per step on the host-buffer (e2e) path (measured: 2-6 within 5 %, 8 +14 %, 16 +38 %)")
+    ap.add_argument("--result", default="split", choices=["split", "full"],
+                    help="device->host form on the e2e path: 72-byte core per site + full records of the LRT-positive sites, or 176 bytes per site")
     ap.add_argument("--wire", default="packed8", choices=["packed8", "plain"],
                     help="host-buffer form of (code, qual) on the e2e path: one byte per entry + qual dictionary, or the two arrays")
     ap.add_argument("--ref-sites-per-thread", type=int, default=6000)
@@ -478,12 +480,33 @@ def main():
             pins.append(pa)
             setattr(t, k, pa.array)
         subs.append(t)
-    outs = [PinnedArray((t.n_sites,), B.SITE_RESULT_DTYPE) for t in subs]
+    # result form: "split" = the 72-byte core of every site + the full 176-byte record of the LRT-positive sites only
+    # (bvc_enqueue_split; the half that stays behind is zero for every other site), "full" = 176 bytes for every site
+    split = args.result == "split"
+    if split:
+        outs = [PinnedArray((t.n_sites,), B.SITE_CORE_DTYPE) for t in subs]
+        vcfs = [PinnedArray((max(1024, t.n_sites // 8),), B.SITE_RESULT_DTYPE) for t in subs]
+        n_vcf = [0] * nsub
+    else:
+        outs = [PinnedArray((t.n_sites,), B.SITE_RESULT_DTYPE) for t in subs]
 
     def e2e_step():
-        tks = [caller.enqueue(t, o.array) for t, o in zip(subs, outs)]
-        for tk in tks:
-            caller.wait(tk)
+        # the dispatcher's pattern (csrc/host/rerun.cc): two tickets in flight, the older one retired before a third is issued
+        fly = []
+
+        def retire():
+            i, tk = fly.pop(0)
+            if split:
+                n_vcf[i] = caller.wait_split(tk)
+            else:
+                caller.wait(tk)
+
+        for i, (t, o) in enumerate(zip(subs, outs)):
+            fly.append((i, caller.enqueue_split(t, o.array, vcfs[i].array) if split else caller.enqueue(t, o.array)))
+            if len(fly) == 2 and i + 1 < nsub:
+                retire()
+        while fly:
+            retire()
 
     for _ in range(args.warmup):
         e2e_step()
@@ -502,7 +525,13 @@ def main():
     d2h = (d2h1 - d2h0) // args.steps
     clocks = sampler.stop() if sampler else None
     e2e_value = world * units_per_gpu / e2e_s
-    same = all(np.array_equal(np.concatenate([o.array for o in outs])[f], recs[f]) for f in ("depth", "lrt_ok", "alt_bases"))
+    got = np.concatenate([o.array for o in outs])
+    same = all(np.array_equal(got[f], recs[f]) for f in ("depth", "lrt_ok", "cvg_strand"))
+    if split:
+        alt = np.concatenate([v.array[o.array["vcf_index"][o.array["lrt_ok"] == 1]]["alt_bases"] for o, v in zip(outs, vcfs)])
+        same = same and np.array_equal(alt, recs["alt_bases"][recs["lrt_ok"] == 1]) and sum(n_vcf) == int((recs["lrt_ok"] == 1).sum())
+    else:
+        same = same and np.array_equal(got["alt_bases"], recs["alt_bases"])
 
     # ---- rooflines (DESIGN.md "Measurement"): the dominant kernel, the streaming kernel, the whole step ----------
     peak, peak_src = _peaks()
@@ -557,7 +586,7 @@ def main():
                    "sites_per_gpu": S, "n_samples": N, "entries_per_gpu": R, "parallelism": "window-sharded x%d, no collective" % world,
                    "l2": "inputs (%.0f MB per launch) exceed the 126 MB L2; no flush needed" % (tile.nbytes() / 1e6)},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "wire": wire, "matches_resident": bool(same)},
+                "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "wire": wire, "result": args.result, "matches_resident": bool(same)},
         "gpu_launches": int(launches),
         "roofline": roof,
         "hbm_stream": {"kernel": "site_hist_kernel", "kernel_ms": hist_ms, "algorithmic_bytes_per_launch": int(hist_bytes),

@@ -139,6 +139,26 @@ const char* bvc_last_error(const bvc_ctx* ctx);   /* ctx may be NULL: returns th
  * Up to two tickets may be in flight; a third bvc_enqueue waits for the oldest. */
 int  bvc_enqueue(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_result* out, uint64_t* ticket);
 int  bvc_wait(bvc_ctx* ctx, uint64_t ticket);
+/* Split result for the PCIe-bound host-buffer path: every site gets the 72-byte core of its record (all a CVG row
+ * prints, src/BaseVarC.cpp:568-575,610); the full 176-byte record travels only for the LRT-positive sites (the VCF rows,
+ * ~0.3 % of a low-pass window), compacted into vcf[0 .. n_vcf) in no particular order -- core[site].vcf_index says where.
+ * For the other sites the VCF half of the record is all zero by definition.  40 % of the bytes of bvc_enqueue's output. */
+typedef struct bvc_site_core {
+    double  cvg_fs, cvg_sor;
+    int32_t n_entries;
+    int32_t depth[4];
+    int32_t cvg_strand[4];
+    int32_t em_fits, em_passes;
+    uint32_t flags;
+    int8_t  cvg_alt_base, lrt_ok, n_alt, reserved;
+    int32_t vcf_index;          /* index into vcf[] of this call when lrt_ok, else -1 */
+} bvc_site_core;
+/* core: [n_sites]; vcf: [vcf_cap] (both caller-owned until the ticket is retired).  Shares the two-slot ticket queue with
+ * bvc_enqueue: a third enqueue retires the oldest ticket (its records are in place by then); bvc_wait_split may be called
+ * for a ticket up to the moment its slot has retired ANOTHER split ticket. */
+int  bvc_enqueue_split(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_core* core, bvc_site_result* vcf, int32_t vcf_cap, uint64_t* ticket);
+/* *n_vcf = LRT-positive sites of the tile.  BVC_ERR_CAPACITY (core valid, vcf untouched) if that exceeds vcf_cap. */
+int  bvc_wait_split(bvc_ctx* ctx, uint64_t ticket, int32_t* n_vcf);
 /* Optional per-group outputs of the most recently enqueued tile (n_groups > 0), valid after bvc_wait:
  * group_depth [n_sites][n_groups][4] int32 (src/BaseVarC.cpp:622-640) and
  * group_af    [n_sites][n_groups][4] double by base code, NaN-free (src/BaseVarC.cpp:641-660). */

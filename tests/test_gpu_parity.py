@@ -98,6 +98,46 @@ def test_packed8_wire_form_same_records(oracle, N, S, depth, model, indel):
     assert nbad == 0, "\n".join(lines)
 
 
+def test_split_result_equals_full_records():
+    """bvc_enqueue_split: the 72-byte core of every site + the full record of the LRT-positive sites only, against the
+    176-byte records of bvc_enqueue on the same tile (integer fields identical, FP64 within the parity tolerance -- the two
+    calls are separate runs of the EM), two tickets in flight, and the capacity error."""
+    tile = synth_tile(500, 6000, 1.0, "highpoly", seed=31, indel_frac=0.01)
+    assert tile.pack8()
+    caller = B.BaseTypeCaller(500, max_sites=4000, max_entries=tile.n_entries)
+    halves = [tile.slice_sites(0, 3500), tile.slice_sites(3500, 6000)]
+    full = np.concatenate([caller.call_sites(t).copy() for t in halves])
+    cores = [np.zeros(t.n_sites, B.SITE_CORE_DTYPE) for t in halves]
+    vcfs = [np.zeros(t.n_sites, B.SITE_RESULT_DTYPE) for t in halves]
+    # four enqueues before the first wait: the third and fourth retire the first two tickets (their records must be home)
+    scratch = [(np.zeros(t.n_sites, B.SITE_CORE_DTYPE), np.zeros(t.n_sites, B.SITE_RESULT_DTYPE)) for t in halves]
+    tks = [caller.enqueue_split(t, c, v) for t, c, v in zip(halves, cores, vcfs)]
+    tks2 = [caller.enqueue_split(t, c, v) for t, (c, v) in zip(halves, scratch)]
+    ns = [caller.wait_split(tk) for tk in tks]
+    assert [caller.wait_split(tk) for tk in tks2] == ns
+    off = 0
+    for t, c, v, n in zip(halves, cores, vcfs, ns):
+        ref = full[off:off + t.n_sites]
+        off += t.n_sites
+        for f in ("n_entries", "depth", "cvg_strand", "em_fits", "cvg_alt_base", "lrt_ok", "n_alt"):
+            assert np.array_equal(c[f], ref[f]), f
+        for f in ("cvg_fs", "cvg_sor"):
+            assert c[f].tobytes() == ref[f].tobytes(), f
+        ok = ref["lrt_ok"] == 1
+        assert n == int(ok.sum()) and n > 50
+        assert (c["vcf_index"][~ok] == -1).all() and sorted(c["vcf_index"][ok].tolist()) == list(range(n))
+        nbad, lines = compare_records(v[c["vcf_index"][ok]], ref[ok])
+        assert nbad == 0, "\n".join(lines)
+        for f in ("af_lrt", "vcf_strand", "ranksum", "vcf_fs"):
+            assert not ref[f][~ok].any(), f                       # the half that does not travel is all zero anyway
+    core = np.zeros(halves[0].n_sites, B.SITE_CORE_DTYPE)
+    tk = caller.enqueue_split(halves[0], core, np.zeros(3, B.SITE_RESULT_DTYPE))
+    with pytest.raises(B.BvcError, match="vcf_cap"):
+        caller.wait_split(tk)
+    assert np.array_equal(core["depth"], full["depth"][:3500])   # the core part is valid all the same
+    caller.close()
+
+
 def test_group_path_parity(oracle):
     """--group: per-group depths (exact) and the group-level LRT allele frequencies against the oracle."""
     from test_host_cpp import group_setup
