@@ -150,7 +150,7 @@ void bvc::fill_args(const bvc_ctx* ctx, const Slot& s, SiteArgs& a, PipeArgs& p)
     a.site_list = nullptr; a.list_n = nullptr;
     p.s = a;
     p.mean_entries = (int)(s.n_entries / (s.n_sites > 0 ? s.n_sites : 1));
-    p.pass_budget = ctx->pass_budget; p.drain_min_pass = ctx->drain_min_pass; p.drain_lanes = ctx->drain_lanes; p.em_min_fits = ctx->em_min_fits;
+    p.pass_budget = ctx->pass_budget; p.drain_min_pass = ctx->drain_min_pass; p.drain_lanes = ctx->drain_lanes; p.em_min_fits = ctx->em_min_fits; p.refill_min = ctx->refill_min; p.long_exact = ctx->long_exact;
     p.packed_hist = (ctx->prm.n_samples < 65536 && !ctx->wide_hist) ? 1 : 0;
     p.sum = s.d_sum; p.cls = s.d_cls; p.cls_cursor = s.d_ctr + 0;
     p.lad = s.d_lad; p.fit = s.d_fit; p.state = s.d_state;
@@ -261,6 +261,8 @@ int bvc_create(bvc_ctx** out, int device, const bvc_params* prm)
     { const char* e = getenv("BVC_PASS_BUDGET"); if (e && atoi(e) > 0) ctx->pass_budget = atoi(e); }       // tuning knobs (A/B runs)
     { const char* e = getenv("BVC_DRAIN_MIN_PASS"); if (e && atoi(e) > 0) ctx->drain_min_pass = atoi(e); }
     { const char* e = getenv("BVC_DRAIN_LANES"); if (e && atoi(e) > 0) ctx->drain_lanes = atoi(e); }
+    { const char* e = getenv("BVC_LONG_EXACT"); ctx->long_exact = (e && e[0] == '1'); }
+    { const char* e = getenv("BVC_REFILL_MIN"); if (e && atoi(e) > 0) ctx->refill_min = atoi(e); }
     { const char* e = getenv("BVC_EM_MIN_FITS"); if (e && atoi(e) >= 0) ctx->em_min_fits = atoi(e); }
     if (!(prm->em_epsilon <= 0.0019)) { ctx->err = "bvc_create: em_epsilon must be <= 0.0019 (see log1p_tiny in bvc_pipeline.cuh)"; return fail(BVC_ERR_ARG); }
 

@@ -70,6 +70,8 @@ struct bvc_ctx {
     bool zero_copy = true;         // BVC_NO_ZERO_COPY=1 forces the full mapq/rpr copy (A/B checks)
     bool wide_hist = false;        // BVC_WIDE_HIST=1: K1 as site_hist_kernel<G> even for small cohorts (A/B checks)
     int em_min_fits = 0;           // BVC_EM_MIN_FITS: stages below this many fits run entirely in em_long_kernel; 0 = one fit per K3 lane
+    int long_exact = 0;            // BVC_LONG_EXACT=1: em_long_kernel with the exact delta on every pass (A/B checks)
+    int refill_min = 4;            // BVC_REFILL_MIN: em_fit_kernel batches its refills (C2: em_fit 0.79 -> 0.73 ms at 4..8, 0.78 at 16; C5 neutral)
     int pass_budget = 64, drain_min_pass = 16, drain_lanes = 8;  // em_fit_kernel -> em_long_kernel hand-over (BVC_PASS_BUDGET / BVC_DRAIN_MIN_PASS)
     bool legacy_only = false;      // BVC_LEGACY_KERNEL=1: the single warp-per-site kernel for every site (A/B checks)
     std::string err;

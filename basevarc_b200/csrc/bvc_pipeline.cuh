@@ -919,6 +919,18 @@ __device__ __forceinline__ void em_class_exact(uint32_t w, const double2* lut2, 
     A.xmax = max(A.xmax, (w >> 9) ? (__double2hiint(x) & 0x7fffffff) : 0);
 }
 
+// ---- K3b's class body without the delta term: the SAME E/M arithmetic as em_class_exact (so a fit's numbers do not depend on
+// which body ran a pass); the pass is then decided by delta_decision's bound, and repeated with em_class_exact only if that is ambiguous
+__device__ __forceinline__ void em_class_plain(uint32_t w, const double2* lut2, double f0, double f1, double f2, double f3, double F, EmAcc& A)
+{
+    const double cnt = cnt_to_double(w >> 9);
+    const double2 ed = lut2[w & (kNQ - 1)];
+    const double ml = fma(sel4_w(w, f0, f1, f2, f3), ed.y, ed.x * F);
+    const double wgt = cnt * rcp_nr2(ml);
+    A.accT = fma(ed.x, wgt, A.accT);
+    acc_by_base(w, ed.y * wgt, A.V0, A.V1, A.V2, A.V3);
+}
+
 __device__ __forceinline__ void load_lut2(double2* lut2, const double* lut)
 {
     for (int i = threadIdx.x; i < kNQ; i += blockDim.x) lut2[i] = make_double2(lut[i], lut[4 * kNQ + i]);
@@ -972,7 +984,10 @@ em_fit_kernel(PipeArgs a)
     for (;;) {
         // ---- refill at the pass boundary: lanes without a fit take the next items (one atomic per warp) ---
         const bool want = !active && !done;
-        const unsigned wm = __ballot_sync(0xffffffffu, want);
+        unsigned wm = __ballot_sync(0xffffffffu, want);
+        // The refill path (~150 warp instructions and a chain of dependent loads) is paid by the whole warp whenever ANY lane
+        // takes a fit, an idle lane costs 1/32 of a pass: lanes wait until refill_min of them want one (or none holds a fit)
+        if (wm && __popc(wm) < a.refill_min && !drain && __any_sync(0xffffffffu, active)) wm = 0;
         if (wm) {
             uint32_t base = 0;
             const int leader = __ffs(wm) - 1;
@@ -1107,7 +1122,10 @@ em_fit_kernel(PipeArgs a)
 // =====================================================================================================
 constexpr int kLongThreads = 128;
 
-__global__ void __launch_bounds__(kLongThreads)
+#ifndef BVC_LONG_MINBLOCKS
+#define BVC_LONG_MINBLOCKS 5               // 87 registers; capped at 80 for 6 blocks per SM it spills 8 bytes and C3's em_long runs 0.86 instead of 0.80 ms
+#endif
+__global__ void __launch_bounds__(kLongThreads, BVC_LONG_MINBLOCKS)
 em_long_kernel(PipeArgs a)
 {
     __shared__ double2 lut2[kNQ];
@@ -1120,7 +1138,7 @@ em_long_kernel(PipeArgs a)
     const int max_iter = a.s.max_iter;
     unsigned long long work = 0;
 
-    bool active = false, done = false;
+    bool active = false, done = false, lowq = false, exact = false;
     const uint32_t* cp = a.cls;
     int ncls = 0, nmaj = 0, pass = 0;
     uint32_t item = 0, fl = 0;
@@ -1147,6 +1165,8 @@ em_long_kernel(PipeArgs a)
                     pass = fr->passes; fl = fr->flags;
                     inv_n = 1.0 / (double)(su.depth[0] + su.depth[1] + su.depth[2] + su.depth[3]);
                     cp = a.cls + su.cls_off; ncls = su.ncls; nmaj = su.n_major;
+                    // a class with qual <= 1 voids delta_decision's sign argument (see em_fit_kernel): exact delta on every pass
+                    lowq = (su.has_q0 & 2) != 0 || a.long_exact != 0; exact = lowq;
                     active = true;
                 } else done = true;
             }
@@ -1155,12 +1175,24 @@ em_long_kernel(PipeArgs a)
         const int nmine = active ? ncls : 0;
         const int trips = (__reduce_max_sync(0xffffffffu, nmine) + kLongGroup - 1) / kLongGroup;
 
+        // The exact delta (a second marginal and a log1p per class, two more butterflies) doubles a pass: the warp evaluates it
+        // only if one of its fits needs it -- a qual <= 1 class, or a pass whose bound-based decision came out ambiguous
+        const bool warp_exact = __any_sync(0xffffffffu, active && exact);
         EmAcc A; A.accT = A.V0 = A.V1 = A.V2 = A.V3 = A.dl = 0.0; A.xmax = 0;
+        if (warp_exact) {
 #pragma unroll 2
-        for (int k = 0; k < trips; ++k) {
-            const int c = k * kLongGroup + g;               // class index -> pool word: the minor classes start behind the padding
-            const uint32_t w = (c < nmine) ? __ldg(cp + (c < nmaj ? c : c + (pad4(nmaj) - nmaj))) : kNullClass;
-            em_class_exact(w, lut2, f0, f1, f2, f3, F, p0, p1, p2, p3, Fp, A);
+            for (int k = 0; k < trips; ++k) {
+                const int c = k * kLongGroup + g;           // class index -> pool word: the minor classes start behind the padding
+                const uint32_t w = (c < nmine) ? __ldg(cp + (c < nmaj ? c : c + (pad4(nmaj) - nmaj))) : kNullClass;
+                em_class_exact(w, lut2, f0, f1, f2, f3, F, p0, p1, p2, p3, Fp, A);
+            }
+        } else {
+#pragma unroll 2
+            for (int k = 0; k < trips; ++k) {
+                const int c = k * kLongGroup + g;
+                const uint32_t w = (c < nmine) ? __ldg(cp + (c < nmaj ? c : c + (pad4(nmaj) - nmaj))) : kNullClass;
+                em_class_plain(w, lut2, f0, f1, f2, f3, F, A);
+            }
         }
 #pragma unroll
         for (int o = kLongGroup / 2; o > 0; o >>= 1) {               // butterfly within the group: all its lanes agree
@@ -1169,19 +1201,31 @@ em_long_kernel(PipeArgs a)
             A.V1 += __shfl_xor_sync(0xffffffffu, A.V1, o);
             A.V2 += __shfl_xor_sync(0xffffffffu, A.V2, o);
             A.V3 += __shfl_xor_sync(0xffffffffu, A.V3, o);
-            A.dl += __shfl_xor_sync(0xffffffffu, A.dl, o);
-            A.xmax = max(A.xmax, __shfl_xor_sync(0xffffffffu, A.xmax, o));
+            if (warp_exact) {
+                A.dl += __shfl_xor_sync(0xffffffffu, A.dl, o);
+                A.xmax = max(A.xmax, __shfl_xor_sync(0xffffffffu, A.xmax, o));
+            }
         }
         if (active) {
             if (g == 0) work += (unsigned long long)ncls;
             const double e0 = f0 * (A.accT + A.V0) * inv_n, e1 = f1 * (A.accT + A.V1) * inv_n;
             const double e2 = f2 * (A.accT + A.V2) * inv_n, e3 = f3 * (A.accT + A.V3) * inv_n;
-            bool stop = (pass == max_iter);
-            if (pass > 0 && A.xmax < kBigXHi) {
-                if (near_rel(A.dl, eps)) fl |= BVC_FLAG_EM_DELTA;
-                if (A.dl < eps) stop = true;                         // Algorithm.cpp:124
+            bool stop = (pass == max_iter), redo = false;
+            if (pass > 0) {
+                if (warp_exact) {
+                    if (A.xmax < kBigXHi) {
+                        if (near_rel(A.dl, eps)) fl |= BVC_FLAG_EM_DELTA;
+                        if (A.dl < eps) stop = true;                 // Algorithm.cpp:124
+                    }
+                } else {
+                    const double P = fabs(p0 - f0) * A.V0 + fabs(p1 - f1) * A.V1 + fabs(p2 - f2) * A.V2 + fabs(p3 - f3) * A.V3;
+                    const int dec = delta_decision(P, eps);
+                    if (dec == 1) stop = true;
+                    else if (dec == 2 && !stop) redo = true;         // this pass again, with the exact sum
+                }
             }
-            if (stop) {
+            if (redo) exact = true;
+            else if (stop) {
                 if (g == 0) {
                     FitRes* fr = a.fit + (size_t)(item >> 2) * 4 + (item & 3);
                     fr->f[0] = f0; fr->f[1] = f1; fr->f[2] = f2; fr->f[3] = f3;
@@ -1193,7 +1237,7 @@ em_long_kernel(PipeArgs a)
                 p0 = f0; p1 = f1; p2 = f2; p3 = f3; Fp = F;
                 f0 = e0; f1 = e1; f2 = e2; f3 = e3;                  // Algorithm.cpp:95-101
                 F = ((f0 + f1) + f2) + f3;
-                ++pass;
+                ++pass; exact = lowq;
             }
         }
         (void)gmask;

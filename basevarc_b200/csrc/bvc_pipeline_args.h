@@ -55,6 +55,8 @@ struct PipeArgs {
     int pass_budget;            // passes a fit may spend in em_fit_kernel before it is parked for em_long_kernel
     int drain_min_pass;         // once the queue is empty, fits at or beyond this pass move to em_long_kernel ...
     int drain_lanes;            // ... provided at most this many lanes of the warp still hold a fit
+    int refill_min;             // em_fit_kernel: lanes without a fit wait until this many of the warp's lanes want one
+    int long_exact;             // 1: em_long_kernel evaluates the exact delta on every pass (A/B check of its bound-based decision)
     int em_min_fits;            // a stage with fewer fits than this skips em_fit_kernel (every fit starts in em_long_kernel)
     SiteArgs s;                 // tile arrays, out, lut, lgam, thresholds
     SiteSum*  sum;              // [n_sites]
