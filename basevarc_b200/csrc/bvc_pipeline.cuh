@@ -814,7 +814,10 @@ queue_scatter_kernel(PipeArgs a)
 constexpr int kEmThreads = 128;
 // hand-over to K3b: PipeArgs::pass_budget (passes a fit may spend in K3) and PipeArgs::drain_min_pass (once the queue
 // is empty, fits at or beyond this pass move to K3b); defaults in bvc_ctx.h
-constexpr int kLongGroup = 8;              // lanes per fit in K3b
+#ifndef BVC_LONG_GROUP
+#define BVC_LONG_GROUP 8                   // measured with the bound-based passes: 4 lanes per fit run C3's em_long in the same 0.80 ms, 2 in 1.01 ms
+#endif
+constexpr int kLongGroup = BVC_LONG_GROUP; // lanes per fit in K3b
 
 // 1/x for normal positive x: MUFU.RCP64H seed (relative error e <= 2^-23, PTX rcp.approx.ftz.f64) + ONE cubic step
 // r (1 + e + e^2), e = 1 - x r: remaining error e^3 <= 2^-69, i.e. correctly rounded up to the last fma (<= 1 ulp)
