@@ -485,7 +485,8 @@ def main():
     split = args.result == "split"
     if split:
         outs = [PinnedArray((t.n_sites,), B.SITE_CORE_DTYPE) for t in subs]
-        vcfs = [PinnedArray((max(1024, t.n_sites // 8),), B.SITE_RESULT_DTYPE) for t in subs]
+        # capacity = every site (C5's high-polymorphism windows call > 1/8 of their sites); only the filled part is copied
+        vcfs = [PinnedArray((t.n_sites,), B.SITE_RESULT_DTYPE) for t in subs]
         n_vcf = [0] * nsub
     else:
         outs = [PinnedArray((t.n_sites,), B.SITE_RESULT_DTYPE) for t in subs]
