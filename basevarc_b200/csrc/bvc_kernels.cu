@@ -211,11 +211,15 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     PipeArgs a = a0;
     const int S = a.s.n_sites;
     int launches = 0;
-    static int occ_hist4 = 0, occ_hist = 0, occ_hist16 = 0, occ_em = 0, occ_vcf = 0, occ_leg = 0, occ_long = 0, occ_ll = 0;
+    static int occ_hist4 = 0, occ_hist = 0, occ_hist16 = 0, occ_em = 0, occ_vcf = 0, occ_leg = 0, occ_long = 0, occ_ll = 0, occ_lad = 0;
     if (!occ_hist) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_long, em_long_kernel, kLongThreads, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ll, fit_loglik_kernel, kEmThreads, 0);
         if (occ_long < 1) occ_long = 1; if (occ_ll < 1) occ_ll = 1;
+        // K4 is a static grid-stride loop: with more blocks than fit on the device (it ran 8 per SM where 72 registers allow 7)
+        // the blocks of the second, nearly empty wave start only when the first wave's equal shares are done -- twice the time
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_lad, ladder_kernel, 128, 0);
+        if (occ_lad < 1) occ_lad = 1;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist4, site_hist4_kernel, kHistWarps * 32, 0);
         if (occ_hist4 < 1) occ_hist4 = 1;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist, site_hist_kernel<32>, kHistWarps * 32, 0);
@@ -268,7 +272,7 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
         mark(kKLoglik);
         fit_loglik_kernel<<<(unsigned)(n_sm * occ_ll), kEmThreads, 0, stream>>>(a);
         mark(kKLadder);
-        ladder_kernel<<<(unsigned)(n_sm * 8), 128, 0, stream>>>(a);
+        ladder_kernel<<<(unsigned)(n_sm * occ_lad), 128, 0, stream>>>(a);
     }
     }
     if (parts & kPartVcf) {
@@ -293,9 +297,14 @@ cudaError_t launch_groups(const SiteArgs& s, const uint32_t* sample, const int32
     const size_t n = (size_t)s.n_sites * n_groups * 4;
     cudaMemsetAsync(gdepth, 0, n * sizeof(int32_t), stream);
     cudaMemsetAsync(gaf, 0, n * sizeof(double), stream);
-    const unsigned grid = (unsigned)(n_sm * 8);
-    group_depth_kernel<<<grid, kGroupWarps * 32, 0, stream>>>(g);
-    group_lrt_kernel<<<grid, kGroupWarps * 32, 0, stream>>>(g);
+    static int occ_gd = 0, occ_gl = 0;                      // one resident wave each (both are static grid-stride loops)
+    if (!occ_gd) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_gd, group_depth_kernel, kGroupWarps * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_gl, group_lrt_kernel, kGroupWarps * 32, 0);
+        if (occ_gd < 1) occ_gd = 1; if (occ_gl < 1) occ_gl = 1;
+    }
+    group_depth_kernel<<<(unsigned)(n_sm * occ_gd), kGroupWarps * 32, 0, stream>>>(g);
+    group_lrt_kernel<<<(unsigned)(n_sm * occ_gl), kGroupWarps * 32, 0, stream>>>(g);
     return cudaGetLastError();
 }
 
