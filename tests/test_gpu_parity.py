@@ -193,3 +193,48 @@ def test_gpu_vs_reference_binary_golden(name):
     caller.close()
     bad = refrun.compare_records_to_text(tile, rec, cvg, vcf)
     assert not bad, "\n".join(bad[:5])
+
+
+def _records(tile, monkeypatch, **env):
+    for k, v in env.items():
+        monkeypatch.setenv(k, str(v))
+    caller = B.BaseTypeCaller(tile.n_samples, max_sites=tile.n_sites, max_entries=tile.n_entries)
+    caller.resident_upload(tile)                      # the device-resident path: the work counters belong to it
+    caller.resident_run(1, False)
+    rec = caller.resident_download().copy()
+    work = caller.work_counters()
+    caller.close()
+    for k in env:
+        monkeypatch.delenv(k)
+    return rec, work
+
+
+@pytest.mark.parametrize("N,S,depth,model,seed", [(10000, 400, 0.3, "lowpass", 21), (2000, 1500, 5.0, "highpoly", 22)])
+def test_em_long_bound_passes_identical_to_exact(monkeypatch, N, S, depth, model, seed):
+    """em_long_kernel decides a pass by delta_decision's bound and evaluates the exact delta (Algorithm.cpp:103-113) only when
+    the bound is ambiguous; its E/M arithmetic is the same either way, so the records must be BYTE-identical to those of the
+    all-exact kernel (BVC_LONG_EXACT=1).  Tiles this small run every fit in em_long_kernel (fewer fits than K3 has lanes)."""
+    tile = synth_tile(N, S, depth, model, seed=seed)
+    q = tile.qual.copy()
+    q[np.random.default_rng(seed).random(q.size) < 0.002] = 1          # qual <= 1 classes: those fits stay on the exact path
+    tile.qual = q
+    exact, w_exact = _records(tile, monkeypatch, BVC_LONG_EXACT=1)
+    bound, w_bound = _records(tile, monkeypatch)
+    assert w_exact["em_class_passes"] == 0 and w_bound["em_class_passes"] == 0 and w_bound["em_long_class_passes"] > 0
+    assert exact.tobytes() == bound.tobytes()
+    # a repeated (ambiguous) pass is counted twice: the bound-based kernel may only do slightly MORE class-passes
+    assert w_exact["em_long_class_passes"] <= w_bound["em_long_class_passes"] <= 1.01 * w_exact["em_long_class_passes"]
+
+
+@pytest.mark.parametrize("refill_min", [1, 6, 32])
+def test_em_fit_batched_refills(oracle, monkeypatch, refill_min):
+    """em_fit_kernel (forced on a small tile with BVC_EM_MIN_FITS=1) with lanes waiting for `refill_min` free lanes before
+    the warp refills: same calls, same pass counts, AF / LRT within tolerance against the per-read oracle."""
+    tile = synth_tile(1000, 6000, 0.5, "lowpass", seed=23)
+    got, work = _records(tile, monkeypatch, BVC_EM_MIN_FITS=1, BVC_REFILL_MIN=refill_min)
+    assert work["em_class_passes"] > 0
+    want = oracle.call_sites(tile, B.default_params(tile.n_samples, 0.001))
+    nbad, lines = compare_records(got, want)
+    assert nbad == 0, "\n".join(lines)
+    assert (got["em_fits"] == want["em_fits"]).all()
+    assert (got["em_passes"] == want["em_passes"]).mean() > 0.999
