@@ -156,13 +156,13 @@ void bvc::fill_args(const bvc_ctx* ctx, const Slot& s, SiteArgs& a, PipeArgs& p)
     p.lad = s.d_lad; p.fit = s.d_fit; p.state = s.d_state;
     p.q_in = s.d_qb; p.q_in_n = s.d_ctr + 2;          // swapped before the first EM stage
     p.q_out = s.d_qa; p.q_out_n = s.d_ctr + 1;
-    p.q_in_head = s.d_ctr + 3;
+    p.q_in_head = s.d_ctr + 17;                        // words 17..19 and the bins behind them are zeroed per EM stage by ONE memset
     p.vcf_list = s.d_vcf_list; p.vcf_n = s.d_ctr + 4;
     p.legacy_list = s.d_legacy_list; p.legacy_n = s.d_ctr + 5;
-    p.q_sorted = s.d_qs; p.q_long = s.d_ql; p.q_long_n = s.d_ctr + 6; p.q_long_head = s.d_ctr + 7;
+    p.q_sorted = s.d_qs; p.q_long = s.d_ql; p.q_long_n = s.d_ctr + 18; p.q_long_head = s.d_ctr + 19;
     p.deep_list = s.d_ql; p.deep_n = s.d_ctr + 16 + bvc::kNBins + 8;
     p.work = reinterpret_cast<unsigned long long*>(s.d_ctr + 8);
-    p.bins = s.d_ctr + 16;
+    p.bins = s.d_ctr + 20;
 }
 
 namespace {

@@ -30,7 +30,7 @@ struct Slot {
     FitRes* d_fit = nullptr;
     uint8_t* d_state = nullptr;
     uint32_t *d_qa = nullptr, *d_qb = nullptr, *d_qs = nullptr, *d_ql = nullptr, *d_vcf_list = nullptr, *d_legacy_list = nullptr;
-    uint32_t* d_ctr = nullptr;     // [kCtrWords]: cls_cursor, qa_n, qb_n, q_head, vcf_n, legacy_n, long_n, work[4] (u64 at word 8), bins at word 16
+    uint32_t* d_ctr = nullptr;     // [kCtrWords]: cls_cursor, qa_n, qb_n, -, vcf_n, legacy_n, -, -, work[4] (u64 at word 8), q_head / long_n / long_head at 17..19, bins at word 20, deep_n behind them
     const uint8_t *k_mapq = nullptr, *k_rpr = nullptr;   // what the kernels read: d_mapq/d_rpr or zero-copy host pointers
     // split result (bvc_enqueue_split): device core records, compacted full records, their count; host side of the ticket
     bvc_site_core* d_core = nullptr;

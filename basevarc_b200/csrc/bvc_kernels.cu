@@ -256,9 +256,13 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
         t = a.q_in; a.q_in = a.q_out; a.q_out = t;
         t = a.q_in_n; a.q_in_n = a.q_out_n; a.q_out_n = t;
         cudaMemsetAsync(a.q_out_n, 0, sizeof(uint32_t), stream);
-        cudaMemsetAsync(a.q_in_head, 0, sizeof(uint32_t), stream);
-        cudaMemsetAsync(a.q_long_n, 0, 2 * sizeof(uint32_t), stream);   // q_long_n, q_long_head
-        cudaMemsetAsync(a.bins, 0, (kNBins + 1) * sizeof(uint32_t), stream);
+        if (a.q_long_n == a.q_in_head + 1 && a.q_long_head == a.q_in_head + 2 && a.bins == a.q_in_head + 3)
+            cudaMemsetAsync(a.q_in_head, 0, (3 + kNBins + 1) * sizeof(uint32_t), stream);   // q_in_head, q_long_n, q_long_head, bins: one range
+        else {
+            cudaMemsetAsync(a.q_in_head, 0, sizeof(uint32_t), stream);
+            cudaMemsetAsync(a.q_long_n, 0, 2 * sizeof(uint32_t), stream);   // q_long_n, q_long_head
+            cudaMemsetAsync(a.bins, 0, (kNBins + 1) * sizeof(uint32_t), stream);
+        }
         mark(kKSort);
         queue_hist_kernel<<<(unsigned)(n_sm * 2), kSortThreads, 0, stream>>>(a);
         mark(kKSort);
