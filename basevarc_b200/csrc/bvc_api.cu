@@ -47,8 +47,7 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
     }
     CK(cudaMalloc(&s.d_out, (S + 1) * sizeof(bvc_site_result)));
     CK(cudaMalloc(&s.d_counter, sizeof(unsigned int)));
-    // class pool: one word per (base, qual) class + up to 6 alignment / padding words per site (pad4 layout)
-    size_t pool = (R < S * (size_t)bvc::kNBins ? R : S * (size_t)bvc::kNBins) + 8 * S;
+    const size_t pool = bvc::pool_words(ctx);
     CK(cudaMalloc(&s.d_sum, (S + 1) * sizeof(bvc::SiteSum)));
     CK(cudaMalloc(&s.d_cls, (pool + 64) * sizeof(uint32_t)));
     CK(cudaMalloc(&s.d_lad, (S + 1) * sizeof(bvc::Ladder)));
@@ -61,6 +60,8 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
     CK(cudaMalloc(&s.d_vcf_list, (S + 16) * sizeof(uint32_t)));
     CK(cudaMalloc(&s.d_legacy_list, (S + 16) * sizeof(uint32_t)));
     CK(cudaMalloc(&s.d_ctr, kCtrWords * sizeof(uint32_t)));
+    CK(cudaHostAlloc(&s.h_err, sizeof(uint32_t), cudaHostAllocDefault));
+    *s.h_err = 0;
     return BVC_OK;
 }
 
@@ -68,7 +69,7 @@ void free_slot(Slot& s)
 {
     cudaFree(s.d_ref); cudaFree(s.d_off); cudaFree(s.d_code); cudaFree(s.d_qual); cudaFree(s.d_mapq);
     cudaFree(s.d_rpr); cudaFree(s.d_pk8); cudaFree(s.d_sample); cudaFree(s.d_core); cudaFree(s.d_vcfc); cudaFree(s.d_vcfc_n);
-    if (s.h_vcfc_n) cudaFreeHost(s.h_vcfc_n); cudaFree(s.d_gdepth); cudaFree(s.d_gaf); cudaFree(s.d_out); cudaFree(s.d_counter);
+    if (s.h_vcfc_n) cudaFreeHost(s.h_vcfc_n); if (s.h_err) cudaFreeHost(s.h_err); cudaFree(s.d_gdepth); cudaFree(s.d_gaf); cudaFree(s.d_out); cudaFree(s.d_counter);
     cudaFree(s.d_sum); cudaFree(s.d_cls); cudaFree(s.d_lad); cudaFree(s.d_fit); cudaFree(s.d_state);
     cudaFree(s.d_qa); cudaFree(s.d_qb); cudaFree(s.d_qs); cudaFree(s.d_ql); cudaFree(s.d_vcf_list); cudaFree(s.d_legacy_list); cudaFree(s.d_ctr);
     if (s.done) cudaEventDestroy(s.done);
@@ -77,6 +78,16 @@ void free_slot(Slot& s)
 }
 
 }  // namespace
+
+// class pool: one word per (base, qual) class + up to 6 alignment / padding words per site (pad4 layout) when K1 allocates
+// with its cursor; site_hist8_kernel's fixed layout needs kMaxClsStride words per site
+size_t bvc::pool_words(const bvc_ctx* ctx)
+{
+    const size_t S = (size_t)ctx->prm.max_sites, R = (size_t)ctx->prm.max_entries;
+    const size_t cursor = (R < S * (size_t)bvc::kNBins ? R : S * (size_t)bvc::kNBins) + 8 * S;
+    const size_t fixed = S * (size_t)bvc::kMaxClsStride;
+    return cursor > fixed ? cursor : fixed;
+}
 
 int bvc::check_tile(bvc_ctx* ctx, const bvc_tile* t, int64_t* n_entries)
 {
@@ -105,22 +116,31 @@ const uint8_t* zero_copy_ptr(bvc_ctx* ctx, const uint8_t* host)
 
 }  // namespace
 
-int bvc::upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool resident)
+int bvc::upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool resident, bool need_arrays)
 {
     const size_t S = (size_t)t->n_sites;
     s.n_sites = t->n_sites; s.n_entries = R;
+    s.packed = false; s.n_dict = 0;
     if (S) CK(cudaMemcpyAsync(s.d_ref, t->ref_base, S, cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.d_off, t->entry_off, (S + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
     ctx->h2d_bytes += (int64_t)(S + (S + 1) * sizeof(uint32_t));
     if (R) {
         if (t->packed8) {
-            // compact wire form: R bytes over PCIe instead of 2R, expanded into the arrays the kernels read
+            // compact wire form: R bytes over PCIe instead of 2R, and the form the tile STAYS in: K1 (site_hist8_kernel) and K5
+            // read the byte directly.  Only the paths that still read the two arrays get them expanded: --group, the
+            // sample-sharded kernels, the IEEE-faithful legacy kernel (a qual-0 read anywhere in the tile, BVC_LEGACY_KERNEL=1),
+            // cohorts of >= 65,536 samples (K1's packed depths are 16-bit) and the A/B switch BVC_EXPAND8=1.
             bvc::QualDict d;
-            for (int i = 0; i < 32; ++i) d.q[i] = i < t->n_qual_dict ? t->qual_dict[i] : (uint8_t)0;
+            bool q0 = false;
+            for (int i = 0; i < 32; ++i) { d.q[i] = i < t->n_qual_dict ? t->qual_dict[i] : (uint8_t)0; q0 = q0 || (i < t->n_qual_dict && d.q[i] == 0); }
+            for (int i = 0; i < t->n_qual_dict; ++i) if (d.q[i] > 127) { set_err(ctx, "bad tile: qual_dict entry > 127"); return BVC_ERR_ARG; }
             CK(cudaMemcpyAsync(s.d_pk8, t->packed8, (size_t)R, cudaMemcpyHostToDevice, s.stream));
-            CK(bvc::launch_expand8(s.d_pk8, s.d_code, s.d_qual, R, d, ctx->n_sm, s.stream));
-            ctx->launches += 1;
             ctx->h2d_bytes += R;
+            s.dict = d; s.n_dict = t->n_qual_dict;
+            if (need_arrays || q0 || ctx->expand8 || ctx->legacy_only || ctx->wide_hist || ctx->prm.n_groups > 0 || ctx->prm.n_samples >= 65536) {
+                CK(bvc::launch_expand8(s.d_pk8, s.d_code, s.d_qual, R, d, ctx->n_sm, s.stream));
+                ctx->launches += 1;
+            } else s.packed = true;
         } else {
             CK(cudaMemcpyAsync(s.d_code, t->code, (size_t)R, cudaMemcpyHostToDevice, s.stream));
             CK(cudaMemcpyAsync(s.d_qual, t->qual, (size_t)R, cudaMemcpyHostToDevice, s.stream));
@@ -144,6 +164,7 @@ int bvc::upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool reside
 void bvc::fill_args(const bvc_ctx* ctx, const Slot& s, SiteArgs& a, PipeArgs& p)
 {
     a.ref_base = s.d_ref; a.entry_off = s.d_off; a.code = s.d_code; a.qual = s.d_qual; a.mapq = s.k_mapq ? s.k_mapq : s.d_mapq; a.rpr = s.k_rpr ? s.k_rpr : s.d_rpr;
+    a.pk8 = s.packed ? s.d_pk8 : nullptr; a.dict = s.dict; a.n_dict = s.n_dict; a.err = s.d_ctr + bvc::kCtrErr;
     a.out = s.d_out; a.counter = s.d_counter; a.lut = ctx->d_lut; a.lgam = ctx->d_lgam;
     a.n_sites = s.n_sites; a.max_iter = ctx->prm.em_max_iter;
     a.min_af = ctx->prm.min_af; a.lrt_thr = ctx->prm.lrt_threshold; a.eps = ctx->prm.em_epsilon;
@@ -152,6 +173,7 @@ void bvc::fill_args(const bvc_ctx* ctx, const Slot& s, SiteArgs& a, PipeArgs& p)
     p.mean_entries = (int)(s.n_entries / (s.n_sites > 0 ? s.n_sites : 1));
     p.pass_budget = ctx->pass_budget; p.drain_min_pass = ctx->drain_min_pass; p.drain_lanes = ctx->drain_lanes; p.em_min_fits = ctx->em_min_fits; p.refill_min = ctx->refill_min; p.long_exact = ctx->long_exact;
     p.packed_hist = (ctx->prm.n_samples < 65536 && !ctx->wide_hist) ? 1 : 0;
+    p.cls_stride = 4 * s.n_dict + 4;
     p.sum = s.d_sum; p.cls = s.d_cls; p.cls_cursor = s.d_ctr + 0;
     p.lad = s.d_lad; p.fit = s.d_fit; p.state = s.d_state;
     p.q_in = s.d_qb; p.q_in_n = s.d_ctr + 2;          // swapped before the first EM stage
@@ -191,6 +213,8 @@ int launch(bvc_ctx* ctx, Slot& s, cudaEvent_t* ev = nullptr, int* kinds = nullpt
         CK(bvc::launch_groups(a, s.d_sample, ctx->d_sample_group, ctx->prm.n_groups, s.d_gdepth, s.d_gaf, ctx->n_sm, s.stream));
         ctx->launches += 2;
     }
+    // what K1 found of the input the ABI rejects (qual > 127, non-indel base > 3, dictionary index out of range)
+    CK(cudaMemcpyAsync(s.h_err, s.d_ctr + bvc::kCtrErr, sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
     return BVC_OK;
 }
 
@@ -257,7 +281,8 @@ int bvc_create(bvc_ctx** out, int device, const bvc_params* prm)
     ctx->n_sm = prop.multiProcessorCount;
     { const char* e = getenv("BVC_LEGACY_KERNEL"); ctx->legacy_only = (e && e[0] == '1'); }
     { const char* e = getenv("BVC_NO_ZERO_COPY"); ctx->zero_copy = !(e && e[0] == '1'); }
-    { const char* e = getenv("BVC_WIDE_HIST"); ctx->wide_hist = (e && e[0] == '1'); }                        // A/B: K1 in its one-site-per-warp form
+    { const char* e = getenv("BVC_WIDE_HIST"); ctx->wide_hist = (e && e[0] == '1'); }
+    { const char* e = getenv("BVC_EXPAND8"); ctx->expand8 = (e && e[0] == '1'); }                        // A/B: K1 in its one-site-per-warp form
     { const char* e = getenv("BVC_PASS_BUDGET"); if (e && atoi(e) > 0) ctx->pass_budget = atoi(e); }       // tuning knobs (A/B runs)
     { const char* e = getenv("BVC_DRAIN_MIN_PASS"); if (e && atoi(e) > 0) ctx->drain_min_pass = atoi(e); }
     { const char* e = getenv("BVC_DRAIN_LANES"); if (e && atoi(e) > 0) ctx->drain_lanes = atoi(e); }
@@ -315,6 +340,13 @@ static int retire_slot(bvc_ctx* ctx, bvc::Slot& s)
 {
     if (!s.ticket) return BVC_OK;
     CK(cudaStreamSynchronize(s.stream));
+    if (s.n_sites && *s.h_err) {
+        s.retired_ticket = s.ticket; s.retired_n = 0; s.retired_rc = BVC_ERR_ARG;
+        s.ticket = 0;
+        set_err(ctx, (*s.h_err & bvc::kErrQual) ? "bad tile: an entry with qual > 127 (or a packed8 dictionary index >= n_qual_dict)"
+                                                : "bad tile: a non-indel entry with base > 3");
+        return BVC_ERR_ARG;
+    }
     if (s.is_split) {
         const int32_t n = (int32_t)*s.h_vcfc_n;
         s.retired_ticket = s.ticket; s.retired_n = n; s.retired_rc = BVC_OK;
@@ -408,7 +440,10 @@ int bvc_wait(bvc_ctx* ctx, uint64_t ticket)
     if (!ctx) return BVC_ERR_ARG;
     Slot& s = ctx->slot[ticket & 1];
     if (ticket == 0 || ticket >= ctx->next_ticket) { set_err(ctx, "bvc_wait: unknown ticket"); return BVC_ERR_STATE; }
-    if (s.ticket != ticket) return BVC_OK;      // already retired by a later enqueue on the same slot
+    if (s.ticket != ticket) {                   // already retired by a later enqueue on the same slot
+        if (s.retired_ticket == ticket && s.retired_rc == BVC_ERR_ARG) { set_err(ctx, "bad tile: rejected on the device (qual > 127, non-indel base > 3 or dictionary index out of range)"); return BVC_ERR_ARG; }
+        return BVC_OK;
+    }
     CK(cudaSetDevice(ctx->device));
     return retire_slot(ctx, s);                 // a split ticket also fetches its records (count: bvc_wait_split)
 }
@@ -490,6 +525,8 @@ int bvc_resident_run(bvc_ctx* ctx, int iters, int flush_l2, float* ms_per_launch
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     if (per_kernel_ms) for (int i = 0; i <= bvc::kMaxPipeLaunches; ++i) cudaEventDestroy(ev[i]);
+    CK(cudaStreamSynchronize(s.stream));
+    if (s.n_sites && *s.h_err) { set_err(ctx, "bad tile: qual > 127, non-indel base > 3 or dictionary index out of range"); return BVC_ERR_ARG; }
     if (ms_per_launch) *ms_per_launch = (float)(total / iters);
     if (per_kernel_ms) for (int k = 0; k < bvc::kNumKernelKinds; ++k) per_kernel_ms[k] = (float)(kind_ms[k] / iters);
     if (n_kernels_out) *n_kernels_out = bvc::kNumKernelKinds;

@@ -12,12 +12,18 @@
 namespace bvc {
 
 constexpr size_t kCtrWords = 16 + kNBins + 16;
+constexpr int kCtrErr = 6;         // d_ctr word of the device error bits
+constexpr int kMaxClsStride = 4 * BVC_PACK8_MAX_QUALS + 4;   // pool words per site of site_hist8_kernel's fixed layout (pad4(major) + the rest)
 
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
     uint8_t *d_ref = nullptr, *d_code = nullptr, *d_qual = nullptr, *d_mapq = nullptr, *d_rpr = nullptr;
-    uint8_t *d_pk8 = nullptr;      // landing buffer of a tile's packed8 form (expanded into d_code / d_qual on the device)
+    uint8_t *d_pk8 = nullptr;      // a tile's packed8 form: what K1 / K5 read (expanded into d_code / d_qual only for the paths that need the arrays)
+    bool packed = false;           // the slot's tile is resident in the one-byte form only (d_code / d_qual not filled)
+    QualDict dict;                 // its qual dictionary
+    int n_dict = 0;
+    uint32_t* h_err = nullptr;     // pinned: the device error word of the slot's last launch (kErr* bits)
     uint32_t *d_off = nullptr, *d_sample = nullptr;
     bvc_site_result* d_out = nullptr;
     unsigned int* d_counter = nullptr;
@@ -69,6 +75,7 @@ struct bvc_ctx {
     int64_t h2d_bytes = 0, d2h_bytes = 0;   // bytes moved by cudaMemcpyAsync on the host-buffer path
     bool zero_copy = true;         // BVC_NO_ZERO_COPY=1 forces the full mapq/rpr copy (A/B checks)
     bool wide_hist = false;        // BVC_WIDE_HIST=1: K1 as site_hist_kernel<G> even for small cohorts (A/B checks)
+    bool expand8 = false;          // BVC_EXPAND8=1: a packed8 tile is expanded into the (code, qual) arrays and K1 runs in its two-array form (A/B checks)
     int em_min_fits = 0;           // BVC_EM_MIN_FITS: stages below this many fits run entirely in em_long_kernel; 0 = one fit per K3 lane
     int long_exact = 0;            // BVC_LONG_EXACT=1: em_long_kernel with the exact delta on every pass (A/B checks)
     int refill_min = 4;            // BVC_REFILL_MIN: em_fit_kernel batches its refills (C2: em_fit 0.79 -> 0.73 ms at 4..8, 0.78 at 16; C5 neutral)
@@ -84,7 +91,9 @@ namespace bvc {
 void set_err(bvc_ctx* ctx, const char* m);     // ctx == NULL: the thread's create-time error
 int  check_tile(bvc_ctx* ctx, const bvc_tile* t, int64_t* n_entries);
 // H2D copies of a tile into the slot (code, qual, offsets, ref; mapq / rpr zero-copy when pinned) on the slot's stream
-int  upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool resident);
+// need_arrays: the caller's kernels read the (code, qual) arrays (sample-sharded mode), so a packed8 tile is expanded
+int  upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool resident, bool need_arrays = false);
+size_t pool_words(const bvc_ctx* ctx);         // capacity of a slot's class pool
 // the argument blocks of the kernels over the slot's buffers
 void fill_args(const bvc_ctx* ctx, const Slot& s, SiteArgs& a, PipeArgs& p);
 void shard_free(bvc_ctx* ctx);                 // called by bvc_destroy

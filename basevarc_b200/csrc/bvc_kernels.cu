@@ -1,5 +1,6 @@
 // bvc_kernels.cu -- kernel entry points (sm_100a) and their launchers.
 // See bvc_site_kernel.cuh for the design and the reference code each phase replaces.
+#include <mutex>
 #include "bvc_kernels.h"
 #include "bvc_site_kernel.cuh"
 #include "bvc_pipeline.cuh"
@@ -211,25 +212,28 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     PipeArgs a = a0;
     const int S = a.s.n_sites;
     int launches = 0;
-    static int occ_hist4 = 0, occ_hist = 0, occ_hist16 = 0, occ_em = 0, occ_vcf = 0, occ_leg = 0, occ_long = 0, occ_ll = 0, occ_lad = 0;
-    if (!occ_hist) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_long, em_long_kernel, kLongThreads, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ll, fit_loglik_kernel, kEmThreads, 0);
-        if (occ_long < 1) occ_long = 1; if (occ_ll < 1) occ_ll = 1;
+    // occupancies: computed once per process (a dispatcher thread per GPU may arrive here concurrently)
+    static std::once_flag occ_once;
+    static int occ_hist8 = 1, occ_hist4 = 1, occ_hist = 1, occ_hist16 = 1, occ_em = 1, occ_vcf = 1, occ_leg = 1, occ_long = 1, occ_ll = 1, occ_lad = 1;
+    std::call_once(occ_once, [] {
+        auto occ = [](int* out, auto kernel, int threads) {
+            int v = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kernel, threads, 0) != cudaSuccess) cudaGetLastError();
+            *out = v < 1 ? 1 : v;
+        };
+        occ(&occ_long, em_long_kernel, kLongThreads);
+        occ(&occ_ll, fit_loglik_kernel, kEmThreads);
         // K4 is a static grid-stride loop: with more blocks than fit on the device (it ran 8 per SM where 72 registers allow 7)
         // the blocks of the second, nearly empty wave start only when the first wave's equal shares are done -- twice the time
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_lad, ladder_kernel, 128, 0);
-        if (occ_lad < 1) occ_lad = 1;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist4, site_hist4_kernel, kHistWarps * 32, 0);
-        if (occ_hist4 < 1) occ_hist4 = 1;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist, site_hist_kernel<32>, kHistWarps * 32, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_hist16, site_hist_kernel<16>, kHistWarps * 32, 0);
-        if (occ_hist16 < 1) occ_hist16 = 1;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_em, em_fit_kernel, kEmThreads, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_vcf, vcf_stats_kernel, kVcfWarps * 32, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_leg, site_call_kernel, kWarpsPerBlock * 32, 0);
-        if (occ_hist < 1) occ_hist = 1; if (occ_em < 1) occ_em = 1; if (occ_vcf < 1) occ_vcf = 1; if (occ_leg < 1) occ_leg = 1;
-    }
+        occ(&occ_lad, ladder_kernel, 128);
+        occ(&occ_hist8, site_hist8_kernel, kHistWarps * 32);
+        occ(&occ_hist4, site_hist4_kernel, kHistWarps * 32);
+        occ(&occ_hist, site_hist_kernel<32>, kHistWarps * 32);
+        occ(&occ_hist16, site_hist_kernel<16>, kHistWarps * 32);
+        occ(&occ_em, em_fit_kernel, kEmThreads);
+        occ(&occ_vcf, vcf_stats_kernel, kVcfWarps * 32);
+        occ(&occ_leg, site_call_kernel, kWarpsPerBlock * 32);
+    });
     auto capped = [&](long long want, int per_sm) { long long g = (long long)n_sm * per_sm; if (g > want) g = want; return (unsigned)(g < 1 ? 1 : g); };
     const unsigned site_blocks = (unsigned)((S + 127) / 128);
     // optional per-launch timing: ev[i] is recorded BEFORE launch i, ev[launches] after the last one
@@ -238,7 +242,9 @@ cudaError_t launch_pipeline(const PipeArgs& a0, int n_sm, cudaStream_t stream, i
     if (parts & kPartHist) {
     mark(kKHist);
     // lanes per site by mean pileup depth of the tile: a full warp from 256 entries per site (measured: C2, 393 entries, 1.11 ms vs 1.23 ms), half a warp below
-    if (a.packed_hist)
+    if (a.s.pk8)
+        site_hist8_kernel<<<capped((S + kHistWarps * kH8Sites - 1) / (kHistWarps * kH8Sites), occ_hist8), kHistWarps * 32, 0, stream>>>(a);
+    else if (a.packed_hist)
         site_hist4_kernel<<<capped((S + kHistWarps * kH4Sites - 1) / (kHistWarps * kH4Sites), occ_hist4), kHistWarps * 32, 0, stream>>>(a);
     else if (a.mean_entries >= 256)
         site_hist_kernel<32><<<capped((S + kHistWarps - 1) / kHistWarps, occ_hist), kHistWarps * 32, 0, stream>>>(a);
@@ -301,12 +307,14 @@ cudaError_t launch_groups(const SiteArgs& s, const uint32_t* sample, const int32
     const size_t n = (size_t)s.n_sites * n_groups * 4;
     cudaMemsetAsync(gdepth, 0, n * sizeof(int32_t), stream);
     cudaMemsetAsync(gaf, 0, n * sizeof(double), stream);
-    static int occ_gd = 0, occ_gl = 0;                      // one resident wave each (both are static grid-stride loops)
-    if (!occ_gd) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_gd, group_depth_kernel, kGroupWarps * 32, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_gl, group_lrt_kernel, kGroupWarps * 32, 0);
-        if (occ_gd < 1) occ_gd = 1; if (occ_gl < 1) occ_gl = 1;
-    }
+    static std::once_flag g_once;
+    static int occ_gd = 1, occ_gl = 1;                      // one resident wave each (both are static grid-stride loops)
+    std::call_once(g_once, [] {
+        int v = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, group_depth_kernel, kGroupWarps * 32, 0) == cudaSuccess && v > 0) occ_gd = v;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, group_lrt_kernel, kGroupWarps * 32, 0) == cudaSuccess && v > 0) occ_gl = v;
+        cudaGetLastError();
+    });
     group_depth_kernel<<<(unsigned)(n_sm * occ_gd), kGroupWarps * 32, 0, stream>>>(g);
     group_lrt_kernel<<<(unsigned)(n_sm * occ_gl), kGroupWarps * 32, 0, stream>>>(g);
     return cudaGetLastError();
@@ -322,12 +330,14 @@ static unsigned shard_grid(long long groups_wanted, int n_sm, int per_sm)
 
 cudaError_t launch_shard_hist(const ShardArgs& a, int n_sm, cudaStream_t stream, int* n_launches)
 {
-    static int occ32 = 0, occ16 = 0;
-    if (!occ32) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ32, shard_hist_kernel<32>, kHistWarps * 32, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ16, shard_hist_kernel<16>, kHistWarps * 32, 0);
-        if (occ32 < 1) occ32 = 1; if (occ16 < 1) occ16 = 1;
-    }
+    static std::once_flag once;
+    static int occ32 = 1, occ16 = 1;
+    std::call_once(once, [] {
+        int v = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, shard_hist_kernel<32>, kHistWarps * 32, 0) == cudaSuccess && v > 0) occ32 = v;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, shard_hist_kernel<16>, kHistWarps * 32, 0) == cudaSuccess && v > 0) occ16 = v;
+        cudaGetLastError();
+    });
     const long long n_pad = (long long)a.world * a.Sr;
     if (a.p.mean_entries >= 256)
         shard_hist_kernel<32><<<shard_grid((n_pad + kHistWarps - 1) / kHistWarps, n_sm, occ32), kHistWarps * 32, 0, stream>>>(a);
@@ -340,8 +350,13 @@ cudaError_t launch_shard_hist(const ShardArgs& a, int n_sm, cudaStream_t stream,
 // owner: merged histograms -> SiteSum + classes, then K2 / EM stages / K4 on the owned sites, then the mask bytes
 cudaError_t launch_shard_merge_and_fit(const ShardArgs& a, int n_sm, cudaStream_t stream, int* n_launches)
 {
-    static int occ = 0;
-    if (!occ) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, shard_merge_kernel<32>, kHistWarps * 32, 0); if (occ < 1) occ = 1; }
+    static std::once_flag once;
+    static int occ = 1;
+    std::call_once(once, [] {
+        int v = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, shard_merge_kernel<32>, kHistWarps * 32, 0) == cudaSuccess && v > 0) occ = v;
+        cudaGetLastError();
+    });
     int n = 0;
     if (a.n_own > 0) {
         shard_merge_kernel<32><<<shard_grid((a.n_own + kHistWarps - 1) / kHistWarps, n_sm, occ), kHistWarps * 32, 0, stream>>>(a);

@@ -9,8 +9,14 @@ namespace bvc {
 constexpr int kWarpsPerBlock = 4;
 constexpr int kNQ = 128;                 // qual bins per base (int8 quals, src/BaseType.h:18)
 constexpr int kNBins = 4 * kNQ;          // (base, qual) classes
+// bits of the device error word (SiteArgs::err): what bvc_wait turns into BVC_ERR_ARG
+constexpr uint32_t kErrQual = 1u;        // a qual > 127 (plain form) / a dictionary index >= n_qual_dict (packed8 form)
+constexpr uint32_t kErrBase = 2u;        // a non-indel entry with base > 3
 // per-warp shared memory: lml f64[512] | hist u32[512] | keys u16[512] | codehist u32[32]
 constexpr int kWarpSmemBytes = kNBins * 8 + kNBins * 4 + kNBins * 2 + 32 * 4;
+
+// packed8 -> (code, qual): include/bvc_gpu.h BVC_PACK8
+struct QualDict { uint8_t q[32]; };
 
 struct SiteArgs {
     const uint8_t*  ref_base;
@@ -19,6 +25,10 @@ struct SiteArgs {
     const uint8_t*  qual;
     const uint8_t*  mapq;
     const uint8_t*  rpr;
+    const uint8_t*  pk8;         // != NULL: the tile is resident in its ONE-byte form (BVC_PACK8) and code / qual are not filled:
+    QualDict        dict;        //   K1 (site_hist8_kernel) and K5 read pk8 + dict directly
+    int             n_dict;
+    uint32_t*       err;         // device error word (kErr* bits): input the ABI promises to reject (include/bvc_gpu.h BVC_ERR_ARG)
     bvc_site_result* out;
     unsigned int*   counter;     // dynamic site fetch
     const uint32_t* site_list;   // optional: process only these sites (legacy path of the pipeline) ...
@@ -57,7 +67,6 @@ cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cu
 // records -> 72-byte cores + compacted full records of the LRT-positive sites (bvc_enqueue_split)
 cudaError_t launch_split_result(const bvc_site_result* rec, int n_sites, bvc_site_core* core, bvc_site_result* vcf, uint32_t* vcf_n,
                                 cudaStream_t stream);
-// packed8 -> (code, qual): include/bvc_gpu.h BVC_PACK8; n is rounded up to whole 16-byte words (the buffers are padded)
-struct QualDict { uint8_t q[32]; };
+// packed8 -> (code, qual) arrays; n is rounded up to whole 16-byte words (the buffers are padded)
 cudaError_t launch_expand8(const uint8_t* pk8, uint8_t* code, uint8_t* qual, int64_t n, const QualDict& dict, int n_sm, cudaStream_t stream);
 }  // namespace bvc

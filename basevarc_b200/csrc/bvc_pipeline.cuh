@@ -103,7 +103,7 @@ template <int G> __device__ __forceinline__ unsigned group_min(unsigned v, int g
 template <int G>
 __device__ __forceinline__ void hist_stream(const uint32_t* __restrict__ code4, const uint32_t* __restrict__ qual4,
                                             uint32_t b0, uint32_t b1, int g, uint32_t* hist,
-                                            uint32_t& qmin, uint32_t& qmax)
+                                            uint32_t& qmin, uint32_t& qmax, uint32_t& bad)
 {
     const uint32_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;
     const uint32_t trips = (__reduce_max_sync(0xffffffffu, w1 - w0) + G - 1) / G;
@@ -111,13 +111,14 @@ __device__ __forceinline__ void hist_stream(const uint32_t* __restrict__ code4, 
         const uint32_t wi = w0 + t * G + g;
         if (wi < w1) {
             uint32_t cw = __ldg(code4 + wi);
-            const uint32_t qw = __ldg(qual4 + wi) & 0x7f7f7f7fu;
+            const uint32_t qraw = __ldg(qual4 + wi), qw = qraw & 0x7f7f7f7fu;
             if (wi == w0 || wi + 1 == w1) {
                 const uint32_t e0 = wi * 4;
                 const uint32_t lo = b0 > e0 ? b0 - e0 : 0u, hi = b1 < e0 + 4 ? b1 - e0 : 4u;     // valid bytes [lo, hi)
                 const uint32_t vm = (hi >= 4 ? 0xffffffffu : ((1u << (8 * hi)) - 1u)) & ~((1u << (8 * lo)) - 1u);
                 cw = (cw & vm) | (0x14141414u & ~vm);
             }
+            bad |= (((qraw >> 7) & ~((cw >> 2) | (cw >> 4)) & 0x01010101u) ? kErrQual : 0u) | (((cw >> 2) & ~(cw >> 4) & 0x01010101u) ? kErrBase : 0u);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const uint32_t c = cw >> (8 * k), q = (qw >> (8 * k)) & 0x7fu;
@@ -254,6 +255,7 @@ site_hist_kernel(PipeArgs a)
 
     const int n_groups = gridDim.x * kHistWarps * kGroups;
     const int first = (blockIdx.x * kHistWarps + wid) * kGroups + gi;
+    uint32_t bad = 0;
     // warp-uniform trip count: every lane runs the same number of site iterations, idle groups just predicate off
     const int n_iter = (a.s.n_sites + n_groups - 1) / n_groups;
     for (int it = 0; it < n_iter; ++it) {
@@ -262,9 +264,11 @@ site_hist_kernel(PipeArgs a)
         const uint32_t b0 = live ? a.s.entry_off[site] : 0u, b1 = live ? a.s.entry_off[site + 1] : 0u;
         const int ref = live ? (a.s.ref_base[site] & 3) : 0;
         uint32_t qmax = 0, qmin = 127;
-        hist_stream<G>(code4, qual4, b0, b1, g, hist, qmin, qmax);
+        hist_stream<G>(code4, qual4, b0, b1, g, hist, qmin, qmax, bad);
         hist_emit<G>(a, site, live, ref, (int)(b1 - b0), qmin, qmax, hist, g, gi);
     }
+    const uint32_t err_all = __reduce_or_sync(0xffffffffu, bad);
+    if (lane == 0 && err_all) atomicOr(a.s.err, err_all);
 }
 
 // =====================================================================================================
@@ -343,7 +347,7 @@ site_hist4_kernel(PipeArgs a)
 
     const int stride = gridDim.x * kHistWarps;
     int batch = blockIdx.x * kHistWarps + wid;
-    uint32_t ov = 0;
+    uint32_t ov = 0, bad_q = 0, bad_b = 0;                      // bit 0 of each byte
     if (batch < n_batches && lane <= kH4Sites) ov = a.s.entry_off[min(batch * kH4Sites + lane, S)];
     uint32_t pc0 = 0, pq0 = 0, pc1 = 0, pq1 = 0;
     first_trips(code4, qual4, __shfl_sync(0xffffffffu, ov, 0), __shfl_sync(0xffffffffu, ov, kH4Sites), lane, pc0, pq0, pc1, pq1);
@@ -363,8 +367,11 @@ site_hist4_kernel(PipeArgs a)
         const uint32_t w0 = o0 >> 2, w1 = (o4 + 3) >> 2;
         const uint32_t A1 = (o1 + 3) >> 2, A2 = (o2 + 3) >> 2, A3 = (o3 + 3) >> 2;     // first word wholly behind boundary k
         auto proc = [&](uint32_t wi, uint32_t cw, uint32_t qw) {
-            qw &= 0x7f7f7f7fu;
             if (wi == w0 || wi + 1 == w1) cw = mask_outside(cw, wi * 4, o0, o4);
+            // input the ABI rejects (include/bvc_gpu.h BVC_ERR_ARG): a counted entry with qual > 127, a non-indel base > 3
+            bad_q |= (qw >> 7) & ~((cw >> 2) | (cw >> 4));
+            bad_b |= (cw >> 2) & ~(cw >> 4);
+            qw &= 0x7f7f7f7fu;
             const uint32_t hb = wi >= A2 ? (wi >= A3 ? hs3 : hs2) : (wi >= A1 ? hs1 : hw_s);    // A1 <= A2 <= A3
             const uint32_t ce = cw & 0x00ff00ffu, co = (cw >> 8) & 0x00ff00ffu;
             const uint32_t qe = qw & 0x00ff00ffu, qo = (qw >> 8) & 0x00ff00ffu;
@@ -575,6 +582,208 @@ site_hist4_kernel(PipeArgs a)
         ov = nov;
         __syncwarp();
     }
+    const uint32_t err_all = __reduce_or_sync(0xffffffffu, ((bad_q & 0x01010101u) ? kErrQual : 0u) | ((bad_b & 0x01010101u) ? kErrBase : 0u));
+    if (lane == 0 && err_all) atomicOr(a.s.err, err_all);
+}
+
+// =====================================================================================================
+// K1 on the ONE-byte form (BVC_PACK8: qi:5 | strand:1 | base:2; the form every tile with <= 30 distinct quals
+// travels and stays resident in).  The byte IS the bin: a site's histogram is 256 words [qi][strand][base], so an
+// entry costs a byte extract, an address add and one red.shared -- no qual/base arithmetic, no predicates (indel
+// entries are qi 31 = the 8 [strand][stale base] bins the CVG table needs, qi 30 counts nowhere).
+//  * A warp takes FOUR consecutive sites; their bytes are one contiguous range read as 16-byte words
+//    (ld.global.nc.v4, the next words in flight while the current ones are counted).  A 16-byte word is credited
+//    to the site of its first byte; the <= 5 words that straddle a site boundary or the ends of the range are
+//    corrected byte-wise afterwards (adds commute, so a wrong credit is undone by the opposite add).
+//  * Emit, one site at a time with lane = dictionary index: two 16-byte shared-memory reads give the lane its
+//    (strand, base) counts, four REDUX sums the packed depths, four ballots the class sets; a class's position in
+//    its base's segment is the number of present classes with a LOWER qual (the dictionary need not be sorted).
+//  * The site's classes land at a FIXED pool offset (site * cls_stride): no allocation atomic, reproducible layout.
+// Reference semantics: src/BaseVarC.cpp:548-602 (counting, argsort, CVG table), src/BaseType.cpp:5-23.
+// =====================================================================================================
+constexpr int kH8Sites = 4;
+constexpr int kH8Words = 256;
+
+__device__ __forceinline__ uint4 ldg16(const uint4* p) { return __ldg(p); }
+
+__global__ void __launch_bounds__(kHistWarps * 32)
+site_hist8_kernel(PipeArgs a)
+{
+    __shared__ __align__(16) uint32_t hist_s[kHistWarps][kH8Sites * kH8Words];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t* hw = hist_s[wid];
+    for (int i = lane; i < kH8Sites * kH8Words; i += 32) hw[i] = 0;
+    const uint32_t hs0 = (uint32_t)__cvta_generic_to_shared(hw);
+    const uint32_t hs1 = hs0 + 4u * kH8Words, hs2 = hs1 + 4u * kH8Words, hs3 = hs2 + 4u * kH8Words;
+    const int nd = a.s.n_dict;
+    // my dictionary qual; lanes whose class sorts before mine (ascending qual, ties by index)
+    const uint32_t dq = lane < nd ? (uint32_t)a.s.dict.q[lane] : 255u;
+    uint32_t lower = 0;
+    for (int j = 0; j < BVC_PACK8_MAX_QUALS; ++j) {
+        const uint32_t qj = __shfl_sync(0xffffffffu, dq, j);
+        if (j < nd && (qj < dq || (qj == dq && j < lane))) lower |= 1u << j;
+    }
+    const bool counted = lane < BVC_PACK8_MAX_QUALS;
+    __syncwarp();
+    const uint4* pk16 = reinterpret_cast<const uint4*>(a.s.pk8);
+    const int S = a.s.n_sites;
+    const int n_batches = (S + kH8Sites - 1) / kH8Sites;
+    const int stride = gridDim.x * kHistWarps;
+    uint32_t err = 0;
+
+    int batch = blockIdx.x * kHistWarps + wid;
+    uint32_t ov = 0;
+    if (batch < n_batches && lane <= kH8Sites) ov = a.s.entry_off[min(batch * kH8Sites + lane, S)];
+    // the first two trips of a batch are loaded while the previous batch is emitted
+    uint4 px0 = make_uint4(0, 0, 0, 0), px1 = px0;
+    auto first_two = [&](uint32_t b0, uint32_t b4) {
+        const uint32_t u1 = (b4 + 15) >> 4;
+        uint32_t vi = (b0 >> 4) + (uint32_t)lane;
+        if (vi < u1) px0 = ldg16(pk16 + vi);
+        vi += 32;
+        if (vi < u1) px1 = ldg16(pk16 + vi);
+    };
+    first_two(__shfl_sync(0xffffffffu, ov, 0), __shfl_sync(0xffffffffu, ov, kH8Sites));
+    for (; batch < n_batches; batch += stride) {
+        const int s0 = batch * kH8Sites;
+        uint32_t nov = 0;
+        if (batch + stride < n_batches && lane <= kH8Sites) nov = a.s.entry_off[min((batch + stride) * kH8Sites + lane, S)];
+        const uint32_t o0 = __shfl_sync(0xffffffffu, ov, 0), o1 = __shfl_sync(0xffffffffu, ov, 1), o2 = __shfl_sync(0xffffffffu, ov, 2),
+                       o3 = __shfl_sync(0xffffffffu, ov, 3), o4 = __shfl_sync(0xffffffffu, ov, 4);
+        const uint32_t v0 = o0 >> 4, v1 = (o4 + 15) >> 4;
+        // 16-byte word v is credited to the site of its first byte: 16 v >= o_k  <=>  v >= B_k
+        const uint32_t B1 = (o1 + 15) >> 4, B2 = (o2 + 15) >> 4, B3 = (o3 + 15) >> 4;
+        auto proc = [&](uint32_t vi, const uint4& x) {
+            const uint32_t hb = vi >= B2 ? (vi >= B3 ? hs3 : hs2) : (vi >= B1 ? hs1 : hs0);
+            const uint32_t xw[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                red_s(hb + (__byte_perm(xw[j], 0, 0x4440) << 2), 1u);
+                red_s(hb + (__byte_perm(xw[j], 0, 0x4441) << 2), 1u);
+                red_s(hb + (__byte_perm(xw[j], 0, 0x4442) << 2), 1u);
+                red_s(hb + (__byte_perm(xw[j], 0, 0x4443) << 2), 1u);
+            }
+        };
+        if (o4 > o0) {
+            uint32_t vi = v0 + (uint32_t)lane;
+            if (vi < v1) proc(vi, px0);
+            vi += 32;
+            if (vi < v1) proc(vi, px1);
+            vi += 32;
+            // the rest two trips at a time, the next pair loaded before the current pair is counted
+            uint4 g0 = make_uint4(0, 0, 0, 0), g1 = g0;
+            if (vi < v1) g0 = ldg16(pk16 + vi);
+            if (vi + 32 < v1) g1 = ldg16(pk16 + vi + 32);
+            for (; vi < v1; vi += 64) {
+                uint4 n0 = make_uint4(0, 0, 0, 0), n1 = n0;
+                if (vi + 64 < v1) n0 = ldg16(pk16 + vi + 64);
+                if (vi + 96 < v1) n1 = ldg16(pk16 + vi + 96);
+                proc(vi, g0);
+                if (vi + 32 < v1) proc(vi + 32, g1);
+                g0 = n0; g1 = n1;
+            }
+            // ---- corrections: every byte of the <= 5 special words (first, last, the three straddlers) whose true site is not
+            // the credited one moves; bytes outside [o0, o4) are taken out.  Half a warp per word, three rounds.
+            const uint32_t sv1 = o1 >> 4, sv2 = o2 >> 4, sv3 = o3 >> 4, sv4 = v1 - 1;
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                const int sp = 2 * r + (lane >> 4);
+                const uint32_t v = sp == 0 ? v0 : sp == 1 ? sv1 : sp == 2 ? sv2 : sp == 3 ? sv3 : sv4;
+                bool on = sp <= 4 && v >= v0 && v < v1;
+                if (sp >= 1 && v == v0) on = false;
+                if (sp >= 2 && v == sv1) on = false;
+                if (sp >= 3 && v == sv2) on = false;
+                if (sp >= 4 && v == sv3) on = false;
+                if (on) {
+                    const uint32_t e = v * 16u + (uint32_t)(lane & 15);
+                    const uint32_t byte = a.s.pk8[e];
+                    const uint32_t kf = (uint32_t)(v >= B1) + (uint32_t)(v >= B2) + (uint32_t)(v >= B3);
+                    const uint32_t ks = (uint32_t)(e >= o1) + (uint32_t)(e >= o2) + (uint32_t)(e >= o3);
+                    const bool inside = e >= o0 && e < o4;
+                    if (!inside || ks != kf) {
+                        red_s(hs0 + 4u * (kf * kH8Words + byte), 0xffffffffu);
+                        if (inside) red_s(hs0 + 4u * (ks * kH8Words + byte), 1u);
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        {
+            const uint32_t n0 = __shfl_sync(0xffffffffu, nov, 0), n4 = __shfl_sync(0xffffffffu, nov, kH8Sites);
+            first_two(n0, n4);                                   // land while this batch is emitted
+            for (uint32_t pa = (n0 & ~127u) + 1024u + (uint32_t)lane * 128u; pa < n4; pa += 32u * 128u)    // the rest: into L2
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(a.s.pk8 + pa));
+        }
+        // ---- emit: one site at a time, lane = dictionary index ---------------------------------------------------
+#pragma unroll
+        for (int k = 0; k < kH8Sites; ++k) {
+            const int site = s0 + k;
+            if (site >= S) break;                               // warp-uniform
+            uint32_t* h = hw + k * kH8Words;
+            uint4* hp = reinterpret_cast<uint4*>(h + lane * 8);
+            const uint4 rv = hp[0], fw = hp[1];                 // reverse / forward strand counts of bases 0..3 at my qual
+            const int n_entries = (int)(k == 0 ? o1 - o0 : k == 1 ? o2 - o1 : k == 2 ? o3 - o2 : o4 - o3);
+            const int ref = a.s.ref_base[site] & 3;
+            const uint32_t x0 = counted ? rv.x + fw.x : 0u, x1 = counted ? rv.y + fw.y : 0u,
+                           x2 = counted ? rv.z + fw.z : 0u, x3 = counted ? rv.w + fw.w : 0u;
+            // a site has < 65,536 entries: two depths per word through one REDUX
+            const uint32_t d01 = __reduce_add_sync(0xffffffffu, x0 | (x1 << 16)), d23 = __reduce_add_sync(0xffffffffu, x2 | (x3 << 16));
+            const uint32_t f01 = __reduce_add_sync(0xffffffffu, counted ? fw.x | (fw.y << 16) : 0u),
+                           f23 = __reduce_add_sync(0xffffffffu, counted ? fw.z | (fw.w << 16) : 0u);
+            const unsigned m0 = __ballot_sync(0xffffffffu, x0 != 0), m1 = __ballot_sync(0xffffffffu, x1 != 0),
+                           m2 = __ballot_sync(0xffffffffu, x2 != 0), m3 = __ballot_sync(0xffffffffu, x3 != 0);
+            const unsigned many = m0 | m1 | m2 | m3;
+            if (many >> nd) err |= kErrQual;                    // a counted entry with a dictionary index >= n_qual_dict
+            const unsigned q0m = __ballot_sync(0xffffffffu, dq == 0), q1m = __ballot_sync(0xffffffffu, dq <= 1);
+            const unsigned lowq = ((many & q0m) ? 1u : 0u) | ((many & q1m) ? 2u : 0u);
+            const int depth[4] = {(int)(d01 & 0xffffu), (int)(d01 >> 16), (int)(d23 & 0xffffu), (int)(d23 >> 16)};
+            const int fwd[4] = {(int)(f01 & 0xffffu), (int)(f01 >> 16), (int)(f23 & 0xffffu), (int)(f23 >> 16)};
+            const int ncb[4] = {__popc(m0), __popc(m1), __popc(m2), __popc(m3)};
+            // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
+            int best = -1, bestd = -1, second = -1, secondd = -1;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                if (depth[b] > bestd) { second = best; secondd = bestd; best = b; bestd = depth[b]; }
+                else if (depth[b] > secondd) { second = b; secondd = depth[b]; }
+            }
+            const int alt = (best != ref) ? best : second;
+            // src/BaseVarC.cpp:587-602: 2x2 table over ALL entries; an indel entry (qi 31) carries its stale base / strand
+            const int fr_ = ref == 0 ? fwd[0] : ref == 1 ? fwd[1] : ref == 2 ? fwd[2] : fwd[3];
+            const int dr_ = ref == 0 ? depth[0] : ref == 1 ? depth[1] : ref == 2 ? depth[2] : depth[3];
+            const int fa_ = alt == 0 ? fwd[0] : alt == 1 ? fwd[1] : alt == 2 ? fwd[2] : fwd[3];
+            const int da_ = alt == 0 ? depth[0] : alt == 1 ? depth[1] : alt == 2 ? depth[2] : depth[3];
+            const uint32_t* ib = h + BVC_PACK8_INDEL * 8;       // [strand][base]
+            const int c0 = fr_ + (int)ib[4 | ref], c1 = (dr_ - fr_) + (int)ib[ref];
+            const int c2 = fa_ + (int)ib[4 | alt], c3 = (da_ - fa_) + (int)ib[alt];
+            __syncwarp();
+            hp[0] = make_uint4(0u, 0u, 0u, 0u); hp[1] = make_uint4(0u, 0u, 0u, 0u);
+            // classes to the pool, the MAJOR base first (K3 runs that segment select-free), null-padded to a multiple of 4
+            const int ncls = ncb[0] + ncb[1] + ncb[2] + ncb[3];
+            const int n_major = best == 0 ? ncb[0] : best == 1 ? ncb[1] : best == 2 ? ncb[2] : ncb[3];
+            const uint32_t off = (uint32_t)site * (uint32_t)a.cls_stride;
+            if (lane < 4 && n_major + lane < pad4(n_major)) a.cls[off + n_major + lane] = kNullClass;
+            uint32_t run = off + (uint32_t)pad4(n_major);
+            const uint32_t xs[4] = {x0, x1, x2, x3};
+            const unsigned ms[4] = {m0, m1, m2, m3};
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                uint32_t pos;
+                if (b == best) pos = off; else { pos = run; run += (uint32_t)ncb[b]; }
+                if (xs[b] && lane < nd) a.cls[pos + __popc(ms[b] & lower)] = (xs[b] << 9) | (uint32_t)(b << 7) | dq;
+            }
+            uint4 v;
+            if (lane == 0) v = make_uint4((uint32_t)depth[0], (uint32_t)depth[1], (uint32_t)depth[2], (uint32_t)depth[3]);
+            else if (lane == 1) v = make_uint4((uint32_t)fwd[0], (uint32_t)fwd[1], (uint32_t)fwd[2], (uint32_t)fwd[3]);
+            else if (lane == 2) v = make_uint4((uint32_t)c0, (uint32_t)c1, (uint32_t)c2, (uint32_t)c3);
+            else v = make_uint4(off, (uint32_t)(ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0)),
+                                (uint32_t)n_entries, (uint32_t)(n_major | (best << 16)));
+            if (lane < 4) reinterpret_cast<uint4*>(a.sum + site)[lane] = v;
+        }
+        ov = nov;
+        __syncwarp();
+    }
+    const uint32_t err_all = __reduce_or_sync(0xffffffffu, err);
+    if (lane == 0 && err_all) atomicOr(a.s.err, err_all);
 }
 
 // =====================================================================================================
@@ -1458,22 +1667,28 @@ vcf_stats_kernel(PipeArgs a)
         const uint32_t* qual4 = reinterpret_cast<const uint32_t*>(a.s.qual);
         const uint32_t* mapq4 = reinterpret_cast<const uint32_t*>(a.s.mapq);
         const uint32_t* rpr4 = reinterpret_cast<const uint32_t*>(a.s.rpr);
+        const uint32_t* pk4 = reinterpret_cast<const uint32_t*>(a.s.pk8);
         for (uint32_t wi = w0 + lane; wi < w1; wi += 32) {
-            const uint32_t cw = __ldg(code4 + wi);
+            // the one-byte form (pk8 != NULL) carries the same (base, is_indel) and the qual as a dictionary index
+            const uint32_t cw = pk4 ? __ldg(pk4 + wi) : __ldg(code4 + wi);
             int g[4]; bool any = false;
+            uint32_t qw = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const uint32_t e = wi * 4 + k;
-                const unsigned c = (cw >> (8 * k)) & 31u;
-                const int base = c & 7;
+                const unsigned c = (cw >> (8 * k)) & 255u;
+                const bool cnt = pk4 ? (c >> 3) < BVC_PACK8_MAX_QUALS : !(c & 16);
+                const int base = pk4 ? (int)(c & 3u) : (int)(c & 7u);
                 g[k] = -1;
-                if (e >= b0 && e < b1 && !(c & 16)) {
+                if (e >= b0 && e < b1 && cnt) {
                     if (base == ref) g[k] = 0; else if (base < 4 && (altmask >> base & 1)) g[k] = 1;
                 }
                 any |= g[k] >= 0;
+                if (pk4) qw |= (uint32_t)a.s.dict.q[cnt ? (c >> 3) : 0u] << (8 * k);
             }
             if (!any) continue;
-            const uint32_t qw = __ldg(qual4 + wi), mw = mapq4[wi], rw = rpr4[wi];
+            if (!pk4) qw = __ldg(qual4 + wi);
+            const uint32_t mw = mapq4[wi], rw = rpr4[wi];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 if (g[k] < 0) continue;

@@ -58,6 +58,7 @@ struct PipeArgs {
     int refill_min;             // em_fit_kernel: lanes without a fit wait until this many of the warp's lanes want one
     int long_exact;             // 1: em_long_kernel evaluates the exact delta on every pass (A/B check of its bound-based decision)
     int em_min_fits;            // a stage with fewer fits than this skips em_fit_kernel (every fit starts in em_long_kernel)
+    int cls_stride;             // site_hist8_kernel: a site's classes live at pool word site * cls_stride (no allocation atomic)
     SiteArgs s;                 // tile arrays, out, lut, lgam, thresholds
     SiteSum*  sum;              // [n_sites]
     uint32_t* cls;              // class pool: cnt << 9 | base << 7 | qual

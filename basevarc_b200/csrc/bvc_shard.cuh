@@ -53,8 +53,9 @@ shard_hist_kernel(ShardArgs a)
         const int site = first + it * n_groups;
         const bool live = site < a.n_tile_sites;
         const uint32_t b0 = live ? a.tile_off[site] : 0u, b1 = live ? a.tile_off[site + 1] : 0u;
-        uint32_t qmax = 0, qmin = 127;
-        hist_stream<G>(code4, qual4, b0, b1, g, hist, qmin, qmax);
+        uint32_t qmax = 0, qmin = 127, badin = 0;
+        hist_stream<G>(code4, qual4, b0, b1, g, hist, qmin, qmax, badin);
+        if (badin) atomicOr(a.err, 1u);                                             // qual > 127 / non-indel base > 3: the call fails (BVC_ERR_ARG)
         qmax = group_max<G>(qmax, gi);
         qmin = group_min<G>(qmin, gi);
         const bool bad = qmin <= qmax && ((int)qmin < a.qlo || (int)qmax > a.qhi);   // a non-indel qual outside the window

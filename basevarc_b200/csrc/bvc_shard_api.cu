@@ -138,7 +138,7 @@ static int shard_upload(bvc_ctx* ctx, const bvc_tile* tile)
     Slot& s = ctx->slot[0];
     if (s.ticket) { CK(cudaStreamSynchronize(s.stream)); s.ticket = 0; }
     CK(cudaEventRecord(st->ev[0], s.stream));
-    if ((rc = upload(ctx, s, tile, R, false)) != BVC_OK) return rc;
+    if ((rc = upload(ctx, s, tile, R, false, true)) != BVC_OK) return rc;     // the shard kernels read the (code, qual) arrays
     ctx->resident = false;
     SiteArgs sa;
     ShardArgs& a = st->a;

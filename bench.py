@@ -445,6 +445,9 @@ def main():
     units_per_gpu = S * N
 
     # ---- kernel-only leg: inputs resident in HBM, device events on the launching stream -----------
+    # the tile is resident in the form it travels in: one byte per entry + qual dictionary (--wire packed8, what the host
+    # packer emits for <= 30 distinct quals; K1 reads the byte directly), or the two (code, qual) arrays (--wire plain)
+    resident_packed = args.wire == "packed8" and tile.pack8()
     caller.resident_upload(tile)
     for _ in range(args.warmup):
         caller.resident_run(1, flush_l2=False)

@@ -3,6 +3,7 @@ import numpy as np
 import pytest
 
 import basevarc_b200 as B
+from basevarc_b200._abi import FLAG_EM_DELTA
 from basevarc_b200.pileup import PileupTile, synth_tile
 from parity import compare_records
 
@@ -33,7 +34,13 @@ def test_synthetic_parity(oracle, name, N, S, depth, model, seed):
     # emitted site set + ALT alleles are bit-exact by the checks above; make sure the case is not vacuous
     assert want["lrt_ok"].sum() > 0
     assert (got["em_fits"] == want["em_fits"]).all()
-    assert (got["em_passes"] == want["em_passes"]).mean() > 0.999
+    # a pass count may differ only where the convergence test delta < epsilon (src/Algorithm.cpp:124) was met within 1e-9:
+    # every such site is listed and must carry BVC_FLAG_EM_DELTA
+    diff = np.nonzero(got["em_passes"] != want["em_passes"])[0]
+    unflagged = [int(i) for i in diff if not (int(got["flags"][i]) & FLAG_EM_DELTA)]
+    assert not unflagged, "em_passes differ without BVC_FLAG_EM_DELTA at sites %s (got %s want %s)" % (
+        unflagged[:10], got["em_passes"][unflagged[:10]].tolist(), want["em_passes"][unflagged[:10]].tolist())
+    assert diff.size <= max(1, tile.n_sites // 1000), "em_passes differ at %d sites: %s" % (diff.size, diff[:20].tolist())
 
 
 def test_empty_and_ragged(oracle):
@@ -72,7 +79,8 @@ def test_qual_windows(oracle, lo, hi):
     tile = synth_tile(300, 900, 0.8, "highpoly", seed=lo + hi, indel_frac=0.02)
     tile.qual = rng.integers(lo, hi + 1, tile.qual.size).astype(np.uint8)
     got, want = _run_both(tile, oracle)
-    nbad, lines = compare_records(got, want)
+    # one qual for every read (5, 5) makes the null models of equal-depth bases tie EXACTLY (BVC_FLAG_ARGMIN_TIE, ~3 % of the sites)
+    nbad, lines = compare_records(got, want, max_flagged_fraction=0.1 if lo == hi else 0.02)
     assert nbad == 0, "\n".join(lines)
     assert want["lrt_ok"].sum() > 0
 
@@ -92,10 +100,63 @@ def test_packed8_wire_form_same_records(oracle, N, S, depth, model, indel):
     caller.resident_upload(tile)
     caller.resident_run(1, flush_l2=False)
     assert caller.resident_download().tobytes() == plain.tobytes()
+    # the dictionary need not be sorted (the host packer fills it in order of first appearance): same records
+    perm = np.random.default_rng(5).permutation(tile.qual_dict.size)
+    inv = np.argsort(perm)
+    qi = tile.packed8 >> 3
+    shuffled = tile.packed8.copy()
+    counted = qi < 30
+    shuffled[counted] = (inv[qi[counted]].astype(np.uint8) << 3) | (tile.packed8[counted] & 7)
+    t2 = tile.slice_sites(0, tile.n_sites)
+    t2.packed8, t2.qual_dict = shuffled, np.ascontiguousarray(tile.qual_dict[perm])
+    assert caller.call_sites(t2).tobytes() == plain.tobytes()
     caller.close()
     want = oracle.call_sites(tile, B.default_params(N))
     nbad, lines = compare_records(packed, want)
     assert nbad == 0, "\n".join(lines)
+
+
+def test_packed8_resident_kernel_equals_expanded_arrays(monkeypatch):
+    """site_hist8_kernel (K1 on the one-byte form, the form a packed8 tile stays resident in) against the same tile expanded
+    into the (code, qual) arrays behind the copy (BVC_EXPAND8=1 -> site_hist4_kernel): byte-identical records, on shapes that
+    exercise the 16-byte-word corrections (tiny and empty sites, one site spanning many words, ragged ends)."""
+    rng = np.random.default_rng(77)
+    for N, S, depth, model, indel in [(1000, 4001, 0.5, "lowpass", 0.005), (60, 3000, 0.05, "lowpass", 0.2), (2000, 403, 5.0, "highpoly", 0.01),
+                                      (40000, 37, 0.3, "lowpass", 0.005)]:
+        tile = synth_tile(N, S, depth, model, seed=int(rng.integers(1 << 30)), indel_frac=indel)
+        assert tile.pack8()
+        monkeypatch.setenv("BVC_EXPAND8", "1")
+        c1 = B.BaseTypeCaller(N, max_sites=S, max_entries=tile.n_entries)
+        want = c1.call_sites(tile).copy()
+        c1.close()
+        monkeypatch.delenv("BVC_EXPAND8")
+        c2 = B.BaseTypeCaller(N, max_sites=S, max_entries=tile.n_entries)
+        got = c2.call_sites(tile).copy()
+        c2.close()
+        assert got.tobytes() == want.tobytes(), (N, S)
+
+
+def test_device_rejects_what_the_abi_promises_to_reject():
+    """include/bvc_gpu.h BVC_ERR_ARG: qual > 127, a non-indel base > 3, a packed8 dictionary index >= n_qual_dict.  A direct
+    C-ABI caller (no host packer in front) gets the error from bvc_wait instead of silently different records."""
+    tile = synth_tile(200, 500, 1.0, "lowpass", seed=3)
+    caller = B.BaseTypeCaller(200, max_sites=500, max_entries=tile.n_entries)
+    ok = caller.call_sites(tile).copy()
+    bad = tile.slice_sites(0, tile.n_sites)
+    bad.qual = tile.qual.copy(); bad.qual[tile.n_entries // 2] = 200
+    with pytest.raises(B.BvcError, match="qual > 127"):
+        caller.call_sites(bad)
+    bad = tile.slice_sites(0, tile.n_sites)
+    bad.code = tile.code.copy(); bad.code[7] = 6            # base 6, not an indel
+    with pytest.raises(B.BvcError, match="base > 3"):
+        caller.call_sites(bad)
+    bad = tile.slice_sites(0, tile.n_sites)
+    assert bad.pack8()
+    bad.packed8 = bad.packed8.copy(); bad.packed8[11] = (29 << 3) | 1      # dictionary index 29 of a 21-entry dictionary
+    with pytest.raises(B.BvcError, match="qual > 127"):
+        caller.call_sites(bad)
+    assert caller.call_sites(tile).tobytes() == ok.tobytes()                   # the context stays usable
+    caller.close()
 
 
 def test_split_result_equals_full_records():
@@ -237,4 +298,10 @@ def test_em_fit_batched_refills(oracle, monkeypatch, refill_min):
     nbad, lines = compare_records(got, want)
     assert nbad == 0, "\n".join(lines)
     assert (got["em_fits"] == want["em_fits"]).all()
-    assert (got["em_passes"] == want["em_passes"]).mean() > 0.999
+    # a pass count may differ only where the convergence test delta < epsilon (src/Algorithm.cpp:124) was met within 1e-9:
+    # every such site is listed and must carry BVC_FLAG_EM_DELTA
+    diff = np.nonzero(got["em_passes"] != want["em_passes"])[0]
+    unflagged = [int(i) for i in diff if not (int(got["flags"][i]) & FLAG_EM_DELTA)]
+    assert not unflagged, "em_passes differ without BVC_FLAG_EM_DELTA at sites %s (got %s want %s)" % (
+        unflagged[:10], got["em_passes"][unflagged[:10]].tolist(), want["em_passes"][unflagged[:10]].tolist())
+    assert diff.size <= max(1, tile.n_sites // 1000), "em_passes differ at %d sites: %s" % (diff.size, diff[:20].tolist())
