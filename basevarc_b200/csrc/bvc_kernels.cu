@@ -438,7 +438,7 @@ expand8_kernel(const uint4* __restrict__ pk, uint4* __restrict__ code, uint4* __
 {
     __shared__ uint8_t code_lut[256], qual_lut[256];
     {
-        const unsigned b = threadIdx.x, qi = b >> 3, strand = (b >> 2) & 1u, base = b & 3u;
+        const unsigned b = threadIdx.x, qi = BVC_PACK8_QI(b), strand = BVC_PACK8_STRAND(b), base = BVC_PACK8_BASE(b);
         code_lut[b] = qi < 30u ? (uint8_t)(base | (strand << 3)) : qi == 31u ? (uint8_t)(base | (strand << 3) | 0x10u) : (uint8_t)(4u | (strand << 3) | 0x10u);
         qual_lut[b] = dict.q[qi < 30u ? qi : 0u];
     }

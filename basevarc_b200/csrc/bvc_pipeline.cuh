@@ -587,7 +587,7 @@ site_hist4_kernel(PipeArgs a)
 }
 
 // =====================================================================================================
-// K1 on the ONE-byte form (BVC_PACK8: qi:5 | strand:1 | base:2; the form every tile with <= 30 distinct quals
+// K1 on the ONE-byte form (BVC_PACK8: base:2 | qi:5 | strand:1; the form every tile with <= 30 distinct quals
 // travels and stays resident in).  The byte IS the bin: a site's histogram is 256 words [qi][strand][base], so an
 // entry costs a byte extract, an address add and one red.shared -- no qual/base arithmetic, no predicates (indel
 // entries are qi 31 = the 8 [strand][stale base] bins the CVG table needs, qi 30 counts nowhere).
@@ -603,16 +603,25 @@ site_hist4_kernel(PipeArgs a)
 // =====================================================================================================
 constexpr int kH8Sites = 4;
 constexpr int kH8Words = 256;
+constexpr int kH8Stage = 128;              // staging words per site: pad4(major classes) + the other classes <= 4 * 30 + 3
 
 __device__ __forceinline__ uint4 ldg16(const uint4* p) { return __ldg(p); }
 
-__global__ void __launch_bounds__(kHistWarps * 32)
+#ifndef BVC_H8_MINBLOCKS
+#define BVC_H8_MINBLOCKS 7
+#endif
+__global__ void __launch_bounds__(kHistWarps * 32, BVC_H8_MINBLOCKS)
 site_hist8_kernel(PipeArgs a)
 {
     __shared__ __align__(16) uint32_t hist_s[kHistWarps][kH8Sites * kH8Words];
+    __shared__ __align__(16) uint32_t stage_s[kHistWarps][kH8Sites * kH8Stage];
+    __shared__ __align__(16) uint32_t zero8[8];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint32_t* hw = hist_s[wid];
+    uint32_t* stage = stage_s[wid];
     for (int i = lane; i < kH8Sites * kH8Words; i += 32) hw[i] = 0;
+    if (threadIdx.x < 8) zero8[threadIdx.x] = 0;
+    __syncthreads();
     const uint32_t hs0 = (uint32_t)__cvta_generic_to_shared(hw);
     const uint32_t hs1 = hs0 + 4u * kH8Words, hs2 = hs1 + 4u * kH8Words, hs3 = hs2 + 4u * kH8Words;
     const int nd = a.s.n_dict;
@@ -624,6 +633,7 @@ site_hist8_kernel(PipeArgs a)
         if (j < nd && (qj < dq || (qj == dq && j < lane))) lower |= 1u << j;
     }
     const bool counted = lane < BVC_PACK8_MAX_QUALS;
+    const unsigned q0m = __ballot_sync(0xffffffffu, dq == 0), q1m = __ballot_sync(0xffffffffu, dq <= 1);
     __syncwarp();
     const uint4* pk16 = reinterpret_cast<const uint4*>(a.s.pk8);
     const int S = a.s.n_sites;
@@ -632,8 +642,8 @@ site_hist8_kernel(PipeArgs a)
     uint32_t err = 0;
 
     int batch = blockIdx.x * kHistWarps + wid;
-    uint32_t ov = 0;
-    if (batch < n_batches && lane <= kH8Sites) ov = a.s.entry_off[min(batch * kH8Sites + lane, S)];
+    uint32_t ov = 0, refv = 0;
+    if (batch < n_batches && lane <= kH8Sites) { ov = a.s.entry_off[min(batch * kH8Sites + lane, S)]; refv = a.s.ref_base[min(batch * kH8Sites + lane, S - 1)]; }
     // the first two trips of a batch are loaded while the previous batch is emitted
     uint4 px0 = make_uint4(0, 0, 0, 0), px1 = px0;
     auto first_two = [&](uint32_t b0, uint32_t b4) {
@@ -646,8 +656,11 @@ site_hist8_kernel(PipeArgs a)
     first_two(__shfl_sync(0xffffffffu, ov, 0), __shfl_sync(0xffffffffu, ov, kH8Sites));
     for (; batch < n_batches; batch += stride) {
         const int s0 = batch * kH8Sites;
-        uint32_t nov = 0;
-        if (batch + stride < n_batches && lane <= kH8Sites) nov = a.s.entry_off[min((batch + stride) * kH8Sites + lane, S)];
+        uint32_t nov = 0, nrefv = 0;                            // the next batch's offsets and reference bases: no dependent load in the emit
+        if (batch + stride < n_batches && lane <= kH8Sites) {
+            nov = a.s.entry_off[min((batch + stride) * kH8Sites + lane, S)];
+            nrefv = a.s.ref_base[min((batch + stride) * kH8Sites + lane, S - 1)];
+        }
         const uint32_t o0 = __shfl_sync(0xffffffffu, ov, 0), o1 = __shfl_sync(0xffffffffu, ov, 1), o2 = __shfl_sync(0xffffffffu, ov, 2),
                        o3 = __shfl_sync(0xffffffffu, ov, 3), o4 = __shfl_sync(0xffffffffu, ov, 4);
         const uint32_t v0 = o0 >> 4, v1 = (o4 + 15) >> 4;
@@ -714,72 +727,80 @@ site_hist8_kernel(PipeArgs a)
             for (uint32_t pa = (n0 & ~127u) + 1024u + (uint32_t)lane * 128u; pa < n4; pa += 32u * 128u)    // the rest: into L2
                 asm volatile("prefetch.global.L2 [%0];" :: "l"(a.s.pk8 + pa));
         }
-        // ---- emit: one site at a time, lane = dictionary index ---------------------------------------------------
+        // ---- emit: one site at a time (four independent chains for the scheduler), lane = dictionary index.  Lanes 30 / 31 (the
+        // indel codes) read a block of zeros, so no count needs masking.
 #pragma unroll
         for (int k = 0; k < kH8Sites; ++k) {
             const int site = s0 + k;
             if (site >= S) break;                               // warp-uniform
             uint32_t* h = hw + k * kH8Words;
-            uint4* hp = reinterpret_cast<uint4*>(h + lane * 8);
-            const uint4 rv = hp[0], fw = hp[1];                 // reverse / forward strand counts of bases 0..3 at my qual
+            // bin = the byte: base << 6 | qi << 1 | strand -> my (reverse, forward) counts of base b are one 8-byte word
+            const uint2* hp = reinterpret_cast<const uint2*>(counted ? h + lane * 2 : zero8);
+            const int hstep = counted ? 32 : 0;                 // uint2 stride between bases
+            const uint2 h0 = hp[0], h1 = hp[hstep], h2 = hp[2 * hstep], h3 = hp[3 * hstep];
+            const uint4 rv = make_uint4(h0.x, h1.x, h2.x, h3.x), fw = make_uint4(h0.y, h1.y, h2.y, h3.y);
             const int n_entries = (int)(k == 0 ? o1 - o0 : k == 1 ? o2 - o1 : k == 2 ? o3 - o2 : o4 - o3);
-            const int ref = a.s.ref_base[site] & 3;
-            const uint32_t x0 = counted ? rv.x + fw.x : 0u, x1 = counted ? rv.y + fw.y : 0u,
-                           x2 = counted ? rv.z + fw.z : 0u, x3 = counted ? rv.w + fw.w : 0u;
+            const int ref = (int)(__shfl_sync(0xffffffffu, refv, k) & 3u);
+            const uint32_t x0 = rv.x + fw.x, x1 = rv.y + fw.y, x2 = rv.z + fw.z, x3 = rv.w + fw.w;
             // a site has < 65,536 entries: two depths per word through one REDUX
-            const uint32_t d01 = __reduce_add_sync(0xffffffffu, x0 | (x1 << 16)), d23 = __reduce_add_sync(0xffffffffu, x2 | (x3 << 16));
-            const uint32_t f01 = __reduce_add_sync(0xffffffffu, counted ? fw.x | (fw.y << 16) : 0u),
-                           f23 = __reduce_add_sync(0xffffffffu, counted ? fw.z | (fw.w << 16) : 0u);
+            const uint32_t d01 = __reduce_add_sync(0xffffffffu, __byte_perm(x0, x1, 0x5410)), d23 = __reduce_add_sync(0xffffffffu, __byte_perm(x2, x3, 0x5410));
+            const uint32_t f01 = __reduce_add_sync(0xffffffffu, __byte_perm(fw.x, fw.y, 0x5410)),
+                           f23 = __reduce_add_sync(0xffffffffu, __byte_perm(fw.z, fw.w, 0x5410));
             const unsigned m0 = __ballot_sync(0xffffffffu, x0 != 0), m1 = __ballot_sync(0xffffffffu, x1 != 0),
                            m2 = __ballot_sync(0xffffffffu, x2 != 0), m3 = __ballot_sync(0xffffffffu, x3 != 0);
+            // (the indel bins -- qi 31, read below by every lane -- are cleared by lane 31 after that read; qi 30 is never read)
+            if (counted) {
+                uint2* cp = reinterpret_cast<uint2*>(h + lane * 2);
+                cp[0] = make_uint2(0u, 0u); cp[32] = make_uint2(0u, 0u); cp[64] = make_uint2(0u, 0u); cp[96] = make_uint2(0u, 0u);
+            }
             const unsigned many = m0 | m1 | m2 | m3;
             if (many >> nd) err |= kErrQual;                    // a counted entry with a dictionary index >= n_qual_dict
-            const unsigned q0m = __ballot_sync(0xffffffffu, dq == 0), q1m = __ballot_sync(0xffffffffu, dq <= 1);
             const unsigned lowq = ((many & q0m) ? 1u : 0u) | ((many & q1m) ? 2u : 0u);
-            const int depth[4] = {(int)(d01 & 0xffffu), (int)(d01 >> 16), (int)(d23 & 0xffffu), (int)(d23 >> 16)};
-            const int fwd[4] = {(int)(f01 & 0xffffu), (int)(f01 >> 16), (int)(f23 & 0xffffu), (int)(f23 >> 16)};
-            const int ncb[4] = {__popc(m0), __popc(m1), __popc(m2), __popc(m3)};
-            // src/BaseVarC.cpp:576-583: descending argsort, ties in index order; top non-ref base
-            int best = -1, bestd = -1, second = -1, secondd = -1;
-#pragma unroll
-            for (int b = 0; b < 4; ++b) {
-                if (depth[b] > bestd) { second = best; secondd = bestd; best = b; bestd = depth[b]; }
-                else if (depth[b] > secondd) { second = b; secondd = depth[b]; }
-            }
+            const int d0 = (int)(d01 & 0xffffu), d1 = (int)(d01 >> 16), d2 = (int)(d23 & 0xffffu), d3 = (int)(d23 >> 16);
+            const int f0 = (int)(f01 & 0xffffu), f1 = (int)(f01 >> 16), f2 = (int)(f23 & 0xffffu), f3 = (int)(f23 >> 16);
+            const int n0 = __popc(m0), n1 = __popc(m1), n2 = __popc(m2), n3 = __popc(m3);
+            // src/BaseVarC.cpp:576-583: descending argsort, ties in index order -> key = depth << 2 | (3 - base); top non-ref base
+            const uint32_t k0 = ((uint32_t)d0 << 2) | 3u, k1 = ((uint32_t)d1 << 2) | 2u, k2 = ((uint32_t)d2 << 2) | 1u, k3 = (uint32_t)d3 << 2;
+            const uint32_t kb = max(max(k0, k1), max(k2, k3));
+            const int best = 3 - (int)(kb & 3u);
+            const uint32_t ks = max(max(best == 0 ? 0u : k0, best == 1 ? 0u : k1), max(best == 2 ? 0u : k2, best == 3 ? 0u : k3));
+            const int second = 3 - (int)(ks & 3u);
             const int alt = (best != ref) ? best : second;
             // src/BaseVarC.cpp:587-602: 2x2 table over ALL entries; an indel entry (qi 31) carries its stale base / strand
-            const int fr_ = ref == 0 ? fwd[0] : ref == 1 ? fwd[1] : ref == 2 ? fwd[2] : fwd[3];
-            const int dr_ = ref == 0 ? depth[0] : ref == 1 ? depth[1] : ref == 2 ? depth[2] : depth[3];
-            const int fa_ = alt == 0 ? fwd[0] : alt == 1 ? fwd[1] : alt == 2 ? fwd[2] : fwd[3];
-            const int da_ = alt == 0 ? depth[0] : alt == 1 ? depth[1] : alt == 2 ? depth[2] : depth[3];
-            const uint32_t* ib = h + BVC_PACK8_INDEL * 8;       // [strand][base]
-            const int c0 = fr_ + (int)ib[4 | ref], c1 = (dr_ - fr_) + (int)ib[ref];
-            const int c2 = fa_ + (int)ib[4 | alt], c3 = (da_ - fa_) + (int)ib[alt];
-            __syncwarp();
-            hp[0] = make_uint4(0u, 0u, 0u, 0u); hp[1] = make_uint4(0u, 0u, 0u, 0u);
-            // classes to the pool, the MAJOR base first (K3 runs that segment select-free), null-padded to a multiple of 4
-            const int ncls = ncb[0] + ncb[1] + ncb[2] + ncb[3];
-            const int n_major = best == 0 ? ncb[0] : best == 1 ? ncb[1] : best == 2 ? ncb[2] : ncb[3];
+            const int df_r = ref == 0 ? f0 : ref == 1 ? f1 : ref == 2 ? f2 : f3, dd_r = ref == 0 ? d0 : ref == 1 ? d1 : ref == 2 ? d2 : d3;
+            const int df_a = alt == 0 ? f0 : alt == 1 ? f1 : alt == 2 ? f2 : f3, dd_a = alt == 0 ? d0 : alt == 1 ? d1 : alt == 2 ? d2 : d3;
+            uint2* ibin = reinterpret_cast<uint2*>(h + BVC_PACK8_INDEL * 2);       // + 32 per base: (reverse, forward) indel entries
+            const uint2 i_r = ibin[32 * ref], i_a = ibin[32 * alt];
+            const int c0 = df_r + (int)i_r.y, c1 = (dd_r - df_r) + (int)i_r.x, c2 = df_a + (int)i_a.y, c3 = (dd_a - df_a) + (int)i_a.x;
+            // pool segments: the MAJOR base first (K3 runs that segment select-free), null-padded to a multiple of 4, then the others
+            // ascending; a class's position in its segment = number of present classes with a lower qual
+            const int n_major = best == 0 ? n0 : best == 1 ? n1 : best == 2 ? n2 : n3;
+            int run = pad4(n_major);
+            const int g0 = best == 0 ? 0 : run; run += best == 0 ? 0 : n0;
+            const int g1 = best == 1 ? 0 : run; run += best == 1 ? 0 : n1;
+            const int g2 = best == 2 ? 0 : run; run += best == 2 ? 0 : n2;
+            const int g3 = best == 3 ? 0 : run; run += best == 3 ? 0 : n3;
+            uint32_t* st = stage + k * kH8Stage;
+            if (lane < 3 && n_major + lane < pad4(n_major)) st[n_major + lane] = kNullClass;
+            if (x0) st[g0 + __popc(m0 & lower)] = (x0 << 9) | dq;
+            if (x1) st[g1 + __popc(m1 & lower)] = (x1 << 9) | (1u << 7) | dq;
+            if (x2) st[g2 + __popc(m2 & lower)] = (x2 << 9) | (2u << 7) | dq;
+            if (x3) st[g3 + __popc(m3 & lower)] = (x3 << 9) | (3u << 7) | dq;
             const uint32_t off = (uint32_t)site * (uint32_t)a.cls_stride;
-            if (lane < 4 && n_major + lane < pad4(n_major)) a.cls[off + n_major + lane] = kNullClass;
-            uint32_t run = off + (uint32_t)pad4(n_major);
-            const uint32_t xs[4] = {x0, x1, x2, x3};
-            const unsigned ms[4] = {m0, m1, m2, m3};
-#pragma unroll
-            for (int b = 0; b < 4; ++b) {
-                uint32_t pos;
-                if (b == best) pos = off; else { pos = run; run += (uint32_t)ncb[b]; }
-                if (xs[b] && lane < nd) a.cls[pos + __popc(ms[b] & lower)] = (xs[b] << 9) | (uint32_t)(b << 7) | dq;
+            if (lane == 0) {                                    // the 64-byte summary: every lane holds the values, one stores them
+                uint4* sp = reinterpret_cast<uint4*>(a.sum + site);
+                sp[0] = make_uint4((uint32_t)d0, (uint32_t)d1, (uint32_t)d2, (uint32_t)d3);
+                sp[1] = make_uint4((uint32_t)f0, (uint32_t)f1, (uint32_t)f2, (uint32_t)f3);
+                sp[2] = make_uint4((uint32_t)c0, (uint32_t)c1, (uint32_t)c2, (uint32_t)c3);
+                sp[3] = make_uint4(off, (uint32_t)((n0 + n1 + n2 + n3) | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0)),
+                                   (uint32_t)n_entries, (uint32_t)(n_major | (best << 16)));
             }
-            uint4 v;
-            if (lane == 0) v = make_uint4((uint32_t)depth[0], (uint32_t)depth[1], (uint32_t)depth[2], (uint32_t)depth[3]);
-            else if (lane == 1) v = make_uint4((uint32_t)fwd[0], (uint32_t)fwd[1], (uint32_t)fwd[2], (uint32_t)fwd[3]);
-            else if (lane == 2) v = make_uint4((uint32_t)c0, (uint32_t)c1, (uint32_t)c2, (uint32_t)c3);
-            else v = make_uint4(off, (uint32_t)(ncls | (alt << 16) | ((lowq & 1u) ? (1 << 24) : 0) | (lowq ? (2 << 24) : 0)),
-                                (uint32_t)n_entries, (uint32_t)(n_major | (best << 16)));
-            if (lane < 4) reinterpret_cast<uint4*>(a.sum + site)[lane] = v;
+            __syncwarp();
+            if (lane < 4) ibin[32 * lane] = make_uint2(0u, 0u);
+            if (lane * 4 < run)                                 // run <= 4 * nd + 3 <= 123 words: one coalesced 16-byte store per four
+                reinterpret_cast<uint4*>(a.cls + off)[lane] = reinterpret_cast<const uint4*>(st)[lane];
         }
-        ov = nov;
+        ov = nov; refv = nrefv;
         __syncwarp();
     }
     const uint32_t err_all = __reduce_or_sync(0xffffffffu, err);
@@ -1677,14 +1698,14 @@ vcf_stats_kernel(PipeArgs a)
             for (int k = 0; k < 4; ++k) {
                 const uint32_t e = wi * 4 + k;
                 const unsigned c = (cw >> (8 * k)) & 255u;
-                const bool cnt = pk4 ? (c >> 3) < BVC_PACK8_MAX_QUALS : !(c & 16);
-                const int base = pk4 ? (int)(c & 3u) : (int)(c & 7u);
+                const bool cnt = pk4 ? BVC_PACK8_QI(c) < BVC_PACK8_MAX_QUALS : !(c & 16);
+                const int base = pk4 ? (int)BVC_PACK8_BASE(c) : (int)(c & 7u);
                 g[k] = -1;
                 if (e >= b0 && e < b1 && cnt) {
                     if (base == ref) g[k] = 0; else if (base < 4 && (altmask >> base & 1)) g[k] = 1;
                 }
                 any |= g[k] >= 0;
-                if (pk4) qw |= (uint32_t)a.s.dict.q[cnt ? (c >> 3) : 0u] << (8 * k);
+                if (pk4) qw |= (uint32_t)a.s.dict.q[cnt ? BVC_PACK8_QI(c) : 0u] << (8 * k);
             }
             if (!any) continue;
             if (!pk4) qw = __ldg(qual4 + wi);

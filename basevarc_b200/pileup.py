@@ -63,7 +63,7 @@ class PileupTile:
         return t
 
     def pack8(self):
-        """Adds the compact wire form (include/bvc_gpu.h BVC_PACK8: qi:5 | strand:1 | base:2 + a dictionary of the tile's
+        """Adds the compact wire form (include/bvc_gpu.h BVC_PACK8: base:2 | qi:5 | strand:1 + a dictionary of the tile's
         distinct quals) when the tile qualifies: <= 30 distinct quals among the counted entries and no non-indel entry with
         a base code > 3.  Returns True if packed8 / qual_dict were set."""
         base, strand, indel = self.code & 7, (self.code >> 3) & 1, (self.code >> 4) & 1
@@ -79,7 +79,7 @@ class PileupTile:
         lut[quals] = np.arange(quals.size, dtype=np.uint8)
         qi = lut[self.qual].astype(np.uint8)
         qi[indel == 1] = np.where(base[indel == 1] == 4, 30, 31).astype(np.uint8)
-        self.packed8 = np.ascontiguousarray((qi << 3) | (strand << 2) | (base & 3)).astype(np.uint8)
+        self.packed8 = np.ascontiguousarray(((base & 3) << 6) | (qi << 1) | strand).astype(np.uint8)
         self.qual_dict = np.ascontiguousarray(quals.astype(np.uint8))
         return True
 

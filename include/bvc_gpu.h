@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define BVC_ABI_VERSION 2
+#define BVC_ABI_VERSION 3
 
 /* error codes (negative); 0 = success */
 #define BVC_OK             0
@@ -88,13 +88,18 @@ typedef struct bvc_tile {
     int32_t reserved1;
 } bvc_tile;
 
-/* packed8 byte: qi:5 | strand:1 | base:2.  qi < 30: a counted entry of base 0..3 with qual qual_dict[qi].
+/* packed8 byte: base:2 | qi:5 | strand:1 (ABI 3; the byte is the bin index of K1's shared-memory histogram, and with the
+ * base in the top bits the entries of a site's dominant base spread over all 32 banks).
+ * qi < 30: a counted entry of base 0..3 with qual qual_dict[qi] (the dictionary need not be sorted).
  * qi == 31: an indel entry with stale base 0..3 / strand (its stale qual is not used by the calling core).
  * qi == 30: an indel entry whose stale base is 4 (N): it counts nowhere; only strand is kept. */
 #define BVC_PACK8_MAX_QUALS 30
 #define BVC_PACK8_INDEL     31u
 #define BVC_PACK8_INDEL_N   30u
-#define BVC_PACK8(qi, strand, base) ((uint8_t)((((qi) & 31u) << 3) | (((strand) & 1u) << 2) | ((base) & 3u)))
+#define BVC_PACK8(qi, strand, base) ((uint8_t)((((base) & 3u) << 6) | (((qi) & 31u) << 1) | ((strand) & 1u)))
+#define BVC_PACK8_QI(b)     (((b) >> 1) & 31u)
+#define BVC_PACK8_STRAND(b) ((b) & 1u)
+#define BVC_PACK8_BASE(b)   (((b) >> 6) & 3u)
 
 /* boundary-flag bits: a hard FP64 threshold of the reference was met within a 1e-9 relative margin
  * at this site, so a differently-ordered summation may legitimately land on the other side. */

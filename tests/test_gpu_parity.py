@@ -103,10 +103,10 @@ def test_packed8_wire_form_same_records(oracle, N, S, depth, model, indel):
     # the dictionary need not be sorted (the host packer fills it in order of first appearance): same records
     perm = np.random.default_rng(5).permutation(tile.qual_dict.size)
     inv = np.argsort(perm)
-    qi = tile.packed8 >> 3
+    qi = (tile.packed8 >> 1) & 31
     shuffled = tile.packed8.copy()
     counted = qi < 30
-    shuffled[counted] = (inv[qi[counted]].astype(np.uint8) << 3) | (tile.packed8[counted] & 7)
+    shuffled[counted] = (inv[qi[counted]].astype(np.uint8) << 1) | (tile.packed8[counted] & 0xc1)
     t2 = tile.slice_sites(0, tile.n_sites)
     t2.packed8, t2.qual_dict = shuffled, np.ascontiguousarray(tile.qual_dict[perm])
     assert caller.call_sites(t2).tobytes() == plain.tobytes()
@@ -152,7 +152,7 @@ def test_device_rejects_what_the_abi_promises_to_reject():
         caller.call_sites(bad)
     bad = tile.slice_sites(0, tile.n_sites)
     assert bad.pack8()
-    bad.packed8 = bad.packed8.copy(); bad.packed8[11] = (29 << 3) | 1      # dictionary index 29 of a 21-entry dictionary
+    bad.packed8 = bad.packed8.copy(); bad.packed8[11] = (1 << 6) | (29 << 1)      # base 1, dictionary index 29 of a 21-entry dictionary
     with pytest.raises(B.BvcError, match="qual > 127"):
         caller.call_sites(bad)
     assert caller.call_sites(tile).tobytes() == ok.tobytes()                   # the context stays usable

@@ -78,7 +78,7 @@ def test_packer_token_grammar_quirks():
 def _unpack8(tile):
     """(code, qual) from the compact wire form, the way the device expands it (basevarc_b200/csrc/bvc_kernels.cu expand8_kernel)."""
     p = tile.packed8
-    qi, strand, base = p >> 3, (p >> 2) & 1, p & 3
+    qi, strand, base = (p >> 1) & 31, p & 1, p >> 6
     code = np.where(qi < 30, base | (strand << 3), np.where(qi == 31, base | (strand << 3) | 0x10, 4 | (strand << 3) | 0x10)).astype(np.uint8)
     qual = tile.qual_dict[np.where(qi < 30, qi, 0)]
     return code, qual
