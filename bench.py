@@ -28,10 +28,17 @@ sys.path.insert(0, ROOT)
 os.environ["NCCL_DEBUG"] = os.environ.get("BVC_NCCL_DEBUG", "NONE")
 
 METRIC = "site*samples/sec for basetype EM+LRT"
-# FP64 operations em_fit_kernel's arithmetic performs per (base, qual) class per singleEM pass, FMA = 2
-# (DESIGN.md "Kernels": exact count 1, ml = e3*F + f_b*d 3, Newton reciprocal 8, weight 1, two accumulations 4;
-#  the convergence test costs nothing per class: see delta_decision in bvc_pipeline.cuh)
-FLOP_PER_CLASS_PASS = 17
+# FP64 operations per unit of work, FMA = 2, counted on the code that ships:
+#  em_fit_kernel, per (base, qual) class per singleEM pass (em_class_major, bvc_pipeline.cuh): exact count DADD 1,
+#    denominator DFMA 2, one Newton step on the MUFU seed 2 DFMA = 4, weight DMUL 1, V += DADD 1, accT DFMA 2 = 11
+#    (7 FP64 instructions + MUFU.RCP64H; `cuobjdump -sass` of the major loop shows exactly these per class)
+#  em_long_kernel, per class per pass (em_class_plain): count 1, e3*F 1, ml DFMA 2, two Newton steps 6, weight 1,
+#    accT DFMA 2, d*w 1, V += 1 = 15
+#  fit_loglik_kernel, per class evaluation: ml 3 + libdevice log + the weighted sums; 36 FP64 instructions per class in
+#    the SASS of its 4x unrolled loop (21 DFMA, 6 DMUL, 9 DADD) = 57
+FLOP_PER_CLASS_PASS = 11
+FLOP_PER_LONG_CLASS_PASS = 15
+FLOP_PER_LOGLIK_EVAL = 57
 UNIT = "site*samples/s"
 B_CONFIG_SAMPLES = {"C2": 1000, "C3": 10000, "C4": 100000, "C5": 2000}
 
@@ -537,31 +544,64 @@ def main():
     else:
         same = same and np.array_equal(got["alt_bases"], recs["alt_bases"])
 
-    # ---- rooflines (DESIGN.md "Measurement"): the dominant kernel, the streaming kernel, the whole step ----------
+    # ---- rooflines (DESIGN.md "Measurement"): one entry per kernel of the step, each against ITS bound with ITS algorithmic
+    # work; `roofline` = the entry of the dominant kernel; `step` = the whole step against its floors ---------------------
     peak, peak_src = _peaks()
     fp64_peak = B.measure_fp64_peak(local)
+    alg_bytes = _alg_bytes(tile)                       # whole step, SURVEY 8(d): 4R + 8S + 192 S_out
+    n_active = int((recs["em_fits"] > 0).sum())        # sites that ran at least one EM fit (the ladder's sites)
+    n_pos = int(recs["lrt_ok"].sum())
+    r_pos = int(recs["n_entries"][recs["lrt_ok"] == 1].astype(np.int64).sum())
+    entry_bytes = 1 if resident_packed else 2          # K1 reads one byte per entry in the packed8 form, code + qual otherwise
+    kernel_work = {
+        # K1: the entries once + offsets / ref (5 B per site) in, the 64-byte site summary out (the class pool, ~4 B per class, not counted)
+        "site_hist_kernel": ("hbm", entry_bytes * R + 5 * S + 64 * S),
+        # K2: summary in; a 176-byte record for the sites finalised here, a 96-byte ladder + 4-byte queue item for the others
+        "site_prepare_kernel": ("hbm", 64 * S + 176 * (S - n_active) + 100 * n_active),
+        "queue_sort_kernels": ("hbm", 3 * 4 * int(work["em_fits"]) + 2 * 64 * int(work["em_fits"])),   # items read twice + written, their site summaries
+        "em_fit_kernel": ("fp64", FLOP_PER_CLASS_PASS * int(work["em_class_passes"])),
+        "em_long_kernel": ("fp64", FLOP_PER_LONG_CLASS_PASS * int(work["em_long_class_passes"])),
+        "fit_loglik_kernel": ("fp64", FLOP_PER_LOGLIK_EVAL * int(work["loglik_class_evals"])),
+        # K4: per active site the ladder state + its fits in, the 176-byte record out
+        "ladder_kernel": ("hbm", (96 + 64 + 96) * n_active + 176 * n_active),
+        # K5: the four entry arrays of the LRT-positive sites in, 64 bytes of record out
+        "vcf_stats_kernel": ("hbm", (entry_bytes + 2) * r_pos + (64 + 64) * n_pos),
+    }
+    rooflines = {}
+    for k, k_ms in per_kernel.items():
+        if k not in kernel_work or k_ms <= 0:
+            continue
+        bound, amount = kernel_work[k]
+        if bound == "fp64":
+            ach, pk, unit = amount / (k_ms * 1e-3) / 1e12, fp64_peak, "TFLOP/s"
+        else:
+            ach, pk, unit = amount / (k_ms * 1e-3) / 1e9, peak, "GB/s"
+        rooflines[k] = {"bound": bound, "kernel_ms": round(k_ms, 4), "algorithmic_" + ("flop" if bound == "fp64" else "bytes") + "_per_step": int(amount),
+                        "achieved": ach, "peak": pk, "unit": unit, "frac": ach / pk}
     dom = max(per_kernel, key=per_kernel.get)
     k_ms = per_kernel[dom]
-    alg_bytes = _alg_bytes(tile)                       # whole step, SURVEY 8(d): 4R + 8S + 192 S_out
-    hist_bytes = 2 * R + 5 * S + 64 * S                # K1: code+qual bytes, offsets+ref, 64-B site summary out
-    hist_ms = per_kernel.get("site_hist_kernel", 0.0)
-    em_flop = FLOP_PER_CLASS_PASS * work["em_class_passes"]
+    roof = dict(rooflines.get(dom, {"bound": "hbm", "achieved": 0.0, "peak": peak, "unit": "GB/s", "frac": 0.0}))
+    roof["peak_source"] = ("measured here (bvc_measure_fp64_peak: dependent-free DFMA chains on all SMs; MEASURED_PEAKS.json has no FP64 entry)"
+                           if roof["bound"] == "fp64" else peak_src)
     if dom == "em_fit_kernel":
-        roof = {"bound": "fp64", "achieved": em_flop / (k_ms * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
-                "peak_source": "measured here (bvc_measure_fp64_peak: dependent-free DFMA chains on all SMs)",
-                "algorithmic_flop_per_launch": em_flop, "class_passes_per_launch": int(work["em_class_passes"]),
-                "flop_per_class_pass": FLOP_PER_CLASS_PASS}
-    else:
-        kb = hist_bytes if dom == "site_hist_kernel" else alg_bytes
-        roof = {"bound": "hbm", "achieved": kb / (k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": int(kb)}
-    traffic = None
-    try:                    # DRAM bytes of that kernel per launch, from the committed ncu --set full capture of this workload
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
-            traffic = json.load(f).get("%s:%d" % (args.workload, S), {}).get(dom)
+        roof.update({"class_passes_per_step": int(work["em_class_passes"]), "flop_per_class_pass": FLOP_PER_CLASS_PASS})
+    hist_bytes = kernel_work["site_hist_kernel"][1]
+    hist_ms = per_kernel.get("site_hist_kernel", 0.0)
+    em_flop = (FLOP_PER_CLASS_PASS * int(work["em_class_passes"]) + FLOP_PER_LONG_CLASS_PASS * int(work["em_long_class_passes"])
+               + FLOP_PER_LOGLIK_EVAL * int(work["loglik_class_evals"]))
+    # DRAM bytes per launch of the dominant kernel and its FP64-pipe utilisation: from this round's committed ncu --set full
+    # capture of the same workload (profiles/r2_traffic.json names the .csv it was read from and the HEAD it was taken at)
+    traffic, ncu_note = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
+            tj = json.load(f)
+        ent = tj.get("%s:%d" % (args.workload, S), {}).get(dom)
+        if ent:
+            traffic, ncu_note = ent.get("dram_bytes_per_launch"), {k: v for k, v in ent.items() if k != "dram_bytes_per_launch"}
+            ncu_note["source"] = tj.get("source")
     except OSError:
         pass
-    roof.update({"frac": roof["achieved"] / roof["peak"], "traffic": traffic, "kernel": dom, "kernel_ms": k_ms,
+    roof.update({"traffic": traffic, "ncu": ncu_note, "kernel": dom, "kernel_ms": k_ms,
                  "kernel_share_of_step": k_ms / max(sum(per_kernel.values()), 1e-9)})
     n_reads = recs["depth"].sum(1).astype(np.float64)
     f_alg = float((n_reads * (21.0 * recs["em_passes"] - 3.0 * recs["em_fits"])).sum())   # per-READ formulation, SURVEY 8(d)
@@ -593,10 +633,14 @@ def main():
                 "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "wire": wire, "result": args.result, "matches_resident": bool(same)},
         "gpu_launches": int(launches),
         "roofline": roof,
-        "hbm_stream": {"kernel": "site_hist_kernel", "kernel_ms": hist_ms, "algorithmic_bytes_per_launch": int(hist_bytes),
+        "rooflines": rooflines,
+        "hbm_stream": {"kernel": "site_hist_kernel (%s form)" % ("one-byte packed8" if resident_packed else "two-array"), "kernel_ms": hist_ms,
+                       "algorithmic_bytes_per_launch": int(hist_bytes),
                        "achieved": hist_bytes / max(hist_ms, 1e-9) / 1e6, "peak": peak, "unit": "GB/s",
                        "frac": hist_bytes / max(hist_ms, 1e-9) / 1e6 / peak},
         "step": {"algorithmic_bytes": int(alg_bytes), "hbm_floor_ms": alg_bytes / peak / 1e6,
+                 "frac_of_hbm_floor": (alg_bytes / peak / 1e6) / ms, "fp64_floor_ms": em_flop / fp64_peak / 1e9,
+                 "frac_of_fp64_floor": (em_flop / fp64_peak / 1e9) / ms, "fp64_peak_tflops": fp64_peak,
                  "em_flop_floor_ms": em_flop / fp64_peak / 1e9, "measured_ms": ms,
                  "per_read_flop_survey": f_alg, "per_read_tflops_equiv": f_alg / (ms * 1e-3) / 1e12,
                  "note": "per_read_* counts the flops of the reference's per-read EM (SURVEY 8d); the class-collapsed "
