@@ -119,9 +119,13 @@ class BaseTypeCaller:
     """One context = one GPU.  Not thread-safe (as the C ABI)."""
 
     def __init__(self, n_samples, maf=0.001, device=0, max_sites=1 << 16, max_entries=None, sample_group=None,
-                 n_groups=0):
+                 n_groups=0, lrt_threshold=None, em_epsilon=None):
         self.lib = load_library()
         p = default_params(n_samples, maf, max_sites, 0)
+        if lrt_threshold is not None:              # the reference's constants (src/BaseType.h:9, src/BaseType.cpp:45): overridden by tests only
+            p.lrt_threshold = float(lrt_threshold)
+        if em_epsilon is not None:
+            p.em_epsilon = float(em_epsilon)
         p.max_entries = int(max_entries if max_entries is not None else min(max_sites * n_samples, (1 << 32) - 1))
         self._sg = None
         if n_groups > 0:

@@ -17,6 +17,14 @@ namespace bvc {
 
 // a hard FP64 threshold met within 1e-9 relative: the site is reported as a threshold-boundary site
 __device__ __forceinline__ bool near_rel(double x, double thr) { return fabs(x - thr) <= 1e-9 * fabs(thr); }
+// Two null models of one ladder step "tie" (BVC_FLAG_ARGMIN_TIE, src/BaseType.cpp:99 std::min_element) when their chi agree
+// within 1e-9 relative OR within 1e-12 of the log-likelihood sums they are differences of: chi = 2 (lr_alt - lr) cancels two
+// sums of magnitude n |log L|, so a tiny chi is only known to ~1e-12 |lr| (seen: two depth-3 error bases at a 10,000-sample
+// site, chi 0.0136, |chi_a - chi_b| 5e-11 -- the argmin is then a coin toss between summation orders).
+__device__ __forceinline__ bool near_tie(double chi, double cmin, double lr_alt, double lr)
+{
+    return fabs(chi - cmin) <= 1e-9 * fmax(fabs(chi), fabs(cmin)) + 1e-12 * (fabs(lr_alt) + fabs(lr));
+}
 
 __device__ __forceinline__ double dm_phred(double p)
 {

@@ -1576,7 +1576,7 @@ __device__ __forceinline__ void ladder_site(const PipeArgs& a, uint32_t item)
         for (int i = 0; i < L.nfit; ++i) {
             const double lr = fr[i].lr;
             const double chi = 2.0 * (L.lr_alt - lr);
-            if (i > 0 && near_rel(chi, cmin)) L.flags |= BVC_FLAG_ARGMIN_TIE;
+            if (i > 0 && near_tie(chi, cmin, L.lr_alt, lr)) L.flags |= BVC_FLAG_ARGMIN_TIE;
             if (i == 0 || chi < cmin) { cmin = chi; lr_min = lr; imin = i; }
             L.em_fits += 1; L.em_passes += fr[i].passes; L.flags |= fr[i].flags;
         }
@@ -1622,7 +1622,7 @@ __device__ __forceinline__ void ladder_site(const PipeArgs& a, uint32_t item)
         for (int i = 0; i < n; ++i) {
             const double lr = (src && n == 2) ? src->f[i] : single_loglik(a, su, cand_at(L.cand4, i));
             const double chi = 2.0 * (L.lr_alt - lr);
-            if (i > 0 && near_rel(chi, cmin)) L.flags |= BVC_FLAG_ARGMIN_TIE;
+            if (i > 0 && near_tie(chi, cmin, L.lr_alt, lr)) L.flags |= BVC_FLAG_ARGMIN_TIE;
             if (i == 0 || chi < cmin) { cmin = chi; lr_min = lr; imin = i; }
             L.em_fits += 1; L.em_passes += 2;
         }

@@ -158,7 +158,7 @@ __device__ __noinline__ void lrt_ladder(const SiteArgs& a, const WarpSmem& w, co
             double lr_c, bp[4];
             em_fit(a, w, lut_s, st, sub, lane, lr_c, bp);
             const double chi = 2.0 * (lr_alt - lr_c);
-            if (!first && near_rel(chi, cmin)) st.flags |= BVC_FLAG_ARGMIN_TIE;
+            if (!first && near_tie(chi, cmin, lr_alt, lr_c)) st.flags |= BVC_FLAG_ARGMIN_TIE;
             if (first || chi < cmin) {                                 // std::min_element: first minimum
                 cmin = chi; lr_min = lr_c; m_min = m;
                 for (int j = 0; j < 4; ++j) bp_min[j] = bp[j];

@@ -10,7 +10,7 @@
  *   WriteVcf numeric part                                    src/BaseType.cpp:149-197
  * It keeps the reference's operation ORDER (sequential sums over reads, `((l0+l1)+l2)+l3`, etc.) so
  * that, compiled with -ffp-contract=off against the same glibc libm, its doubles are bit-identical
- * to the reference objects'.  PARITY IS PINNED: tests/test_oracle_vs_ref.py checks every function
+ * to the reference objects'.  PARITY IS PINNED: tests/test_oracle.py checks every function
  * here against oracle/_ref/libref_oracle.so (the unmodified reference objects) whenever that
  * library is present, and tests/golden/ holds vectors generated from it (the reference itself has no
  * golden vectors or known-answer tests for this path).
@@ -357,13 +357,25 @@ static void o_lrt(o_bt* bt, int32_t ref, double min_af, const int8_t* base_comb,
     if (out->var_qual == 0) out->var_qual = 0.0;
 }
 
+/* The reference's compile-time constants (epsilon 0.001 and 100 iterations, BaseType.cpp:45-46; LRT_THRESHOLD 24, BaseType.h:9)
+ * as arguments: bvc_params carries them (bvc_default_params sets the reference's values) and the threshold-boundary tests move
+ * them onto a site's own delta / chi. */
+static int o_lrt_reads(int32_t n, const int8_t* bases, const int8_t* quals, int32_t ref, double min_af,
+                       const int8_t* base_comb, int32_t n_comb, double eps, int iters, double lrt_thr, bvc_oracle_lrt* out);
+
 int bvc_oracle_lrt_reads(int32_t n, const int8_t* bases, const int8_t* quals, int32_t ref, double min_af,
                          const int8_t* base_comb, int32_t n_comb, bvc_oracle_lrt* out)
+{
+    return o_lrt_reads(n, bases, quals, ref, min_af, base_comb, n_comb, 0.001, 100, 24.0, out);
+}
+
+static int o_lrt_reads(int32_t n, const int8_t* bases, const int8_t* quals, int32_t ref, double min_af,
+                       const int8_t* base_comb, int32_t n_comb, double eps, int iters, double lrt_thr, bvc_oracle_lrt* out)
 {
     static const int8_t all4[NT] = {0, 1, 2, 3};
     o_bt bt; memset(&bt, 0, sizeof(bt));
     bt.n = n; bt.bases = bases; bt.quals = quals;
-    bt.eps = 0.001; bt.iters = 100; bt.lrt_thr = 24.0;                                    /* BaseType.cpp:45-46, BaseType.h:9 */
+    bt.eps = eps; bt.iters = iters; bt.lrt_thr = lrt_thr;
     size_t m = (size_t)(n > 0 ? n : 1);
     bt.L = (double*)malloc(sizeof(double) * m * NT);
     bt.ml = (double*)calloc(m, sizeof(double)); bt.ml2 = (double*)calloc(m, sizeof(double));
@@ -425,7 +437,7 @@ static int o_site(const bvc_params* prm, const bvc_tile* t, int32_t s, bvc_site_
     r->cvg_sor = o_sor(r->cvg_strand[0], r->cvg_strand[1], r->cvg_strand[2], r->cvg_strand[3]);
 
     bvc_oracle_lrt L;                                                       /* :612-613 */
-    bvc_oracle_lrt_reads(n, bases, quals, ref, prm->min_af, NULL, 0, &L);
+    o_lrt_reads(n, bases, quals, ref, prm->min_af, NULL, 0, prm->em_epsilon, prm->em_max_iter, prm->lrt_threshold, &L);
     r->lrt_ok = (int8_t)L.ok; r->n_alt = (int8_t)L.n_alt;
     for (int i = 0; i < 3; ++i) r->alt_bases[i] = (int8_t)(i < L.n_alt ? L.alt_bases[i] : -1);
     for (int j = 0; j < 4; ++j) r->af_lrt[j] = L.af_lrt[j];
@@ -451,7 +463,7 @@ static int o_site(const bvc_params* prm, const bvc_tile* t, int32_t s, bvc_site_
             }
             if (L.ok && m > 0) {
                 bvc_oracle_lrt GL;
-                bvc_oracle_lrt_reads(m, bases, quals, ref, prm->min_af, comb, nc, &GL);
+                o_lrt_reads(m, bases, quals, ref, prm->min_af, comb, nc, prm->em_epsilon, prm->em_max_iter, prm->lrt_threshold, &GL);
                 for (int i = 0; i < L.n_alt; ++i) {
                     int b = L.alt_bases[i];
                     ga[b] = o_in(GL.alt_bases, GL.n_alt, b) ? GL.af_lrt[b] : -1.0;   /* -1 = printed as "0" (:651) */

@@ -4,6 +4,9 @@ Integer / index fields: bit-exact.  FP64 fields: |a-b| <= RTOL*max(|a|,|b|) with
 tolerance BASELINE.json's north_star states), NaN == NaN, and an absolute floor of 1e-12 for values
 that are differences of O(1..1e4) log-likelihood sums (chi, and var_qual derived from it).
 """
+import os
+import threading
+
 import numpy as np
 
 from basevarc_b200._abi import EXACT_FIELDS, EXACT_FIELDS_IF_OK, FLOAT_FIELDS, FLOAT_FIELDS_IF_OK
@@ -24,7 +27,10 @@ def _close(a, b, rtol=RTOL, atol=0.0):
 # fields no FP64 threshold can move: counted straight from the entries (src/BaseVarC.cpp:548-608)
 HARD_FIELDS = ("n_entries", "depth", "cvg_strand", "cvg_alt_base", "cvg_fs", "cvg_sor")
 CHI_ATOL_PER_READ = 5e-11        # chi / var_qual: absolute floor per read of the site
-MAX_FLAGGED_FRACTION = 0.02      # a kernel that flags liberally would excuse itself: at most this share of the sites may carry a flag
+# a kernel that flagged liberally would excuse itself: at most this share of the sites may carry a flag (C2-like windows: ~1.7 %,
+# nearly all BVC_FLAG_ARGMIN_TIE -- two error bases with mirror-image evidence make two null models tie exactly) ...
+MAX_FLAGGED_FRACTION = 0.05
+MAX_EXCUSED_FRACTION = 0.002     # ... and at most this share may actually NEED the excuse (mismatch in a threshold-downstream field)
 
 
 def compare_records(got, want, allow_flagged=True, max_flagged_fraction=MAX_FLAGGED_FRACTION):
@@ -78,5 +84,33 @@ def compare_records(got, want, allow_flagged=True, max_flagged_fraction=MAX_FLAG
     if allow_flagged and n_flagged_bad:
         lines.append("%d mismatching sites carry a threshold-boundary flag (listed, not counted): %s" % (
             n_flagged_bad, np.nonzero(bad & flagged & ~bad_hard)[0][:20].tolist()))
+        # degenerate test tiles (one qual for every read) pass a larger max_flagged_fraction: they may need the excuse more often
+        allowed = max(3, MAX_EXCUSED_FRACTION * n_sites, 0.5 * max_flagged_fraction * n_sites if max_flagged_fraction > MAX_FLAGGED_FRACTION else 0)
+        if n_flagged_bad > allowed:
+            lines.append("too many sites need the threshold-boundary excuse (%d > %d)" % (n_flagged_bad, allowed))
+            return int(bad.sum()), lines
         bad &= ~(flagged & ~bad_hard)
     return int(bad.sum()), lines
+
+
+def oracle_threaded(oracle, tile, params, threads=None):
+    """The per-read oracle over every site of `tile` on the host's cores (ctypes drops the GIL; sites are independent)."""
+    threads = threads or min(32, os.cpu_count() or 1)
+    out = np.zeros(tile.n_sites, got_dtype(oracle))
+    bounds = np.linspace(0, tile.n_sites, threads + 1).astype(int)
+
+    def work(a, b):
+        if b > a:
+            out[a:b] = oracle.call_sites(tile, params, int(a), int(b))
+
+    ths = [threading.Thread(target=work, args=(bounds[i], bounds[i + 1])) for i in range(threads)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    return out
+
+
+def got_dtype(oracle):
+    from basevarc_b200._abi import SITE_RESULT_DTYPE
+    return SITE_RESULT_DTYPE
