@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libbvc_gpu.so")
 EXPORTS = (
     "bvc_device_count", "bvc_default_params", "bvc_create", "bvc_destroy", "bvc_last_error", "bvc_enqueue", "bvc_wait",
     "bvc_enqueue_split", "bvc_wait_split",
-    "bvc_fetch_groups", "bvc_host_alloc", "bvc_host_free", "bvc_resident_upload", "bvc_resident_run",
+    "bvc_fetch_groups", "bvc_host_alloc", "bvc_host_free", "bvc_host_register", "bvc_host_unregister", "bvc_resident_upload", "bvc_resident_run",
     "bvc_resident_download", "bvc_kernel_launch_count", "bvc_measure_fp64_peak", "bvc_kernel_name", "bvc_transfer_bytes", "bvc_work_counters",
     "bvc_shard_unique_id", "bvc_shard_init", "bvc_shard_call", "bvc_shard_upload", "bvc_shard_run", "bvc_shard_init_group",
     "bvc_shard_call_group", "bvc_shard_stats", "bvc_shard_phase_name",

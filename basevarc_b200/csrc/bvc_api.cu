@@ -474,6 +474,14 @@ void* bvc_host_alloc(size_t bytes)
 }
 void bvc_host_free(void* p) { if (p) cudaFreeHost(p); }
 
+int bvc_host_register(void* p, size_t bytes)
+{
+    if (!p || !bytes) return BVC_ERR_ARG;
+    if (cudaHostRegister(p, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped) != cudaSuccess) { cudaGetLastError(); return BVC_ERR_CUDA; }
+    return BVC_OK;
+}
+void bvc_host_unregister(void* p) { if (p && cudaHostUnregister(p) != cudaSuccess) cudaGetLastError(); }
+
 int bvc_resident_upload(bvc_ctx* ctx, const bvc_tile* tile)
 {
     if (!ctx) return BVC_ERR_ARG;

@@ -31,10 +31,19 @@ void Packer::clear()
 void Packer::reserve_entries(size_t need)
 {
     if (need <= cap_) return;
-    size_t c = cap_ ? cap_ : 4096;
+    size_t c = cap_ ? cap_ : (need > 4096 ? need : 4096);      // the first request is taken as given (Packer::reserve: fixed capacity)
     while (c < need) c *= 2;
     code_.resize(c); qual_.resize(c); mapq_.resize(c); rpr_.resize(c); smp_.resize(c); pk8_.resize(c);
     cap_ = c;
+}
+
+int Packer::buffers(const void** ptr, size_t* bytes, int max) const
+{
+    const void* p[6] = {code_.data(), qual_.data(), mapq_.data(), rpr_.data(), pk8_.data(), smp_.data()};
+    const size_t b[6] = {cap_, cap_, cap_, cap_, cap_, cap_ * sizeof(uint32_t)};
+    int n = 0;
+    for (int i = 0; i < 6 && n < max; ++i) if (p[i] && b[i]) { ptr[n] = p[i]; bytes[n] = b[i]; ++n; }
+    return n;
 }
 
 void Packer::begin_site(int32_t pos, uint8_t ref_base)

@@ -30,6 +30,13 @@ public:
     const char* indel(int64_t entry) const;
     const std::string& error() const { return err_; }
     int32_t n_samples() const { return n_samples_; }
+    // Fixed capacity: the per-entry arrays are sized once and never move afterwards, so the dispatcher can page-lock them
+    // (bvc_host_register) and the GPU library copies / reads them asynchronously.  buffers() lists them as (pointer, bytes).
+    void reserve(size_t entries) { reserve_entries(entries); }
+    size_t capacity() const { return cap_; }
+    int buffers(const void** ptr, size_t* bytes, int max) const;
+    // ---- packed tile files (packed_io.cc): a tile adopted from / dumped to the binary form of include/bvc_host.h
+    friend class PackedIo;
 
 private:
     int32_t n_samples_;

@@ -39,6 +39,7 @@
 #include "bgzf_io.hpp"
 #include "fasta.hpp"
 #include "format.hpp"
+#include "packed_io.hpp"
 #include "packer.hpp"
 
 namespace bvc_host {
@@ -60,7 +61,10 @@ const char* kUsage =
     "  --rerun,                 Read previous loaded data and rerun\n"
     "  --keep_tmp,              Don't remove tmp files when basetype finished\n"
     "  --gpus <INT>             GPUs to use [all visible; env BVC_GPUS]\n"
-    "  --tile_sites <INT>       Sites per GPU tile [auto]\n";
+    "  --tile_sites <INT>       Sites per GPU tile [auto]\n"
+    "  --pack                   Convert the text batch files into packed tile files (PREFIX.tmp.thread.{t}/packed.bvc; no GPU\n"
+    "                           needed); --rerun reads them instead of the text files whenever every window has one\n"
+    "  --no_packed              --rerun from the text batch files even if packed tile files exist\n";
 
 const char* kCvgHeader =
     "##fileformat=CVGv1.0\n"
@@ -89,6 +93,7 @@ const char* kVcfHeader =
 
 struct Options {
     bool rerun = false, load = false, keep_tmp = false, verbose = false;
+    bool pack = false, no_packed = false;      // --pack: text batch files -> packed tile files (no GPU); --no_packed: ignore packed files
     int mapq = 10, thread = 1, batch = 10, gpus = 0, tile_sites = 0;
     double maf = 0.001;
     std::string input, reference, group, region, output;
@@ -106,6 +111,7 @@ bool parse_options(int argc, char** argv, Options& o)
         {"maf", required_argument, nullptr, 'a'},     {"rerun", no_argument, nullptr, 8},
         {"load", no_argument, nullptr, 7},            {"keep_tmp", no_argument, nullptr, 6},
         {"gpus", required_argument, nullptr, 1},      {"tile_sites", required_argument, nullptr, 2},
+        {"pack", no_argument, nullptr, 3},            {"no_packed", no_argument, nullptr, 4},
         {nullptr, 0, nullptr, 0}};
     bool die = false;
     optind = 1;
@@ -127,6 +133,8 @@ bool parse_options(int argc, char** argv, Options& o)
         case 6: o.keep_tmp = true; break;
         case 1: o.gpus = atoi(a); break;
         case 2: o.tile_sites = atoi(a); break;
+        case 3: o.pack = true; break;
+        case 4: o.no_packed = true; break;
         case 'v': o.verbose = true; break;
         default: die = true;
         }
@@ -169,7 +177,12 @@ inline long long now_ns()
 struct TileJob {
     explicit TileJob(int32_t n_samples) : pk(n_samples) {}
     Packer pk;
-    std::vector<bvc_site_result> rec;
+    // result of a tile: the SPLIT form (bvc_enqueue_split: a 72-byte core per site + the full records of the LRT-positive sites)
+    // unless --group is on (its outputs hang off the full-record ticket)
+    std::vector<bvc_site_core> core;
+    std::vector<bvc_site_result> vcf;
+    int32_t n_vcf = 0;
+    std::vector<bvc_site_result> rec;      // full records (--group only)
     std::vector<int32_t> group_depth;      // [n_sites][n_groups][4]
     std::vector<double> group_af;
     std::mutex m;
@@ -198,6 +211,7 @@ public:
         cv_.notify_one();
         if (th_.joinable()) th_.join();
         if (ctx_) { launches_ = bvc_kernel_launch_count(ctx_); bvc_destroy(ctx_); ctx_ = nullptr; }
+        free_stages();
     }
     long long launches() const { return launches_; }
     long long create_ns() const { return create_ns_; }
@@ -205,12 +219,51 @@ public:
     int tiles() const { return tiles_; }
 
 private:
-    struct Flight { TileJob* job; uint64_t ticket; };
+    struct Flight { TileJob* job; uint64_t ticket; int stage; };
+    // Two page-locked staging sets, one per ticket in flight (allocated once, right after the context): a tile's arrays are
+    // copied in (a few MB at memcpy speed), so bvc_enqueue_split's transfers run asynchronously from pinned memory, mapq / rpr
+    // are read in place over PCIe at the LRT-positive sites only instead of being copied, and the results land in pinned
+    // memory -- the data path bench.py's `e2e` measures.  (Page-locking every window's own arrays instead -- cudaHostRegister of
+    // ~0.6 GB for 16 windows -- cost 0.65 s of a 1.4 s command.)  --group keeps the full-record path on the job's own arrays.
+    struct Stage {
+        uint8_t *pk8 = nullptr, *code = nullptr, *qual = nullptr, *mapq = nullptr, *rpr = nullptr, *ref = nullptr;
+        uint32_t* off = nullptr;
+        bvc_site_core* core = nullptr;
+        bvc_site_result* vcf = nullptr;
+    };
+    bool alloc_stages()
+    {
+        if (prm_.n_groups > 0 || getenv("BVC_NO_HOST_STAGING")) return true;
+        const size_t R = (size_t)prm_.max_entries + 64, S = (size_t)prm_.max_sites + 1;
+        for (Stage& st : stage_) {
+            st.pk8 = (uint8_t*)bvc_host_alloc(R); st.code = (uint8_t*)bvc_host_alloc(R); st.qual = (uint8_t*)bvc_host_alloc(R);
+            st.mapq = (uint8_t*)bvc_host_alloc(R); st.rpr = (uint8_t*)bvc_host_alloc(R); st.ref = (uint8_t*)bvc_host_alloc(S);
+            st.off = (uint32_t*)bvc_host_alloc((S + 1) * sizeof(uint32_t));
+            st.core = (bvc_site_core*)bvc_host_alloc(S * sizeof(bvc_site_core));
+            st.vcf = (bvc_site_result*)bvc_host_alloc(S * sizeof(bvc_site_result));
+            if (!st.pk8 || !st.code || !st.qual || !st.mapq || !st.rpr || !st.ref || !st.off || !st.core || !st.vcf) return false;
+        }
+        staged_ = true;
+        return true;
+    }
+    void free_stages()
+    {
+        for (Stage& st : stage_) {
+            bvc_host_free(st.pk8); bvc_host_free(st.code); bvc_host_free(st.qual); bvc_host_free(st.mapq); bvc_host_free(st.rpr);
+            bvc_host_free(st.ref); bvc_host_free(st.off); bvc_host_free(st.core); bvc_host_free(st.vcf);
+            st = Stage();
+        }
+    }
     void finish(const Flight& f)
     {
         const long long tb = now_ns();
-        int rc = bvc_wait(ctx_, f.ticket);
+        int rc = prm_.n_groups > 0 ? bvc_wait(ctx_, f.ticket) : bvc_wait_split(ctx_, f.ticket, &f.job->n_vcf);
         std::string err = rc == BVC_OK ? "" : bvc_last_error(ctx_);
+        if (rc == BVC_OK && staged_ && f.stage >= 0) {               // results home from the staging set
+            const Stage& st = stage_[f.stage];
+            memcpy(f.job->core.data(), st.core, (size_t)f.job->pk.n_sites() * sizeof(bvc_site_core));
+            if (f.job->n_vcf > 0) memcpy(f.job->vcf.data(), st.vcf, (size_t)f.job->n_vcf * sizeof(bvc_site_result));
+        }
         if (rc == BVC_OK && prm_.n_groups > 0 && f.job->pk.n_sites() > 0) {
             rc = bvc_fetch_groups(ctx_, f.ticket, f.job->group_depth.data(), f.job->group_af.data());
             if (rc != BVC_OK) err = bvc_last_error(ctx_);
@@ -223,9 +276,11 @@ private:
     {
         const long long tc0 = now_ns();
         const int rc0 = bvc_create(&ctx_, device_, &prm_);
+        int rc_stage = BVC_OK;
+        if (rc0 == BVC_OK && !alloc_stages()) rc_stage = BVC_ERR_CUDA;
         create_ns_ = now_ns() - tc0;
-        if (rc0 != BVC_OK) {
-            init_err_ = std::string("GPU ") + std::to_string(device_) + ": " + bvc_last_error(nullptr);
+        if (rc0 != BVC_OK || rc_stage != BVC_OK) {
+            init_err_ = std::string("GPU ") + std::to_string(device_) + ": " + (rc0 != BVC_OK ? bvc_last_error(nullptr) : "cannot allocate the page-locked staging buffers");
             for (;;) {                                         // fail whatever is submitted until stop()
                 TileJob* j = nullptr;
                 {
@@ -234,7 +289,7 @@ private:
                     if (q_.empty()) return;
                     j = q_.front(); q_.pop_front();
                 }
-                { std::lock_guard<std::mutex> lk(j->m); j->rc = rc0; j->err = init_err_; j->done = true; }
+                { std::lock_guard<std::mutex> lk(j->m); j->rc = rc0 != BVC_OK ? rc0 : rc_stage; j->err = init_err_; j->done = true; }
                 j->cv.notify_all();
             }
         }
@@ -256,17 +311,33 @@ private:
                 if (prm_.n_groups == 0) t.sample = nullptr;
                 uint64_t tk = 0;
                 const long long tb = now_ns();
-                const int rc = bvc_enqueue(ctx_, &t, j->rec.data(), &tk);
+                int stage = -1, rc;
+                if (prm_.n_groups > 0) rc = bvc_enqueue(ctx_, &t, j->rec.data(), &tk);
+                else if (!staged_) rc = bvc_enqueue_split(ctx_, &t, j->core.data(), j->vcf.data(), (int32_t)j->vcf.size(), &tk);
+                else {
+                    stage = (int)(n_enq_++ & 1);                     // at most two tickets in flight: the older one's set is free again
+                    Stage& st = stage_[stage];
+                    const size_t S = (size_t)t.n_sites, R = t.n_sites > 0 ? (size_t)t.entry_off[S] : 0;
+                    memcpy(st.ref, t.ref_base, S); memcpy(st.off, t.entry_off, (S + 1) * sizeof(uint32_t));
+                    memcpy(st.mapq, t.mapq, R); memcpy(st.rpr, t.rpr, R);
+                    if (t.packed8) { memcpy(st.pk8, t.packed8, R); t.packed8 = st.pk8; t.code = nullptr; t.qual = nullptr; }
+                    else { memcpy(st.code, t.code, R); memcpy(st.qual, t.qual, R); t.code = st.code; t.qual = st.qual; }
+                    t.ref_base = st.ref; t.entry_off = st.off; t.mapq = st.mapq; t.rpr = st.rpr;
+                    rc = bvc_enqueue_split(ctx_, &t, st.core, st.vcf, prm_.max_sites, &tk);
+                }
                 busy_ns_ += now_ns() - tb;
                 if (rc != BVC_OK) {
                     { std::lock_guard<std::mutex> lk(j->m); j->rc = rc; j->err = bvc_last_error(ctx_); j->done = true; }
                     j->cv.notify_all();
-                } else fly.push_back({j, tk});
+                } else fly.push_back({j, tk, stage});
             } else if (!fly.empty()) { finish(fly.front()); fly.pop_front(); }
         }
     }
     int device_;
     bvc_params prm_;
+    Stage stage_[2];
+    bool staged_ = false;
+    unsigned n_enq_ = 0;
     bvc_ctx* ctx_ = nullptr;
     std::thread th_;
     std::mutex m_;
@@ -285,6 +356,8 @@ struct Shared {
     long long rg_s = 0;
     std::vector<int32_t> pv;
     int32_t N = 0, nb = 0, tile_sites = 0;
+    bool packed_in = false;                 // the windows are read from packed tile files (PREFIX.tmp.thread.{t}/packed.bvc)
+    std::string sams;                       // sample names, tab-separated (with --pack: stored in every packed file)
     int64_t tile_entries = 0;
     int n_groups = 0;
     std::vector<std::string> group_names;
@@ -307,14 +380,25 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
     const int T = o.thread;
     std::vector<std::unique_ptr<BgzfReader>> in;
     std::vector<std::string> names;
-    for (int j = 0; j < sh->nb; ++j) {
-        names.push_back(o.output + ".tmp.thread." + std::to_string(ithread) + "/batch." + std::to_string(j));
-        in.emplace_back(new BgzfReader());
-        std::string e;
-        if (!in.back()->open(names.back(), &e)) { sh->fail(e); return; }
-    }
+    const std::string dir = o.output + ".tmp.thread." + std::to_string(ithread);
+    PackedIo pin, pout;                                      // packed tiles in (instead of the text files) / out (--pack)
     std::string line;
-    for (auto& r : in) r->getline(line);                     // sample-name lines (header is built by the caller)
+    if (sh->packed_in) {
+        std::string e;
+        if (!pin.open(dir + "/packed.bvc", &e)) { sh->fail(e); return; }
+    } else {
+        for (int j = 0; j < sh->nb; ++j) {
+            names.push_back(dir + "/batch." + std::to_string(j));
+            in.emplace_back(new BgzfReader());
+            std::string e;
+            if (!in.back()->open(names.back(), &e)) { sh->fail(e); return; }
+        }
+        for (auto& r : in) r->getline(line);                 // sample-name lines (header is built by the caller)
+    }
+    if (o.pack) {
+        std::string e;
+        if (!pout.create(dir + "/packed.bvc.tmp", sh->N, sh->sams, &e)) { sh->fail(e); return; }
+    }
     BgzfWriter wv, wc;
     wv.open_memory(); wc.open_memory();
     if (ithread == 0) { wv.write(sh->headvcf); wc.write(sh->headcvg); }
@@ -326,12 +410,27 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
     const size_t it_end = (ithread == T - 1) ? P : std::min(P, (size_t)(ithread + 1) * window);
 
     TileJob jobs[2] = {TileJob(sh->N), TileJob(sh->N)};
+    for (auto& j : jobs) {
+        // fixed capacity (a tile is flushed before it can outgrow it): no reallocation while a window is packed
+        j.pk.reserve((size_t)sh->tile_entries + 2 * (size_t)sh->N + 64);
+        if (sh->n_groups == 0) { j.core.resize((size_t)sh->tile_sites + 1); j.vcf.resize((size_t)sh->tile_sites + 1); }
+    }
     // the two packers share ONE stale-token state in the reference (a single `ai` per window): hand it over by
     // packing strictly in site order and copying the state forward (Packer::adopt_state)
     int cur = 0, count = 0;
     long long t_read = 0, t_pack = 0, t_wait = 0, t_format = 0, t_write = 0;
     bool pending[2] = {false, false};
     std::string vline, cline;
+    // whatever way this function is left, no job may still be queued or in flight in the dispatcher: it writes the job's
+    // records, status and condition variable, and bvc_enqueue's device-to-host copies target the job's arrays
+    struct PendingGuard {
+        TileJob* jobs; bool* pending;
+        ~PendingGuard()
+        {
+            for (int k = 0; k < 2; ++k)
+                if (pending[k]) { std::unique_lock<std::mutex> lk(jobs[k].m); jobs[k].cv.wait(lk, [&] { return jobs[k].done; }); pending[k] = false; }
+        }
+    } guard{jobs, pending};
 
     auto drain = [&](int k) -> bool {                         // wait for job k, format its sites, release it
         TileJob& j = jobs[k];
@@ -344,8 +443,26 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
         j.pk.tile(&t);
         const int32_t* pos = j.pk.positions();
         const int G = sh->n_groups;
+        bvc_site_result full;
         for (int32_t s = 0; s < j.pk.n_sites(); ++s) {
-            const bvc_site_result* r = &j.rec[(size_t)s];
+            const bvc_site_result* r;
+            if (G) r = &j.rec[(size_t)s];
+            else {
+                // split result: the full record of an LRT-positive site is in vcf[], every other site's VCF half is zero
+                const bvc_site_core& c = j.core[(size_t)s];
+                if (c.lrt_ok) {
+                    if (c.vcf_index < 0 || c.vcf_index >= j.n_vcf) { sh->fail("GPU call returned an inconsistent split result"); return false; }
+                    r = &j.vcf[(size_t)c.vcf_index];
+                } else {
+                    memset(&full, 0, sizeof full);
+                    full.cvg_fs = c.cvg_fs; full.cvg_sor = c.cvg_sor; full.n_entries = c.n_entries;
+                    for (int b = 0; b < 4; ++b) { full.depth[b] = c.depth[b]; full.cvg_strand[b] = c.cvg_strand[b]; }
+                    full.em_fits = c.em_fits; full.em_passes = c.em_passes; full.flags = c.flags;
+                    full.cvg_alt_base = c.cvg_alt_base; full.n_alt = c.n_alt;
+                    full.alt_bases[0] = full.alt_bases[1] = full.alt_bases[2] = -1;
+                    r = &full;
+                }
+            }
             const int32_t* gd = G ? &j.group_depth[(size_t)s * G * 4] : nullptr;
             const double* ga = G ? &j.group_af[(size_t)s * G * 4] : nullptr;
             const long long t0 = now_ns();
@@ -361,8 +478,8 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
     };
     auto flush = [&](int k) {                                 // hand job k to the GPU
         TileJob& j = jobs[k];
-        j.rec.resize((size_t)j.pk.n_sites());
         if (sh->n_groups) {
+            j.rec.resize((size_t)j.pk.n_sites());
             j.group_depth.assign((size_t)j.pk.n_sites() * sh->n_groups * 4, 0);
             j.group_af.assign((size_t)j.pk.n_sites() * sh->n_groups * 4, 0.0);
         }
@@ -371,42 +488,74 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
         gpu->submit(&j);
     };
 
-    for (; it < it_end && !sh->failed; ++it) {
-        TileJob& j = jobs[cur];
-        const int32_t p = sh->pv[it];
-        const int rb = base_code(sh->refseq[(size_t)(p - sh->rg_s)]);
-        j.pk.begin_site(p, (uint8_t)rb);
-        for (auto& r : in) {
-            const char* lp; size_t ln;
-            const long long t0 = now_ns();
-            const bool got = r->getline_view(&lp, &ln);
-            const long long t1 = now_ns();
-            t_read += t1 - t0;
-            if (got) {
-                if (j.pk.add_line(lp, ln) != BVC_OK) { sh->fail(j.pk.error()); return; }
-                t_pack += now_ns() - t1;
-            } else if (r->failed()) { sh->fail("corrupt batch file: " + r->error()); return; }
+    // one tile into job k: sites of the window until the tile is full or the window ends.  1: more input may follow, 0: the
+    // window is exhausted, -1: error (reported)
+    auto fill_text = [&](TileJob& j) -> int {
+        for (; it < it_end; ++it) {
+            const int32_t p = sh->pv[it];
+            const int rb = base_code(sh->refseq[(size_t)(p - sh->rg_s)]);
+            j.pk.begin_site(p, (uint8_t)rb);
+            for (auto& r : in) {
+                const char* lp; size_t ln;
+                const long long t0 = now_ns();
+                const bool got = r->getline_view(&lp, &ln);
+                const long long t1 = now_ns();
+                t_read += t1 - t0;
+                if (got) {
+                    if (j.pk.add_line(lp, ln) != BVC_OK) { sh->fail(j.pk.error()); return -1; }
+                    t_pack += now_ns() - t1;
+                } else if (r->failed()) { sh->fail("corrupt batch file: " + r->error()); return -1; }
+            }
+            if (j.pk.end_site() == 0) j.pk.drop_last_site();  // no entries: the reference prints nothing (:442)
+            if (j.pk.n_sites() >= sh->tile_sites || j.pk.n_entries() + sh->N > sh->tile_entries) { ++it; return 1; }
         }
-        if (j.pk.end_site() == 0) j.pk.drop_last_site();      // no entries: the reference prints nothing (:442)
-        if (j.pk.n_sites() >= sh->tile_sites || j.pk.n_entries() + sh->N > sh->tile_entries) {
-            flush(cur);
-            const int other = cur ^ 1;
-            if (pending[other] && !drain(other)) return;
-            jobs[other].pk.clear();
-            jobs[other].pk.adopt_state(jobs[cur].pk);
-            cur = other;
+        return 0;
+    };
+    auto fill_packed = [&](TileJob& j) -> int {
+        std::string e;
+        const long long t0 = now_ns();
+        const int rc = pin.next_tile(j.pk, &e);
+        t_read += now_ns() - t0;
+        if (rc < 0) sh->fail(e);
+        return rc;
+    };
+    if (o.pack) {
+        // --pack: the same read + tokenise loop, the tiles go to PREFIX.tmp.thread.{t}/packed.bvc instead of the GPU
+        TileJob& j = jobs[0];
+        for (int more = 1; more > 0 && !sh->failed;) {
+            more = fill_text(j);
+            if (more < 0) return;
+            std::string e;
+            if (j.pk.n_sites() > 0 && !pout.add_tile(j.pk, &e)) { sh->fail(e); return; }
+            j.pk.clear();                                      // keeps the stale-token state (Q1)
         }
+        std::string e;
+        if (!pout.finish(&e) || rename((dir + "/packed.bvc.tmp").c_str(), (dir + "/packed.bvc").c_str()) != 0) { sh->fail(e.empty() ? "cannot rename packed.bvc.tmp" : e); return; }
+        sh->ns_read += t_read; sh->ns_pack += t_pack;
+        return;
     }
-    if (sh->failed) { for (int k = 0; k < 2; ++k) if (pending[k]) { std::unique_lock<std::mutex> lk(jobs[k].m); jobs[k].cv.wait(lk, [&] { return jobs[k].done; }); } return; }
-    if (jobs[cur].pk.n_sites() > 0) flush(cur);
-    // drain in submission order: the job submitted first is the one that is not `cur` (if still pending)
-    if (pending[cur ^ 1] && !drain(cur ^ 1)) return;
-    if (pending[cur] && !drain(cur)) return;
+    for (int more = 1; more > 0 && !sh->failed;) {
+        TileJob& j = jobs[cur];
+        more = sh->packed_in ? fill_packed(j) : fill_text(j);
+        if (more < 0) return;
+        if (j.pk.n_sites() == 0) continue;
+        flush(cur);
+        const int other = cur ^ 1;
+        if (pending[other] && !drain(other)) return;
+        jobs[other].pk.clear();
+        jobs[other].pk.adopt_state(jobs[cur].pk);
+        cur = other;
+    }
+    if (sh->failed) return;                                   // (the guard waits for what is still in flight)
+    if (pending[cur ^ 1] && !drain(cur ^ 1)) return;          // the tile submitted last
     { const long long t0 = now_ns(); wv.close(false); wc.close(false); t_write += now_ns() - t0; }
     sh->ns_read += t_read; sh->ns_pack += t_pack; sh->ns_wait += t_wait; sh->ns_format += t_format; sh->ns_write += t_write;
     *vcf_out = std::move(wv.memory());
     *cvg_out = std::move(wc.memory());
-    if (!o.keep_tmp) for (auto& n : names) remove(n.c_str());  // src/BaseVarC.cpp:458-462
+    if (!o.keep_tmp) {                                         // src/BaseVarC.cpp:458-462
+        for (auto& n : names) remove(n.c_str());
+        if (sh->packed_in) remove((dir + "/packed.bvc").c_str());
+    }
 }
 
 }  // namespace
@@ -457,12 +606,19 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
         std::cerr << "ERROR: --thread " << T << " does not partition " << sh.pv.size() << " sites (the reference reads past its site list here)" << std::endl;
         return EXIT_FAILURE;
     }
+    // packed tile files (written by --pack or by a --load patched as INTEGRATION.md shows): when every window
+    // has a complete one for this cohort they are read instead of the text batch files -- no inflate, no tokeniser
+    if (!o.no_packed && !o.pack) {
+        int npk = 0;
+        for (int i = 0; i < T; ++i) if (PackedIo::is_complete(o.output + ".tmp.thread." + std::to_string(i) + "/packed.bvc", sh.N)) ++npk;
+        sh.packed_in = npk == T;
+    }
     // batch files: all T x nb must be complete BGZF files (src/BaseVarC.cpp:214-233)
     int ngz = 0;
-    for (int j = 0; j < sh.nb; ++j)
+    for (int j = 0; j < sh.nb && !sh.packed_in; ++j)
         for (int i = 0; i < T; ++i)
             if (bgzf_is_complete(o.output + ".tmp.thread." + std::to_string(i) + "/batch." + std::to_string(j))) ++ngz;
-    if (ngz != T * sh.nb) {
+    if (!sh.packed_in && ngz != T * sh.nb) {
         std::cerr << "ERROR: " << ngz << " of " << T * sh.nb << " batch files are complete under " << o.output
                   << ".tmp.thread.*; BAM decoding stays with the reference: run `BaseVarC basetype --load` with the same -t/-b first" << std::endl;
         return EXIT_FAILURE;
@@ -472,12 +628,25 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
 
     // sample names = first line of every batch file of window 0, concatenated (src/BaseVarC.cpp:333-338)
     std::string sams;
-    for (int j = 0; j < sh.nb; ++j) {
-        BgzfReader r; std::string l;
-        if (!r.open(o.output + ".tmp.thread.0/batch." + std::to_string(j), &err)) { std::cerr << "ERROR: " << err << std::endl; return EXIT_FAILURE; }
-        if (r.getline(l)) sams += l;
+    int64_t packed_sites = 0, packed_entries = 0;
+    if (sh.packed_in) {
+        for (int i = 0; i < T; ++i) {
+            PackedIo r;
+            if (!r.open(o.output + ".tmp.thread." + std::to_string(i) + "/packed.bvc", &err)) { std::cerr << "ERROR: " << err << std::endl; return EXIT_FAILURE; }
+            if (i == 0) sams = r.names();
+            packed_sites = std::max<int64_t>(packed_sites, r.header().max_sites);
+            packed_entries = std::max<int64_t>(packed_entries, (int64_t)r.header().max_entries);
+        }
+        std::cerr << "reading packed tile files (" << o.output << ".tmp.thread.*/packed.bvc) instead of the text batch files" << std::endl;
+    } else {
+        for (int j = 0; j < sh.nb; ++j) {
+            BgzfReader r; std::string l;
+            if (!r.open(o.output + ".tmp.thread.0/batch." + std::to_string(j), &err)) { std::cerr << "ERROR: " << err << std::endl; return EXIT_FAILURE; }
+            if (r.getline(l)) sams += l;
+        }
+        if (!sams.empty()) sams.pop_back();
     }
-    if (!sams.empty()) sams.pop_back();
+    sh.sams = sams;
     // population groups (src/BaseVarC.cpp:340-370): std::map order = sorted group names
     std::vector<int32_t> sample_group((size_t)sh.N, -1);
     sh.headcvg = kCvgHeader; sh.headvcf = kVcfHeader;
@@ -504,6 +673,19 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     sh.headvcf += "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\t" + sams + "\n";
     sh.headcvg += "\n";
 
+    if (o.pack) {
+        // text batch files -> packed tile files, one per window; no GPU involved
+        sh.tile_sites = o.tile_sites > 0 ? o.tile_sites : (int32_t)std::max<int64_t>(64, std::min<int64_t>(2048, ((int64_t)8 << 20) / sh.N));
+        sh.tile_entries = std::max<int64_t>((int64_t)sh.tile_sites * sh.N, 2 * (int64_t)sh.N);
+        std::vector<std::string> none((size_t)T);
+        std::vector<std::thread> packers;
+        for (int i = 0; i < T; ++i) packers.emplace_back(window_worker, &sh, nullptr, i, &none[(size_t)i], &none[(size_t)i]);
+        for (auto& w : packers) w.join();
+        devices.wait();
+        if (sh.failed) { std::cerr << "ERROR: " << sh.err << std::endl; return EXIT_FAILURE; }
+        std::cout << "basetype packing done -- " << now_string();
+        return EXIT_SUCCESS;
+    }
     // tile geometry and one dispatcher per GPU
     const auto dev = devices.get();
     const int n_dev = dev.first;
@@ -515,6 +697,7 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     // window; the context's buffers (sized by max_entries) stay small, which keeps its creation short.
     sh.tile_sites = o.tile_sites > 0 ? o.tile_sites : (int32_t)std::max<int64_t>(64, std::min<int64_t>(2048, ((int64_t)8 << 20) / sh.N));
     sh.tile_entries = std::max<int64_t>((int64_t)sh.tile_sites * sh.N, 2 * (int64_t)sh.N);
+    if (sh.packed_in) { sh.tile_sites = (int32_t)std::max<int64_t>(1, packed_sites); sh.tile_entries = std::max<int64_t>(packed_entries, 2 * (int64_t)sh.N); }
     bvc_params prm;
     bvc_default_params(&prm, sh.N, o.maf);
     prm.max_sites = sh.tile_sites;

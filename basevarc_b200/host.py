@@ -22,6 +22,8 @@ HOST_EXPORTS = (
     "bvc_packer_create", "bvc_packer_destroy", "bvc_packer_clear", "bvc_packer_begin_site", "bvc_packer_add_line",
     "bvc_packer_end_site", "bvc_packer_n_sites", "bvc_packer_n_entries", "bvc_packer_tile", "bvc_packer_positions",
     "bvc_packer_indel", "bvc_packer_error", "bvc_format_cvg", "bvc_format_vcf", "bvc_format_fixed", "bvc_basetype_main", "bvc_write_batch_files",
+    "bvc_packed_open", "bvc_packed_next", "bvc_packed_names", "bvc_packed_error", "bvc_packed_close", "bvc_packed_is_complete",
+    "bvc_write_packed_files",
 )
 
 _hlib = None
@@ -68,6 +70,17 @@ def load_host_library():
     L.bvc_format_fixed.restype = C.c_size_t
     L.bvc_basetype_main.argtypes = [C.c_int, C.POINTER(C.c_char_p)]
     L.bvc_write_batch_files.argtypes = [C.POINTER(Tile), C.c_int32, C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_char_p]
+    L.bvc_packed_open.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int64)]
+    L.bvc_packed_open.restype = C.c_void_p
+    L.bvc_packed_next.argtypes = [C.c_void_p, C.c_void_p]
+    L.bvc_packed_names.argtypes = [C.c_void_p]
+    L.bvc_packed_names.restype = C.c_char_p
+    L.bvc_packed_error.argtypes = [C.c_void_p]
+    L.bvc_packed_error.restype = C.c_char_p
+    L.bvc_packed_close.argtypes = [C.c_void_p]
+    L.bvc_packed_close.restype = None
+    L.bvc_packed_is_complete.argtypes = [C.c_char_p, C.c_int32]
+    L.bvc_write_packed_files.argtypes = [C.POINTER(Tile), C.c_int32, C.c_void_p, C.c_char_p, C.c_int32, C.c_int32, C.c_char_p]
     _hlib = L
     return L
 
@@ -183,3 +196,40 @@ def write_batch_files(tile, prefix, threads, batch, level=1, indel_token="+A"):
                                  indel_token.encode())
     if rc != 0:
         raise BvcError("bvc_write_batch_files failed (%d): bad (sites, threads) partition or unwritable prefix" % rc)
+
+
+def write_packed_files(tile, prefix, threads, tile_sites=2048, indel_token="+A"):
+    """bvc_write_packed_files: a tile as packed tile files (include/bvc_host.h), one per window; sites numbered by tile.pos."""
+    L = load_host_library()
+    os.makedirs(os.path.dirname(os.path.abspath(prefix)), exist_ok=True)
+    ct = tile.as_ctypes(with_sample=True)
+    pos = np.ascontiguousarray(tile.pos, np.int32)
+    rc = L.bvc_write_packed_files(C.byref(ct), tile.n_samples, pos.ctypes.data, prefix.encode(), int(threads), int(tile_sites),
+                                  indel_token.encode())
+    if rc != 0:
+        raise BvcError("bvc_write_packed_files failed (%d)" % rc)
+
+
+def read_packed_file(path):
+    """Every tile of a packed tile file: (sample names, [(positions, PileupTile, {entry: indel text})])."""
+    L = load_host_library()
+    n, nt, ms, me = C.c_int32(0), C.c_int32(0), C.c_int32(0), C.c_int64(0)
+    r = L.bvc_packed_open(path.encode(), C.byref(n), C.byref(nt), C.byref(ms), C.byref(me))
+    if not r:
+        raise BvcError("cannot open packed tile file %s" % path)
+    names = L.bvc_packed_names(r).decode()
+    pk = Packer(n.value)
+    out = []
+    try:
+        while True:
+            rc = L.bvc_packed_next(r, pk.h)
+            if rc == 0:
+                break
+            if rc < 0:
+                raise BvcError(L.bvc_packed_error(r).decode())
+            t = pk.to_tile()
+            out.append((np.array(t.pos, copy=True), t, dict(t.indel_text)))
+    finally:
+        L.bvc_packed_close(r)
+        pk.close()
+    return names, out

@@ -172,6 +172,10 @@ int  bvc_fetch_groups(bvc_ctx* ctx, uint64_t ticket, int32_t* group_depth, doubl
 /* Pinned host allocation helpers (cudaHostAlloc / cudaFreeHost). */
 void* bvc_host_alloc(size_t bytes);
 void  bvc_host_free(void* p);
+/* Page-lock caller-owned memory in place (cudaHostRegister / cudaHostUnregister): what the dispatcher does with a packer's
+ * arrays once, so bvc_enqueue's copies are asynchronous and mapq / rpr are read in place.  0, or BVC_ERR_CUDA. */
+int   bvc_host_register(void* p, size_t bytes);
+void  bvc_host_unregister(void* p);
 
 /* Device-resident path, used by bench.py for the kernel-only figure: upload once, run many times.
  * bvc_resident_run launches the site kernels `iters` times on the context's stream, optionally

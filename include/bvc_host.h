@@ -74,6 +74,36 @@ size_t bvc_format_fixed(char* buf, size_t cap, double v, int32_t digits);
 int bvc_write_batch_files(const bvc_tile* tile, int32_t n_samples, const char* prefix, int32_t threads, int32_t batch,
                           int32_t level, const char* indel_token);
 
+/* ---- packed tile files: the binary packed batch format ---------------------------------------
+ * The reference's `--load` writes one text token per (site, sample) into BGZF batch files (src/BaseVarC.cpp:509-527)
+ * and every `--rerun` inflates and tokenises them again (:403-441).  A packed file holds the same information as
+ * ready-made tiles in the structure-of-arrays form the GPU library takes, so a rerun reads arrays straight into
+ * page-locked buffers.  One file per reference thread directory: PREFIX.tmp.thread.{t}/packed.bvc, written by
+ * `BaseVarC_b200 basetype --pack` (from the text batch files, no GPU needed), by bvc_write_packed_files (fixtures), or
+ * by a `--load` patched as INTEGRATION.md shows; `--rerun` reads them whenever every window has a complete one
+ * (`--no_packed` forces the text files).  Little-endian; every array padded to 16 bytes:
+ *   file header (64 B): "BVCPACK1", version = 1, n_samples, n_tiles (written LAST: 0 = incomplete), max_sites,
+ *                       max_entries (u64), names_bytes; then the window's sample names, tab-separated
+ *   per tile:  header (64 B): "TILE", n_sites S, n_entries R, n_dict, n_indel, indel_bytes, qual dictionary [32]
+ *              pos i32[S] | ref_base u8[S] | entry_off u32[S+1] | covered-sample bitmap u8[S][ceil(N/8)]
+ *              (entries of a site are in ascending sample order, so N bits replace a 4-byte sample index per entry)
+ *              packed8 u8[R] (n_dict > 0; BVC_PACK8) or code u8[R] + qual u8[R] (n_dict == 0: > 30 distinct quals)
+ *              mapq u8[R] | rpr u8[R]
+ *              indel entries: index u32[n_indel] | stale qual u8[n_indel] | text offsets u32[n_indel+1] | token text
+ * 3.0 B per entry + N/8 B per site against ~14 B of text per token. */
+typedef struct bvc_packed_reader bvc_packed_reader;
+bvc_packed_reader* bvc_packed_open(const char* path, int32_t* n_samples, int32_t* n_tiles, int32_t* max_sites, int64_t* max_entries);
+/* Replaces the packer's sites with the next tile: 1, 0 at the end of the file, -1 on a corrupt file (bvc_packed_error). */
+int  bvc_packed_next(bvc_packed_reader* r, bvc_packer* into);
+const char* bvc_packed_names(const bvc_packed_reader* r);
+const char* bvc_packed_error(const bvc_packed_reader* r);
+void bvc_packed_close(bvc_packed_reader* r);
+int  bvc_packed_is_complete(const char* path, int32_t n_samples);
+/* A tile -> PREFIX.tmp.thread.{t}/packed.bvc for t < threads (window partition of src/BaseVarC.cpp:399-403), tiles of
+ * tile_sites sites; pos [n_sites] (NULL: 1, 2, ...); samples named S0..S{N-1}; tile->sample, code and qual are required. */
+int  bvc_write_packed_files(const bvc_tile* tile, int32_t n_samples, const int32_t* pos, const char* prefix, int32_t threads,
+                            int32_t tile_sites, const char* indel_token);
+
 /* ---- the command: `BaseVarC basetype --rerun ...` with the compute phase on the GPU(s) ----------------------
  * argv as the reference's runBaseType sees it (argv[0] = "basetype").  Returns the process exit status. */
 int bvc_basetype_main(int argc, char** argv);
