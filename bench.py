@@ -24,8 +24,11 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# NCCL prints its version banner on STDOUT at the VERSION and WARN debug levels: the contract is ONE JSON line there
-os.environ["NCCL_DEBUG"] = os.environ.get("BVC_NCCL_DEBUG", "NONE")
+# NCCL prints its banner on STDOUT at the VERSION and WARN debug levels (the contract is ONE JSON line there), so its log goes
+# to a FILE per process at INFO level: the communicator lines ("... nranks N ...") are then observable (comm_nranks below)
+NCCL_LOG = os.path.join(os.environ.get("BVC_NCCL_LOG_DIR", "/tmp"), "bvc_nccl_%d_%%h_%%p.log" % os.getpid())
+os.environ["NCCL_DEBUG"] = os.environ.get("BVC_NCCL_DEBUG", "INFO")        # (the image presets NCCL_DEBUG=VERSION)
+os.environ["NCCL_DEBUG_FILE"] = os.environ.get("BVC_NCCL_DEBUG_FILE", NCCL_LOG)
 
 METRIC = "site*samples/sec for basetype EM+LRT"
 # FP64 operations per unit of work, FMA = 2, counted on the code that ships:
@@ -99,6 +102,89 @@ class ClockSampler:
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def nccl_ranks_seen():
+    """(max nranks in this process's NCCL log, whether NVLS shows up) -- None when no communicator line was logged."""
+    import glob
+    import re
+    pat = os.environ.get("NCCL_DEBUG_FILE", NCCL_LOG).replace("%h", "*").replace("%p", "*")
+    best, nvls = None, False
+    for fn in glob.glob(pat):
+        try:
+            with open(fn, errors="replace") as f:
+                txt = f.read()
+        except OSError:
+            continue
+        for m in re.finditer(r"nranks (\d+)", txt):
+            best = max(best or 0, int(m.group(1)))
+        nvls = nvls or ("NVLS" in txt)
+    return best, nvls
+
+
+def bind_rank_to_cores(local, world):
+    """Give every rank of the node its own slice of the host cores that are local to its GPU (sysfs local_cpulist of the GPU's
+    PCI function), before any pinned buffer is allocated (first touch).  Returns a description for the JSON line."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local)
+        bdf = "%04x:%02x:%02x.0" % (getattr(pr, "pci_domain_id", 0), pr.pci_bus_id, pr.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/local_cpulist" % bdf) as f:
+            txt = f.read().strip()
+        cpus = []
+        for part in txt.split(","):
+            a, _, b = part.partition("-")
+            cpus += list(range(int(a), int(b or a) + 1))
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0))) or sorted(os.sched_getaffinity(0))
+        share = max(1, len(allowed) // max(world, 1))
+        mine = allowed[(local * share) % len(allowed):][:share] or allowed
+        os.sched_setaffinity(0, mine)
+        numa = None
+        try:
+            with open("/sys/bus/pci/devices/%s/numa_node" % bdf) as f:
+                numa = int(f.read())
+        except (OSError, ValueError):
+            pass
+        return {"gpu_pci": bdf, "gpu_local_cpulist": txt, "gpu_numa_node": numa, "bound_to": "%d-%d" % (mine[0], mine[-1]), "n_cores": len(mine)}
+    except Exception as e:                      # no sysfs / not permitted: unbound, and say so
+        return {"bound_to": None, "why": repr(e)[:120]}
+
+
+def copy_probe(local, nbytes_h2d, nbytes_d2h, barrier, reps=5):
+    """Copy-only probe of the e2e leg's link: the same number of bytes, page-locked host memory, cudaMemcpyAsync only, all ranks
+    at once.  Returns (H2D GB/s, D2H GB/s, both directions at once GB/s each) of THIS rank (events on the copy streams)."""
+    import torch
+    dev = torch.device("cuda", local)
+    h_in = torch.empty(nbytes_h2d, dtype=torch.uint8).pin_memory()
+    d_in = torch.empty(nbytes_h2d, dtype=torch.uint8, device=dev)
+    d_out = torch.empty(max(nbytes_d2h, 1), dtype=torch.uint8, device=dev)
+    h_out = torch.empty(max(nbytes_d2h, 1), dtype=torch.uint8).pin_memory()
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def timed(do_in, do_out):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(s1):
+            e0.record()
+            for _ in range(reps if do_in else 0):
+                d_in.copy_(h_in, non_blocking=True)
+            e1.record()
+        with torch.cuda.stream(s2):
+            f0.record()
+            for _ in range(reps if do_out else 0):
+                h_out.copy_(d_out, non_blocking=True)
+            f1.record()
+        torch.cuda.synchronize(dev)
+        gi = reps * nbytes_h2d / (e0.elapsed_time(e1) * 1e-3) / 1e9 if do_in else None
+        go = reps * nbytes_d2h / (f0.elapsed_time(f1) * 1e-3) / 1e9 if do_out else None
+        return gi, go
+
+    timed(True, True)                           # warm-up
+    h2d, _ = timed(True, False)
+    _, d2h = timed(False, True)
+    bi, bo = timed(True, True)
+    return {"h2d_gbs": h2d, "d2h_gbs": d2h, "both_h2d_gbs": bi, "both_d2h_gbs": bo}
 
 
 def _workload(name, n_sites, rank):
@@ -294,7 +380,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
-def run_sharded(args):
+def run_sharded(args, return_line=False):
     """--workload C4: the SAMPLE-SHARDED path.  Every rank holds its own sample range of the same
     window; per tile one reduce-scatter of integer histograms + all-gather + all-reduce over NCCL.  Total work is
     fixed (100,000 samples), so scaling is "strong"."""
@@ -337,7 +423,8 @@ def run_sharded(args):
     dist.broadcast_object_list(uid, src=0)
     qlo, qhi = args.qual_window
     caller = B.ShardedCaller(N, rank, world, uid[0], qual_lo=qlo, qual_hi=qhi, device=local, max_sites=S, max_entries=max(R, 1))
-    units = S * N                                   # whole job: every rank works on the same S sites x N samples
+    passes = 1 if not args.window_sites else max(1, -(-args.window_sites // S))      # the whole window = passes x the resident tile
+    units = S * N * passes                          # whole job: every rank works on the same sites x N samples
 
     # ---- resident leg: local entries already in HBM; device events per phase (max over ranks of the step time) ----
     caller.shard_upload(tile)
@@ -350,7 +437,7 @@ def run_sharded(args):
     l0 = caller.kernel_launches
     t0 = time.perf_counter()
     phases = {}
-    for _ in range(args.steps):
+    for _ in range(args.steps * passes):
         first, recs = caller.shard_run()
         st = caller.shard_stats()
         for k, v in st["phase_ms"].items():
@@ -378,7 +465,7 @@ def run_sharded(args):
     h2d0, d2h0 = caller.transfer_bytes
     x0 = caller.shard_stats()["exchange_bytes"]
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(args.steps * passes):
         first2, recs2 = caller.shard_call(tile, out.array)
     barrier()
     e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
@@ -405,7 +492,8 @@ def run_sharded(args):
         caller.close()
         if own_pg:
             dist.destroy_process_group()
-        return
+        return None
+    comm_nranks, nvls = nccl_ranks_seen()
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
@@ -416,8 +504,9 @@ def run_sharded(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "%s: synthetic %d samples x %d sites at %.1fx depth, sample-sharded over %d GPU(s)" % (args.workload, N, S, cfg["depth"], world),
-                   "sites": S, "n_samples": N, "entries_all_ranks": int(R_all), "qual_window": [qlo, qhi],
+        "config": {"workload": "%s: synthetic %d samples x %d sites at %.1fx depth, sample-sharded over %d GPU(s)%s" % (
+                       args.workload, N, S * passes, cfg["depth"], world, "" if passes == 1 else ": %d passes over a resident %d-site tile" % (passes, S)),
+                   "sites": S * passes, "tile_sites": S, "passes_per_step": passes, "n_samples": N, "entries_all_ranks": int(R_all), "qual_window": [qlo, qhi],
                    "parallelism": "sample-sharded x%d: reduce-scatter of per-site histograms + all-gather + all-reduce (NCCL)" % world,
                    "l2": "inputs (%.0f MB per rank) exceed the 126 MB L2; no flush needed" % (tile.nbytes() / 1e6) if tile.nbytes() > 126e6
                          else "inputs (%.0f MB per rank) fit the L2: use --sites to grow the tile" % (tile.nbytes() / 1e6)},
@@ -427,10 +516,14 @@ def run_sharded(args):
         "roofline": roof,
         "phases_ms": {k: round(v, 4) for k, v in phases.items()},
         "exchange_bytes_per_step": int(xbytes), "wall_ms_per_step": wall_ms,
+        "exchange_gbs_per_rank": (xbytes / max(world, 1)) / max((phases.get("reduce_scatter", 0) + phases.get("all_gather", 0) + phases.get("all_reduce", 0)) * 1e-3, 1e-12) / 1e9,
+        "comm_nranks": comm_nranks, "nccl_nvls": nvls,
         "cpu_baseline": cpu, "clocks": clocks, "sites_lrt_positive": int(n_pos),
     }
-    print(json.dumps(line))
     caller.close()
+    if return_line:
+        return {k: line[k] for k in ("value", "unit", "ms_per_step", "scaling", "config", "phases_ms", "exchange_bytes_per_step", "comm_nranks", "nccl_nvls")}
+    print(json.dumps(line))
     if own_pg:
         dist.destroy_process_group()
 
@@ -451,6 +544,11 @@ def main():
     ap.add_argument("--ref-sites-per-thread", type=int, default=6000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--qual-window", type=int, nargs=2, default=[1, 63], help="exchange window of the sample-sharded mode (C4)")
+    ap.add_argument("--window-sites", type=int, default=0,
+                    help="the WHOLE job in sites (e.g. 10000000 for C3's 10 Mb): region-sharded over the ranks (strong scaling), every rank "
+                         "running ceil(window / ranks / --sites) passes over its resident --sites tile (the generator's sites are i.i.d.)")
+    ap.add_argument("--no-bind", action="store_true", help="do not bind the rank to its GPU's local cores")
+    ap.add_argument("--no-also", action="store_true", help="N > 1: skip the short sample-sharded (NCCL) run appended as `also`")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -464,6 +562,7 @@ def main():
     import basevarc_b200 as B
     from basevarc_b200.caller import PinnedArray
     torch.cuda.set_device(local)
+    binding = None if args.no_bind else bind_rank_to_cores(local, world)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -484,7 +583,11 @@ def main():
     cfg, tile = _workload(args.workload, args.sites, rank)
     S, N, R = tile.n_sites, tile.n_samples, tile.n_entries
     caller = B.BaseTypeCaller(N, device=local, max_sites=S, max_entries=R)
-    units_per_gpu = S * N
+    # --window-sites: the named job (e.g. C3's 10 Mb) region-sharded over the ranks -- every rank runs `passes` passes over its
+    # resident tile (sites are independent and the generator's sites i.i.d., so a pass over the same tile is the work of the next
+    # S sites of the window); total work is fixed: strong scaling.  Default: one pass = one window per GPU (weak scaling).
+    passes = 1 if not args.window_sites else max(1, -(-args.window_sites // (world * S)))
+    units_per_gpu = S * N * passes
 
     # ---- kernel-only leg: inputs resident in HBM, device events on the launching stream -----------
     # the tile is resident in the form it travels in: one byte per entry + qual dictionary (--wire packed8, what the host
@@ -498,7 +601,8 @@ def main():
         sampler.wait_started()
     barrier()
     l0 = caller.kernel_launches
-    ms, _ = caller.resident_run(args.steps, flush_l2=False)
+    ms, _ = caller.resident_run(args.steps * passes, flush_l2=False)
+    ms *= passes                                       # a step = all the passes of this rank
     barrier()
     launches = caller.kernel_launches - l0
     ms_step = max_over_ranks(ms)
@@ -559,16 +663,26 @@ def main():
     barrier()
     h2d0, d2h0 = caller.transfer_bytes
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(args.steps * passes):
         e2e_step()
     barrier()
     e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
     h2d1, d2h1 = caller.transfer_bytes
     # copied bytes (counted by the library from the tensors it copies) + the pinned mapq/rpr words the
     # rank-sum kernel reads in place over PCIe at LRT-positive sites (2 arrays, rounded up to 32-bit words)
-    zc = int((recs["n_entries"][recs["lrt_ok"] == 1].astype(np.int64) + 6).sum()) * 2
+    zc = int((recs["n_entries"][recs["lrt_ok"] == 1].astype(np.int64) + 6).sum()) * 2 * passes
     h2d = (h2d1 - h2d0) // args.steps + zc
     d2h = (d2h1 - d2h0) // args.steps
+    # ---- copy-only probe of the same link: the bytes of one pass, cudaMemcpyAsync only, every rank at the same time --------
+    probe = copy_probe(local, int(h2d // passes), int(d2h // passes), barrier)
+    probe["rank"] = rank
+    probe["e2e_h2d_gbs_achieved"] = h2d / e2e_s / 1e9
+    if binding:
+        probe["binding"] = binding
+    probes = [probe]
+    if dist is not None:
+        probes = [None] * world
+        dist.all_gather_object(probes, probe)
     clocks = sampler.stop() if sampler else None
     e2e_value = world * units_per_gpu / e2e_s
     got = np.concatenate([o.array for o in outs])
@@ -641,10 +755,23 @@ def main():
     n_reads = recs["depth"].sum(1).astype(np.float64)
     f_alg = float((n_reads * (21.0 * recs["em_passes"] - 3.0 * recs["em_fits"])).sum())   # per-READ formulation, SURVEY 8(d)
 
+    # ---- N > 1: a short run of the SAMPLE-SHARDED path (the one with a collective) so that the scaling record carries NCCL
+    # evidence; its own line is what `--workload C4` prints
+    also = None
+    if world > 1 and not args.no_also:
+        import copy
+        a2 = copy.copy(args)
+        a2.workload, a2.sites, a2.steps, a2.warmup, a2.no_cpu_baseline, a2.window_sites = "C4", 16384, 2, 1, True, 0
+        caller.close()
+        try:
+            also = run_sharded(a2, return_line=True)
+        except Exception as e:                      # the C2 line must survive a failing side run
+            also = {"error": repr(e)[:300]}
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
         return
+    comm_nranks, nvls = nccl_ranks_seen()
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
@@ -659,13 +786,22 @@ def main():
             cpu["rerun_cli"] = dropin
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.window_sites else "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": "%s: synthetic %d samples x %d sites at %.1fx depth per GPU" % (args.workload, N, S, cfg["depth"]),
-                   "sites_per_gpu": S, "n_samples": N, "entries_per_gpu": R, "parallelism": "window-sharded x%d, no collective" % world,
+        "config": {"workload": ("%s: synthetic %d samples x %d sites at %.1fx depth per GPU" % (args.workload, N, S, cfg["depth"])) if not args.window_sites else
+                               ("%s: synthetic %d samples x %d sites at %.1fx depth, region-sharded over %d GPU(s): %d passes per rank over a resident %d-site tile" % (
+                                   args.workload, N, passes * world * S, cfg["depth"], world, passes, S)),
+                   "sites_per_gpu": S * passes, "tile_sites": S, "passes_per_step": passes, "n_samples": N, "entries_per_gpu": R * passes,
+                   "parallelism": "window-sharded x%d, no collective" % world,
                    "l2": "inputs (%.0f MB per launch) exceed the 126 MB L2; no flush needed" % (tile.nbytes() / 1e6)},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "wire": wire, "result": args.result, "matches_resident": bool(same)},
+                "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "wire": wire, "result": args.result, "matches_resident": bool(same),
+                "h2d_gbs_per_gpu": h2d / e2e_s / 1e9},
+        "copy_probe": {"what": "cudaMemcpyAsync only, pinned host memory, the bytes of one pass, all ranks at once; GB/s per rank",
+                       "ranks": probes,
+                       "aggregate_h2d_gbs": float(sum(p["h2d_gbs"] for p in probes)),
+                       "aggregate_e2e_h2d_gbs": float(sum(p["e2e_h2d_gbs_achieved"] for p in probes))},
+        "comm_nranks": comm_nranks, "nccl_nvls": nvls, "also": also,
         "gpu_launches": int(launches),
         "roofline": roof,
         "rooflines": rooflines,
