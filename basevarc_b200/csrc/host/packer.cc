@@ -26,6 +26,7 @@ void Packer::clear()
     sample_ = 0;
     for (auto& q : qidx_) q = -1;
     ndict_ = 0; pk8_ok_ = true;
+    trace_.clear(); early_.clear(); site_numeric_ = false;
 }
 
 void Packer::reserve_entries(size_t need)
@@ -51,6 +52,7 @@ void Packer::begin_site(int32_t pos, uint8_t ref_base)
     pos_.push_back(pos);
     ref_base_.push_back(ref_base);
     sample_ = 0;
+    site_numeric_ = false;
 }
 
 // One token through the reference's general grammar: strtok_r on ",", std::atoi per field (whitespace, sign, digits),
@@ -75,6 +77,7 @@ int Packer::add_token_slow(const char* tok, const char* tend)
             }
             f = fe;
         }
+        site_numeric_ = true;
         if (st_base_ != 4) {                             // N base: skipped, the sample index still advances
             if (st_base_ > 4 || st_qual_ > 127) {
                 err_ = "token with base > 4 or qual > 127 at site " + std::to_string(pos_.empty() ? 0 : pos_.back());
@@ -87,6 +90,7 @@ int Packer::add_token_slow(const char* tok, const char* tend)
         }
     } else if (c0 != '.') {
         // indel token: only is_indel and the text change; every other field keeps its stale value (Q1)
+        if (track_ && !site_numeric_) early_.emplace_back((uint32_t)(ref_base_.size() - 1), (uint32_t)n_);
         indel_.emplace((int64_t)n_, std::string(tok, (size_t)(tend - tok)));
         code_[n_] = BVC_MAKE_CODE(st_base_, st_strand_, 1);
         qual_[n_] = st_qual_ > 127 ? (uint8_t)127 : st_qual_; mapq_[n_] = st_mapq_; rpr_[n_] = st_rpr_; smp_[n_] = sample_;
@@ -132,6 +136,7 @@ int Packer::add_line(const char* line, size_t len)
                 if (b <= 4 && (b == 4 || q8 <= 127)) {       // errors are reported by the slow path
                     st_base_ = (uint8_t)b; st_mapq_ = (uint8_t)(v[0] & 255u); st_qual_ = (uint8_t)q8;
                     st_rpr_ = (uint8_t)(v[2] & 255u); st_strand_ = (uint8_t)((unsigned)(q[0] - '0') & 1u);
+                    site_numeric_ = true;
                     if (b != 4) {
                         code[n] = BVC_MAKE_CODE(st_base_, st_strand_, 0);
                         qual[n] = st_qual_; mapq[n] = st_mapq_; rpr[n] = st_rpr_; smp[n] = sample;
@@ -159,7 +164,25 @@ int32_t Packer::end_site()
 {
     const uint32_t n = (uint32_t)n_ - entry_off_.back();
     entry_off_.push_back((uint32_t)n_);
+    if (track_) trace_.push_back(SiteTrace{(uint8_t)site_numeric_, st_base_, st_mapq_, st_qual_, st_rpr_, st_strand_});
     return (int32_t)n;
+}
+
+void Packer::patch_entry(uint32_t e, const SiteTrace& st)
+{
+    code_[e] = BVC_MAKE_CODE(st.base, st.strand, 1);
+    qual_[e] = st.qual > 127 ? (uint8_t)127 : st.qual; mapq_[e] = st.mapq; rpr_[e] = st.rpr;
+    if (st.base > 4) pk8_ok_ = false;
+    pk8_[e] = BVC_PACK8(st.base == 4 ? BVC_PACK8_INDEL_N : BVC_PACK8_INDEL, st.strand, st.base);
+}
+
+void Packer::append_raw(uint8_t code, uint8_t qual, uint8_t mapq, uint8_t rpr, uint32_t sample, const char* indel_text)
+{
+    reserve_entries(n_ + 1);
+    code_[n_] = code; qual_[n_] = qual; mapq_[n_] = mapq; rpr_[n_] = rpr; smp_[n_] = sample; pk8_[n_] = 0;
+    pk8_ok_ = false;
+    if (indel_text) indel_.emplace((int64_t)n_, indel_text);
+    ++n_;
 }
 
 void Packer::drop_last_site()

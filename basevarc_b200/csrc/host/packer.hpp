@@ -37,6 +37,24 @@ public:
     int buffers(const void** ptr, size_t* bytes, int max) const;
     // ---- packed tile files (packed_io.cc): a tile adopted from / dumped to the binary form of include/bvc_host.h
     friend class PackedIo;
+    // ---- sample-sharded windows (shard_rerun.cc): this packer sees only ITS range of a site's batch files, but the reference's
+    // reused `AlleleInfo ai` (Q1) runs through ALL of them in file order.  With tracking on, the packer records per site whether
+    // its range held a numeric token and the stale fields it ended the site with, and which indel entries came BEFORE the first
+    // numeric token of the range: those carry the fields of the PRECEDING range / site and are patched once every rank has packed.
+    struct SiteTrace { uint8_t has_numeric, base, mapq, qual, rpr, strand; };
+    void track_ranges(bool on) { track_ = on; }
+    const std::vector<SiteTrace>& traces() const { return trace_; }
+    const std::vector<std::pair<uint32_t, uint32_t>>& early_indels() const { return early_; }     // (site of the tile, entry)
+    void patch_entry(uint32_t entry, const SiteTrace& st);
+    void set_state(const SiteTrace& st) { st_base_ = st.base; st_mapq_ = st.mapq; st_qual_ = st.qual; st_rpr_ = st.rpr; st_strand_ = st.strand; }
+    // one raw entry into the current site (merged per-site views of the sharded formatter); indel_text != NULL for an indel entry
+    void append_raw(uint8_t code, uint8_t qual, uint8_t mapq, uint8_t rpr, uint32_t sample, const char* indel_text);
+    const uint8_t* codes() const { return code_.data(); }
+    const uint8_t* quals() const { return qual_.data(); }
+    const uint8_t* mapqs() const { return mapq_.data(); }
+    const uint8_t* rprs() const { return rpr_.data(); }
+    const uint32_t* samples() const { return smp_.data(); }
+    const uint32_t* offsets() const { return entry_off_.data(); }
 
 private:
     int32_t n_samples_;
@@ -69,6 +87,9 @@ private:
     int add_token_slow(const char* tok, const char* tend);
     std::unordered_map<int64_t, std::string> indel_;
     std::string err_;
+    bool track_ = false, site_numeric_ = false;
+    std::vector<SiteTrace> trace_;
+    std::vector<std::pair<uint32_t, uint32_t>> early_;
 };
 
 }  // namespace bvc_host

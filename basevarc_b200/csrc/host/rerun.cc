@@ -64,7 +64,9 @@ const char* kUsage =
     "  --tile_sites <INT>       Sites per GPU tile [auto]\n"
     "  --pack                   Convert the text batch files into packed tile files (PREFIX.tmp.thread.{t}/packed.bvc; no GPU\n"
     "                           needed); --rerun reads them instead of the text files whenever every window has one\n"
-    "  --no_packed              --rerun from the text batch files even if packed tile files exist\n";
+    "  --no_packed              --rerun from the text batch files even if packed tile files exist\n"
+    "  --shard_samples <INT>    Sample-sharded calling for very wide cohorts: rank r of W reads the batch files [r*J/W, (r+1)*J/W)\n"
+    "                           of every window, one GPU per rank with NCCL (fewer GPUs than ranks: all ranks on GPU 0)\n";
 
 const char* kCvgHeader =
     "##fileformat=CVGv1.0\n"
@@ -93,6 +95,7 @@ const char* kVcfHeader =
 
 struct Options {
     bool rerun = false, load = false, keep_tmp = false, verbose = false;
+    int shard_samples = 0;                     // --shard_samples W: the sample-sharded compute phase over W ranks (shard_rerun.inc)
     bool pack = false, no_packed = false;      // --pack: text batch files -> packed tile files (no GPU); --no_packed: ignore packed files
     int mapq = 10, thread = 1, batch = 10, gpus = 0, tile_sites = 0;
     double maf = 0.001;
@@ -112,6 +115,7 @@ bool parse_options(int argc, char** argv, Options& o)
         {"load", no_argument, nullptr, 7},            {"keep_tmp", no_argument, nullptr, 6},
         {"gpus", required_argument, nullptr, 1},      {"tile_sites", required_argument, nullptr, 2},
         {"pack", no_argument, nullptr, 3},            {"no_packed", no_argument, nullptr, 4},
+        {"shard_samples", required_argument, nullptr, 5},
         {nullptr, 0, nullptr, 0}};
     bool die = false;
     optind = 1;
@@ -135,6 +139,7 @@ bool parse_options(int argc, char** argv, Options& o)
         case 2: o.tile_sites = atoi(a); break;
         case 3: o.pack = true; break;
         case 4: o.no_packed = true; break;
+        case 5: o.shard_samples = atoi(a); break;
         case 'v': o.verbose = true; break;
         default: die = true;
         }
@@ -558,6 +563,8 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
     }
 }
 
+#include "shard_rerun.inc"
+
 }  // namespace
 }  // namespace bvc_host
 
@@ -691,6 +698,16 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     const int n_dev = dev.first;
     if (const char* e = getenv("BVC_GPUS")) if (o.gpus <= 0) o.gpus = atoi(e);
     if (n_dev <= 0) { std::cerr << "ERROR: no CUDA device: the basetype calling core has no CPU path (" << dev.second << ")" << std::endl; return EXIT_FAILURE; }
+    if (o.shard_samples > 0) {
+        if (sh.packed_in) { std::cerr << "ERROR: --shard_samples reads the text batch files (a packed tile file holds whole-cohort tiles): add --no_packed" << std::endl; return EXIT_FAILURE; }
+        const int rc = run_sharded_windows(sh, o.shard_samples, n_dev);
+        if (rc == EXIT_SUCCESS) {
+            std::cout << "basetype computing done -- " << now_string();
+            std::cout << "basetype elapsed cpu secs : " << double(clock() - ctb) / CLOCKS_PER_SEC << std::endl;
+            std::cout << "basetype done" << std::endl;
+        }
+        return rc;
+    }
     const int G = std::max(1, std::min(std::min(o.gpus > 0 ? o.gpus : n_dev, n_dev), T));
     // Tiles of ~2,048 sites (fewer for wide cohorts: <= 8 M entries): with one worker per window feeding it, the GPU is
     // never the bottleneck, so small tiles cost nothing there and let packing, kernels and formatting overlap inside a

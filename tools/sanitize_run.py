@@ -1,0 +1,55 @@
+#!/usr/bin/env python
+"""What compute-sanitizer wraps (one tool per gpurun call):
+    compute-sanitizer --tool memcheck  python tools/sanitize_run.py
+    compute-sanitizer --tool racecheck python tools/sanitize_run.py
+smoke()'s tile and small C2- / C5- / C3-like tiles through every kernel of the tile path: the one-byte form (site_hist8_kernel),
+the two-array form (site_hist4_kernel), the wide form (site_hist_kernel<G>, >= 65,536 samples), the split result, a qual-0 site
+(the legacy warp-per-site kernel) and --group; every result is compared with the oracle so a clean sanitizer log belongs to a
+CORRECT run."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import basevarc_b200 as B  # noqa: E402
+import oracle_py  # noqa: E402
+from parity import compare_records  # noqa: E402
+
+
+def check(name, tile, packed, **kw):
+    if packed:
+        assert tile.pack8()
+    c = B.BaseTypeCaller(tile.n_samples, max_sites=tile.n_sites, max_entries=tile.n_entries, **kw)
+    got = c.call_sites(tile).copy()
+    core, vcf = c.call_sites_split(tile)
+    c.resident_upload(tile)
+    c.resident_run(1, False)
+    res = c.resident_download().copy()
+    launches = c.kernel_launches
+    c.close()
+    want = oracle_py.call_sites(tile, B.default_params(tile.n_samples))
+    nbad, lines = compare_records(got, want, max_flagged_fraction=0.1)
+    assert nbad == 0, "\n".join(lines)
+    assert np.array_equal(res["depth"], got["depth"]) and np.array_equal(core["depth"], got["depth"])
+    print("%-28s %6d sites %9d entries  %4d LRT-positive  %d kernel launches: ok" % (name, tile.n_sites, tile.n_entries, int(got["lrt_ok"].sum()), launches), flush=True)
+
+
+def main():
+    check("smoke (C2-like, packed8)", B.synth_tile(1000, 2000, 0.5, "lowpass", seed=7), True)
+    check("C2-like, two-array form", B.synth_tile(1000, 1500, 0.5, "lowpass", seed=8, indel_frac=0.01), False)
+    check("C5-like, packed8", B.synth_tile(2000, 300, 5.0, "highpoly", seed=9, indel_frac=0.01), True)
+    check("C3-like, packed8", B.synth_tile(10000, 120, 0.3, "lowpass", seed=10), True)
+    check("thin / ragged, packed8", B.synth_tile(60, 3000, 0.05, "lowpass", seed=11, indel_frac=0.2), True)
+    check("wide (70,000 samples)", B.synth_tile(70000, 24, 0.1, "highpoly", seed=12), False)
+    t = B.synth_tile(64, 400, 1.5, "highpoly", seed=13, indel_frac=0.1)
+    q = t.qual.copy(); q[::17] = 0; q[::19] = 1; t.qual = q
+    check("qual 0 / 1 (legacy kernel)", t, False)
+    print("sanitize_run: all tiles agree with the oracle")
+
+
+if __name__ == "__main__":
+    main()
