@@ -482,7 +482,7 @@ def run_sharded(args, return_line=False):
     peak, peak_src = _peaks()
     B_words = 16 + 8 * (qhi - qlo + 1)
     n_pad = world * ((S + world - 1) // world)
-    hist_bytes = 2 * R + 5 * S + 4 * B_words * n_pad      # per rank: code + qual in, offsets + ref, dense records out
+    hist_bytes = (2 * R + 5 * S + 4 * B_words * n_pad) * passes      # per rank and step: code + qual in, offsets + ref, dense records out
     roof = {"bound": "hbm", "kernel": "shard_hist_kernel", "kernel_ms": phases["shard_hist"],
             "achieved": hist_bytes / (phases["shard_hist"] * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "peak_source": peak_src,
             "algorithmic_bytes_per_launch": int(hist_bytes), "traffic": None,
@@ -809,11 +809,12 @@ def main():
                        "algorithmic_bytes_per_launch": int(hist_bytes),
                        "achieved": hist_bytes / max(hist_ms, 1e-9) / 1e6, "peak": peak, "unit": "GB/s",
                        "frac": hist_bytes / max(hist_ms, 1e-9) / 1e6 / peak},
+        # (per PASS over the resident tile: kernels_ms, rooflines and the work counters are those of one pass; a step is `passes` of them)
         "step": {"algorithmic_bytes": int(alg_bytes), "hbm_floor_ms": alg_bytes / peak / 1e6,
-                 "frac_of_hbm_floor": (alg_bytes / peak / 1e6) / ms, "fp64_floor_ms": em_flop / fp64_peak / 1e9,
-                 "frac_of_fp64_floor": (em_flop / fp64_peak / 1e9) / ms, "fp64_peak_tflops": fp64_peak,
-                 "em_flop_floor_ms": em_flop / fp64_peak / 1e9, "measured_ms": ms,
-                 "per_read_flop_survey": f_alg, "per_read_tflops_equiv": f_alg / (ms * 1e-3) / 1e12,
+                 "frac_of_hbm_floor": (alg_bytes / peak / 1e6) / (ms / passes), "fp64_floor_ms": em_flop / fp64_peak / 1e9,
+                 "frac_of_fp64_floor": (em_flop / fp64_peak / 1e9) / (ms / passes), "fp64_peak_tflops": fp64_peak,
+                 "em_flop_floor_ms": em_flop / fp64_peak / 1e9, "measured_ms": ms / passes, "passes_per_step": passes,
+                 "per_read_flop_survey": f_alg, "per_read_tflops_equiv": f_alg / (ms / passes * 1e-3) / 1e12,
                  "note": "per_read_* counts the flops of the reference's per-read EM (SURVEY 8d); the class-collapsed "
                          "kernels do ~n_reads/n_classes fewer, so it is an equivalence figure, not pipe utilisation"},
         "work": {k: int(v) for k, v in work.items()},

@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 nvidia-smi topo -m > gpurun_out/r2_topo_n$N.txt 2>&1
 run --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/r2_bench_c2_n$N.json 2> gpurun_out/r2_bench_c2_n$N.err || tail -5 gpurun_out/r2_bench_c2_n$N.err
 run --workload C3 --sites 150000 --window-sites 10000000 --steps 3 --warmup 3 --no-cpu-baseline --no-also > gpurun_out/r2_bench_c3_n$N.json 2> gpurun_out/r2_bench_c3_n$N.err || tail -5 gpurun_out/r2_bench_c3_n$N.err
-run --workload C4 --sites 32768 --window-sites 1000000 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r2_bench_c4_n$N.json 2> gpurun_out/r2_bench_c4_n$N.err || tail -5 gpurun_out/r2_bench_c4_n$N.err
+run --workload C4 --sites $((32768 * N)) --window-sites 1000000 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r2_bench_c4_n$N.json 2> gpurun_out/r2_bench_c4_n$N.err || tail -5 gpurun_out/r2_bench_c4_n$N.err
 if [ "$N" = 1 ]; then
   run --workload C5 --sites 200000 --window-sites 1000000 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r2_bench_c5_1m.json 2> gpurun_out/r2_bench_c5_1m.err || tail -5 gpurun_out/r2_bench_c5_1m.err
 fi
