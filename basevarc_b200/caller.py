@@ -21,8 +21,10 @@ EXPORTS = (
     "bvc_fetch_groups", "bvc_host_alloc", "bvc_host_free", "bvc_host_register", "bvc_host_unregister", "bvc_resident_upload", "bvc_resident_run",
     "bvc_resident_download", "bvc_kernel_launch_count", "bvc_measure_fp64_peak", "bvc_kernel_name", "bvc_transfer_bytes", "bvc_work_counters",
     "bvc_shard_unique_id", "bvc_shard_init", "bvc_shard_call", "bvc_shard_upload", "bvc_shard_run", "bvc_shard_init_group",
-    "bvc_shard_call_group", "bvc_shard_stats", "bvc_shard_phase_name",
+    "bvc_shard_call_group", "bvc_shard_stats", "bvc_shard_phase_name", "bvc_call_sites_noalloc",
 )
+NOALLOC_MAX_SITES = 65536       # include/bvc_gpu.h BVC_NOALLOC_*
+NOALLOC_MAX_SAMPLES = 16384
 SHARD_ID_BYTES = 128
 SHARD_N_PHASES = 9
 
@@ -80,8 +82,21 @@ def load_library():
     L.bvc_shard_stats.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
     L.bvc_shard_phase_name.argtypes = [C.c_int]
     L.bvc_shard_phase_name.restype = C.c_char_p
+    L.bvc_call_sites_noalloc.argtypes = [C.c_int, C.POINTER(Params), C.POINTER(Tile), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     _lib = L
     return L
+
+
+def call_sites_noalloc(params, n_sites, n_entries, d_ref_base, d_entry_off, d_code, d_qual, d_mapq, d_rpr, d_out, d_status=None,
+                       stream=None, device=0):
+    """bvc_call_sites_noalloc (include/bvc_gpu.h): every d_* is a DEVICE address (int); enqueues on `stream` and returns."""
+    L = load_library()
+    t = Tile()
+    t.n_sites = int(n_sites)
+    t.ref_base, t.entry_off, t.code, t.qual, t.mapq, t.rpr = d_ref_base, d_entry_off, d_code, d_qual, d_mapq, d_rpr
+    rc = L.bvc_call_sites_noalloc(int(device), C.byref(params), C.byref(t), int(n_entries), d_out, d_status, stream)
+    if rc != 0:
+        raise BvcError("bvc_call_sites_noalloc failed (%d): %s" % (rc, L.bvc_last_error(None).decode()))
 
 
 def measure_fp64_peak(device=0):

@@ -1,7 +1,11 @@
 // bvc_kernels.cu -- kernel entry points (sm_100a) and their launchers.
 // See bvc_site_kernel.cuh for the design and the reference code each phase replaces.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
 #include <mutex>
 #include "bvc_kernels.h"
+#include "bvc_ctx.h"
 #include "bvc_site_kernel.cuh"
 #include "bvc_pipeline.cuh"
 #include "bvc_groups.cuh"
@@ -476,3 +480,155 @@ cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cu
 }
 
 }  // namespace bvc
+
+// ---- bvc_call_sites_noalloc: the allocation-free call (include/bvc_gpu.h) ---------------------------------------------
+// No counterpart in the reference.  site_call_kernel with everything it
+// needs besides the caller's tile and records in ONE file-scope device array: no context, no cudaMalloc.
+namespace bvc {
+namespace {
+
+constexpr size_t kNaCtrlBytes = 256;                                            // counter, list_n, err (words 0..2)
+constexpr size_t kNaLutBytes  = 5 * kNQ * sizeof(double);
+constexpr size_t kNaLgamN     = (size_t)BVC_NOALLOC_MAX_SAMPLES + 3;
+constexpr size_t kNaLgamBytes = (kNaLgamN * sizeof(double) + 255) / 256 * 256;
+constexpr size_t kNaListBytes = (size_t)BVC_NOALLOC_MAX_SITES * sizeof(uint32_t);
+constexpr size_t kNaLutOff = kNaCtrlBytes, kNaLgamOff = kNaLutOff + kNaLutBytes, kNaListOff = kNaLgamOff + kNaLgamBytes;
+constexpr size_t kNaBytes = kNaListOff + kNaListBytes;                           // 398,848 bytes
+
+// In HOST code this name is only a stand-in for the symbol, not a device address: the address comes from
+// cudaGetSymbolAddress (noalloc_setup), once per device.  Every call on a device shares it.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaBytes];
+
+constexpr int kNaMaxDev = 64;
+std::mutex g_na_mutex;
+unsigned char* g_na_ptr[kNaMaxDev];        // device address of g_noalloc_scratch on device d (nullptr: not set up yet)
+int g_na_sm[kNaMaxDev];
+double g_na_lut[5 * kNQ], g_na_lgam[kNaLgamN];   // host copies of the tables (static: no host allocation either)
+
+// thread per site: the offsets; grid-stride over the entries: what K1 rejects on the pipeline path.  Writes the site list.
+__global__ void __launch_bounds__(256)
+noalloc_check_kernel(const uint32_t* __restrict__ off, const uint8_t* __restrict__ code, const uint8_t* __restrict__ qual,
+                     int n_sites, unsigned long long n_entries, uint32_t max_per_site, uint32_t* list, uint32_t* err)
+{
+    const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x, nt = (unsigned long long)gridDim.x * blockDim.x;
+    uint32_t bad = 0;
+    for (unsigned long long s = tid; s < (unsigned long long)n_sites; s += nt) {
+        const uint32_t a = off[s], b = off[s + 1];
+        if ((s == 0 && a != 0) || b < a || b - a > max_per_site || (unsigned long long)b > n_entries) bad |= BVC_NOALLOC_BAD_OFFSETS;
+        list[s] = (uint32_t)s;
+    }
+    for (unsigned long long e = tid; e < n_entries; e += nt) {
+        const unsigned c = code[e];
+        if (qual[e] > 127) bad |= BVC_NOALLOC_BAD_QUAL;
+        if (!(c & 16u) && (c & 7u) > 3u) bad |= BVC_NOALLOC_BAD_BASE;
+    }
+    bad = __reduce_or_sync(0xffffffffu, bad);
+    if (bad && (threadIdx.x & 31) == 0) atomicOr(err, bad);
+}
+
+// one thread: the number of sites site_call_kernel may touch (all or none) and the caller's status word
+__global__ void noalloc_finish_kernel(const uint32_t* err, uint32_t* list_n, uint32_t n_sites, uint32_t* status)
+{
+    const uint32_t e = *err;
+    *list_n = e ? 0u : n_sites;
+    if (status) *status = e;
+}
+
+int noalloc_fail(int rc, const char* what, cudaError_t e = cudaSuccess)
+{
+    char b[256];
+    if (e != cudaSuccess) { snprintf(b, sizeof b, "bvc_call_sites_noalloc: %s: %s", what, cudaGetErrorString(e)); cudaGetLastError(); }
+    else snprintf(b, sizeof b, "bvc_call_sites_noalloc: %s", what);
+    set_err(nullptr, b);
+    return rc;
+}
+
+// once per device, with that device current
+int noalloc_setup(int device)
+{
+    std::lock_guard<std::mutex> lk(g_na_mutex);
+    if (g_na_ptr[device]) return BVC_OK;
+    int major = 0, sm = 0;
+    cudaError_t e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, device);
+    if (e != cudaSuccess) return noalloc_fail(BVC_ERR_CUDA, "cudaDeviceGetAttribute", e);
+    if (major < 10) return noalloc_fail(BVC_ERR_CUDA, "device is not sm_100 class (kernels are built for sm_100a only)");
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) return noalloc_fail(BVC_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch)", e);
+    // the tables of bvc_create (glibc exp / log / lgamma; src/BaseType.cpp:13-15, src/BaseType.h:10), same expressions
+    for (int q = 0; q < kNQ; ++q) {
+        const double er = exp(-0.23025850929940458 * q);
+        g_na_lut[q] = er / 3.0; g_na_lut[kNQ + q] = 1.0 - er;
+        g_na_lut[2 * kNQ + q] = log(er / 3.0); g_na_lut[3 * kNQ + q] = log(1.0 - er);
+        g_na_lut[4 * kNQ + q] = (1.0 - er) - er / 3.0;
+    }
+    for (size_t k = 0; k < kNaLgamN; ++k) g_na_lgam[k] = k == 0 ? 0.0 : lgamma((double)k);
+    unsigned char* d = static_cast<unsigned char*>(p);
+    e = cudaMemcpy(d + kNaLutOff, g_na_lut, sizeof g_na_lut, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d + kNaLgamOff, g_na_lgam, sizeof g_na_lgam, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return noalloc_fail(BVC_ERR_CUDA, "copy of the tables into the static array (first call on a device must be outside stream capture)", e);
+    g_na_sm[device] = sm;
+    g_na_ptr[device] = d;
+    return BVC_OK;
+}
+
+}  // namespace
+}  // namespace bvc
+
+extern "C" int bvc_call_sites_noalloc(int device, const bvc_params* prm, const bvc_tile* t, int64_t n_entries,
+                                      bvc_site_result* d_out, uint32_t* d_status, void* stream)
+{
+    using namespace bvc;
+    if (!prm || !t) return noalloc_fail(BVC_ERR_ARG, "NULL argument");
+    if (prm->abi_version != BVC_ABI_VERSION) return noalloc_fail(BVC_ERR_ARG, "abi_version mismatch");
+    if (prm->n_samples <= 0 || !(prm->min_af > 0) || prm->em_max_iter < 0 || prm->n_groups != 0)
+        return noalloc_fail(BVC_ERR_ARG, "bad parameter (n_samples, min_af > 0, em_max_iter >= 0, n_groups == 0)");
+    if (t->n_sites < 0 || n_entries < 0) return noalloc_fail(BVC_ERR_ARG, "n_sites < 0 or n_entries < 0");
+    if (t->n_sites > BVC_NOALLOC_MAX_SITES || prm->n_samples > BVC_NOALLOC_MAX_SAMPLES || n_entries >= ((int64_t)1 << 32)) {
+        char b[200];
+        snprintf(b, sizeof b, "tile beyond the static scratch array: n_sites %d (max %d), n_samples %d (max %d), n_entries %lld (max 2^32-1)",
+                 t->n_sites, BVC_NOALLOC_MAX_SITES, prm->n_samples, BVC_NOALLOC_MAX_SAMPLES, (long long)n_entries);
+        return noalloc_fail(BVC_ERR_CAPACITY, b);
+    }
+    if (t->packed8) return noalloc_fail(BVC_ERR_ARG, "packed8 tiles are not served (pass code / qual)");
+    if (t->n_sites > 0 && (!t->ref_base || !t->entry_off || !d_out)) return noalloc_fail(BVC_ERR_ARG, "NULL ref_base / entry_off / d_out");
+    if (n_entries > 0 && (!t->code || !t->qual || !t->mapq || !t->rpr)) return noalloc_fail(BVC_ERR_ARG, "NULL entry array");
+    int ndev = 0, prev = -1;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return noalloc_fail(BVC_ERR_CUDA, "no CUDA device (this library has no CPU path)"); }
+    if (device < 0 || device >= ndev || device >= kNaMaxDev) return noalloc_fail(BVC_ERR_ARG, "device index out of range");
+    cudaError_t e = cudaGetDevice(&prev);
+    if (e == cudaSuccess && prev != device) e = cudaSetDevice(device);
+    if (e != cudaSuccess) return noalloc_fail(BVC_ERR_CUDA, "cudaSetDevice", e);
+    int rc = noalloc_setup(device);
+    if (rc == BVC_OK && t->n_sites > 0) {
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        unsigned char* d = g_na_ptr[device];
+        uint32_t* ctrl = reinterpret_cast<uint32_t*>(d);
+        uint32_t* list = reinterpret_cast<uint32_t*>(d + kNaListOff);
+        const int n_sm = g_na_sm[device];
+        // the array keeps the last call's contents: the counter, the list length and the error word start at zero
+        e = cudaMemsetAsync(ctrl, 0, kNaCtrlBytes, st);
+        if (e == cudaSuccess) {
+            long long work = n_entries > t->n_sites ? n_entries : t->n_sites, blocks = (work + 255) / 256;
+            if (blocks > (long long)n_sm * 8) blocks = (long long)n_sm * 8;
+            noalloc_check_kernel<<<(unsigned)blocks, 256, 0, st>>>(t->entry_off, t->code, t->qual, t->n_sites, (unsigned long long)n_entries,
+                                                                  (uint32_t)prm->n_samples, list, ctrl + 2);
+            noalloc_finish_kernel<<<1, 1, 0, st>>>(ctrl + 2, ctrl + 1, (uint32_t)t->n_sites, d_status);
+            e = cudaGetLastError();
+        }
+        if (e == cudaSuccess) {
+            SiteArgs a;
+            a.ref_base = t->ref_base; a.entry_off = t->entry_off; a.code = t->code; a.qual = t->qual; a.mapq = t->mapq; a.rpr = t->rpr;
+            a.pk8 = nullptr; memset(&a.dict, 0, sizeof a.dict); a.n_dict = 0; a.err = ctrl + 2;
+            a.out = d_out; a.counter = ctrl; a.site_list = list; a.list_n = ctrl + 1;
+            a.lut = reinterpret_cast<const double*>(d + kNaLutOff); a.lgam = reinterpret_cast<const double*>(d + kNaLgamOff);
+            a.n_sites = t->n_sites; a.max_iter = prm->em_max_iter;
+            a.min_af = prm->min_af; a.lrt_thr = prm->lrt_threshold; a.eps = prm->em_epsilon;
+            e = launch_site_call(a, n_sm, st);
+        }
+        if (e != cudaSuccess) rc = noalloc_fail(BVC_ERR_CUDA, "launch", e);
+    }
+    if (prev >= 0 && prev != device) cudaSetDevice(prev);
+    return rc;
+}

@@ -231,6 +231,39 @@ const char* bvc_shard_phase_name(int i);
 /* FP64 pipe microbenchmark (dependent-free DFMA chains on all SMs): returns TFLOP/s (2 flop/FMA). */
 int  bvc_measure_fp64_peak(int device, double* tflops);
 
+/* ---- Allocation-free call -------------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same records as
+ * bvc_enqueue + bvc_wait for one small tile, computed by the one-warp-per-site kernel (site_call_kernel,
+ * csrc/bvc_kernels.cu), with NO context and no allocation of any kind: the caller passes the tile and the record
+ * array as DEVICE pointers, and everything the kernel needs besides -- its dynamic site counter, the checked site
+ * list, the error word, the per-qual likelihood table and the lgamma table -- lives in ONE file-scope
+ * `static __device__` array of the library (~390 KB, held by every GPU that loads the library until the process
+ * exits).  Limits, fixed at build time: n_sites <= BVC_NOALLOC_MAX_SITES, prm->n_samples <= BVC_NOALLOC_MAX_SAMPLES,
+ * n_entries < 2^32; anything larger fails with BVC_ERR_CAPACITY and a message in bvc_last_error(NULL).
+ *   d_tile     a bvc_tile whose array pointers are device pointers (ref_base, entry_off, code, qual, mapq, rpr);
+ *              packed8 must be NULL (the plain two-array form only), sample is ignored
+ *   n_entries  length of the entry arrays; entry_off[n_sites] must not exceed it (entry_off lives on the device, so the
+ *              host side cannot read it)
+ *   prm        as for bvc_create: n_samples, min_af, lrt_threshold, em_epsilon, em_max_iter are used; n_groups must be 0
+ *   d_out      [n_sites] records, device memory
+ *   d_status   one device word, may be NULL: 0, or a mask of BVC_NOALLOC_BAD_* found by a checking kernel that runs first
+ *              (the checks bvc_wait reports as BVC_ERR_ARG).  When it is non-zero NO record is written.
+ *   stream     a cudaStream_t of `device` (NULL = the default stream).  The call only enqueues (one 256-byte memset and
+ *              three kernels) and returns; it never synchronises.
+ * The first call on a device also does the set-up for that device (the address of the array, two synchronous table
+ * copies): make that call outside stream capture -- a call with n_sites == 0 does the set-up and nothing else.
+ * All calls on a device SHARE the array, which keeps the previous call's contents: the call clears the words that must
+ * start at zero itself, but two calls that overlap on the GPU (different streams, or graphs replayed concurrently)
+ * race on it.  Order them on one stream or with events. */
+#define BVC_NOALLOC_MAX_SITES    65536
+#define BVC_NOALLOC_MAX_SAMPLES  16384
+#define BVC_NOALLOC_BAD_QUAL     1u    /* an entry with qual > 127 */
+#define BVC_NOALLOC_BAD_BASE     2u    /* a non-indel entry with base > 3 */
+#define BVC_NOALLOC_BAD_OFFSETS  4u    /* entry_off[0] != 0, not ascending, beyond n_entries, or a site with > n_samples entries */
+int  bvc_call_sites_noalloc(int device, const bvc_params* prm, const bvc_tile* d_tile, int64_t n_entries,
+                            bvc_site_result* d_out, uint32_t* d_status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
