@@ -4,7 +4,9 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "bvc_ctx.h"
@@ -24,6 +26,74 @@ void set_err(bvc_ctx* ctx, const char* m)
 {
     if (ctx) ctx->err = m; else g_create_error = m;
 }
+
+// ---- guard bands (BVC_GUARD=1) ----------------------------------------------------------------------------------------
+namespace {
+constexpr size_t kGuardBytes = 4096;
+struct GuardRec { unsigned char* base; size_t bytes; int serial; };
+std::mutex g_guard_mu;
+std::unordered_map<void*, GuardRec> g_guard;
+int g_guard_serial = 0;
+bool guard_on()
+{
+    static const bool on = [] { const char* e = getenv("BVC_GUARD"); return e && e[0] == '1'; }();
+    return on;
+}
+}  // namespace
+
+cudaError_t gmalloc_bytes(void** p, size_t bytes)
+{
+    if (!guard_on()) return cudaMalloc(p, bytes);
+    unsigned char* b = nullptr;
+    cudaError_t e = cudaMalloc(&b, bytes + 2 * kGuardBytes);
+    if (e != cudaSuccess) return e;
+    e = cudaMemset(b, 0xA5, bytes + 2 * kGuardBytes);
+    if (e != cudaSuccess) { cudaFree(b); return e; }
+    *p = b + kGuardBytes;
+    std::lock_guard<std::mutex> lk(g_guard_mu);
+    g_guard[*p] = GuardRec{b, bytes, g_guard_serial++};
+    return cudaSuccess;
+}
+
+cudaError_t gfree(void* p)
+{
+    if (!guard_on() || !p) return cudaFree(p);
+    unsigned char* b = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_guard_mu);
+        auto it = g_guard.find(p);
+        if (it == g_guard.end()) return cudaFree(p);
+        b = it->second.base;
+        g_guard.erase(it);
+    }
+    return cudaFree(b);
+}
+
+int guard_verify(bvc_ctx* ctx)
+{
+    if (!guard_on()) return BVC_OK;
+    std::lock_guard<std::mutex> lk(g_guard_mu);
+    std::vector<unsigned char> h(2 * kGuardBytes);
+    for (auto& kv : g_guard) {
+        const GuardRec& r = kv.second;
+        if (cudaMemcpy(h.data(), r.base, kGuardBytes, cudaMemcpyDeviceToHost) != cudaSuccess ||
+            cudaMemcpy(h.data() + kGuardBytes, r.base + kGuardBytes + r.bytes, kGuardBytes, cudaMemcpyDeviceToHost) != cudaSuccess) {
+            cudaGetLastError();
+            set_err(ctx, "BVC_GUARD: cannot read a guard band back");
+            return BVC_ERR_CUDA;
+        }
+        for (size_t i = 0; i < 2 * kGuardBytes; ++i)
+            if (h[i] != 0xA5) {
+                char b[200];
+                snprintf(b, sizeof b, "BVC_GUARD: allocation #%d (%zu bytes) was written out of bounds: %s band, byte %zu", r.serial, r.bytes,
+                         i < kGuardBytes ? "front" : "back", i < kGuardBytes ? kGuardBytes - i : i - kGuardBytes);
+                set_err(ctx, b);
+                fprintf(stderr, "%s\n", b);
+                return BVC_ERR_CUDA;
+            }
+    }
+    return BVC_OK;
+}
 }  // namespace bvc
 
 namespace {
@@ -33,33 +103,33 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
     const size_t S = (size_t)ctx->prm.max_sites, R = (size_t)ctx->prm.max_entries;
     CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
-    CK(cudaMalloc(&s.d_ref, S + 16));
-    CK(cudaMalloc(&s.d_off, (S + 1) * sizeof(uint32_t)));
-    CK(cudaMalloc(&s.d_code, R + 16));
-    CK(cudaMalloc(&s.d_qual, R + 16));
-    CK(cudaMalloc(&s.d_mapq, R + 16));
-    CK(cudaMalloc(&s.d_rpr, R + 16));
-    CK(cudaMalloc(&s.d_pk8, R + 16));
+    CK(bvc::gmalloc(&s.d_ref, S + 16));
+    CK(bvc::gmalloc(&s.d_off, (S + 1) * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&s.d_code, R + 16));
+    CK(bvc::gmalloc(&s.d_qual, R + 16));
+    CK(bvc::gmalloc(&s.d_mapq, R + 16));
+    CK(bvc::gmalloc(&s.d_rpr, R + 16));
+    CK(bvc::gmalloc(&s.d_pk8, R + 16));
     if (ctx->prm.n_groups > 0) {
-        CK(cudaMalloc(&s.d_sample, (R + 4) * sizeof(uint32_t)));
-        CK(cudaMalloc(&s.d_gdepth, (S + 1) * (size_t)ctx->prm.n_groups * 4 * sizeof(int32_t)));
-        CK(cudaMalloc(&s.d_gaf, (S + 1) * (size_t)ctx->prm.n_groups * 4 * sizeof(double)));
+        CK(bvc::gmalloc(&s.d_sample, (R + 4) * sizeof(uint32_t)));
+        CK(bvc::gmalloc(&s.d_gdepth, (S + 1) * (size_t)ctx->prm.n_groups * 4 * sizeof(int32_t)));
+        CK(bvc::gmalloc(&s.d_gaf, (S + 1) * (size_t)ctx->prm.n_groups * 4 * sizeof(double)));
     }
-    CK(cudaMalloc(&s.d_out, (S + 1) * sizeof(bvc_site_result)));
-    CK(cudaMalloc(&s.d_counter, sizeof(unsigned int)));
+    CK(bvc::gmalloc(&s.d_out, (S + 1) * sizeof(bvc_site_result)));
+    CK(bvc::gmalloc(&s.d_counter, sizeof(unsigned int)));
     const size_t pool = bvc::pool_words(ctx);
-    CK(cudaMalloc(&s.d_sum, (S + 1) * sizeof(bvc::SiteSum)));
-    CK(cudaMalloc(&s.d_cls, (pool + 64) * sizeof(uint32_t)));
-    CK(cudaMalloc(&s.d_lad, (S + 1) * sizeof(bvc::Ladder)));
-    CK(cudaMalloc(&s.d_fit, (S + 1) * 4 * sizeof(bvc::FitRes)));
-    CK(cudaMalloc(&s.d_state, S + 16));
-    CK(cudaMalloc(&s.d_qa, (4 * S + 16) * sizeof(uint32_t)));
-    CK(cudaMalloc(&s.d_qb, (4 * S + 16) * sizeof(uint32_t)));
-    CK(cudaMalloc(&s.d_qs, (4 * S + 16) * sizeof(uint32_t)));
-    CK(cudaMalloc(&s.d_ql, (4 * S + 16) * sizeof(uint32_t)));
-    CK(cudaMalloc(&s.d_vcf_list, (S + 16) * sizeof(uint32_t)));
-    CK(cudaMalloc(&s.d_legacy_list, (S + 16) * sizeof(uint32_t)));
-    CK(cudaMalloc(&s.d_ctr, kCtrWords * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&s.d_sum, (S + 1) * sizeof(bvc::SiteSum)));
+    CK(bvc::gmalloc(&s.d_cls, (pool + 64) * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&s.d_lad, (S + 1) * sizeof(bvc::Ladder)));
+    CK(bvc::gmalloc(&s.d_fit, (S + 1) * 4 * sizeof(bvc::FitRes)));
+    CK(bvc::gmalloc(&s.d_state, S + 16));
+    CK(bvc::gmalloc(&s.d_qa, (4 * S + 16) * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&s.d_qb, (4 * S + 16) * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&s.d_qs, (4 * S + 16) * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&s.d_ql, (4 * S + 16) * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&s.d_vcf_list, (S + 16) * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&s.d_legacy_list, (S + 16) * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&s.d_ctr, kCtrWords * sizeof(uint32_t)));
     CK(cudaHostAlloc(&s.h_err, sizeof(uint32_t), cudaHostAllocDefault));
     *s.h_err = 0;
     return BVC_OK;
@@ -67,11 +137,11 @@ int alloc_slot(bvc_ctx* ctx, Slot& s)
 
 void free_slot(Slot& s)
 {
-    cudaFree(s.d_ref); cudaFree(s.d_off); cudaFree(s.d_code); cudaFree(s.d_qual); cudaFree(s.d_mapq);
-    cudaFree(s.d_rpr); cudaFree(s.d_pk8); cudaFree(s.d_sample); cudaFree(s.d_core); cudaFree(s.d_vcfc); cudaFree(s.d_vcfc_n);
-    if (s.h_vcfc_n) cudaFreeHost(s.h_vcfc_n); if (s.h_err) cudaFreeHost(s.h_err); cudaFree(s.d_gdepth); cudaFree(s.d_gaf); cudaFree(s.d_out); cudaFree(s.d_counter);
-    cudaFree(s.d_sum); cudaFree(s.d_cls); cudaFree(s.d_lad); cudaFree(s.d_fit); cudaFree(s.d_state);
-    cudaFree(s.d_qa); cudaFree(s.d_qb); cudaFree(s.d_qs); cudaFree(s.d_ql); cudaFree(s.d_vcf_list); cudaFree(s.d_legacy_list); cudaFree(s.d_ctr);
+    bvc::gfree(s.d_ref); bvc::gfree(s.d_off); bvc::gfree(s.d_code); bvc::gfree(s.d_qual); bvc::gfree(s.d_mapq);
+    bvc::gfree(s.d_rpr); bvc::gfree(s.d_pk8); bvc::gfree(s.d_sample); bvc::gfree(s.d_core); bvc::gfree(s.d_vcfc); bvc::gfree(s.d_vcfc_n);
+    if (s.h_vcfc_n) cudaFreeHost(s.h_vcfc_n); if (s.h_err) cudaFreeHost(s.h_err); bvc::gfree(s.d_gdepth); bvc::gfree(s.d_gaf); bvc::gfree(s.d_out); bvc::gfree(s.d_counter);
+    bvc::gfree(s.d_sum); bvc::gfree(s.d_cls); bvc::gfree(s.d_lad); bvc::gfree(s.d_fit); bvc::gfree(s.d_state);
+    bvc::gfree(s.d_qa); bvc::gfree(s.d_qb); bvc::gfree(s.d_qs); bvc::gfree(s.d_ql); bvc::gfree(s.d_vcf_list); bvc::gfree(s.d_legacy_list); bvc::gfree(s.d_ctr);
     if (s.done) cudaEventDestroy(s.done);
     if (s.stream) cudaStreamDestroy(s.stream);
     s = Slot();
@@ -304,8 +374,8 @@ int bvc_create(bvc_ctx** out, int device, const bvc_params* prm)
         if (e == cudaSuccess) return true;
         ctx->err = std::string(what) + ": " + cudaGetErrorString(e); return false;
     };
-    if (!ck(cudaMalloc(&ctx->d_lut, lut.size() * sizeof(double)), "cudaMalloc lut") ||
-        !ck(cudaMalloc(&ctx->d_lgam, lgam.size() * sizeof(double)), "cudaMalloc lgam") ||
+    if (!ck(bvc::gmalloc(&ctx->d_lut, lut.size() * sizeof(double)), "cudaMalloc lut") ||
+        !ck(bvc::gmalloc(&ctx->d_lgam, lgam.size() * sizeof(double)), "cudaMalloc lgam") ||
         !ck(cudaMemcpy(ctx->d_lut, lut.data(), lut.size() * sizeof(double), cudaMemcpyHostToDevice), "copy lut") ||
         !ck(cudaMemcpy(ctx->d_lgam, lgam.data(), lgam.size() * sizeof(double), cudaMemcpyHostToDevice), "copy lgam"))
         return fail(BVC_ERR_CUDA);
@@ -313,11 +383,13 @@ int bvc_create(bvc_ctx** out, int device, const bvc_params* prm)
         for (int i = 0; i < prm->n_samples; ++i)
             if (ctx->sample_group[(size_t)i] >= prm->n_groups) { ctx->err = "bvc_create: sample_group id out of range"; return fail(BVC_ERR_ARG); }
         if (ctx->legacy_only) { ctx->err = "bvc_create: BVC_LEGACY_KERNEL=1 does not serve the --group path"; return fail(BVC_ERR_ARG); }
-        if (!ck(cudaMalloc(&ctx->d_sample_group, (size_t)prm->n_samples * sizeof(int32_t)), "cudaMalloc sample_group") ||
+        if (!ck(bvc::gmalloc(&ctx->d_sample_group, (size_t)prm->n_samples * sizeof(int32_t)), "cudaMalloc sample_group") ||
             !ck(cudaMemcpy(ctx->d_sample_group, ctx->sample_group.data(), (size_t)prm->n_samples * sizeof(int32_t), cudaMemcpyHostToDevice), "copy sample_group"))
             return fail(BVC_ERR_CUDA);
     }
     for (int i = 0; i < 2; ++i) { int rc = alloc_slot(ctx, ctx->slot[i]); if (rc != BVC_OK) return fail(rc); }
+    { const char* e = getenv("BVC_GUARD_SELFTEST");             // positive control of BVC_GUARD=1: one byte behind slot 0's site counter
+      if (e && e[0] == '1') cudaMemset(reinterpret_cast<unsigned char*>(ctx->slot[0].d_counter) + sizeof(unsigned int), 0, 1); }
     *out = ctx;
     return BVC_OK;
 }
@@ -326,9 +398,11 @@ void bvc_destroy(bvc_ctx* ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    for (int i = 0; i < 2; ++i) { if (ctx->slot[i].stream) cudaStreamSynchronize(ctx->slot[i].stream); free_slot(ctx->slot[i]); }
+    for (int i = 0; i < 2; ++i) if (ctx->slot[i].stream) cudaStreamSynchronize(ctx->slot[i].stream);
+    if (bvc::guard_verify(nullptr) != BVC_OK) abort();          // BVC_GUARD=1 only: an out-of-bounds write nobody waited for
+    for (int i = 0; i < 2; ++i) free_slot(ctx->slot[i]);
     bvc::shard_free(ctx);
-    cudaFree(ctx->d_lut); cudaFree(ctx->d_lgam); cudaFree(ctx->d_flush); cudaFree(ctx->d_sample_group);
+    bvc::gfree(ctx->d_lut); bvc::gfree(ctx->d_lgam); bvc::gfree(ctx->d_flush); bvc::gfree(ctx->d_sample_group);
     delete ctx;
 }
 
@@ -340,6 +414,7 @@ static int retire_slot(bvc_ctx* ctx, bvc::Slot& s)
 {
     if (!s.ticket) return BVC_OK;
     CK(cudaStreamSynchronize(s.stream));
+    { const int g = bvc::guard_verify(ctx); if (g != BVC_OK) { s.ticket = 0; return g; } }
     if (s.n_sites && *s.h_err) {
         s.retired_ticket = s.ticket; s.retired_n = 0; s.retired_rc = BVC_ERR_ARG;
         s.ticket = 0;
@@ -397,9 +472,9 @@ int bvc_enqueue_split(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_core* core, b
     if ((rc = retire_slot(ctx, s)) != BVC_OK) return rc;
     if (!s.d_core) {                                   // first split call on this slot
         const size_t S = (size_t)ctx->prm.max_sites;
-        CK(cudaMalloc(&s.d_core, (S + 1) * sizeof(bvc_site_core)));
-        CK(cudaMalloc(&s.d_vcfc, (S + 1) * sizeof(bvc_site_result)));
-        CK(cudaMalloc(&s.d_vcfc_n, sizeof(uint32_t)));
+        CK(bvc::gmalloc(&s.d_core, (S + 1) * sizeof(bvc_site_core)));
+        CK(bvc::gmalloc(&s.d_vcfc, (S + 1) * sizeof(bvc_site_result)));
+        CK(bvc::gmalloc(&s.d_vcfc_n, sizeof(uint32_t)));
         CK(cudaHostAlloc(&s.h_vcfc_n, sizeof(uint32_t), cudaHostAllocDefault));
     }
     if ((rc = upload(ctx, s, tile, R, false)) != BVC_OK) return rc;
@@ -504,7 +579,7 @@ int bvc_resident_run(bvc_ctx* ctx, int iters, int flush_l2, float* ms_per_launch
     if (!ctx->resident || iters <= 0) { set_err(ctx, "bvc_resident_run: no resident tile / iters <= 0"); return BVC_ERR_STATE; }
     CK(cudaSetDevice(ctx->device));
     Slot& s = ctx->slot[0];
-    if (flush_l2 && !ctx->d_flush) { ctx->flush_bytes = (size_t)256 << 20; CK(cudaMalloc(&ctx->d_flush, ctx->flush_bytes)); }
+    if (flush_l2 && !ctx->d_flush) { ctx->flush_bytes = (size_t)256 << 20; CK(bvc::gmalloc(&ctx->d_flush, ctx->flush_bytes)); }
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     // per-kernel breakdown: an event before every launch (only when asked for: the records sit between kernels)
@@ -568,7 +643,7 @@ int bvc_resident_download(bvc_ctx* ctx, bvc_site_result* out)
     Slot& s = ctx->slot[0];
     CK(cudaStreamSynchronize(s.stream));
     if (s.n_sites) CK(cudaMemcpy(out, s.d_out, (size_t)s.n_sites * sizeof(bvc_site_result), cudaMemcpyDeviceToHost));
-    return BVC_OK;
+    return bvc::guard_verify(ctx);
 }
 
 int64_t bvc_kernel_launch_count(const bvc_ctx* ctx) { return ctx ? ctx->launches : 0; }
@@ -584,7 +659,7 @@ int bvc_measure_fp64_peak(int device, double* tflops)
     CK(cudaGetDeviceProperties(&prop, device));
     const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 15;
     double* d = nullptr;
-    CK(cudaMalloc(&d, (size_t)blocks * threads * sizeof(double)));
+    CK(bvc::gmalloc(&d, (size_t)blocks * threads * sizeof(double)));
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     float best = 1e30f;
@@ -597,7 +672,7 @@ int bvc_measure_fp64_peak(int device, double* tflops)
         CK(cudaEventElapsedTime(&ms, e0, e1));
         if (rep > 0 && ms < best) best = ms;
     }
-    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); bvc::gfree(d);
     *tflops = 2.0 * 8.0 * (double)iters * blocks * threads / (best * 1e-3) / 1e12;
     return BVC_OK;
 }

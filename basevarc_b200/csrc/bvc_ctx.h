@@ -97,6 +97,13 @@ size_t pool_words(const bvc_ctx* ctx);         // capacity of a slot's class poo
 // the argument blocks of the kernels over the slot's buffers
 void fill_args(const bvc_ctx* ctx, const Slot& s, SiteArgs& a, PipeArgs& p);
 void shard_free(bvc_ctx* ctx);                 // called by bvc_destroy
+// Device allocations of the library.  BVC_GUARD=1 (debug; compute-sanitizer is not available on every pool): every allocation
+// gets a 4 KB band of 0xA5 on both sides and the whole of it is pre-filled with 0xA5; guard_verify() reads all bands of the
+// process back and names the first one a kernel wrote into (bvc_wait / bvc_wait_split / bvc_shard_* / bvc_destroy call it).
+cudaError_t gmalloc_bytes(void** p, size_t bytes);
+template <class T> inline cudaError_t gmalloc(T** p, size_t bytes) { return gmalloc_bytes(reinterpret_cast<void**>(p), bytes); }
+cudaError_t gfree(void* p);
+int guard_verify(bvc_ctx* ctx);                // BVC_OK, or BVC_ERR_CUDA with the error text set
 
 }  // namespace bvc
 

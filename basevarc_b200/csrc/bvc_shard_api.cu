@@ -87,7 +87,7 @@ void shard_free(bvc_ctx* ctx)
     ShardState* st = ctx->shard;
     if (!st) return;
     if (st->comm) nccl_api()->CommDestroy(st->comm);
-    cudaFree(st->d_dense); cudaFree(st->d_mask_all); cudaFree(st->d_pos_list); cudaFree(st->d_flags); cudaFree(st->d_hv);
+    bvc::gfree(st->d_dense); bvc::gfree(st->d_mask_all); bvc::gfree(st->d_pos_list); bvc::gfree(st->d_flags); bvc::gfree(st->d_hv);
     if (st->h_flags) cudaFreeHost(st->h_flags);
     for (auto& e : st->ev) if (e) cudaEventDestroy(e);
     delete st;
@@ -108,10 +108,10 @@ static int shard_alloc(bvc_ctx* ctx, int rank, int world, int qlo, int qhi, bool
     st->B = kShardHdr + 8 * (qhi - qlo + 1);
     st->sr_cap = (ctx->prm.max_sites + world - 1) / world;
     const size_t n_pad = (size_t)world * st->sr_cap;
-    CK(cudaMalloc(&st->d_dense, n_pad * st->B * sizeof(uint32_t)));
-    CK(cudaMalloc(&st->d_mask_all, n_pad + 16));
-    CK(cudaMalloc(&st->d_pos_list, (n_pad + 16) * sizeof(uint32_t)));
-    CK(cudaMalloc(&st->d_flags, 4 * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&st->d_dense, n_pad * st->B * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&st->d_mask_all, n_pad + 16));
+    CK(bvc::gmalloc(&st->d_pos_list, (n_pad + 16) * sizeof(uint32_t)));
+    CK(bvc::gmalloc(&st->d_flags, 4 * sizeof(uint32_t)));
     CK(cudaHostAlloc(&st->h_flags, 4 * sizeof(uint32_t), cudaHostAllocDefault));
     for (auto& e : st->ev) CK(cudaEventCreate(&e));
     // the class pool must hold every (base, qual) class of the owned sites, whatever the local entry capacity
@@ -120,8 +120,8 @@ static int shard_alloc(bvc_ctx* ctx, int rank, int world, int qlo, int qhi, bool
     const size_t have = (R < S * (size_t)kNBins ? R : S * (size_t)kNBins) + 8 * S;
     const size_t need = (size_t)st->sr_cap * (4 * (size_t)(qhi - qlo + 1) + 8);
     if (need > have) {
-        CK(cudaFree(s.d_cls)); s.d_cls = nullptr;
-        CK(cudaMalloc(&s.d_cls, (need + 64) * sizeof(uint32_t)));
+        CK(bvc::gfree(s.d_cls)); s.d_cls = nullptr;
+        CK(bvc::gmalloc(&s.d_cls, (need + 64) * sizeof(uint32_t)));
     }
     return BVC_OK;
 }
@@ -207,8 +207,8 @@ static int shard_phase_vcf_hist(bvc_ctx* ctx)
     if (st->n_pos > st->hv_cap) {
         size_t cap = st->hv_cap ? st->hv_cap : 1024;
         while (cap < st->n_pos) cap *= 2;
-        CK(cudaFree(st->d_hv)); st->d_hv = nullptr; st->hv_cap = 0;
-        CK(cudaMalloc(&st->d_hv, cap * kVcfHistWords * sizeof(uint32_t)));
+        CK(bvc::gfree(st->d_hv)); st->d_hv = nullptr; st->hv_cap = 0;
+        CK(bvc::gmalloc(&st->d_hv, cap * kVcfHistWords * sizeof(uint32_t)));
         st->hv_cap = cap;
     }
     st->a.hv = st->d_hv;
@@ -238,7 +238,7 @@ static int shard_phase_finish(bvc_ctx* ctx, bvc_site_result* out, int32_t* first
     if (first_site) *first_site = st->a.rank * st->a.Sr;
     if (n_out) *n_out = st->a.n_own;
     if (st->h_flags[1] & 1u) return BVC_ERR_ARG;
-    return BVC_OK;
+    return guard_verify(ctx);
 }
 
 // ---- NCCL run: the phases with the three collectives between them --------------------------------------------

@@ -48,6 +48,52 @@ def main():
     t = B.synth_tile(64, 400, 1.5, "highpoly", seed=13, indel_frac=0.1)
     q = t.qual.copy(); q[::17] = 0; q[::19] = 1; t.qual = q
     check("qual 0 / 1 (legacy kernel)", t, False)
+    # --group (bvc_groups.cuh)
+    t = B.synth_tile(300, 500, 1.0, "highpoly", seed=14)
+    sg = (np.arange(300) % 4 - 1).astype(np.int32)            # groups 0..2 and -1 (no group)
+    c = B.BaseTypeCaller(300, max_sites=t.n_sites, max_entries=t.n_entries, sample_group=sg, n_groups=3)
+    got, gd, ga = c.call_sites_with_groups(t)
+    c.close()
+    want = oracle_py.call_sites(t, B.default_params(300))
+    nbad, lines = compare_records(got, want, max_flagged_fraction=0.1)
+    assert nbad == 0 and gd.sum() > 0, "\n".join(lines)
+    print("--group, 3 groups: ok", flush=True)
+    # sample-sharded mode, in-process exchange (bvc_shard.cuh), 3 ranks, ragged last slice
+    t = B.synth_tile(30000, 50, 0.1, "highpoly", seed=15)
+    shards = t.shard_samples(3)
+    g = B.ShardGroup(t.n_samples, 3, max_sites=t.n_sites, max_entries=max(x.n_entries for x in shards))
+    got = g.call_sites(shards)
+    g.close()
+    want = oracle_py.call_sites(t, B.default_params(t.n_samples))
+    nbad, lines = compare_records(got, want, max_flagged_fraction=0.1)
+    assert nbad == 0, "\n".join(lines)
+    print("sample-sharded x3 (in-process exchange): ok", flush=True)
+    # bvc_call_sites_noalloc (static scratch array), two calls in a row; device memory through cudart (bvc_host_alloc is pinned
+    # HOST memory the kernels read in place: no torch needed under the sanitizer)
+    import ctypes as C
+    from basevarc_b200 import caller as bc
+    from basevarc_b200._abi import SITE_RESULT_DTYPE
+    for seed in (16, 17):
+        t = B.synth_tile(200, 800, 0.8, "highpoly", seed=seed, indel_frac=0.02)
+        bufs = {}
+        for k in ("ref_base", "entry_off", "code", "qual", "mapq", "rpr"):
+            a = getattr(t, k)
+            bufs[k] = bc.PinnedArray(a.shape, a.dtype)
+            bufs[k].array[...] = a
+        out = bc.PinnedArray((t.n_sites,), SITE_RESULT_DTYPE)
+        st = bc.PinnedArray((1,), np.uint32)
+        st.array[0] = 99
+        bc.call_sites_noalloc(B.default_params(200), t.n_sites, t.n_entries, *(bufs[k].ptr for k in ("ref_base", "entry_off", "code", "qual", "mapq", "rpr")),
+                              out.ptr, st.ptr, None)
+        rt = C.CDLL("/usr/local/cuda/lib64/libcudart.so.12")
+        assert rt.cudaDeviceSynchronize() == 0
+        c = B.BaseTypeCaller(200, max_sites=t.n_sites, max_entries=t.n_entries)
+        ref = c.call_sites(t)
+        c.close()
+        assert int(st.array[0]) == 0
+        nbad, lines = compare_records(out.array.copy(), ref, max_flagged_fraction=0.1)
+        assert nbad == 0, "\n".join(lines)
+    print("bvc_call_sites_noalloc x2: ok", flush=True)
     print("sanitize_run: all tiles agree with the oracle")
 
 
