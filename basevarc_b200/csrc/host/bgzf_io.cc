@@ -1,6 +1,8 @@
 // bgzf_io.cc -- see bgzf_io.hpp
 #include "bgzf_io.hpp"
+#include "fast_inflate.hpp"
 
+#include <stdlib.h>
 #include <string.h>
 #include <zlib.h>
 
@@ -37,8 +39,9 @@ bool BgzfReader::open(const std::string& path, std::string* err)
     f_ = fopen(path.c_str(), "rb");
     if (!f_) { if (err) *err = "cannot open " + path; return false; }
     setvbuf(f_, nullptr, _IOFBF, 1 << 20);
-    comp_.resize(kMaxBlock);
-    buf_.resize(kMaxBlock);
+    comp_.resize(kMaxBlock + kFastInflateInPad);
+    buf_.resize(kMaxBlock + kFastInflateOutSlack);
+    { const char* e = getenv("BVC_ZLIB_INFLATE"); use_fast_ = !(e && e[0] == '1'); }
     pos_ = len_ = 0; failed_ = eof_ = false; carry_.clear(); err_.clear();
     return true;
 }
@@ -73,6 +76,12 @@ bool BgzfReader::fill()
         const size_t isize = rd32(h + bsize - 4);
         if (isize > kMaxBlock) { failed_ = true; err_ = "bad BGZF ISIZE"; return false; }
         if (isize == 0) continue;              // empty block (EOF marker or flush point)
+        // the whole-buffer decoder first (fast_inflate.hpp); whatever it declines -- or gets wrong by the CRC -- goes to zlib
+        size_t fast_len = 0;
+        const bool fast_ok = use_fast_ && fast_inflate(h + head, rest - 8, reinterpret_cast<uint8_t*>(buf_.data()), kMaxBlock, &fast_len) && fast_len == isize &&
+                             fast_crc32(reinterpret_cast<const uint8_t*>(buf_.data()), isize) == rd32(h + bsize - 8);
+        if (fast_ok) { pos_ = 0; len_ = isize; return true; }
+        if (use_fast_) ++zlib_blocks_;
         if (!zs_) {
             z_stream* z = new z_stream;
             memset(z, 0, sizeof *z);
@@ -84,7 +93,7 @@ bool BgzfReader::fill()
         zs.next_out = reinterpret_cast<Bytef*>(buf_.data()); zs.avail_out = (uInt)kMaxBlock;
         const int rc = inflate(&zs, Z_FINISH);
         if (rc != Z_STREAM_END || zs.total_out != isize) { failed_ = true; err_ = "inflate failed"; return false; }
-        if ((uint32_t)crc32(crc32(0L, Z_NULL, 0), reinterpret_cast<const Bytef*>(buf_.data()), (uInt)isize) != rd32(h + bsize - 8)) {
+        if (fast_crc32(reinterpret_cast<const uint8_t*>(buf_.data()), isize) != rd32(h + bsize - 8)) {
             failed_ = true; err_ = "BGZF CRC mismatch"; return false;
         }
         pos_ = 0; len_ = isize;
@@ -169,7 +178,7 @@ bool BgzfWriter::flush_block(const char* data, size_t n)
     }
     const size_t clen = zs.total_out, bsize = 18 + clen + 8;
     wr16(out + 16, (uint16_t)(bsize - 1));
-    wr32(out + 18 + clen, (uint32_t)crc32(crc32(0L, Z_NULL, 0), reinterpret_cast<const Bytef*>(data), (uInt)n));
+    wr32(out + 18 + clen, fast_crc32(reinterpret_cast<const uint8_t*>(data), n));
     wr32(out + 18 + clen + 4, (uint32_t)n);
     return sink(out, bsize);
 }

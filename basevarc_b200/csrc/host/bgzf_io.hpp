@@ -32,6 +32,8 @@ public:
     bool getline_view(const char** ptr, size_t* len);
     bool failed() const { return failed_; }
     const std::string& error() const { return err_; }
+    // blocks the whole-buffer decoder declined and zlib inflated instead (0 on well-formed files; BVC_ZLIB_INFLATE=1: zlib only)
+    size_t zlib_blocks() const { return zlib_blocks_; }
 
 private:
     bool fill();            // inflate the next non-empty block into buf_
@@ -40,7 +42,8 @@ private:
     std::vector<char> buf_;
     size_t pos_ = 0, len_ = 0;
     std::string carry_;     // a line that spans blocks
-    bool failed_ = false, eof_ = false;
+    bool failed_ = false, eof_ = false, use_fast_ = true;
+    size_t zlib_blocks_ = 0;
     std::string err_;
     void* zs_ = nullptr;    // z_stream kept across blocks (inflateReset instead of init / end per block)
 };

@@ -5,6 +5,7 @@
 
 #include "../../../include/bvc_host.h"
 #include "format.hpp"
+#include "fast_inflate.hpp"
 #include "packed_io.hpp"
 #include "packer.hpp"
 #include <sys/stat.h>
@@ -74,6 +75,21 @@ const char* bvc_packed_names(const bvc_packed_reader* r) { return r ? r->io.name
 const char* bvc_packed_error(const bvc_packed_reader* r) { return r ? r->err.c_str() : "no reader"; }
 void bvc_packed_close(bvc_packed_reader* r) { delete r; }
 int bvc_packed_is_complete(const char* path, int32_t n_samples) { return path && bvc_host::PackedIo::is_complete(path, n_samples) ? 1 : 0; }
+
+int bvc_fast_inflate(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_cap, size_t* out_len)
+{
+    if ((!in && in_len) || (!out && out_cap) || !out_len) return 0;
+    // the decoder wants readable padding behind the input and writable slack behind the output: private copies
+    std::vector<uint8_t> ib(in_len + bvc_host::kFastInflateInPad, 0), ob(out_cap + bvc_host::kFastInflateOutSlack);
+    if (in_len) memcpy(ib.data(), in, in_len);
+    size_t n = 0;
+    if (!bvc_host::fast_inflate(ib.data(), in_len, ob.data(), out_cap, &n) || n > out_cap) return 0;
+    if (n) memcpy(out, ob.data(), n);
+    *out_len = n;
+    return 1;
+}
+
+uint32_t bvc_fast_crc32(const uint8_t* buf, size_t len) { return bvc_host::fast_crc32(buf, len); }
 
 int bvc_write_packed_files(const bvc_tile* t, int32_t n_samples, const int32_t* pos, const char* prefix, int32_t threads,
                            int32_t tile_sites, const char* indel_token)

@@ -65,6 +65,7 @@ const char* kUsage =
     "  --pack                   Convert the text batch files into packed tile files (PREFIX.tmp.thread.{t}/packed.bvc; no GPU\n"
     "                           needed); --rerun reads them instead of the text files whenever every window has one\n"
     "  --no_packed              --rerun from the text batch files even if packed tile files exist\n"
+    "  --pending_mb <INT>       Host memory (MiB, all windows together) for tiles packed ahead while the GPU starts up [2048]\n"
     "  --shard_samples <INT>    Sample-sharded calling for very wide cohorts: rank r of W reads the batch files [r*J/W, (r+1)*J/W)\n"
     "                           of every window, one GPU per rank with NCCL (fewer GPUs than ranks: all ranks on GPU 0)\n";
 
@@ -98,6 +99,7 @@ struct Options {
     int shard_samples = 0;                     // --shard_samples W: the sample-sharded compute phase over W ranks (shard_rerun.inc)
     bool pack = false, no_packed = false;      // --pack: text batch files -> packed tile files (no GPU); --no_packed: ignore packed files
     int mapq = 10, thread = 1, batch = 10, gpus = 0, tile_sites = 0;
+    int pending_mb = 2048;                     // --pending_mb: host memory all windows together may hold in tiles waiting for the GPU
     double maf = 0.001;
     std::string input, reference, group, region, output;
 };
@@ -115,7 +117,7 @@ bool parse_options(int argc, char** argv, Options& o)
         {"load", no_argument, nullptr, 7},            {"keep_tmp", no_argument, nullptr, 6},
         {"gpus", required_argument, nullptr, 1},      {"tile_sites", required_argument, nullptr, 2},
         {"pack", no_argument, nullptr, 3},            {"no_packed", no_argument, nullptr, 4},
-        {"shard_samples", required_argument, nullptr, 5},
+        {"shard_samples", required_argument, nullptr, 5}, {"pending_mb", required_argument, nullptr, 9},
         {nullptr, 0, nullptr, 0}};
     bool die = false;
     optind = 1;
@@ -140,6 +142,7 @@ bool parse_options(int argc, char** argv, Options& o)
         case 3: o.pack = true; break;
         case 4: o.no_packed = true; break;
         case 5: o.shard_samples = atoi(a); break;
+        case 9: o.pending_mb = atoi(a); break;
         case 'v': o.verbose = true; break;
         default: die = true;
         }
@@ -364,6 +367,8 @@ struct Shared {
     bool packed_in = false;                 // the windows are read from packed tile files (PREFIX.tmp.thread.{t}/packed.bvc)
     std::string sams;                       // sample names, tab-separated (with --pack: stored in every packed file)
     int64_t tile_entries = 0;
+    int max_jobs = 2;                       // tiles a window may hold (filled, in flight or being filled): 2 + what --pending_mb allows
+    std::atomic<int> max_jobs_used{0};
     int n_groups = 0;
     std::vector<std::string> group_names;
     std::vector<const char*> group_name_ptrs;
@@ -414,35 +419,45 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
     size_t it = std::min(P, (size_t)ithread * window);
     const size_t it_end = (ithread == T - 1) ? P : std::min(P, (size_t)(ithread + 1) * window);
 
-    TileJob jobs[2] = {TileJob(sh->N), TileJob(sh->N)};
-    for (auto& j : jobs) {
-        // fixed capacity (a tile is flushed before it can outgrow it): no reallocation while a window is packed
-        j.pk.reserve((size_t)sh->tile_entries + 2 * (size_t)sh->N + 64);
+    // Jobs of this window: `fly` = submitted and not yet formatted, in site order; `idle` = free to fill.  Two jobs are the steady
+    // state (the GPU is far ahead of the packer); while the GPU is BEHIND -- CUDA start-up takes 0.6-1.0 s, a whole window's worth
+    // of packing for a small job -- the worker does not wait for its oldest job but takes another one, up to sh->max_jobs (the
+    // host-memory budget --pending_mb split over the windows), and keeps packing.
+    std::vector<std::unique_ptr<TileJob>> all_jobs;
+    std::deque<TileJob*> fly;
+    std::vector<TileJob*> idle;
+    auto new_job = [&]() -> TileJob* {
+        all_jobs.emplace_back(new TileJob(sh->N));
+        TileJob& j = *all_jobs.back();
+        // text input: fixed capacity (a tile is flushed before it can outgrow it), no reallocation while a window is packed;
+        // packed input: PackedIo::next_tile sizes the arrays to the tile it reads
+        if (!sh->packed_in) j.pk.reserve((size_t)sh->tile_entries + 2 * (size_t)sh->N + 64);
         if (sh->n_groups == 0) { j.core.resize((size_t)sh->tile_sites + 1); j.vcf.resize((size_t)sh->tile_sites + 1); }
-    }
-    // the two packers share ONE stale-token state in the reference (a single `ai` per window): hand it over by
+        return &j;
+    };
+    // the packers share ONE stale-token state in the reference (a single `ai` per window): hand it over by
     // packing strictly in site order and copying the state forward (Packer::adopt_state)
-    int cur = 0, count = 0;
+    int count = 0;
     long long t_read = 0, t_pack = 0, t_wait = 0, t_format = 0, t_write = 0;
-    bool pending[2] = {false, false};
     std::string vline, cline;
     // whatever way this function is left, no job may still be queued or in flight in the dispatcher: it writes the job's
     // records, status and condition variable, and bvc_enqueue's device-to-host copies target the job's arrays
     struct PendingGuard {
-        TileJob* jobs; bool* pending;
+        std::deque<TileJob*>* fly;
         ~PendingGuard()
         {
-            for (int k = 0; k < 2; ++k)
-                if (pending[k]) { std::unique_lock<std::mutex> lk(jobs[k].m); jobs[k].cv.wait(lk, [&] { return jobs[k].done; }); pending[k] = false; }
+            for (TileJob* j : *fly) { std::unique_lock<std::mutex> lk(j->m); j->cv.wait(lk, [&] { return j->done; }); }
+            fly->clear();
         }
-    } guard{jobs, pending};
+    } guard{&fly};
 
-    auto drain = [&](int k) -> bool {                         // wait for job k, format its sites, release it
-        TileJob& j = jobs[k];
+    auto drain = [&]() -> bool {                              // wait for the oldest job in flight, format its sites, release it
+        TileJob& j = *fly.front();
         const long long tw = now_ns();
         { std::unique_lock<std::mutex> lk(j.m); j.cv.wait(lk, [&] { return j.done; }); }
         t_wait += now_ns() - tw;
-        pending[k] = false;
+        fly.pop_front();
+        idle.push_back(&j);
         if (j.rc != BVC_OK) { sh->fail("GPU call failed: " + j.err); return false; }
         bvc_tile t;
         j.pk.tile(&t);
@@ -481,16 +496,26 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
         }
         return true;
     };
-    auto flush = [&](int k) {                                 // hand job k to the GPU
-        TileJob& j = jobs[k];
+    auto flush = [&](TileJob& j) {                            // hand a job to the GPU
         if (sh->n_groups) {
             j.rec.resize((size_t)j.pk.n_sites());
             j.group_depth.assign((size_t)j.pk.n_sites() * sh->n_groups * 4, 0);
             j.group_af.assign((size_t)j.pk.n_sites() * sh->n_groups * 4, 0.0);
         }
         j.done = false;
-        pending[k] = true;
+        fly.push_back(&j);
         gpu->submit(&j);
+    };
+    auto is_done = [](TileJob& j) { std::lock_guard<std::mutex> lk(j.m); return j.done; };
+    // a job to fill next: an idle one; else the oldest in flight if the GPU has finished it (or no further job may be taken)
+    auto take_job = [&]() -> TileJob* {
+        while (idle.empty()) {
+            if (!fly.empty() && (is_done(*fly.front()) || (int)all_jobs.size() >= std::max(2, sh->max_jobs))) { if (!drain()) return nullptr; }
+            else return new_job();
+        }
+        TileJob* j = idle.back();
+        idle.pop_back();
+        return j;
     };
 
     // one tile into job k: sites of the window until the tile is full or the window ends.  1: more input may follow, 0: the
@@ -526,7 +551,7 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
     };
     if (o.pack) {
         // --pack: the same read + tokenise loop, the tiles go to PREFIX.tmp.thread.{t}/packed.bvc instead of the GPU
-        TileJob& j = jobs[0];
+        TileJob& j = *new_job();
         for (int more = 1; more > 0 && !sh->failed;) {
             more = fill_text(j);
             if (more < 0) return;
@@ -539,20 +564,23 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
         sh->ns_read += t_read; sh->ns_pack += t_pack;
         return;
     }
+    TileJob* prev = nullptr;
     for (int more = 1; more > 0 && !sh->failed;) {
-        TileJob& j = jobs[cur];
-        more = sh->packed_in ? fill_packed(j) : fill_text(j);
-        if (more < 0) return;
-        if (j.pk.n_sites() == 0) continue;
-        flush(cur);
-        const int other = cur ^ 1;
-        if (pending[other] && !drain(other)) return;
-        jobs[other].pk.clear();
-        jobs[other].pk.adopt_state(jobs[cur].pk);
-        cur = other;
+        TileJob* j = take_job();
+        if (!j) return;
+        j->pk.clear();
+        if (prev) j->pk.adopt_state(prev->pk);
+        do {                                                   // (a tile whose sites are all empty is not submitted)
+            more = sh->packed_in ? fill_packed(*j) : fill_text(*j);
+            if (more < 0) return;
+        } while (more > 0 && j->pk.n_sites() == 0 && !sh->failed);
+        if (j->pk.n_sites() == 0) { idle.push_back(j); break; }
+        flush(*j);
+        prev = j;
     }
     if (sh->failed) return;                                   // (the guard waits for what is still in flight)
-    if (pending[cur ^ 1] && !drain(cur ^ 1)) return;          // the tile submitted last
+    while (!fly.empty()) if (!drain()) return;
+    sh->max_jobs_used.store(std::max(sh->max_jobs_used.load(), (int)all_jobs.size()));
     { const long long t0 = now_ns(); wv.close(false); wc.close(false); t_write += now_ns() - t0; }
     sh->ns_read += t_read; sh->ns_pack += t_pack; sh->ns_wait += t_wait; sh->ns_format += t_format; sh->ns_write += t_write;
     *vcf_out = std::move(wv.memory());
@@ -715,6 +743,11 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     sh.tile_sites = o.tile_sites > 0 ? o.tile_sites : (int32_t)std::max<int64_t>(64, std::min<int64_t>(2048, ((int64_t)8 << 20) / sh.N));
     sh.tile_entries = std::max<int64_t>((int64_t)sh.tile_sites * sh.N, 2 * (int64_t)sh.N);
     if (sh.packed_in) { sh.tile_sites = (int32_t)std::max<int64_t>(1, packed_sites); sh.tile_entries = std::max<int64_t>(packed_entries, 2 * (int64_t)sh.N); }
+    {   // a job = the packer's six arrays (9 B per entry of capacity) + the split result arrays
+        const double job_bytes = 9.0 * (double)(sh.tile_entries + 2 * (int64_t)sh.N + 64) + (double)sh.tile_sites * (sizeof(bvc_site_core) + sizeof(bvc_site_result));
+        const double per_window = (double)std::max(0, o.pending_mb) * 1048576.0 / T;
+        sh.max_jobs = (int)std::max(2.0, std::min(64.0, per_window / job_bytes));
+    }
     bvc_params prm;
     bvc_default_params(&prm, sh.N, o.maf);
     prm.max_sites = sh.tile_sites;
@@ -754,9 +787,9 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
         char b[512];
         snprintf(b, sizeof b, "basetype host phases : checks beside CUDA start-up %.3f s, windows (context creation inside) %.3f s wall on %d threads, "
                  "context teardown %.3f s, output files %.3f s; context creation %.3f s, %d tiles, %.3f s inside enqueue / wait; thread-seconds: inflate+getline %.3f, "
-                 "tokenise+pack %.3f, wait for gpu %.3f, format %.3f, bgzf deflate %.3f",
+                 "tokenise+pack %.3f, wait for gpu %.3f, format %.3f, bgzf deflate %.3f; tiles held per window: up to %d of %d allowed",
                  (t_init1 - t_init0) * 1e-9, (t_work1 - t_init1) * 1e-9, T, (t_stop1 - t_work1) * 1e-9, (now_ns() - t_stop1) * 1e-9, create_ns * 1e-9, n_tiles, busy_ns * 1e-9, sh.ns_read * 1e-9, sh.ns_pack * 1e-9, sh.ns_wait * 1e-9,
-                 sh.ns_format * 1e-9, sh.ns_write * 1e-9);
+                 sh.ns_format * 1e-9, sh.ns_write * 1e-9, sh.max_jobs_used.load(), sh.max_jobs);
         std::cout << b << std::endl;
     }
     std::cout << "basetype done" << std::endl;

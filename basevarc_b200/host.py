@@ -23,7 +23,7 @@ HOST_EXPORTS = (
     "bvc_packer_end_site", "bvc_packer_n_sites", "bvc_packer_n_entries", "bvc_packer_tile", "bvc_packer_positions",
     "bvc_packer_indel", "bvc_packer_error", "bvc_format_cvg", "bvc_format_vcf", "bvc_format_fixed", "bvc_basetype_main", "bvc_write_batch_files",
     "bvc_packed_open", "bvc_packed_next", "bvc_packed_names", "bvc_packed_error", "bvc_packed_close", "bvc_packed_is_complete",
-    "bvc_write_packed_files",
+    "bvc_write_packed_files", "bvc_fast_inflate", "bvc_fast_crc32",
 )
 
 _hlib = None
@@ -80,6 +80,9 @@ def load_host_library():
     L.bvc_packed_close.argtypes = [C.c_void_p]
     L.bvc_packed_close.restype = None
     L.bvc_packed_is_complete.argtypes = [C.c_char_p, C.c_int32]
+    L.bvc_fast_inflate.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.bvc_fast_crc32.argtypes = [C.c_char_p, C.c_size_t]
+    L.bvc_fast_crc32.restype = C.c_uint32
     L.bvc_write_packed_files.argtypes = [C.POINTER(Tile), C.c_int32, C.c_void_p, C.c_char_p, C.c_int32, C.c_int32, C.c_char_p]
     _hlib = L
     return L
@@ -196,6 +199,19 @@ def write_batch_files(tile, prefix, threads, batch, level=1, indel_token="+A"):
                                  indel_token.encode())
     if rc != 0:
         raise BvcError("bvc_write_batch_files failed (%d): bad (sites, threads) partition or unwritable prefix" % rc)
+
+
+def fast_inflate(raw, out_cap=65536):
+    """bvc_fast_inflate on a raw deflate stream: the inflated bytes, or None when the decoder declines the stream."""
+    L = load_host_library()
+    out = C.create_string_buffer(max(out_cap, 1))
+    n = C.c_size_t(0)
+    ok = L.bvc_fast_inflate(raw, len(raw), out, out_cap, C.byref(n))
+    return out.raw[:n.value] if ok else None
+
+
+def fast_crc32(data):
+    return int(load_host_library().bvc_fast_crc32(data, len(data)))
 
 
 def write_packed_files(tile, prefix, threads, tile_sites=2048, indel_token="+A"):

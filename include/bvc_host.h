@@ -104,6 +104,17 @@ int  bvc_packed_is_complete(const char* path, int32_t n_samples);
 int  bvc_write_packed_files(const bvc_tile* tile, int32_t n_samples, const int32_t* pos, const char* prefix, int32_t threads,
                             int32_t tile_sites, const char* indel_token);
 
+/* ---- BGZF block decoding --------------------------------------------------------------------
+ * The reference reads its batch files with htslib's bgzf_getline, i.e. zlib's inflate (src/BaseVarC.cpp:407,
+ * SeqLib/htslib/bgzf.c).  The drop-in's reader inflates a block with a whole-buffer DEFLATE decoder written from RFC 1951
+ * (csrc/host/fast_inflate.cc: 2.2x zlib on batch-file text) and checks its CRC-32 by carry-less multiplication; a block the
+ * decoder declines, or whose CRC does not match, is inflated again by zlib, whose answer stands (BVC_ZLIB_INFLATE=1: zlib only).
+ * These two are that decoder and that CRC on caller buffers, for tests:
+ * bvc_fast_inflate: raw deflate stream in[0, in_len) -> out[0, *out_len), 1 = decoded, 0 = declined (malformed stream, output
+ * larger than out_cap, or a construct it leaves to zlib); bvc_fast_crc32 = zlib's crc32(0, buf, len). */
+int bvc_fast_inflate(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_cap, size_t* out_len);
+uint32_t bvc_fast_crc32(const uint8_t* buf, size_t len);
+
 /* ---- the command: `BaseVarC basetype --rerun ...` with the compute phase on the GPU(s) ----------------------
  * argv as the reference's runBaseType sees it (argv[0] = "basetype").  Returns the process exit status. */
 int bvc_basetype_main(int argc, char** argv);
