@@ -6,6 +6,12 @@
 #include <string.h>
 #include <zlib.h>
 
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <thread>
+#include <utility>
+
 namespace bvc_host {
 
 namespace {
@@ -33,30 +39,108 @@ bool bgzf_is_complete(const std::string& path)
 }
 
 // ---- reader ------------------------------------------------------------------------------------------
+// A block goes through two steps: read_block (the file's next non-empty block into a slot: sequential, cheap) and decode_block
+// (inflate + CRC: where the time goes).  Without an inflate pool both run on the caller's thread, one slot.  With a pool
+// (InflatePool::start; the dispatcher starts one when it has fewer window threads than cores) the reader keeps kSlots blocks
+// read ahead and queued for the pool, so the window thread finds its next block already inflated.
+namespace {
+struct ZStream {                     // zlib's verdict on blocks the whole-buffer decoder declines: one stream per thread
+    z_stream z; bool init = false;
+    ~ZStream() { if (init) inflateEnd(&z); }
+};
+thread_local ZStream t_zs;
+}  // namespace
+
+struct BgzfReader::Block {
+    std::vector<unsigned char> comp;
+    std::vector<char> out;
+    size_t head = 0, bsize = 0, isize = 0;
+    int state = 0;                   // 0 free, 1 queued / being decoded, 2 decoded, 3 failed
+    bool used_zlib = false;
+    std::string err;
+};
+
+class InflatePool::Impl {
+public:
+    std::mutex m;
+    std::condition_variable cv;
+    std::deque<std::pair<BgzfReader*, int>> q;
+    std::vector<std::thread> th;
+    bool stop = false;
+    void run()
+    {
+        for (;;) {
+            std::pair<BgzfReader*, int> t;
+            {
+                std::unique_lock<std::mutex> lk(m);
+                cv.wait(lk, [&] { return stop || !q.empty(); });
+                if (q.empty()) return;
+                t = q.front(); q.pop_front();
+            }
+            t.first->decode_slot(t.second);
+        }
+    }
+};
+
+InflatePool& InflatePool::instance() { static InflatePool p; return p; }
+InflatePool::~InflatePool() { stop(); }
+int InflatePool::threads() const { return impl_ ? (int)impl_->th.size() : 0; }
+void InflatePool::start(int n)
+{
+    if (impl_ || n <= 0) return;
+    impl_ = new Impl;
+    for (int i = 0; i < n; ++i) impl_->th.emplace_back([this] { impl_->run(); });
+}
+void InflatePool::stop()
+{
+    if (!impl_) return;
+    { std::lock_guard<std::mutex> lk(impl_->m); impl_->stop = true; }
+    impl_->cv.notify_all();
+    for (auto& t : impl_->th) t.join();
+    delete impl_;
+    impl_ = nullptr;
+}
+void InflatePool::submit(BgzfReader* r, int slot)
+{
+    { std::lock_guard<std::mutex> lk(impl_->m); impl_->q.emplace_back(r, slot); }
+    impl_->cv.notify_one();
+}
+
+BgzfReader::BgzfReader() = default;
+BgzfReader::~BgzfReader() { close(); }
+
 bool BgzfReader::open(const std::string& path, std::string* err)
 {
     close();
     f_ = fopen(path.c_str(), "rb");
     if (!f_) { if (err) *err = "cannot open " + path; return false; }
     setvbuf(f_, nullptr, _IOFBF, 1 << 20);
-    comp_.resize(kMaxBlock + kFastInflateInPad);
-    buf_.resize(kMaxBlock + kFastInflateOutSlack);
+    async_ = InflatePool::instance().threads() > 0;
+    blk_.reset(new Block[kSlots]);
+    for (int i = 0; i < (async_ ? kSlots : 1); ++i) { blk_[i].comp.resize(kMaxBlock + kFastInflateInPad); blk_[i].out.resize(kMaxBlock + kFastInflateOutSlack); }
     { const char* e = getenv("BVC_ZLIB_INFLATE"); use_fast_ = !(e && e[0] == '1'); }
-    pos_ = len_ = 0; failed_ = eof_ = false; carry_.clear(); err_.clear();
+    head_ = 0; queued_ = 0; cur_ = nullptr;
+    pos_ = len_ = 0; failed_ = eof_ = false; carry_.clear(); err_.clear(); zlib_blocks_ = 0;
     return true;
 }
 
 void BgzfReader::close()
 {
+    if (blk_ && async_) {                                        // nothing of this reader may still be in the pool
+        std::unique_lock<std::mutex> lk(m_);
+        cv_.wait(lk, [&] { for (int i = 0; i < kSlots; ++i) if (blk_[i].state == 1) return false; return true; });
+    }
     if (f_) fclose(f_);
     f_ = nullptr;
-    if (zs_) { inflateEnd(static_cast<z_stream*>(zs_)); delete static_cast<z_stream*>(zs_); zs_ = nullptr; }
+    blk_.reset();
+    cur_ = nullptr;
 }
 
-bool BgzfReader::fill()
+// The file's next non-empty block into `b`.  false: end of file, or a malformed container (failed_).
+bool BgzfReader::read_block(Block& b)
 {
     while (!eof_) {
-        unsigned char* h = comp_.data();
+        unsigned char* h = b.comp.data();
         size_t got = fread(h, 1, 12, f_);
         if (got == 0) { eof_ = true; return false; }
         if (got != 12 || h[0] != 0x1f || h[1] != 0x8b || h[2] != 8 || !(h[3] & 4)) { failed_ = true; err_ = "not a BGZF block"; return false; }
@@ -76,30 +160,76 @@ bool BgzfReader::fill()
         const size_t isize = rd32(h + bsize - 4);
         if (isize > kMaxBlock) { failed_ = true; err_ = "bad BGZF ISIZE"; return false; }
         if (isize == 0) continue;              // empty block (EOF marker or flush point)
-        // the whole-buffer decoder first (fast_inflate.hpp); whatever it declines -- or gets wrong by the CRC -- goes to zlib
-        size_t fast_len = 0;
-        const bool fast_ok = use_fast_ && fast_inflate(h + head, rest - 8, reinterpret_cast<uint8_t*>(buf_.data()), kMaxBlock, &fast_len) && fast_len == isize &&
-                             fast_crc32(reinterpret_cast<const uint8_t*>(buf_.data()), isize) == rd32(h + bsize - 8);
-        if (fast_ok) { pos_ = 0; len_ = isize; return true; }
-        if (use_fast_) ++zlib_blocks_;
-        if (!zs_) {
-            z_stream* z = new z_stream;
-            memset(z, 0, sizeof *z);
-            if (inflateInit2(z, -15) != Z_OK) { delete z; failed_ = true; err_ = "inflateInit2 failed"; return false; }
-            zs_ = z;
-        } else if (inflateReset(static_cast<z_stream*>(zs_)) != Z_OK) { failed_ = true; err_ = "inflateReset failed"; return false; }
-        z_stream& zs = *static_cast<z_stream*>(zs_);
-        zs.next_in = h + head; zs.avail_in = (uInt)(rest - 8);
-        zs.next_out = reinterpret_cast<Bytef*>(buf_.data()); zs.avail_out = (uInt)kMaxBlock;
-        const int rc = inflate(&zs, Z_FINISH);
-        if (rc != Z_STREAM_END || zs.total_out != isize) { failed_ = true; err_ = "inflate failed"; return false; }
-        if (fast_crc32(reinterpret_cast<const uint8_t*>(buf_.data()), isize) != rd32(h + bsize - 8)) {
-            failed_ = true; err_ = "BGZF CRC mismatch"; return false;
-        }
-        pos_ = 0; len_ = isize;
+        b.head = head; b.bsize = bsize; b.isize = isize;
         return true;
     }
     return false;
+}
+
+// Inflate + CRC of a block that read_block filled (any thread).  false: b.err says why.
+bool BgzfReader::decode_block(Block& b, bool use_fast)
+{
+    unsigned char* h = b.comp.data();
+    const size_t rest = b.bsize - b.head, isize = b.isize;
+    const uint32_t want_crc = rd32(h + b.bsize - 8);
+    uint8_t* out = reinterpret_cast<uint8_t*>(b.out.data());
+    // the whole-buffer decoder first (fast_inflate.hpp); whatever it declines -- or gets wrong by the CRC -- goes to zlib
+    size_t fast_len = 0;
+    b.used_zlib = false;
+    if (use_fast && fast_inflate(h + b.head, rest - 8, out, kMaxBlock, &fast_len) && fast_len == isize && fast_crc32(out, isize) == want_crc) return true;
+    b.used_zlib = use_fast;
+    ZStream& zs = t_zs;
+    if (!zs.init) {
+        memset(&zs.z, 0, sizeof zs.z);
+        if (inflateInit2(&zs.z, -15) != Z_OK) { b.err = "inflateInit2 failed"; return false; }
+        zs.init = true;
+    } else if (inflateReset(&zs.z) != Z_OK) { b.err = "inflateReset failed"; return false; }
+    zs.z.next_in = h + b.head; zs.z.avail_in = (uInt)(rest - 8);
+    zs.z.next_out = out; zs.z.avail_out = (uInt)kMaxBlock;
+    const int rc = inflate(&zs.z, Z_FINISH);
+    if (rc != Z_STREAM_END || zs.z.total_out != isize) { b.err = "inflate failed"; return false; }
+    if (fast_crc32(out, isize) != want_crc) { b.err = "BGZF CRC mismatch"; return false; }
+    return true;
+}
+
+void BgzfReader::decode_slot(int slot)                           // pool thread
+{
+    Block& b = blk_[slot];
+    const bool ok = decode_block(b, use_fast_);
+    { std::lock_guard<std::mutex> lk(m_); b.state = ok ? 2 : 3; }
+    cv_.notify_all();
+}
+
+bool BgzfReader::fill()
+{
+    if (failed_) return false;
+    if (!async_) {
+        Block& b = blk_[0];
+        if (!read_block(b)) return false;
+        if (!decode_block(b, use_fast_)) { failed_ = true; err_ = b.err; return false; }
+        if (b.used_zlib) ++zlib_blocks_;
+        cur_ = b.out.data(); pos_ = 0; len_ = b.isize;
+        return true;
+    }
+    if (cur_) {                                                  // the block just consumed: its slot is free again
+        blk_[head_].state = 0;
+        head_ = (head_ + 1) % kSlots; --queued_;
+        cur_ = nullptr;
+    }
+    while (queued_ < kSlots && !eof_ && !failed_) {              // keep the pool kSlots blocks ahead of the caller
+        const int slot = (head_ + queued_) % kSlots;
+        if (!read_block(blk_[slot])) break;
+        { std::lock_guard<std::mutex> lk(m_); blk_[slot].state = 1; }
+        ++queued_;
+        InflatePool::instance().submit(this, slot);
+    }
+    if (queued_ == 0) return false;                              // end of file (or failed_ by read_block with nothing decoded pending)
+    Block& b = blk_[head_];
+    { std::unique_lock<std::mutex> lk(m_); cv_.wait(lk, [&] { return b.state != 1; }); }
+    if (b.state == 3) { failed_ = true; err_ = b.err; return false; }
+    if (b.used_zlib) ++zlib_blocks_;
+    cur_ = b.out.data(); pos_ = 0; len_ = b.isize;
+    return true;
 }
 
 bool BgzfReader::getline_view(const char** ptr, size_t* len)
@@ -111,7 +241,7 @@ bool BgzfReader::getline_view(const char** ptr, size_t* len)
             if (have_carry && !failed_) { *ptr = carry_.data(); *len = carry_.size(); return true; }   // last line without '\n'
             return false;
         }
-        const char* b = buf_.data() + pos_;
+        const char* b = cur_ + pos_;
         const char* nl = static_cast<const char*>(memchr(b, '\n', len_ - pos_));
         if (nl) {
             const size_t n = (size_t)(nl - b);

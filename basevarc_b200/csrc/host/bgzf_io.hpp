@@ -8,6 +8,9 @@
 #pragma once
 #include <stdint.h>
 #include <stdio.h>
+#include <condition_variable>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -17,10 +20,27 @@ namespace bvc_host {
 // (bgzf_compression(fp) == 2 && bgzf_check_EOF(fp) == 1, src/BaseVarC.cpp:224-227).
 bool bgzf_is_complete(const std::string& path);
 
+// Optional process-wide pool of inflate threads (BGZF blocks are independent gzip members).  Readers opened
+// while it runs keep their next blocks queued in it; without it (the default) a reader inflates on its caller's thread.
+class BgzfReader;
+class InflatePool {
+public:
+    static InflatePool& instance();
+    void start(int n_threads);          // once, before the readers are opened; n <= 0: no pool
+    void stop();                        // after the readers are closed
+    int threads() const;
+    void submit(BgzfReader* r, int slot);
+private:
+    InflatePool() = default;
+    ~InflatePool();
+    class Impl;
+    Impl* impl_ = nullptr;
+};
+
 class BgzfReader {
 public:
-    BgzfReader() = default;
-    ~BgzfReader() { close(); }
+    BgzfReader();
+    ~BgzfReader();
     BgzfReader(const BgzfReader&) = delete;
     BgzfReader& operator=(const BgzfReader&) = delete;
     bool open(const std::string& path, std::string* err);
@@ -36,16 +56,24 @@ public:
     size_t zlib_blocks() const { return zlib_blocks_; }
 
 private:
-    bool fill();            // inflate the next non-empty block into buf_
+    friend class InflatePool;
+    struct Block;
+    static constexpr int kSlots = 3;    // with a pool: the block being consumed + two read ahead
+    bool fill();                        // the next non-empty block, inflated, becomes the current one
+    bool read_block(Block& b);
+    static bool decode_block(Block& b, bool use_fast);
+    void decode_slot(int slot);         // called by a pool thread
     FILE* f_ = nullptr;
-    std::vector<unsigned char> comp_;
-    std::vector<char> buf_;
+    std::unique_ptr<Block[]> blk_;
+    int head_ = 0, queued_ = 0;         // ring of slots handed to the pool, oldest first
+    const char* cur_ = nullptr;         // inflated bytes of the current block
     size_t pos_ = 0, len_ = 0;
-    std::string carry_;     // a line that spans blocks
-    bool failed_ = false, eof_ = false, use_fast_ = true;
+    std::string carry_;                 // a line that spans blocks
+    bool failed_ = false, eof_ = false, use_fast_ = true, async_ = false;
     size_t zlib_blocks_ = 0;
     std::string err_;
-    void* zs_ = nullptr;    // z_stream kept across blocks (inflateReset instead of init / end per block)
+    std::mutex m_;                      // slot states (pool threads <-> the reader's thread)
+    std::condition_variable cv_;
 };
 
 // Writes BGZF either to a file or to an in-memory byte string (take()).  close() appends the EOF block

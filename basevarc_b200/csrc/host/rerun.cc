@@ -12,6 +12,7 @@
 // The load phase (BAM decoding, bt_r) is NOT here: it stays with the reference binary (`--load`); this
 // command needs complete batch files and says so otherwise.
 #include <getopt.h>
+#include <sched.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -660,6 +661,18 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     }
     std::cout << "basetype loading done -- " << now_string();
     if (o.load) return EXIT_SUCCESS;
+    // with fewer reading threads (windows, or ranks of --shard_samples) than cores, the spare cores inflate the
+    // BGZF blocks of the text batch files ahead of the tokenisers (one core is left to the GPU dispatcher)
+    struct PoolGuard { ~PoolGuard() { InflatePool::instance().stop(); } } pool_guard;
+    if (!sh.packed_in) {
+        cpu_set_t cs;
+        const int ncpu = sched_getaffinity(0, sizeof cs, &cs) == 0 ? CPU_COUNT(&cs) : (int)std::thread::hardware_concurrency();
+        const int readers = o.shard_samples > 0 ? o.shard_samples : T;
+        int n = ncpu - readers - (o.pack ? 0 : 1);
+        if (const char* e = getenv("BVC_INFLATE_THREADS")) n = atoi(e);
+        InflatePool::instance().start(n);
+        if (o.verbose) std::cout << "basetype inflate pool : " << InflatePool::instance().threads() << " threads beside " << readers << " reading threads on " << ncpu << " cores" << std::endl;
+    }
 
     // sample names = first line of every batch file of window 0, concatenated (src/BaseVarC.cpp:333-338)
     std::string sams;

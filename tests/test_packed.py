@@ -122,3 +122,19 @@ def test_rerun_from_packed_files_prints_the_reference_text(tmp_path):
     # --no_packed insists on the text files (now gone): the command refuses, pointing at --load
     r = subprocess.run([host.BIN_PATH, "basetype", "--rerun", "--no_packed"] + args, cwd=tmp_path, capture_output=True, text=True, timeout=600)
     assert r.returncode != 0 and "batch files are complete" in r.stderr
+
+
+def test_inflate_pool_gives_the_same_packed_files(tmp_path):
+    """BGZF blocks inflated ahead by a pool of threads, by the caller's thread, and by zlib only."""
+    outs = []
+    for name, env in (("pool", {"BVC_INFLATE_THREADS": "3"}), ("inline", {"BVC_INFLATE_THREADS": "0"}),
+                      ("zlib", {"BVC_INFLATE_THREADS": "2", "BVC_ZLIB_INFLATE": "1"})):
+        d = tmp_path / name
+        d.mkdir()
+        args = _c1_workdir(d)
+        r = subprocess.run([host.BIN_PATH, "basetype", "--pack", "-v", "--tile_sites", "500"] + args, cwd=d, env=dict(os.environ, **env),
+                           capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        assert ("inflate pool : %s threads" % env["BVC_INFLATE_THREADS"]) in r.stdout
+        outs.append([open(d / ("test.out.tmp.thread.%d" % t) / "packed.bvc", "rb").read() for t in range(T)])
+    assert outs[0] == outs[1] == outs[2] and all(len(b) > 1000 for b in outs[0])
