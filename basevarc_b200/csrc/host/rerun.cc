@@ -66,7 +66,7 @@ const char* kUsage =
     "  --pack                   Convert the text batch files into packed tile files (PREFIX.tmp.thread.{t}/packed.bvc; no GPU\n"
     "                           needed); --rerun reads them instead of the text files whenever every window has one\n"
     "  --no_packed              --rerun from the text batch files even if packed tile files exist\n"
-    "  --pending_mb <INT>       Host memory (MiB, all windows together) for tiles packed ahead while the GPU starts up [2048]\n"
+    "  --pending_mb <INT>       Host memory (MiB, all windows together) for tiles packed ahead while the GPU starts up [4096]\n"
     "  --shard_samples <INT>    Sample-sharded calling for very wide cohorts: rank r of W reads the batch files [r*J/W, (r+1)*J/W)\n"
     "                           of every window, one GPU per rank with NCCL (fewer GPUs than ranks: all ranks on GPU 0)\n";
 
@@ -100,7 +100,7 @@ struct Options {
     int shard_samples = 0;                     // --shard_samples W: the sample-sharded compute phase over W ranks (shard_rerun.inc)
     bool pack = false, no_packed = false;      // --pack: text batch files -> packed tile files (no GPU); --no_packed: ignore packed files
     int mapq = 10, thread = 1, batch = 10, gpus = 0, tile_sites = 0;
-    int pending_mb = 2048;                     // --pending_mb: host memory all windows together may hold in tiles waiting for the GPU
+    int pending_mb = 4096;                     // --pending_mb: host memory all windows together may hold in tiles waiting for the GPU
     double maf = 0.001;
     std::string input, reference, group, region, output;
 };

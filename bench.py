@@ -543,6 +543,7 @@ def main():
                     help="host-buffer form of (code, qual) on the e2e path: one byte per entry + qual dictionary, or the two arrays")
     ap.add_argument("--ref-sites-per-thread", type=int, default=6000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-drain", action="store_true", help="e2e leg: wait for every ticket at the end of each step (default: the tile stream runs on across steps)")
     ap.add_argument("--qual-window", type=int, nargs=2, default=[1, 63], help="exchange window of the sample-sharded mode (C4)")
     ap.add_argument("--window-sites", type=int, default=0,
                     help="the WHOLE job in sites (e.g. 10000000 for C3's 10 Mb): region-sharded over the ranks (strong scaling), every rank "
@@ -640,31 +641,36 @@ def main():
     else:
         outs = [PinnedArray((t.n_sites,), B.SITE_RESULT_DTYPE) for t in subs]
 
-    def e2e_step():
-        # the dispatcher's pattern (csrc/host/rerun.cc): two tickets in flight, the older one retired before a third is issued
-        fly = []
+    # the dispatcher's pattern (csrc/host/rerun.cc): two tickets in flight, the older one retired before a third is issued.  A
+    # window is a STREAM of tiles, so by default the stream runs on across the step boundary (the result of step s's last tile
+    # is read while step s+1's first tile uploads) and is drained once, before the closing barrier; --e2e-drain empties it at
+    # the end of every step instead (one upload and one compute + read-back per step are then not overlapped).
+    fly = []
 
-        def retire():
-            i, tk = fly.pop(0)
-            if split:
-                n_vcf[i] = caller.wait_split(tk)
-            else:
-                caller.wait(tk)
+    def retire():
+        i, tk = fly.pop(0)
+        if split:
+            n_vcf[i] = caller.wait_split(tk)
+        else:
+            caller.wait(tk)
 
+    def e2e_step(drain):
         for i, (t, o) in enumerate(zip(subs, outs)):
-            fly.append((i, caller.enqueue_split(t, o.array, vcfs[i].array) if split else caller.enqueue(t, o.array)))
-            if len(fly) == 2 and i + 1 < nsub:
+            if len(fly) == 2:
                 retire()
-        while fly:
+            fly.append((i, caller.enqueue_split(t, o.array, vcfs[i].array) if split else caller.enqueue(t, o.array)))
+        while drain and fly:
             retire()
 
     for _ in range(args.warmup):
-        e2e_step()
+        e2e_step(True)
     barrier()
     h2d0, d2h0 = caller.transfer_bytes
     t0 = time.perf_counter()
     for _ in range(args.steps * passes):
-        e2e_step()
+        e2e_step(args.e2e_drain)
+    while fly:
+        retire()
     barrier()
     e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
     h2d1, d2h1 = caller.transfer_bytes
@@ -795,7 +801,7 @@ def main():
                    "parallelism": "window-sharded x%d, no collective" % world,
                    "l2": "inputs (%.0f MB per launch) exceed the 126 MB L2; no flush needed" % (tile.nbytes() / 1e6)},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "wire": wire, "result": args.result, "matches_resident": bool(same),
+                "ms_per_step": e2e_s * 1e3, "subtiles": nsub, "stream": "drained every step" if args.e2e_drain else "tiles stream across step boundaries, drained once before the closing barrier", "wire": wire, "result": args.result, "matches_resident": bool(same),
                 "h2d_gbs_per_gpu": h2d / e2e_s / 1e9},
         "copy_probe": {"what": "cudaMemcpyAsync only, pinned host memory, the bytes of one pass, all ranks at once; GB/s per rank",
                        "ranks": probes,
