@@ -351,6 +351,15 @@ cudaError_t launch_shard_hist(const ShardArgs& a, int n_sm, cudaStream_t stream,
     return cudaGetLastError();
 }
 
+cudaError_t launch_shard_qual_range(const uint8_t* code, const uint8_t* qual, size_t n_entries, uint32_t* out, int n_sm, cudaStream_t stream)
+{
+    size_t blocks = (n_entries / 4 + 255) / 256;
+    if (blocks > (size_t)n_sm * 8) blocks = (size_t)n_sm * 8;
+    if (blocks < 1) blocks = 1;
+    shard_qual_range_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(code), reinterpret_cast<const uint32_t*>(qual), n_entries, out);
+    return cudaGetLastError();
+}
+
 // owner: merged histograms -> SiteSum + classes, then K2 / EM stages / K4 on the owned sites, then the mask bytes
 cudaError_t launch_shard_merge_and_fit(const ShardArgs& a, int n_sm, cudaStream_t stream, int* n_launches)
 {

@@ -28,6 +28,30 @@
 
 namespace bvc {
 
+// ---- A0: the quals this rank's entries actually carry ---------------------------------------------------------------
+// out[0] = max(127 - qual), out[1] = max(qual) over the non-indel entries (both start at 0): after a MAX all-reduce over the
+// ranks the cohort's qual range of this tile is [127 - out[0], out[1]], and the exchange window shrinks to it -- the dense
+// record is 16 + 8 words per qual of the window, and the reduce-scatter of those records is what bounds the mode at 8 GPUs.
+__global__ void __launch_bounds__(256)
+shard_qual_range_kernel(const uint32_t* __restrict__ code4, const uint32_t* __restrict__ qual4, size_t n_entries, uint32_t* out)
+{
+    const size_t n4 = n_entries / 4, tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (size_t)gridDim.x * blockDim.x;
+    uint32_t lo = 127, hi = 0, seen = 0;
+    auto one = [&](uint32_t c, uint32_t q) { if (!(c & 16u)) { q &= 127u; lo = min(lo, q); hi = max(hi, q); seen = 1; } };
+    for (size_t i = tid; i < n4; i += nt) {
+        const uint32_t c = __ldg(code4 + i), q = __ldg(qual4 + i);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) one((c >> (8 * k)) & 0xffu, (q >> (8 * k)) & 0xffu);
+    }
+    if (tid == 0) {
+        const uint8_t* c1 = reinterpret_cast<const uint8_t*>(code4); const uint8_t* q1 = reinterpret_cast<const uint8_t*>(qual4);
+        for (size_t e = n4 * 4; e < n_entries; ++e) one(c1[e], q1[e]);
+    }
+    uint32_t a = seen ? 127u - lo : 0u, b = seen ? hi : 0u;
+    a = __reduce_max_sync(0xffffffffu, a); b = __reduce_max_sync(0xffffffffu, b);
+    if ((threadIdx.x & 31) == 0 && (a | b)) { atomicMax(out, a); atomicMax(out + 1, b); }
+}
+
 // ---- A: local histogram of every tile site -> dense words ------------------------------------------------------
 template <int G>
 __global__ void __launch_bounds__(kHistWarps * 32)

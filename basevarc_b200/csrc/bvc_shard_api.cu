@@ -59,10 +59,11 @@ struct ShardState {
     uint32_t* d_dense = nullptr;        // [world * sr_cap][B]
     uint8_t*  d_mask_all = nullptr;     // [world * sr_cap]
     uint32_t* d_pos_list = nullptr;     // [world * sr_cap]
-    uint32_t* d_flags = nullptr;        // [0] pos_n, [1] err
+    uint32_t* d_flags = nullptr;        // [0] pos_n, [1] err, [2] max(127 - qual), [3] max(qual) of the tile (shard_qual_range_kernel)
     uint32_t* d_hv = nullptr;           // [hv_cap][kVcfHistWords]
     size_t hv_cap = 0;
-    uint32_t* h_flags = nullptr;        // pinned [2]
+    uint32_t* h_flags = nullptr;        // pinned [8]: [0..3] read back from d_flags, [4..5] this rank's qual range of the tile in flight
+    bool fit_window = true;             // shrink the exchange window to the tile's quals (BVC_SHARD_FIXED_WINDOW=1: keep the one of bvc_shard_init)
     cudaEvent_t ev[kShardPhases + 1] = {};
     float phase_ms[kShardPhases] = {};
     int64_t exchange_bytes = 0;         // payload bytes this rank handed to the collectives (cumulative)
@@ -105,6 +106,7 @@ static int shard_alloc(bvc_ctx* ctx, int rank, int world, int qlo, int qhi, bool
     ShardState* st = new ShardState();
     ctx->shard = st;
     st->rank = rank; st->world = world; st->qlo = qlo; st->qhi = qhi; st->group = group;
+    { const char* e = getenv("BVC_SHARD_FIXED_WINDOW"); st->fit_window = !(e && e[0] == '1'); }
     st->B = kShardHdr + 8 * (qhi - qlo + 1);
     st->sr_cap = (ctx->prm.max_sites + world - 1) / world;
     const size_t n_pad = (size_t)world * st->sr_cap;
@@ -112,7 +114,8 @@ static int shard_alloc(bvc_ctx* ctx, int rank, int world, int qlo, int qhi, bool
     CK(bvc::gmalloc(&st->d_mask_all, n_pad + 16));
     CK(bvc::gmalloc(&st->d_pos_list, (n_pad + 16) * sizeof(uint32_t)));
     CK(bvc::gmalloc(&st->d_flags, 4 * sizeof(uint32_t)));
-    CK(cudaHostAlloc(&st->h_flags, 4 * sizeof(uint32_t), cudaHostAllocDefault));
+    CK(cudaHostAlloc(&st->h_flags, 8 * sizeof(uint32_t), cudaHostAllocDefault));
+    memset(st->h_flags, 0, 8 * sizeof(uint32_t));
     for (auto& e : st->ev) CK(cudaEventCreate(&e));
     // the class pool must hold every (base, qual) class of the owned sites, whatever the local entry capacity
     Slot& s = ctx->slot[0];
@@ -155,8 +158,54 @@ static int shard_upload(bvc_ctx* ctx, const bvc_tile* tile)
     // the owner's pipeline sees its slice only: local site index s <-> tile site lo + s
     a.p.s.n_sites = a.n_own;
     a.p.s.ref_base = s.d_ref + (a.n_own > 0 ? lo : 0);
+    // this rank's qual range of the tile (h_flags[4] = max(127 - qual), [5] = max(qual); 0, 0 = no counted entry): from the
+    // dictionary when the tile came in its one-byte form (a superset of the quals in use is fine), else one pass on the device
+    st->h_flags[4] = st->h_flags[5] = 0;
+    if (st->fit_window && R > 0) {
+        if (tile->packed8 && tile->qual_dict && tile->n_qual_dict > 0) {
+            for (int i = 0; i < tile->n_qual_dict; ++i) {
+                const uint32_t q = tile->qual_dict[i] & 127u;
+                if (127u - q > st->h_flags[4]) st->h_flags[4] = 127u - q;
+                if (q > st->h_flags[5]) st->h_flags[5] = q;
+            }
+        } else {
+            CK(cudaMemsetAsync(st->d_flags + 2, 0, 2 * sizeof(uint32_t), s.stream));
+            CK(launch_shard_qual_range(s.d_code, s.d_qual, (size_t)R, st->d_flags + 2, ctx->n_sm, s.stream));
+            ctx->launches += 1;
+            CK(cudaMemcpyAsync(st->h_flags + 4, st->d_flags + 2, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+            CK(cudaStreamSynchronize(s.stream));
+        }
+    }
     st->have_tile = true;
     return BVC_OK;
+}
+
+// Phase A in three steps so that the ranks can agree on the tile's qual window between them: (1) this rank's qual range,
+// (2) [the caller combines the ranges: a 2-word MAX all-reduce, or a host loop for an in-process group] shard_apply_window,
+// (3) the histogram kernel over the agreed window.
+static int shard_phase_range(bvc_ctx* ctx)
+{
+    ShardState* st = ctx->shard;
+    Slot& s = ctx->slot[0];
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaEventRecord(st->ev[1], s.stream));
+    CK(cudaMemsetAsync(st->d_flags, 0, 4 * sizeof(uint32_t), s.stream));
+    return BVC_OK;
+}
+
+// the agreed range [127 - lo_neg, hi] (0, 0: no counted entry anywhere) -> this tile's window inside the one of bvc_shard_init
+static void shard_apply_window(ShardState* st, uint32_t lo_neg, uint32_t hi)
+{
+    ShardArgs& a = st->a;
+    a.qlo = st->qlo; a.qhi = st->qhi;
+    if (st->fit_window) {
+        int lo = 127 - (int)lo_neg, h = (int)hi;
+        if (lo > h) { lo = st->qlo; h = st->qlo; }                 // no counted entry: the narrowest window
+        // a qual outside the window of bvc_shard_init stays outside: the histogram kernel reports it (BVC_ERR_ARG)
+        a.qlo = lo < st->qlo ? st->qlo : (lo > st->qhi ? st->qhi : lo);
+        a.qhi = h > st->qhi ? st->qhi : (h < a.qlo ? a.qlo : h);
+    }
+    a.B = kShardHdr + 8 * (a.qhi - a.qlo + 1);
 }
 
 static int shard_phase_hist(bvc_ctx* ctx)
@@ -164,8 +213,6 @@ static int shard_phase_hist(bvc_ctx* ctx)
     ShardState* st = ctx->shard;
     Slot& s = ctx->slot[0];
     CK(cudaSetDevice(ctx->device));
-    CK(cudaEventRecord(st->ev[1], s.stream));
-    CK(cudaMemsetAsync(st->d_flags, 0, 4 * sizeof(uint32_t), s.stream));
     int n = 0;
     CK(launch_shard_hist(st->a, ctx->n_sm, s.stream, &n));
     ctx->launches += n;
@@ -249,6 +296,14 @@ static int shard_run_nccl(bvc_ctx* ctx, bvc_site_result* out, int32_t* first_sit
     Slot& s = ctx->slot[0];
     const ShardArgs& a = st->a;
     int rc;
+    if ((rc = shard_phase_range(ctx)) != BVC_OK) return rc;
+    if (st->fit_window) {                                         // exchange 0: two words, MAX
+        CK(cudaMemcpyAsync(st->d_flags + 2, st->h_flags + 4, 2 * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
+        NC(nc->AllReduce(st->d_flags + 2, st->d_flags + 2, 2, ncclUint32, ncclMax, st->comm, s.stream));
+        CK(cudaMemcpyAsync(st->h_flags + 2, st->d_flags + 2, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+        CK(cudaStreamSynchronize(s.stream));
+    }
+    shard_apply_window(st, st->h_flags[2], st->h_flags[3]);
     if ((rc = shard_phase_hist(ctx)) != BVC_OK) return rc;
     const size_t seg = (size_t)a.Sr * a.B;
     NC(nc->ReduceScatter(a.dense, a.dense + (size_t)a.rank * seg, seg, ncclUint32, ncclSum, st->comm, s.stream));
@@ -357,7 +412,20 @@ int bvc_shard_call_group(bvc_ctx** ctxs, int world, const bvc_tile* const* tiles
     auto sync_all = [&]() { for (int r = 0; r < world; ++r) cudaStreamSynchronize(ctxs[r]->slot[0].stream); };
     for (int r = 0; r < world; ++r) {
         if ((rc = shard_upload(ctxs[r], tiles[r])) != BVC_OK) return rc;
-        if ((rc = shard_phase_hist(ctxs[r])) != BVC_OK) return rc;
+        if ((rc = shard_phase_range(ctxs[r])) != BVC_OK) return rc;
+    }
+    {   // exchange 0: the tile's qual range over all ranks
+        uint32_t lo_neg = 0, hi = 0;
+        for (int r = 0; r < world; ++r) {
+            ShardState* q = ctxs[r]->shard;
+            if (!q->fit_window) continue;
+            if (q->h_flags[4] > lo_neg) lo_neg = q->h_flags[4];
+            if (q->h_flags[5] > hi) hi = q->h_flags[5];
+        }
+        for (int r = 0; r < world; ++r) {
+            shard_apply_window(ctxs[r]->shard, lo_neg, hi);
+            if ((rc = shard_phase_hist(ctxs[r])) != BVC_OK) return rc;
+        }
     }
     sync_all();
     {   // exchange 1: rank r's segment <- sum over ranks

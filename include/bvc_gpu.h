@@ -204,6 +204,8 @@ void bvc_transfer_bytes(const bvc_ctx* ctx, int64_t* h2d, int64_t* d2h);
  * own sample range (its range of batch files).  Per tile the ranks exchange integer sufficient statistics once:
  * reduce-scatter of the per-site (base, qual, strand) histograms, all-gather of one byte per site, all-reduce of
  * the rank-sum histograms of the LRT-positive sites (NCCL over NVLink; the library dlopens libnccl.so.2).
+ * (The histograms cover the quals the tile's entries actually carry: the ranks first agree on that range with a 2-word MAX
+ * all-reduce, inside the window given to bvc_shard_init; BVC_SHARD_FIXED_WINDOW=1 keeps the whole window.)
  * Rank r returns the records of the site slice [r*ceil(S/W), ...) of the tile.  bvc_create must have been called
  * with n_samples = the size of the WHOLE cohort (min_af and the lgamma table depend on it) and n_groups = 0.
  * Every collective call below must be made by all W ranks with tiles of the same n_sites / ref_base.

@@ -76,3 +76,24 @@ def test_sharded_qual_window_and_errors():
     with pytest.raises(B.BvcError):                           # not initialised for sharding
         c._check(c.lib.bvc_shard_run(c.ctx, None, None, None), "bvc_shard_run")
     c.close()
+
+
+def test_exchange_window_is_fitted_to_the_tile(monkeypatch):
+    """Per tile the ranks agree on the quals their entries carry (a 2-word MAX exchange) and the dense records shrink to that
+    range: same records as with the window of bvc_shard_init, fewer bytes through the reduce-scatter."""
+    tile = synth_tile(2000, 600, 1.0, "highpoly", seed=41, indel_frac=0.02)      # quals 20..40 inside the window 1..63
+    fitted, st_fit = _group_call(tile, 3)
+    monkeypatch.setenv("BVC_SHARD_FIXED_WINDOW", "1")
+    fixed, st_fix = _group_call(tile, 3)
+    monkeypatch.delenv("BVC_SHARD_FIXED_WINDOW")
+    assert fitted.tobytes() == fixed.tobytes()
+    # dense record: 16 + 8 words per qual of the window -> (16 + 8*21) / (16 + 8*63) = 0.35 of those bytes; the rank-sum histograms
+    # of the LRT-positive sites (6 KB each, many on this tile) are exchanged as before
+    assert st_fit["exchange_bytes"] < 0.6 * st_fix["exchange_bytes"], (st_fit["exchange_bytes"], st_fix["exchange_bytes"])
+    # a rank without a single counted entry, and a tile without any: the window collapses, nothing breaks
+    one = synth_tile(3, 40, 0.4, "lowpass", seed=42)
+    got, _ = _group_call(one, 3)
+    caller = B.BaseTypeCaller(one.n_samples, max_sites=one.n_sites, max_entries=max(one.n_entries, 1))
+    ref = caller.call_sites(one)
+    caller.close()
+    assert got.tobytes() == ref.tobytes()
