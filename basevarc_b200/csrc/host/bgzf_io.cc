@@ -8,6 +8,7 @@
 
 #include <condition_variable>
 #include <deque>
+#include <functional>
 #include <mutex>
 #include <thread>
 #include <utility>
@@ -64,20 +65,20 @@ class InflatePool::Impl {
 public:
     std::mutex m;
     std::condition_variable cv;
-    std::deque<std::pair<BgzfReader*, int>> q;
+    std::deque<std::function<void()>> q;
     std::vector<std::thread> th;
     bool stop = false;
     void run()
     {
         for (;;) {
-            std::pair<BgzfReader*, int> t;
+            std::function<void()> t;
             {
                 std::unique_lock<std::mutex> lk(m);
                 cv.wait(lk, [&] { return stop || !q.empty(); });
                 if (q.empty()) return;
-                t = q.front(); q.pop_front();
+                t = std::move(q.front()); q.pop_front();
             }
-            t.first->decode_slot(t.second);
+            t();
         }
     }
 };
@@ -100,11 +101,12 @@ void InflatePool::stop()
     delete impl_;
     impl_ = nullptr;
 }
-void InflatePool::submit(BgzfReader* r, int slot)
+void InflatePool::submit(std::function<void()> task)
 {
-    { std::lock_guard<std::mutex> lk(impl_->m); impl_->q.emplace_back(r, slot); }
+    { std::lock_guard<std::mutex> lk(impl_->m); impl_->q.emplace_back(std::move(task)); }
     impl_->cv.notify_one();
 }
+void InflatePool::submit(BgzfReader* r, int slot) { submit([r, slot] { r->decode_slot(slot); }); }
 
 BgzfReader::BgzfReader() = default;
 BgzfReader::~BgzfReader() { close(); }
@@ -196,7 +198,9 @@ void BgzfReader::decode_slot(int slot)                           // pool thread
 {
     Block& b = blk_[slot];
     const bool ok = decode_block(b, use_fast_);
-    { std::lock_guard<std::mutex> lk(m_); b.state = ok ? 2 : 3; }
+    // notified under the lock: the reader may be destroyed as soon as its thread sees the slot done
+    std::lock_guard<std::mutex> lk(m_);
+    b.state = ok ? 2 : 3;
     cv_.notify_all();
 }
 
@@ -288,14 +292,14 @@ bool BgzfWriter::sink(const void* p, size_t n)
     return fwrite(p, 1, n, f_) == n;
 }
 
-bool BgzfWriter::flush_block(const char* data, size_t n)
+// One BGZF block from data[0, n), n <= kBlockData, appended to `out` (any thread).
+static bool compress_block(const char* data, size_t n, int level, std::string& dst)
 {
     unsigned char out[kMaxBlock + 64];
     static const unsigned char head[16] = {0x1f, 0x8b, 0x08, 0x04, 0, 0, 0, 0, 0, 0xff, 0x06, 0x00, 'B', 'C', 0x02, 0x00};
     memcpy(out, head, 16);
     z_stream zs;
     memset(&zs, 0, sizeof zs);
-    int level = level_;
     for (;;) {
         if (deflateInit2(&zs, level, Z_DEFLATED, -15, 8, Z_DEFAULT_STRATEGY) != Z_OK) return false;
         zs.next_in = reinterpret_cast<Bytef*>(const_cast<char*>(data)); zs.avail_in = (uInt)n;
@@ -310,7 +314,57 @@ bool BgzfWriter::flush_block(const char* data, size_t n)
     wr16(out + 16, (uint16_t)(bsize - 1));
     wr32(out + 18 + clen, fast_crc32(reinterpret_cast<const uint8_t*>(data), n));
     wr32(out + 18 + clen + 4, (uint32_t)n);
-    return sink(out, bsize);
+    dst.append(reinterpret_cast<const char*>(out), bsize);
+    return true;
+}
+
+// A block handed to the pool (memory sink only): compressed by a pool thread, appended to mem_ in order by the writer's thread.
+struct BgzfWriter::Pending {
+    std::vector<char> in;
+    std::string out;
+    bool done = false, ok = false;
+};
+
+BgzfWriter::BgzfWriter(int level) : level_(level) {}
+BgzfWriter::~BgzfWriter() { close(); }
+
+bool BgzfWriter::collect(bool all)
+{
+    bool ok = true;
+    while (!fly_.empty()) {
+        Pending& p = *fly_.front();
+        {
+            std::unique_lock<std::mutex> lk(m_);
+            if (!p.done) {
+                if (!all && fly_.size() < kMaxFly) break;
+                cv_.wait(lk, [&] { return p.done; });
+            }
+        }
+        ok = p.ok && ok;
+        mem_.append(p.out);
+        fly_.pop_front();
+    }
+    return ok;
+}
+
+bool BgzfWriter::flush_block(const char* data, size_t n)
+{
+    if (mem_mode_ && InflatePool::instance().threads() > 0) {
+        fly_.emplace_back(new Pending);
+        Pending* p = fly_.back().get();
+        p->in.assign(data, data + n);
+        const int level = level_;
+        InflatePool::instance().submit([this, p, level] {
+            const bool ok = compress_block(p->in.data(), p->in.size(), level, p->out);
+            std::lock_guard<std::mutex> lk(m_);               // notified under the lock: the writer may go away once it sees `done`
+            p->ok = ok; p->done = true;
+            cv_.notify_all();
+        });
+        return collect(false);
+    }
+    if (mem_mode_) return compress_block(data, n, level_, mem_);
+    std::string tmp;
+    return compress_block(data, n, level_, tmp) && sink(tmp.data(), tmp.size());
 }
 
 bool BgzfWriter::write(const char* data, size_t n)
@@ -334,6 +388,7 @@ bool BgzfWriter::close(bool eof_marker)
     if (!open_) return true;
     bool ok = true;
     if (!pend_.empty()) { ok = flush_block(pend_.data(), pend_.size()); pend_.clear(); }
+    ok = collect(true) && ok;
     if (eof_marker) ok = sink(kEofBlock, 28) && ok;
     if (f_) { ok = (fclose(f_) == 0) && ok; f_ = nullptr; }
     open_ = false;

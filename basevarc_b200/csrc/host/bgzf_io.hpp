@@ -9,6 +9,8 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <condition_variable>
+#include <deque>
+#include <functional>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -20,8 +22,9 @@ namespace bvc_host {
 // (bgzf_compression(fp) == 2 && bgzf_check_EOF(fp) == 1, src/BaseVarC.cpp:224-227).
 bool bgzf_is_complete(const std::string& path);
 
-// Optional process-wide pool of inflate threads (BGZF blocks are independent gzip members).  Readers opened
-// while it runs keep their next blocks queued in it; without it (the default) a reader inflates on its caller's thread.
+// Optional process-wide pool of threads for BGZF blocks (blocks are independent gzip members).  Readers
+// opened while it runs keep their next blocks queued in it, and memory-sink writers hand it their full blocks to deflate;
+// without it (the default) both work on their caller's thread.
 class BgzfReader;
 class InflatePool {
 public:
@@ -30,6 +33,7 @@ public:
     void stop();                        // after the readers are closed
     int threads() const;
     void submit(BgzfReader* r, int slot);
+    void submit(std::function<void()> task);
 private:
     InflatePool() = default;
     ~InflatePool();
@@ -81,12 +85,12 @@ private:
 // independent gzip members, so concatenating compressed windows equals compressing the concatenation).
 class BgzfWriter {
 public:
-    explicit BgzfWriter(int level = 6) : level_(level) {}
-    ~BgzfWriter() { close(); }
+    explicit BgzfWriter(int level = 6);
+    ~BgzfWriter();
     BgzfWriter(const BgzfWriter&) = delete;
     BgzfWriter& operator=(const BgzfWriter&) = delete;
     bool open(const std::string& path);        // file sink
-    void open_memory();                        // memory sink
+    void open_memory();                        // memory sink; with an InflatePool running, full blocks are deflated by the pool
     bool write(const char* data, size_t n);
     bool write(const std::string& s) { return write(s.data(), s.size()); }
     bool close(bool eof_marker = true);
@@ -94,12 +98,18 @@ public:
     static const unsigned char kEofBlock[28];
 
 private:
+    struct Pending;
+    static constexpr size_t kMaxFly = 8;       // blocks in the pool per writer before write() waits for the oldest
     bool flush_block(const char* data, size_t n);
+    bool collect(bool all);                    // finished blocks, oldest first, into mem_
     bool sink(const void* p, size_t n);
     FILE* f_ = nullptr;
     bool mem_mode_ = false, open_ = false;
     std::string mem_;
     std::vector<char> pend_;
+    std::deque<std::unique_ptr<Pending>> fly_;
+    std::mutex m_;
+    std::condition_variable cv_;
     int level_;
 };
 

@@ -278,8 +278,8 @@ private:
             if (rc != BVC_OK) err = bvc_last_error(ctx_);
         }
         busy_ns_ += now_ns() - tb; ++tiles_;
-        { std::lock_guard<std::mutex> lk(f.job->m); f.job->rc = rc; f.job->err = err; f.job->done = true; }
-        f.job->cv.notify_all();
+        // notified under the lock: the window thread may free the job as soon as it sees `done`
+        { std::lock_guard<std::mutex> lk(f.job->m); f.job->rc = rc; f.job->err = err; f.job->done = true; f.job->cv.notify_all(); }
     }
     void run()
     {
@@ -298,8 +298,7 @@ private:
                     if (q_.empty()) return;
                     j = q_.front(); q_.pop_front();
                 }
-                { std::lock_guard<std::mutex> lk(j->m); j->rc = rc0 != BVC_OK ? rc0 : rc_stage; j->err = init_err_; j->done = true; }
-                j->cv.notify_all();
+                { std::lock_guard<std::mutex> lk(j->m); j->rc = rc0 != BVC_OK ? rc0 : rc_stage; j->err = init_err_; j->done = true; j->cv.notify_all(); }
             }
         }
         std::deque<Flight> fly;
@@ -336,8 +335,7 @@ private:
                 }
                 busy_ns_ += now_ns() - tb;
                 if (rc != BVC_OK) {
-                    { std::lock_guard<std::mutex> lk(j->m); j->rc = rc; j->err = bvc_last_error(ctx_); j->done = true; }
-                    j->cv.notify_all();
+                    { std::lock_guard<std::mutex> lk(j->m); j->rc = rc; j->err = bvc_last_error(ctx_); j->done = true; j->cv.notify_all(); }
                 } else fly.push_back({j, tk, stage});
             } else if (!fly.empty()) { finish(fly.front()); fly.pop_front(); }
         }
@@ -661,10 +659,11 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     }
     std::cout << "basetype loading done -- " << now_string();
     if (o.load) return EXIT_SUCCESS;
-    // with fewer reading threads (windows, or ranks of --shard_samples) than cores, the spare cores inflate the
-    // BGZF blocks of the text batch files ahead of the tokenisers (one core is left to the GPU dispatcher)
+    // with fewer window threads (or ranks of --shard_samples) than cores, the spare cores inflate the BGZF
+    // blocks of the text batch files ahead of the tokenisers and deflate the windows' output blocks (one core is left to the GPU
+    // dispatcher)
     struct PoolGuard { ~PoolGuard() { InflatePool::instance().stop(); } } pool_guard;
-    if (!sh.packed_in) {
+    {
         cpu_set_t cs;
         const int ncpu = sched_getaffinity(0, sizeof cs, &cs) == 0 ? CPU_COUNT(&cs) : (int)std::thread::hardware_concurrency();
         const int readers = o.shard_samples > 0 ? o.shard_samples : T;
