@@ -357,25 +357,6 @@ private:
     int tiles_ = 0;
 };
 
-// The GPU dispatchers of a run.  They are built by a starter thread once the driver has come up (cuInit alone is 0.1-0.9 s
-// in a fresh process), while the window threads are already inflating and packing: a window asks for its dispatcher when its
-// first tile is full.
-struct GpuFleet {
-    std::mutex m;
-    std::condition_variable cv;
-    bool ready = false;
-    std::vector<std::unique_ptr<GpuServer>> gpus;
-    int G = 0, T = 1;
-    long long ready_ns = 0;                     // when the dispatchers existed (relative to the start of the run)
-    std::string err;
-    GpuServer* get(int window)
-    {
-        std::unique_lock<std::mutex> lk(m);
-        cv.wait(lk, [&] { return ready; });
-        return G > 0 ? gpus[(size_t)((long long)window * G / T)].get() : nullptr;
-    }
-};
-
 struct Shared {
     Options opt;
     std::string chr, refseq;
@@ -402,9 +383,8 @@ struct Shared {
 
 
 // ---- one thread per window: read + tokenise -> tile -> GPU -> format -> BGZF (in memory) ---------------------
-void window_worker(Shared* sh, GpuFleet* fleet, int ithread, std::string* vcf_out, std::string* cvg_out)
+void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out, std::string* cvg_out)
 {
-    GpuServer* gpu = nullptr;                                // asked for when the first tile is full (GpuFleet)
     const Options& o = sh->opt;
     const int T = o.thread;
     std::vector<std::unique_ptr<BgzfReader>> in;
@@ -515,13 +495,7 @@ void window_worker(Shared* sh, GpuFleet* fleet, int ithread, std::string* vcf_ou
         }
         return true;
     };
-    auto flush = [&](TileJob& j) -> bool {                    // hand a job to the GPU
-        if (!gpu) {
-            const long long tw = now_ns();
-            gpu = fleet->get(ithread);
-            t_wait += now_ns() - tw;
-            if (!gpu) { sh->fail(fleet->err); return false; }
-        }
+    auto flush = [&](TileJob& j) {                            // hand a job to the GPU
         if (sh->n_groups) {
             j.rec.resize((size_t)j.pk.n_sites());
             j.group_depth.assign((size_t)j.pk.n_sites() * sh->n_groups * 4, 0);
@@ -530,7 +504,6 @@ void window_worker(Shared* sh, GpuFleet* fleet, int ithread, std::string* vcf_ou
         j.done = false;
         fly.push_back(&j);
         gpu->submit(&j);
-        return true;
     };
     auto is_done = [](TileJob& j) { std::lock_guard<std::mutex> lk(j.m); return j.done; };
     // a job to fill next: an idle one; else the oldest in flight if the GPU has finished it (or no further job may be taken)
@@ -601,7 +574,7 @@ void window_worker(Shared* sh, GpuFleet* fleet, int ithread, std::string* vcf_ou
             if (more < 0) return;
         } while (more > 0 && j->pk.n_sites() == 0 && !sh->failed);
         if (j->pk.n_sites() == 0) { idle.push_back(j); break; }
-        if (!flush(*j)) return;
+        flush(*j);
         prev = j;
     }
     if (sh->failed) return;                                   // (the guard waits for what is still in flight)
@@ -761,11 +734,11 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
         return EXIT_SUCCESS;
     }
     // tile geometry and one dispatcher per GPU
+    const auto dev = devices.get();
+    const int n_dev = dev.first;
     if (const char* e = getenv("BVC_GPUS")) if (o.gpus <= 0) o.gpus = atoi(e);
+    if (n_dev <= 0) { std::cerr << "ERROR: no CUDA device: the basetype calling core has no CPU path (" << dev.second << ")" << std::endl; return EXIT_FAILURE; }
     if (o.shard_samples > 0) {
-        const auto dev = devices.get();
-        const int n_dev = dev.first;
-        if (n_dev <= 0) { std::cerr << "ERROR: no CUDA device: the basetype calling core has no CPU path (" << dev.second << ")" << std::endl; return EXIT_FAILURE; }
         if (sh.packed_in) { std::cerr << "ERROR: --shard_samples reads the text batch files (a packed tile file holds whole-cohort tiles): add --no_packed" << std::endl; return EXIT_FAILURE; }
         const int rc = run_sharded_windows(sh, o.shard_samples, n_dev);
         if (rc == EXIT_SUCCESS) {
@@ -775,6 +748,7 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
         }
         return rc;
     }
+    const int G = std::max(1, std::min(std::min(o.gpus > 0 ? o.gpus : n_dev, n_dev), T));
     // Tiles of ~2,048 sites (fewer for wide cohorts: <= 8 M entries): with one worker per window feeding it, the GPU is
     // never the bottleneck, so small tiles cost nothing there and let packing, kernels and formatting overlap inside a
     // window; the context's buffers (sized by max_entries) stay small, which keeps its creation short.
@@ -792,31 +766,15 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     prm.max_entries = sh.tile_entries;
     prm.n_groups = sh.n_groups;
     prm.sample_group = sh.n_groups ? sample_group.data() : nullptr;
-    // the dispatchers come up beside the windows' first tiles (GpuFleet): windows [g*T/G, (g+1)*T/G) -> GPU g
-    GpuFleet fleet;
-    fleet.T = T;
-    std::thread starter([&] {
-        const auto dev = devices.get();
-        std::lock_guard<std::mutex> lk(fleet.m);
-        if (dev.first <= 0) fleet.err = "no CUDA device: the basetype calling core has no CPU path (" + dev.second + ")";
-        else {
-            fleet.G = std::max(1, std::min(std::min(o.gpus > 0 ? o.gpus : dev.first, dev.first), T));
-            for (int g = 0; g < fleet.G; ++g) { fleet.gpus.emplace_back(new GpuServer(g, prm)); fleet.gpus.back()->start(); }
-        }
-        fleet.ready_ns = now_ns() - t_init0;
-        fleet.ready = true;
-        fleet.cv.notify_all();
-    });
+    std::vector<std::unique_ptr<GpuServer>> gpus;
+    for (int g = 0; g < G; ++g) { gpus.emplace_back(new GpuServer(g, prm)); gpus.back()->start(); }
     const long long t_init1 = now_ns();
+    // windows [g*T/G, (g+1)*T/G) -> GPU g
     std::vector<std::string> vcf((size_t)T), cvg((size_t)T);
     std::vector<std::thread> workers;
-    for (int i = 0; i < T; ++i) workers.emplace_back(window_worker, &sh, &fleet, i, &vcf[(size_t)i], &cvg[(size_t)i]);
+    for (int i = 0; i < T; ++i) workers.emplace_back(window_worker, &sh, gpus[(size_t)((long long)i * G / T)].get(), i, &vcf[(size_t)i], &cvg[(size_t)i]);
     for (auto& w : workers) w.join();
-    starter.join();
     const long long t_work1 = now_ns();
-    auto& gpus = fleet.gpus;
-    const int G = fleet.G;
-    if (G == 0) { std::cerr << "ERROR: " << fleet.err << std::endl; return EXIT_FAILURE; }     // also when no window had a tile to submit
     long long launches = 0;
     long long create_ns = 0, busy_ns = 0; int n_tiles = 0;
     for (auto& s : gpus) { s->stop(); launches += s->launches(); create_ns = std::max(create_ns, s->create_ns()); busy_ns += s->busy_ns(); n_tiles += s->tiles(); }
@@ -839,10 +797,10 @@ extern "C" int bvc_basetype_main(int argc, char** argv)
     if (o.verbose) {
         std::cout << "basetype gpu kernels launched : " << launches << " on " << G << " GPU(s)" << std::endl;
         char b[512];
-        snprintf(b, sizeof b, "basetype host phases : checks %.3f s, driver up after %.3f s, windows (context creation inside) %.3f s wall on %d threads, "
+        snprintf(b, sizeof b, "basetype host phases : checks beside CUDA start-up %.3f s, windows (context creation inside) %.3f s wall on %d threads, "
                  "context teardown %.3f s, output files %.3f s; context creation %.3f s, %d tiles, %.3f s inside enqueue / wait; thread-seconds: inflate+getline %.3f, "
                  "tokenise+pack %.3f, wait for gpu %.3f, format %.3f, bgzf deflate %.3f; tiles held per window: up to %d of %d allowed",
-                 (t_init1 - t_init0) * 1e-9, fleet.ready_ns * 1e-9, (t_work1 - t_init1) * 1e-9, T, (t_stop1 - t_work1) * 1e-9, (now_ns() - t_stop1) * 1e-9, create_ns * 1e-9, n_tiles, busy_ns * 1e-9, sh.ns_read * 1e-9, sh.ns_pack * 1e-9, sh.ns_wait * 1e-9,
+                 (t_init1 - t_init0) * 1e-9, (t_work1 - t_init1) * 1e-9, T, (t_stop1 - t_work1) * 1e-9, (now_ns() - t_stop1) * 1e-9, create_ns * 1e-9, n_tiles, busy_ns * 1e-9, sh.ns_read * 1e-9, sh.ns_pack * 1e-9, sh.ns_wait * 1e-9,
                  sh.ns_format * 1e-9, sh.ns_write * 1e-9, sh.max_jobs_used.load(), sh.max_jobs);
         std::cout << b << std::endl;
     }
