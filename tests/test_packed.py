@@ -138,3 +138,25 @@ def test_inflate_pool_gives_the_same_packed_files(tmp_path):
         assert ("inflate pool : %s threads" % env["BVC_INFLATE_THREADS"]) in r.stdout
         outs.append([open(d / ("test.out.tmp.thread.%d" % t) / "packed.bvc", "rb").read() for t in range(T)])
     assert outs[0] == outs[1] == outs[2] and all(len(b) > 1000 for b in outs[0])
+
+
+@pytest.mark.parametrize("threads", ["0", "3"])
+def test_corrupt_batch_file_fails_the_command_with_and_without_the_pool(tmp_path, threads):
+    """A flipped byte inside a BGZF block (CRC mismatch after zlib's second opinion) and a block cut short: the command stops with
+    the reader's message -- with the block pool too, where the failure surfaces on a pool thread."""
+    for kind in ("flip", "cut"):
+        d = tmp_path / kind
+        d.mkdir()
+        args = _c1_workdir(d)
+        victim = d / "test.out.tmp.thread.1" / "batch.3"
+        blob = bytearray(open(victim, "rb").read())
+        if kind == "flip":
+            blob[len(blob) // 2] ^= 0x10
+        else:
+            blob = blob[:len(blob) // 2]
+        open(victim, "wb").write(bytes(blob))
+        r = subprocess.run([host.BIN_PATH, "basetype", "--pack"] + args, cwd=d, env=dict(os.environ, BVC_INFLATE_THREADS=threads),
+                           capture_output=True, text=True, timeout=120)
+        assert r.returncode != 0, kind
+        assert "corrupt batch file" in r.stderr or "complete" in r.stderr, r.stderr[-500:]
+        assert not os.path.exists(d / "test.out.tmp.thread.1" / "packed.bvc")      # nothing half-written passes for a packed file
