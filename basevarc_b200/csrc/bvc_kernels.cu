@@ -351,6 +351,30 @@ cudaError_t launch_shard_hist(const ShardArgs& a, int n_sm, cudaStream_t stream,
     return cudaGetLastError();
 }
 
+// phase A on the one-byte form: site_hist8_kernel's streaming with the dense exchange record as its output
+cudaError_t launch_shard_hist8(const ShardArgs& a, const uint8_t* pk8, int n_sm, cudaStream_t stream, int* n_launches)
+{
+    static std::once_flag once;
+    static int occ = 1;
+    std::call_once(once, [] {
+        int v = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, shard_hist8_kernel, kHistWarps * 32, 0) == cudaSuccess && v > 0) occ = v;
+        cudaGetLastError();
+    });
+    const size_t n_pad = (size_t)a.world * a.Sr;
+    cudaError_t e = cudaMemsetAsync(a.dense, 0, n_pad * (size_t)a.B * sizeof(uint32_t), stream);     // a lane writes only its own qual's words
+    if (e != cudaSuccess) return e;
+    if (n_launches) *n_launches = 0;
+    if (a.n_tile_sites <= 0) return cudaSuccess;
+    PipeArgs p = a.p;
+    p.s.entry_off = a.tile_off; p.s.ref_base = a.tile_ref; p.s.n_sites = a.n_tile_sites; p.s.pk8 = pk8;
+    const DenseArgs dn{a.dense, a.err, a.B, a.qlo, a.qhi};
+    const long long batches = ((long long)a.n_tile_sites + kHistWarps * kH8Sites - 1) / (kHistWarps * kH8Sites);
+    shard_hist8_kernel<<<shard_grid(batches, n_sm, occ), kHistWarps * 32, 0, stream>>>(p, dn);
+    if (n_launches) *n_launches = 1;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_shard_qual_range(const uint8_t* code, const uint8_t* qual, size_t n_entries, uint32_t* out, int n_sm, cudaStream_t stream)
 {
     size_t blocks = (n_entries / 4 + 255) / 256;

@@ -56,6 +56,7 @@ cudaError_t launch_pipeline(const PipeArgs& a, int n_sm, cudaStream_t stream, in
 struct ShardArgs;
 cudaError_t launch_shard_qual_range(const uint8_t* code, const uint8_t* qual, size_t n_entries, uint32_t* out, int n_sm, cudaStream_t stream);
 cudaError_t launch_shard_hist(const ShardArgs& a, int n_sm, cudaStream_t stream, int* n_launches);
+cudaError_t launch_shard_hist8(const ShardArgs& a, const uint8_t* pk8, int n_sm, cudaStream_t stream, int* n_launches);
 cudaError_t launch_shard_merge_and_fit(const ShardArgs& a, int n_sm, cudaStream_t stream, int* n_launches);
 cudaError_t launch_shard_poslist(const ShardArgs& a, cudaStream_t stream, int* n_launches);
 cudaError_t launch_shard_vcf_hist(const ShardArgs& a, int n_sm, uint32_t n_pos, cudaStream_t stream, int* n_launches);

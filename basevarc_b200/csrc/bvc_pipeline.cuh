@@ -610,8 +610,13 @@ __device__ __forceinline__ uint4 ldg16(const uint4* p) { return __ldg(p); }
 #ifndef BVC_H8_MINBLOCKS
 #define BVC_H8_MINBLOCKS 7
 #endif
-__global__ void __launch_bounds__(kHistWarps * 32, BVC_H8_MINBLOCKS)
-site_hist8_kernel(PipeArgs a)
+// kDense (sample-sharded mode, bvc_shard.cuh): the same streaming, but a site's counts go out as the dense exchange record
+// [8 indel bins | n_entries | 7 spare | 4 bases x (qual window) x 2 strands] instead of SiteSum + classes.  The caller zeroes
+// the dense buffer first: a lane writes only the words of ITS dictionary qual.
+struct DenseArgs { uint32_t* dense; uint32_t* err; int B, qlo, qhi; };
+
+template <bool kDense>
+__device__ __forceinline__ void site_hist8_body(const PipeArgs& a, const DenseArgs& dn)
 {
     __shared__ __align__(16) uint32_t hist_s[kHistWarps][kH8Sites * kH8Words];
     __shared__ __align__(16) uint32_t stage_s[kHistWarps][kH8Sites * kH8Stage];
@@ -740,6 +745,28 @@ site_hist8_kernel(PipeArgs a)
             const uint2 h0 = hp[0], h1 = hp[hstep], h2 = hp[2 * hstep], h3 = hp[3 * hstep];
             const uint4 rv = make_uint4(h0.x, h1.x, h2.x, h3.x), fw = make_uint4(h0.y, h1.y, h2.y, h3.y);
             const int n_entries = (int)(k == 0 ? o1 - o0 : k == 1 ? o2 - o1 : k == 2 ? o3 - o2 : o4 - o3);
+            if constexpr (kDense) {
+                const bool mine = ((h0.x | h0.y) | (h1.x | h1.y) | (h2.x | h2.y) | (h3.x | h3.y)) != 0;
+                const bool in_win = lane < nd && (int)dq >= dn.qlo && (int)dq <= dn.qhi;
+                if (mine && !in_win) err |= 1u;                 // a dictionary index >= n_qual_dict, or a qual outside the exchange window
+                uint32_t* dst = dn.dense + (size_t)site * dn.B;
+                // header: the 8 indel bins in K1w's order (strand << 2 | stale base), then n_entries
+                const uint32_t hw8 = lane < 8 ? h[BVC_PACK8_INDEL * 2 + 64 * (lane & 3) + (lane >> 2)] : (uint32_t)n_entries;
+                __syncwarp();
+                if (counted) {
+                    uint2* cp = reinterpret_cast<uint2*>(h + lane * 2);
+                    cp[0] = make_uint2(0u, 0u); cp[32] = make_uint2(0u, 0u); cp[64] = make_uint2(0u, 0u); cp[96] = make_uint2(0u, 0u);
+                }
+                if (lane < 4) *reinterpret_cast<uint2*>(h + BVC_PACK8_INDEL * 2 + 64 * lane) = make_uint2(0u, 0u);
+                if (lane < 9) dst[lane] = hw8;
+                if (mine && in_win) {
+                    const int half = dn.qhi - dn.qlo + 1;       // uint2 words per base
+                    uint2* bp = reinterpret_cast<uint2*>(dst + kShardHdr) + ((int)dq - dn.qlo);
+                    bp[0] = h0; bp[half] = h1; bp[2 * half] = h2; bp[3 * half] = h3;
+                }
+                __syncwarp();
+                continue;
+            }
             const int ref = (int)(__shfl_sync(0xffffffffu, refv, k) & 3u);
             const uint32_t x0 = rv.x + fw.x, x1 = rv.y + fw.y, x2 = rv.z + fw.z, x3 = rv.w + fw.w;
             // a site has < 65,536 entries: two depths per word through one REDUX
@@ -804,7 +831,20 @@ site_hist8_kernel(PipeArgs a)
         __syncwarp();
     }
     const uint32_t err_all = __reduce_or_sync(0xffffffffu, err);
-    if (lane == 0 && err_all) atomicOr(a.s.err, err_all);
+    if (lane == 0 && err_all) atomicOr(kDense ? dn.err : a.s.err, err_all);
+}
+
+__global__ void __launch_bounds__(kHistWarps * 32, BVC_H8_MINBLOCKS)
+site_hist8_kernel(PipeArgs a)
+{
+    site_hist8_body<false>(a, DenseArgs{nullptr, nullptr, 0, 0, 0});
+}
+
+// sample-sharded mode, phase A on the one-byte form (a.s: the LOCAL tile -- entry_off, n_sites, pk8, dict)
+__global__ void __launch_bounds__(kHistWarps * 32, BVC_H8_MINBLOCKS)
+shard_hist8_kernel(PipeArgs a, DenseArgs dn)
+{
+    site_hist8_body<true>(a, dn);
 }
 
 // =====================================================================================================

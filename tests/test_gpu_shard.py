@@ -12,9 +12,11 @@ from parity import compare_records
 pytestmark = pytest.mark.gpu
 
 
-def _group_call(tile, world, qlo=1, qhi=63):
+def _group_call(tile, world, qlo=1, qhi=63, one_byte=False):
     shards = tile.shard_samples(world)
     assert sum(t.n_entries for t in shards) == tile.n_entries
+    if one_byte:                                              # every rank sends its tile in the one-byte form (its own dictionary)
+        assert all(t.pack8() for t in shards if t.n_entries)
     grp = B.ShardGroup(tile.n_samples, world, qual_lo=qlo, qual_hi=qhi, max_sites=max(tile.n_sites, 1),
                        max_entries=max(max(t.n_entries for t in shards), 1))
     try:
@@ -97,3 +99,26 @@ def test_exchange_window_is_fitted_to_the_tile(monkeypatch):
     ref = caller.call_sites(one)
     caller.close()
     assert got.tobytes() == ref.tobytes()
+
+
+@pytest.mark.parametrize("world,S", [(3, 1501), (2, 7), (4, 1024)])
+def test_sharded_one_byte_form_bitwise(monkeypatch, world, S):
+    """Tiles that arrive in the one-byte form run phase A through site_hist8_kernel's streaming (four sites per warp, dense record
+    out): bit-identical to the two-array path and to the unsharded GPU path; indel entries (stale base 0..3 and N), ragged sites."""
+    tile = synth_tile(2400, S, 0.9, "highpoly", seed=51 + world, indel_frac=0.05)
+    c = tile.code.copy()
+    ind = np.nonzero((c & 16) != 0)[0]
+    c[ind[::7]] = (c[ind[::7]] & 0x18) | 4                     # some indel entries whose stale base is N (qi 30)
+    tile.code = c
+    monkeypatch.setenv("BVC_SHARD_HIST8", "1")
+    got, _ = _group_call(tile, world, one_byte=True)
+    monkeypatch.setenv("BVC_SHARD_HIST_ARRAYS", "1")
+    arrays, _ = _group_call(tile, world, one_byte=True)
+    monkeypatch.delenv("BVC_SHARD_HIST_ARRAYS")
+    assert got.tobytes() == arrays.tobytes()
+    caller = B.BaseTypeCaller(tile.n_samples, max_sites=tile.n_sites, max_entries=tile.n_entries)
+    ref = caller.call_sites(tile)
+    caller.close()
+    assert got.tobytes() == ref.tobytes()
+    with pytest.raises(B.BvcError, match="outside the exchange window"):
+        _group_call(tile, world, qlo=25, qhi=40, one_byte=True)
