@@ -63,7 +63,7 @@ struct ShardState {
     uint32_t* d_hv = nullptr;           // [hv_cap][kVcfHistWords]
     size_t hv_cap = 0;
     uint32_t* h_flags = nullptr;        // pinned [8]: [0..3] read back from d_flags, [4..5] this rank's qual range of the tile in flight
-    bool hist8 = false;                 // the tile in flight came in its one-byte form: phase A runs site_hist8_kernel's streaming (BVC_SHARD_HIST_ARRAYS=1: never)
+    bool hist8 = false;                 // the tile in flight came in its one-byte form: with BVC_SHARD_HIST8=1 phase A runs site_hist8_kernel's streaming
     bool fit_window = true;             // shrink the exchange window to the tile's quals (BVC_SHARD_FIXED_WINDOW=1: keep the one of bvc_shard_init)
     cudaEvent_t ev[kShardPhases + 1] = {};
     float phase_ms[kShardPhases] = {};
@@ -161,7 +161,7 @@ static int shard_upload(bvc_ctx* ctx, const bvc_tile* tile)
     a.p.s.ref_base = s.d_ref + (a.n_own > 0 ? lo : 0);
     // this rank's qual range of the tile (h_flags[4] = max(127 - qual), [5] = max(qual); 0, 0 = no counted entry): from the
     // dictionary when the tile came in its one-byte form (a superset of the quals in use is fine), else one pass on the device
-    st->hist8 = R > 0 && tile->packed8 && tile->qual_dict && tile->n_qual_dict > 0 && getenv("BVC_SHARD_HIST8") && !getenv("BVC_SHARD_HIST_ARRAYS");   // opt-in until measured
+    st->hist8 = R > 0 && tile->packed8 && tile->qual_dict && tile->n_qual_dict > 0 && getenv("BVC_SHARD_HIST8") && !getenv("BVC_SHARD_HIST_ARRAYS");   // opt-in: measured equal to the two-array path
     st->h_flags[4] = st->h_flags[5] = 0;
     if (st->fit_window && R > 0) {
         if (tile->packed8 && tile->qual_dict && tile->n_qual_dict > 0) {
