@@ -105,3 +105,25 @@ def test_100k_sites_per_config_against_the_threaded_oracle(oracle, workload, n_s
     assert not unflagged, "em_passes differ without BVC_FLAG_EM_DELTA / ARGMIN_TIE at %s" % unflagged[:10]
     assert diff.size <= n_sites // 2000, "em_passes differ at %d sites" % diff.size
     assert want["lrt_ok"].sum() > 100
+
+
+def test_c4_shape_sample_sharded_against_the_threaded_oracle(oracle):
+    """BASELINE config C4 at its full WIDTH: 100,000 samples (~9,500 entries per site), 3,000 consecutive sites, every site
+    against the per-read oracle on the whole cohort -- through the sample-sharded path (3 ranks, one-byte tiles, the per-tile
+    exchange window) and through the plain path (the wide K1 form), which must also agree with each other bit for bit."""
+    tile = B.synth_config("C4", n_sites=3000, seed=777)
+    want = oracle_threaded(oracle, tile, B.default_params(tile.n_samples))
+    shards = tile.shard_samples(3)
+    assert all(t.pack8() for t in shards)
+    grp = B.ShardGroup(tile.n_samples, 3, max_sites=tile.n_sites, max_entries=max(t.n_entries for t in shards))
+    try:
+        got = grp.call_sites(shards)
+    finally:
+        grp.close()
+    nbad, lines = compare_records(got, want)
+    assert nbad == 0, "\n".join(lines)
+    assert (got["em_fits"] == want["em_fits"]).all() and want["lrt_ok"].sum() > 10
+    caller = B.BaseTypeCaller(tile.n_samples, max_sites=tile.n_sites, max_entries=tile.n_entries)
+    plain = caller.call_sites(tile)
+    caller.close()
+    assert plain.tobytes() == got.tobytes()
