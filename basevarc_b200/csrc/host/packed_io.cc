@@ -114,7 +114,7 @@ bool PackedIo::is_complete(const std::string& path, int32_t n_samples)
     return r.open(path, &e) && r.hdr_.n_samples == (uint32_t)n_samples && r.hdr_.n_tiles > 0;
 }
 
-int PackedIo::next_tile(Packer& pk, std::string* err)
+int PackedIo::next_tile(Packer& pk, std::string* err, bool lazy)
 {
     if (tiles_read_ >= hdr_.n_tiles) return 0;
     auto bad = [&](const char* what) { if (err) *err = std::string("corrupt packed tile file: ") + what; return -1; };
@@ -142,24 +142,38 @@ int PackedIo::next_tile(Packer& pk, std::string* err)
         }
         const uint8_t* p = pk.pk8_.data();
         uint8_t* c = pk.code_.data(); uint8_t* q = pk.qual_.data();
-        for (size_t e = 0; e < R; ++e) { c[e] = code_lut[p[e]]; q[e] = qual_lut[p[e]]; }
+        if (lazy) memset(c, 0, R);                               // the indel entries' codes follow with the indel table
+        else for (size_t e = 0; e < R; ++e) { c[e] = code_lut[p[e]]; q[e] = qual_lut[p[e]]; }
         memcpy(pk.dict_, th.dict, 32);
         pk.ndict_ = (int)th.n_dict; pk.pk8_ok_ = true;
         for (int i = 0; i < pk.ndict_; ++i) pk.qidx_[pk.dict_[i] & 127] = (int8_t)i;
     } else {
         if (!get(pk.code_.data(), R) || !get(pk.qual_.data(), R)) return bad("code / qual arrays");
         pk.pk8_ok_ = false;
+        lazy = false;                                            // two-array tiles are stored expanded
     }
     if (!get(pk.mapq_.data(), R) || !get(pk.rpr_.data(), R)) return bad("mapq / rpr arrays");
-    // sample indices back from the bitmaps
-    uint32_t* smp = pk.smp_.data();
-    for (size_t s = 0; s < S; ++s) {
-        size_t e = pk.entry_off_[s];
-        const size_t e1 = pk.entry_off_[s + 1];
-        const uint8_t* bm = &bitmap_[s * nb];
-        for (size_t k = 0; k < nb; ++k)
-            for (unsigned w = bm[k]; w; w &= w - 1) { if (e >= e1) return bad("bitmap / offsets disagree"); smp[e++] = (uint32_t)(k * 8 + (unsigned)__builtin_ctz(w)); }
-        if (e != e1) return bad("bitmap / offsets disagree");
+    if (lazy) {
+        // covered samples stay in their bitmaps (Packer::expand_site); the rows must still add up to the offsets
+        for (size_t s = 0; s < S; ++s) {
+            const uint8_t* bm = &bitmap_[s * nb];
+            size_t n = 0, k = 0;
+            for (; k + 8 <= nb; k += 8) { uint64_t w; memcpy(&w, bm + k, 8); n += (size_t)__builtin_popcountll(w); }
+            for (; k < nb; ++k) n += (size_t)__builtin_popcount(bm[k]);
+            if (n != (size_t)(pk.entry_off_[s + 1] - pk.entry_off_[s])) return bad("bitmap / offsets disagree");
+        }
+        pk.lazy_bitmap_.swap(bitmap_);
+    } else {
+        // sample indices back from the bitmaps
+        uint32_t* smp = pk.smp_.data();
+        for (size_t s = 0; s < S; ++s) {
+            size_t e = pk.entry_off_[s];
+            const size_t e1 = pk.entry_off_[s + 1];
+            const uint8_t* bm = &bitmap_[s * nb];
+            for (size_t k = 0; k < nb; ++k)
+                for (unsigned w = bm[k]; w; w &= w - 1) { if (e >= e1) return bad("bitmap / offsets disagree"); smp[e++] = (uint32_t)(k * 8 + (unsigned)__builtin_ctz(w)); }
+            if (e != e1) return bad("bitmap / offsets disagree");
+        }
     }
     ie_.resize(th.n_indel); iq_.resize(th.n_indel); io_.resize((size_t)th.n_indel + 1); itext_.resize(th.indel_bytes);
     if (!get(ie_.data(), ie_.size() * 4) || !get(iq_.data(), iq_.size()) || !get(io_.data(), io_.size() * 4) || !get(&itext_[0], itext_.size()))
@@ -167,8 +181,14 @@ int PackedIo::next_tile(Packer& pk, std::string* err)
     for (size_t i = 0; i < ie_.size(); ++i) {
         if (ie_[i] >= R || io_[i] > io_[i + 1] || io_[i + 1] > itext_.size()) return bad("indel table");
         pk.qual_[ie_[i]] = iq_[i];
+        if (lazy) {
+            const unsigned b = pk.pk8_[ie_[i]], qi = BVC_PACK8_QI(b);
+            if (qi < BVC_PACK8_MAX_QUALS) return bad("indel table points at a counted entry");
+            pk.code_[ie_[i]] = qi == BVC_PACK8_INDEL ? BVC_MAKE_CODE(BVC_PACK8_BASE(b), BVC_PACK8_STRAND(b), 1) : BVC_MAKE_CODE(4, BVC_PACK8_STRAND(b), 1);
+        }
         pk.indel_.emplace((int64_t)ie_[i], itext_.substr(io_[i], io_[i + 1] - io_[i]));
     }
+    pk.lazy_ = lazy;
     pk.n_ = R;
     ++tiles_read_;
     return 1;

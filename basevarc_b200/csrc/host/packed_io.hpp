@@ -55,7 +55,8 @@ public:
     const PackedFileHeader& header() const { return hdr_; }
     const std::string& names() const { return names_; }
     // Replaces the packer's sites with the next tile of the file.  Returns 1, 0 at the end of the file, -1 on a corrupt file.
-    int next_tile(Packer& pk, std::string* err);
+    // lazy (the dispatcher; one-byte tiles only): the per-entry (code, qual, sample) arrays are left to Packer::expand_site
+    int next_tile(Packer& pk, std::string* err, bool lazy = false);
     static bool is_complete(const std::string& path, int32_t n_samples);
     // sites [s0, s1) of a tile as the packer's content (fixtures / benchmarks: bvc_write_packed_files); tile->sample is required,
     // indel entries get the token text `itok`, pos == NULL numbers the sites 1, 2, ...

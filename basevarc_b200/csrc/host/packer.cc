@@ -27,6 +27,7 @@ void Packer::clear()
     for (auto& q : qidx_) q = -1;
     ndict_ = 0; pk8_ok_ = true;
     trace_.clear(); early_.clear(); site_numeric_ = false;
+    lazy_ = false;
 }
 
 void Packer::reserve_entries(size_t need)
@@ -183,6 +184,22 @@ void Packer::append_raw(uint8_t code, uint8_t qual, uint8_t mapq, uint8_t rpr, u
     pk8_ok_ = false;
     if (indel_text) indel_.emplace((int64_t)n_, indel_text);
     ++n_;
+}
+
+void Packer::expand_site(int32_t site)
+{
+    if (!lazy_) return;
+    const size_t nb = ((size_t)n_samples_ + 7) / 8;
+    const uint32_t e0 = entry_off_[(size_t)site], e1 = entry_off_[(size_t)site + 1];
+    for (uint32_t e = e0; e < e1; ++e) {
+        const unsigned b = pk8_[e], qi = BVC_PACK8_QI(b), st = BVC_PACK8_STRAND(b), base = BVC_PACK8_BASE(b);
+        if (qi < BVC_PACK8_MAX_QUALS) { code_[e] = BVC_MAKE_CODE(base, st, 0); qual_[e] = qi < (unsigned)ndict_ ? dict_[qi] : (uint8_t)0; }
+        else code_[e] = qi == BVC_PACK8_INDEL ? BVC_MAKE_CODE(base, st, 1) : BVC_MAKE_CODE(4, st, 1);     // (stale qual: set with the indel table)
+    }
+    const uint8_t* bm = &lazy_bitmap_[(size_t)site * nb];
+    uint32_t e = e0;
+    for (size_t k = 0; k < nb && e < e1; ++k)
+        for (unsigned w = bm[k]; w && e < e1; w &= w - 1) smp_[e++] = (uint32_t)(k * 8 + (unsigned)__builtin_ctz(w));
 }
 
 void Packer::drop_last_site()

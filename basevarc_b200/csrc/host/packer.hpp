@@ -49,6 +49,9 @@ public:
     void set_state(const SiteTrace& st) { st_base_ = st.base; st_mapq_ = st.mapq; st_qual_ = st.qual; st_rpr_ = st.rpr; st_strand_ = st.strand; }
     // one raw entry into the current site (merged per-site views of the sharded formatter); indel_text != NULL for an indel entry
     void append_raw(uint8_t code, uint8_t qual, uint8_t mapq, uint8_t rpr, uint32_t sample, const char* indel_text);
+    // code / qual / sample of the entries of one site of a lazily read tile (no-op otherwise; idempotent)
+    void expand_site(int32_t site);
+    bool lazy() const { return lazy_; }
     const uint8_t* codes() const { return code_.data(); }
     const uint8_t* quals() const { return qual_.data(); }
     const uint8_t* mapqs() const { return mapq_.data(); }
@@ -70,6 +73,11 @@ private:
     size_t n_ = 0, cap_ = 0;
     // compact wire form of (code, qual) built alongside (include/bvc_gpu.h BVC_PACK8): valid while the tile has <= 30 quals
     std::vector<uint8_t> pk8_;
+    // A tile read LAZILY from a packed tile file (PackedIo::next_tile with lazy = true: the dispatcher): code_ carries only the
+    // indel entries (all the CVG line looks at), qual_ / smp_ nothing; expand_site fills the three arrays for one site -- the VCF
+    // columns of an LRT-positive site are the only reader of them (src/BaseType.cpp:152-163).
+    std::vector<uint8_t> lazy_bitmap_;     // [n_sites][ceil(N/8)] covered samples
+    bool lazy_ = false;
     uint8_t dict_[32] = {0};
     int8_t qidx_[128];
     int ndict_ = 0;

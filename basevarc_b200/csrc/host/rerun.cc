@@ -485,6 +485,7 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
             const int32_t* gd = G ? &j.group_depth[(size_t)s * G * 4] : nullptr;
             const double* ga = G ? &j.group_af[(size_t)s * G * 4] : nullptr;
             const long long t0 = now_ns();
+            if (r->lrt_ok) j.pk.expand_site(s);
             if (r->lrt_ok) format_vcf(vline, sh->chr.c_str(), pos[s], &t, s, r, sh->N, G, sh->group_name_ptrs.data(), gd, ga);
             format_cvg(cline, sh->chr.c_str(), pos[s], &t, s, r, &j.pk, G, gd);
             const long long t1 = now_ns();
@@ -543,7 +544,7 @@ void window_worker(Shared* sh, GpuServer* gpu, int ithread, std::string* vcf_out
     auto fill_packed = [&](TileJob& j) -> int {
         std::string e;
         const long long t0 = now_ns();
-        const int rc = pin.next_tile(j.pk, &e);
+        const int rc = pin.next_tile(j.pk, &e, sh->n_groups == 0);      // lazily: only the VCF columns of an LRT-positive site read code / qual / sample
         t_read += now_ns() - t0;
         if (rc < 0) sh->fail(e);
         return rc;

@@ -160,3 +160,28 @@ def test_corrupt_batch_file_fails_the_command_with_and_without_the_pool(tmp_path
         assert r.returncode != 0, kind
         assert "corrupt batch file" in r.stderr or "complete" in r.stderr, r.stderr[-500:]
         assert not os.path.exists(d / "test.out.tmp.thread.1" / "packed.bvc")      # nothing half-written passes for a packed file
+
+
+def test_lazy_read_of_packed_tiles_equals_the_full_read(tmp_path):
+    """The dispatcher reads one-byte tiles lazily (indel entries only; code / qual / sample of a site on demand for the VCF
+    columns): tools/ubench/packed_lazy_test.cc holds PackedIo / Packer to the full read on C1's files and on a synthetic
+    window with many indel entries, N-base ones included."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "packed_lazy_test")
+    cc = subprocess.run(["g++", "-O1", "-std=c++17", "-I" + os.path.join(root, "include"), "-I" + os.path.join(root, "basevarc_b200", "csrc", "host"),
+                         os.path.join(root, "tools", "ubench", "packed_lazy_test.cc"), os.path.join(root, "basevarc_b200", "csrc", "host", "packed_io.cc"),
+                         os.path.join(root, "basevarc_b200", "csrc", "host", "packer.cc"), "-o", exe], capture_output=True, text=True, timeout=300)
+    assert cc.returncode == 0, cc.stderr[-2000:]
+    args = _c1_workdir(tmp_path)
+    r = subprocess.run([host.BIN_PATH, "basetype", "--pack", "--tile_sites", "600"] + args, cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    files = [str(tmp_path / ("test.out.tmp.thread.%d" % t) / "packed.bvc") for t in range(T)]
+    tile = synth_tile(300, 2500, 1.2, "highpoly", seed=5, indel_frac=0.08)
+    c = tile.code.copy()
+    ind = np.nonzero((c & 16) != 0)[0]
+    c[ind[::5]] = (c[ind[::5]] & 0x18) | 4
+    tile.code = c
+    host.write_packed_files(tile, str(tmp_path / "syn"), 2, tile_sites=400)
+    files += [str(tmp_path / ("syn.tmp.thread.%d" % k) / "packed.bvc") for k in range(2)]
+    r = subprocess.run([exe] + files, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "lazy == full" in r.stdout, r.stdout + r.stderr
