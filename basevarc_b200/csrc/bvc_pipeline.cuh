@@ -1698,6 +1698,10 @@ __global__ void __launch_bounds__(kVcfWarps * 32)
 vcf_stats_kernel(PipeArgs a)
 {
     __shared__ uint32_t H_s[kVcfWarps][6 * 256];
+    __shared__ uint8_t dict_s[32];                      // the qual dictionary: indexed per entry (a kernel parameter indexed by a
+                                                        // lane-varying value is served one distinct address at a time)
+    if (threadIdx.x < 32) dict_s[threadIdx.x] = a.s.dict.q[threadIdx.x];
+    __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint32_t* H = H_s[wid];
     const uint32_t n_list = *a.vcf_n;
@@ -1745,10 +1749,12 @@ vcf_stats_kernel(PipeArgs a)
                     if (base == ref) g[k] = 0; else if (base < 4 && (altmask >> base & 1)) g[k] = 1;
                 }
                 any |= g[k] >= 0;
-                if (pk4) qw |= (uint32_t)a.s.dict.q[cnt ? BVC_PACK8_QI(c) : 0u] << (8 * k);
             }
             if (!any) continue;
-            if (!pk4) qw = __ldg(qual4 + wi);
+            if (pk4) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) if (g[k] >= 0) qw |= (uint32_t)dict_s[BVC_PACK8_QI((cw >> (8 * k)) & 255u)] << (8 * k);
+            } else qw = __ldg(qual4 + wi);
             const uint32_t mw = mapq4[wi], rw = rpr4[wi];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
