@@ -1694,7 +1694,10 @@ ladder_kernel(PipeArgs a)
 // =====================================================================================================
 constexpr int kVcfWarps = 4;
 
-__global__ void __launch_bounds__(kVcfWarps * 32)
+#ifndef BVC_VCF_MINBLOCKS
+#define BVC_VCF_MINBLOCKS 8                // 64 registers (132 B of spills) for 8 blocks per SM: the kernel is latency-bound (27 % of the warp slots at
+#endif                                    // 88 registers); C5's 25k LRT-positive sites: 0.337 -> 0.283 ms (7 blocks: 0.291)
+__global__ void __launch_bounds__(kVcfWarps * 32, BVC_VCF_MINBLOCKS)
 vcf_stats_kernel(PipeArgs a)
 {
     __shared__ uint32_t H_s[kVcfWarps][6 * 256];
