@@ -958,7 +958,10 @@ cvg_fisher_deep_kernel(PipeArgs a)
     }
 }
 
-__global__ void __launch_bounds__(128)
+#ifndef BVC_PREP_MINBLOCKS
+#define BVC_PREP_MINBLOCKS 1                 // 72 registers; 8 blocks per SM (64 registers) measured: 0.137 against 0.134 ms, no gain
+#endif
+__global__ void __launch_bounds__(128, BVC_PREP_MINBLOCKS)
 site_prepare_kernel(PipeArgs a)
 {
     const int site = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1679,7 +1682,10 @@ __device__ __forceinline__ void ladder_site(const PipeArgs& a, uint32_t item)
     finalize_site(a, site, ref, su, L.cvg_fs, L.cvg_sor, L.cand4, n, L.frq[0], L.frq[1], L.frq[2], L.frq[3], L.chi_t, L.em_fits, L.em_passes, L.flags);
 }
 
-__global__ void __launch_bounds__(128)
+#ifndef BVC_LADDER_MINBLOCKS
+#define BVC_LADDER_MINBLOCKS 1               // 80 registers; 8 blocks per SM (64 registers) measured: 0.245 against 0.240 ms, no gain
+#endif
+__global__ void __launch_bounds__(128, BVC_LADDER_MINBLOCKS)
 ladder_kernel(PipeArgs a)
 {
     // the sites with fits in flight are exactly the slot-0 items of this stage's (unsorted) queue
