@@ -54,6 +54,21 @@ class Tile(C.Structure):
     ]
 
 
+class CodedTile(C.Structure):
+    """bvc_coded_tile (include/bvc_gpu.h, coded wire form)."""
+    _fields_ = [
+        ("bits", C.c_int32),
+        ("n_codes", C.c_int32),
+        ("code_byte", C.c_uint8 * 64),
+        ("words", C.c_void_p),
+        ("escapes", C.c_void_p),
+        ("chunk_escapes", C.c_void_p),
+        ("n_escape", C.c_int64),
+    ]
+
+
+CODED_CHUNK = 8192
+
 SITE_RESULT_DTYPE = np.dtype(
     [
         ("cvg_fs", "<f8"),

@@ -10,7 +10,7 @@ import os
 
 import numpy as np
 
-from ._abi import SITE_CORE_DTYPE, SITE_RESULT_DTYPE, Params, Tile, default_params
+from ._abi import CODED_CHUNK, CodedTile, SITE_CORE_DTYPE, SITE_RESULT_DTYPE, Params, Tile, default_params
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbvc_gpu.so")
@@ -22,6 +22,7 @@ EXPORTS = (
     "bvc_resident_download", "bvc_kernel_launch_count", "bvc_measure_fp64_peak", "bvc_kernel_name", "bvc_transfer_bytes", "bvc_work_counters",
     "bvc_shard_unique_id", "bvc_shard_init", "bvc_shard_call", "bvc_shard_upload", "bvc_shard_run", "bvc_shard_init_group",
     "bvc_shard_call_group", "bvc_shard_stats", "bvc_shard_phase_name", "bvc_call_sites_noalloc",
+    "bvc_coded_words", "bvc_encode_codes", "bvc_decode_codes_host", "bvc_enqueue_split_coded",
 )
 NOALLOC_MAX_SITES = 65536       # include/bvc_gpu.h BVC_NOALLOC_*
 NOALLOC_MAX_SAMPLES = 16384
@@ -82,6 +83,11 @@ def load_library():
     L.bvc_shard_stats.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
     L.bvc_shard_phase_name.argtypes = [C.c_int]
     L.bvc_shard_phase_name.restype = C.c_char_p
+    L.bvc_coded_words.argtypes = [C.c_int64, C.c_int]
+    L.bvc_coded_words.restype = C.c_size_t
+    L.bvc_encode_codes.argtypes = [C.POINTER(Tile), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(CodedTile)]
+    L.bvc_decode_codes_host.argtypes = [C.POINTER(CodedTile), C.POINTER(Tile), C.c_void_p]
+    L.bvc_enqueue_split_coded.argtypes = [C.c_void_p, C.POINTER(Tile), C.POINTER(CodedTile), C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_uint64)]
     L.bvc_call_sites_noalloc.argtypes = [C.c_int, C.POINTER(Params), C.POINTER(Tile), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     _lib = L
     return L
@@ -106,6 +112,44 @@ def measure_fp64_peak(device=0):
     if rc != 0:
         raise BvcError("bvc_measure_fp64_peak: %s" % L.bvc_last_error(None).decode())
     return t.value
+
+
+class CodedArrays:
+    """A tile's packed8 bytes in the coded wire form (include/bvc_gpu.h): the bvc_coded_tile + the arrays it points into.
+    `alloc(shape, dtype)` supplies the arrays (numpy by default; bench.py passes a pinned allocator)."""
+
+    def __init__(self, tile, alloc=None):
+        L = load_library()
+        assert tile.packed8 is not None, "tile.pack8() first"
+        n = tile.n_entries
+        mk = alloc or (lambda shape, dtype: np.zeros(shape, dtype))
+        self._keep = [mk((max(int(L.bvc_coded_words(n, 6)), 1),), np.uint32), mk((n // 8 + 16,), np.uint8), mk((n // CODED_CHUNK + 2,), np.uint32)]
+        arrs = [getattr(k, "array", k) for k in self._keep]
+        self.words, self.escapes, self.chunk_escapes = arrs
+        self.ct = CodedTile()
+        self._tile_ct = tile.as_ctypes(with_sample=False)
+        self._tile = tile
+        rc = L.bvc_encode_codes(C.byref(self._tile_ct), self.words.ctypes.data, self.escapes.ctypes.data, self.chunk_escapes.ctypes.data, C.byref(self.ct))
+        if rc != 0:
+            raise BvcError("bvc_encode_codes failed (%d)" % rc)
+        self.n = n
+
+    @property
+    def bits(self):
+        return int(self.ct.bits)
+
+    @property
+    def wire_bytes(self):
+        """Bytes this form puts on the wire for the (code, qual) information of the tile."""
+        L = load_library()
+        return int(L.bvc_coded_words(self.n, self.bits)) * 4 + int(self.ct.n_escape) + (self.n // CODED_CHUNK + 2) * 4 if self.bits else self.n
+
+    def decode_host(self):
+        out = np.zeros(self.n, np.uint8)
+        rc = load_library().bvc_decode_codes_host(C.byref(self.ct), C.byref(self._tile_ct), out.ctypes.data)
+        if rc != 0:
+            raise BvcError("bvc_decode_codes_host failed (%d)" % rc)
+        return out
 
 
 class PinnedArray:
@@ -181,6 +225,15 @@ class BaseTypeCaller:
         tk = C.c_uint64(0)
         self._check(self.lib.bvc_enqueue_split(self.ctx, C.byref(ct), core.ctypes.data, vcf.ctypes.data if vcf.shape[0] else None,
                                                int(vcf.shape[0]), C.byref(tk)), "bvc_enqueue_split")
+        return tk.value
+
+    def enqueue_split_coded(self, tile, coded, core, vcf):
+        """bvc_enqueue_split_coded: `tile` carries qual_dict (tile.pack8() done) and `coded` = CodedArrays(tile)."""
+        ct = tile.as_ctypes(with_sample=False, drop_code_qual=True)
+        ct.packed8 = None
+        tk = C.c_uint64(0)
+        self._check(self.lib.bvc_enqueue_split_coded(self.ctx, C.byref(ct), C.byref(coded.ct), core.ctypes.data, vcf.ctypes.data if vcf.shape[0] else None,
+                                                     int(vcf.shape[0]), C.byref(tk)), "bvc_enqueue_split_coded")
         return tk.value
 
     def wait_split(self, ticket):

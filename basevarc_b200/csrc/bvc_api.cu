@@ -4,12 +4,14 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <mutex>
 #include <string>
 #include <unordered_map>
 #include <vector>
 
 #include "bvc_ctx.h"
+#include "bvc_codes.h"
 
 using bvc::Slot;
 using bvc::kCtrWords;
@@ -164,8 +166,9 @@ int bvc::check_tile(bvc_ctx* ctx, const bvc_tile* t, int64_t* n_entries)
     if (!t || t->n_sites < 0 || !t->entry_off || (t->n_sites > 0 && !t->ref_base)) { set_err(ctx, "bad tile: NULL array or n_sites < 0"); return BVC_ERR_ARG; }
     if (t->entry_off[0] != 0) { set_err(ctx, "bad tile: entry_off[0] != 0"); return BVC_ERR_ARG; }
     const int64_t R = t->entry_off[t->n_sites];
-    if (R > 0 && (!t->mapq || !t->rpr || (!t->packed8 && (!t->code || !t->qual)))) { set_err(ctx, "bad tile: NULL entry array"); return BVC_ERR_ARG; }
-    if (R > 0 && t->packed8 && (!t->qual_dict || t->n_qual_dict < 1 || t->n_qual_dict > BVC_PACK8_MAX_QUALS)) { set_err(ctx, "bad tile: packed8 needs qual_dict with 1..30 entries"); return BVC_ERR_ARG; }
+    const bool coded = ctx->pending_coded != nullptr;
+    if (R > 0 && (!t->mapq || !t->rpr || (!coded && !t->packed8 && (!t->code || !t->qual)))) { set_err(ctx, "bad tile: NULL entry array"); return BVC_ERR_ARG; }
+    if (R > 0 && (t->packed8 || coded) && (!t->qual_dict || t->n_qual_dict < 1 || t->n_qual_dict > BVC_PACK8_MAX_QUALS)) { set_err(ctx, "bad tile: packed8 needs qual_dict with 1..30 entries"); return BVC_ERR_ARG; }
     if (ctx->prm.n_groups > 0 && R > 0 && !t->sample) { set_err(ctx, "bad tile: groups need the sample array"); return BVC_ERR_ARG; }
     if (t->n_sites > ctx->prm.max_sites || R > ctx->prm.max_entries) { set_err(ctx, "tile exceeds the capacity given at bvc_create"); return BVC_ERR_CAPACITY; }
     *n_entries = R;
@@ -195,7 +198,8 @@ int bvc::upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool reside
     CK(cudaMemcpyAsync(s.d_off, t->entry_off, (S + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
     ctx->h2d_bytes += (int64_t)(S + (S + 1) * sizeof(uint32_t));
     if (R) {
-        if (t->packed8) {
+        const bvc_coded_tile* cd = ctx->pending_coded;
+        if (t->packed8 || cd) {
             // compact wire form: R bytes over PCIe instead of 2R, and the form the tile STAYS in: K1 (site_hist8_kernel) and K5
             // read the byte directly.  Only the paths that still read the two arrays get them expanded: --group, the
             // sample-sharded kernels, the IEEE-faithful legacy kernel (a qual-0 read anywhere in the tile, BVC_LEGACY_KERNEL=1),
@@ -204,8 +208,23 @@ int bvc::upload(bvc_ctx* ctx, Slot& s, const bvc_tile* t, int64_t R, bool reside
             bool q0 = false;
             for (int i = 0; i < 32; ++i) { d.q[i] = i < t->n_qual_dict ? t->qual_dict[i] : (uint8_t)0; q0 = q0 || (i < t->n_qual_dict && d.q[i] == 0); }
             for (int i = 0; i < t->n_qual_dict; ++i) if (d.q[i] > 127) { set_err(ctx, "bad tile: qual_dict entry > 127"); return BVC_ERR_ARG; }
-            CK(cudaMemcpyAsync(s.d_pk8, t->packed8, (size_t)R, cudaMemcpyHostToDevice, s.stream));
-            ctx->h2d_bytes += R;
+            if (cd) {
+                // coded wire form: the bit stream rides in d_code, the escapes and their per-chunk offsets in d_qual (both unused
+                // by a tile that stays in its one-byte form; expand8 below runs AFTER the decode if the arrays are needed)
+                const size_t wbytes = bvc_coded_words(R, cd->bits) * sizeof(uint32_t), nch = (size_t)((R + bvc::kCodedChunk - 1) / bvc::kCodedChunk) + 1;
+                const size_t esc_room = ((size_t)cd->n_escape + 15) & ~(size_t)15;
+                if (wbytes > (size_t)R + 16 || esc_room + nch * sizeof(uint32_t) > (size_t)R + 16) { set_err(ctx, "bad coded tile: more escapes than n/8 (send packed8)"); return BVC_ERR_ARG; }
+                CK(cudaMemcpyAsync(s.d_code, cd->words, wbytes, cudaMemcpyHostToDevice, s.stream));
+                if (cd->n_escape) CK(cudaMemcpyAsync(s.d_qual, cd->escapes, (size_t)cd->n_escape, cudaMemcpyHostToDevice, s.stream));
+                CK(cudaMemcpyAsync(s.d_qual + esc_room, cd->chunk_escapes, nch * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
+                ctx->h2d_bytes += (int64_t)(wbytes + (size_t)cd->n_escape + nch * sizeof(uint32_t));
+                CK(bvc::launch_decode_codes(cd->bits, reinterpret_cast<const uint32_t*>(s.d_code), s.d_qual, reinterpret_cast<const uint32_t*>(s.d_qual + esc_room),
+                                            cd->code_byte, s.d_off, s.d_ref, t->n_sites, s.d_pk8, R, ctx->n_sm, s.stream));
+                ctx->launches += 1;
+            } else {
+                CK(cudaMemcpyAsync(s.d_pk8, t->packed8, (size_t)R, cudaMemcpyHostToDevice, s.stream));
+                ctx->h2d_bytes += R;
+            }
             s.dict = d; s.n_dict = t->n_qual_dict;
             if (need_arrays || q0 || ctx->expand8 || ctx->legacy_only || ctx->wide_hist || ctx->prm.n_groups > 0 || ctx->prm.n_samples >= 65536) {
                 CK(bvc::launch_expand8(s.d_pk8, s.d_code, s.d_qual, R, d, ctx->n_sm, s.stream));
@@ -491,6 +510,103 @@ int bvc_enqueue_split(bvc_ctx* ctx, const bvc_tile* tile, bvc_site_core* core, b
     ctx->resident = false;
     *ticket = tk;
     return BVC_OK;
+}
+
+size_t bvc_coded_words(int64_t n_entries, int bits) { return n_entries > 0 ? (size_t)((n_entries + 31) / 32) * (size_t)bits : 0; }
+
+int bvc_encode_codes(const bvc_tile* t, uint32_t* words, uint8_t* escapes, uint32_t* chunk_escapes, bvc_coded_tile* out)
+{
+    if (!out || !t || t->n_sites < 0 || !t->entry_off) return BVC_ERR_ARG;
+    const uint8_t* pk = t->packed8;
+    const int64_t n = t->entry_off[t->n_sites];
+    if (n > 0 && (!pk || !t->ref_base || !words || !escapes || !chunk_escapes)) return BVC_ERR_ARG;
+    memset(out, 0, sizeof *out);
+    if (n < 4096) return BVC_OK;                                    // not worth a kernel: send packed8
+    // relative bytes (base field -> (base - ref) & 3) into a scratch copy: one pass over the sites
+    std::vector<uint8_t> rel((size_t)n);
+    for (int32_t s = 0; s < t->n_sites; ++s) {
+        const unsigned ref = t->ref_base[s] & 3u;
+        if (t->entry_off[s] > t->entry_off[s + 1]) return BVC_ERR_ARG;
+        for (uint32_t e = t->entry_off[s]; e < t->entry_off[s + 1]; ++e) rel[e] = bvc::abs_to_rel(pk[e], ref);
+    }
+    int64_t hist[256] = {0};
+    for (int64_t e = 0; e < n; ++e) hist[rel[e]]++;
+    int order[256];
+    for (int i = 0; i < 256; ++i) order[i] = i;
+    std::stable_sort(order, order + 256, [&](int a, int b) { return hist[a] > hist[b]; });
+    int best = 0; int64_t best_cost = n - n / 10, best_esc = 0;      // must save >= 10 % of the packed8 bytes
+    for (int W = 4; W <= 6; ++W) {
+        const int nd = (1 << W) - 1;
+        int64_t direct = 0;
+        for (int i = 0; i < nd; ++i) direct += hist[order[i]];
+        const int64_t esc = n - direct, cost = (int64_t)bvc_coded_words(n, W) * 4 + esc;
+        if (esc <= n / 8 && cost < best_cost) { best = W; best_cost = cost; best_esc = esc; }
+    }
+    if (!best) return BVC_OK;
+    const int W = best, nd = (1 << W) - 1;
+    const uint32_t ESC = (uint32_t)nd;
+    uint8_t rank[256];
+    memset(rank, (int)ESC, sizeof rank);
+    for (int i = 0; i < nd; ++i) if (hist[order[i]] > 0) { rank[order[i]] = (uint8_t)i; out->code_byte[i] = (uint8_t)order[i]; out->n_codes = i + 1; }
+    const int64_t n_units = (n + 31) / 32;
+    int64_t ne = 0;
+    for (int64_t u = 0; u < n_units; ++u) {
+        if ((u & 255) == 0) chunk_escapes[u >> 8] = (uint32_t)ne;
+        uint32_t w[7] = {0, 0, 0, 0, 0, 0, 0};
+        for (int j = 0; j < 32; ++j) {
+            const int64_t e = u * 32 + j;
+            const uint32_t c = e < n ? rank[rel[(size_t)e]] : 0u;
+            if (e < n && c == ESC) escapes[ne++] = pk[e];
+            const int bit = j * W, wi = bit >> 5, sh = bit & 31;
+            w[wi] |= c << sh;
+            if (sh + W > 32) w[wi + 1] |= c >> (32 - sh);
+        }
+        for (int i = 0; i < W; ++i) words[u * W + i] = w[i];
+    }
+    chunk_escapes[(n + bvc::kCodedChunk - 1) / bvc::kCodedChunk] = (uint32_t)ne;
+    if (ne != best_esc) return BVC_ERR_STATE;
+    out->bits = W; out->words = words; out->escapes = escapes; out->chunk_escapes = chunk_escapes; out->n_escape = ne;
+    return BVC_OK;
+}
+
+int bvc_decode_codes_host(const bvc_coded_tile* c, const bvc_tile* t, uint8_t* dst)
+{
+    if (!t || t->n_sites < 0 || !t->entry_off) return BVC_ERR_ARG;
+    const int64_t n = t->entry_off[t->n_sites];
+    if (n > 0 && !t->ref_base) return BVC_ERR_ARG;
+    int32_t site = 0;
+    if (!c || n < 0 || (n > 0 && (!dst || c->bits < 4 || c->bits > 6 || !c->words || !c->chunk_escapes))) return BVC_ERR_ARG;
+    int64_t ne = 0;
+    for (int64_t u = 0; u * 32 < n; ++u) {
+        if ((u & 255) == 0 && c->chunk_escapes[u >> 8] != (uint32_t)ne) return BVC_ERR_STATE;      // the per-chunk offsets the kernel starts from
+        uint32_t w[7] = {0, 0, 0, 0, 0, 0, 0};
+        for (int i = 0; i < c->bits; ++i) w[i] = c->words[u * c->bits + i];
+        uint8_t out[32]; uint32_t em = 0;
+        if (c->bits == 4) bvc::decode_unit<4>(w, c->code_byte, out, &em);
+        else if (c->bits == 5) bvc::decode_unit<5>(w, c->code_byte, out, &em);
+        else bvc::decode_unit<6>(w, c->code_byte, out, &em);
+        for (int j = 0; j < 32 && u * 32 + j < n; ++j) {
+            const int64_t e = u * 32 + j;
+            while (e >= (int64_t)t->entry_off[site + 1]) ++site;
+            dst[e] = (em >> j & 1u) ? c->escapes[ne++] : bvc::rel_to_abs(out[j], t->ref_base[site] & 3u);
+        }
+    }
+    return ne == c->n_escape ? BVC_OK : BVC_ERR_STATE;
+}
+
+int bvc_enqueue_split_coded(bvc_ctx* ctx, const bvc_tile* tile, const bvc_coded_tile* coded, bvc_site_core* core, bvc_site_result* vcf,
+                            int32_t vcf_cap, uint64_t* ticket)
+{
+    if (!ctx) return BVC_ERR_ARG;
+    if (!tile || !coded || coded->bits < 4 || coded->bits > 6 || !coded->words || !coded->chunk_escapes || coded->n_escape < 0 ||
+        (coded->n_escape > 0 && !coded->escapes) || tile->packed8) {
+        set_err(ctx, "bvc_enqueue_split_coded: bad coded tile (bits 4..6, arrays, packed8 must be NULL)");
+        return BVC_ERR_ARG;
+    }
+    ctx->pending_coded = coded;
+    const int rc = bvc_enqueue_split(ctx, tile, core, vcf, vcf_cap, ticket);
+    ctx->pending_coded = nullptr;
+    return rc;
 }
 
 int bvc_wait_split(bvc_ctx* ctx, uint64_t ticket, int32_t* n_vcf)

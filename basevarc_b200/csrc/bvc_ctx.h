@@ -83,6 +83,7 @@ struct bvc_ctx {
     bool legacy_only = false;      // BVC_LEGACY_KERNEL=1: the single warp-per-site kernel for every site (A/B checks)
     std::string err;
     bool resident = false;
+    const bvc_coded_tile* pending_coded = nullptr;   // set by bvc_enqueue_split_coded for the upload of ITS tile only
     bvc::ShardState* shard = nullptr;   // sample-sharded mode (bvc_shard_init / bvc_shard_init_group)
 };
 

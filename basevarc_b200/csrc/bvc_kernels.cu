@@ -6,6 +6,7 @@
 #include <mutex>
 #include "bvc_kernels.h"
 #include "bvc_ctx.h"
+#include "bvc_codes.h"
 #include "bvc_site_kernel.cuh"
 #include "bvc_pipeline.cuh"
 #include "bvc_groups.cuh"
@@ -509,6 +510,91 @@ cudaError_t launch_expand8(const uint8_t* pk8, uint8_t* code, uint8_t* qual, int
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream)
 {
     fp64_peak_kernel<<<blocks, threads, 0, stream>>>(out, iters);
+    return cudaGetLastError();
+}
+
+}  // namespace bvc
+
+// ---- coded wire form -> resident packed8 bytes (bvc_codes.h): a block decodes one chunk of 8,192 entries ---------------
+namespace bvc {
+
+struct CodeLut { uint8_t b[64]; };
+
+template <int W>
+__global__ void __launch_bounds__(256)
+decode_codes_kernel(const uint32_t* __restrict__ words, const uint8_t* __restrict__ esc, const uint32_t* __restrict__ chunk_esc,
+                    CodeLut lut, const uint32_t* __restrict__ entry_off, const uint8_t* __restrict__ ref_base, int n_sites,
+                    uint8_t* __restrict__ pk8, long long n)
+{
+    __shared__ uint8_t lut_s[64];
+    __shared__ uint32_t warp_tot[8];
+    if (threadIdx.x < 64) lut_s[threadIdx.x] = lut.b[threadIdx.x];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long long n_chunks = (n + kCodedChunk - 1) / kCodedChunk;
+    for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const long long unit = chunk * 256 + threadIdx.x, e0 = unit * 32;
+        uint32_t w[W + 1];
+        uint8_t out[32];
+        uint32_t em = 0;
+        const bool on = e0 < n;
+        if (on) {
+#pragma unroll
+            for (int i = 0; i < W; ++i) w[i] = __ldg(words + unit * W + i);
+            w[W] = 0;
+            decode_unit<W>(w, lut_s, out, &em);
+            if (e0 + 32 > n) em &= (1u << (int)(n - e0)) - 1u;           // padding codes behind the last entry are not escapes
+            // relative -> absolute base: the site of entry e0 (largest s with entry_off[s] <= e0), then walk on with the entries
+            int lo = 0, hi = n_sites;                                    // entry_off[lo] <= e0 < entry_off[hi] (= n)
+            while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if ((long long)__ldg(entry_off + mid) <= e0) lo = mid; else hi = mid; }
+            int site = lo;
+            long long next = (long long)__ldg(entry_off + site + 1);
+            unsigned ref = __ldg(ref_base + site) & 3u;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const long long e = e0 + j;
+                if (e < n) {
+                    while (e >= next) { ++site; next = (long long)__ldg(entry_off + site + 1); ref = __ldg(ref_base + site) & 3u; }
+                    out[j] = rel_to_abs(out[j], ref);
+                }
+            }
+        }
+        // exclusive prefix of the escape counts over the block: the chunk's escapes lie in entry order behind chunk_esc[chunk]
+        const uint32_t cnt = (uint32_t)__popc(em);
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += up; }
+        if (lane == 31) warp_tot[wid] = incl;
+        __syncthreads();
+        uint32_t base = __ldg(chunk_esc + chunk) + incl - cnt;
+        for (int k = 0; k < wid; ++k) base += warp_tot[k];
+        __syncthreads();                                              // warp_tot is rewritten by the next chunk
+        if (on) {
+            for (uint32_t m = em; m; m &= m - 1) out[__ffs(m) - 1] = __ldg(esc + base++);
+            if (e0 + 32 <= n) {
+                uint4 v[2];
+                memcpy(v, out, 32);
+                reinterpret_cast<uint4*>(pk8 + e0)[0] = v[0];
+                reinterpret_cast<uint4*>(pk8 + e0)[1] = v[1];
+            } else {
+                for (int j = 0; j < 32 && e0 + j < n; ++j) pk8[e0 + j] = out[j];
+            }
+        }
+    }
+}
+
+cudaError_t launch_decode_codes(int bits, const uint32_t* words, const uint8_t* esc, const uint32_t* chunk_esc, const uint8_t* code_byte,
+                                const uint32_t* entry_off, const uint8_t* ref_base, int n_sites, uint8_t* pk8, int64_t n, int n_sm, cudaStream_t stream)
+{
+    if (n <= 0) return cudaSuccess;
+    CodeLut lut;
+    memcpy(lut.b, code_byte, 64);
+    long long blocks = (n + kCodedChunk - 1) / kCodedChunk;
+    if (blocks > (long long)n_sm * 8) blocks = (long long)n_sm * 8;
+    if (bits == 4) decode_codes_kernel<4><<<(unsigned)blocks, 256, 0, stream>>>(words, esc, chunk_esc, lut, entry_off, ref_base, n_sites, pk8, (long long)n);
+    else if (bits == 5) decode_codes_kernel<5><<<(unsigned)blocks, 256, 0, stream>>>(words, esc, chunk_esc, lut, entry_off, ref_base, n_sites, pk8, (long long)n);
+    else if (bits == 6) decode_codes_kernel<6><<<(unsigned)blocks, 256, 0, stream>>>(words, esc, chunk_esc, lut, entry_off, ref_base, n_sites, pk8, (long long)n);
+    else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }
 

@@ -69,6 +69,9 @@ cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cu
 // records -> 72-byte cores + compacted full records of the LRT-positive sites (bvc_enqueue_split)
 cudaError_t launch_split_result(const bvc_site_result* rec, int n_sites, bvc_site_core* core, bvc_site_result* vcf, uint32_t* vcf_n,
                                 cudaStream_t stream);
+// coded wire form (bvc_codes.h) -> packed8 bytes
+cudaError_t launch_decode_codes(int bits, const uint32_t* words, const uint8_t* esc, const uint32_t* chunk_esc, const uint8_t* code_byte,
+                                const uint32_t* entry_off, const uint8_t* ref_base, int n_sites, uint8_t* pk8, int64_t n, int n_sm, cudaStream_t stream);
 // packed8 -> (code, qual) arrays; n is rounded up to whole 16-byte words (the buffers are padded)
 cudaError_t launch_expand8(const uint8_t* pk8, uint8_t* code, uint8_t* qual, int64_t n, const QualDict& dict, int n_sm, cudaStream_t stream);
 }  // namespace bvc

@@ -452,7 +452,7 @@ def run_sharded(args, return_line=False):
 
     # ---- e2e leg: pinned host buffers through bvc_shard_call (H2D + collectives + D2H inside the region) --------
     pins = {}
-    packed = args.wire == "packed8" and tile.pack8()
+    packed = args.wire in ("packed8", "coded") and tile.pack8()
     for k in ("ref_base", "entry_off", "mapq", "rpr") + (("packed8",) if packed else ("code", "qual")):
         src = getattr(tile, k)
         pins[k] = PinnedArray(src.shape, src.dtype)
@@ -539,7 +539,7 @@ def main():
     ap.add_argument("--subtiles", type=int, default=4, help="sub-tiles per step on the host-buffer (e2e) path (measured: 2-6 within 5 %, 8 +14 %, 16 +38 %)")
     ap.add_argument("--result", default="split", choices=["split", "full"],
                     help="device->host form on the e2e path: 72-byte core per site + full records of the LRT-positive sites, or 176 bytes per site")
-    ap.add_argument("--wire", default="packed8", choices=["packed8", "plain"],
+    ap.add_argument("--wire", default="coded", choices=["packed8", "plain", "coded"],
                     help="host-buffer form of (code, qual) on the e2e path: one byte per entry + qual dictionary, or the two arrays")
     ap.add_argument("--ref-sites-per-thread", type=int, default=6000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -593,7 +593,7 @@ def main():
     # ---- kernel-only leg: inputs resident in HBM, device events on the launching stream -----------
     # the tile is resident in the form it travels in: one byte per entry + qual dictionary (--wire packed8, what the host
     # packer emits for <= 30 distinct quals; K1 reads the byte directly), or the two (code, qual) arrays (--wire plain)
-    resident_packed = args.wire == "packed8" and tile.pack8()
+    resident_packed = args.wire in ("packed8", "coded") and tile.pack8()
     caller.resident_upload(tile)
     for _ in range(args.warmup):
         caller.resident_run(1, flush_l2=False)
@@ -616,12 +616,12 @@ def main():
     # ---- e2e leg: host buffers through bvc_enqueue / bvc_wait (pinned H2D + D2H inside the region) --
     nsub = max(1, min(args.subtiles, S))
     bounds = np.linspace(0, S, nsub + 1).astype(int)
-    subs, pins = [], []
+    subs, pins, coded = [], [], []
     for i in range(nsub):
         t = tile.slice_sites(int(bounds[i]), int(bounds[i + 1]))
         # the compact wire form (one byte per entry + qual dictionary; what the host packer emits for a tile with <= 30
         # distinct quals) unless --wire plain: the e2e path is PCIe-bound, this halves the bytes of the two big arrays
-        packed = args.wire == "packed8" and t.pack8()
+        packed = args.wire in ("packed8", "coded") and t.pack8()
         wire = "packed8" if packed else "plain"
         for k in ("ref_base", "entry_off", "mapq", "rpr") + (("packed8",) if packed else ("code", "qual")):
             src = getattr(t, k)
@@ -630,6 +630,16 @@ def main():
             pins.append(pa)
             setattr(t, k, pa.array)
         subs.append(t)
+        # --wire coded: the packed8 bytes as 4 / 5 / 6-bit codes relative to the site's reference base + escapes (include/bvc_gpu.h,
+        # "coded wire form"), decoded back into the resident packed8 bytes by a kernel inside the enqueue; split result only
+        cod = None
+        if packed and args.wire == "coded" and args.result == "split":
+            cod = B.CodedArrays(t, alloc=lambda shape, dtype: PinnedArray(shape, dtype))
+            if not cod.bits:
+                cod = None
+        coded.append(cod)
+        if cod is not None:
+            wire = "coded%d" % cod.bits
     # result form: "split" = the 72-byte core of every site + the full 176-byte record of the LRT-positive sites only
     # (bvc_enqueue_split; the half that stays behind is zero for every other site), "full" = 176 bytes for every site
     split = args.result == "split"
@@ -658,7 +668,10 @@ def main():
         for i, (t, o) in enumerate(zip(subs, outs)):
             if len(fly) == 2:
                 retire()
-            fly.append((i, caller.enqueue_split(t, o.array, vcfs[i].array) if split else caller.enqueue(t, o.array)))
+            if coded[i] is not None:
+                fly.append((i, caller.enqueue_split_coded(t, coded[i], o.array, vcfs[i].array)))
+            else:
+                fly.append((i, caller.enqueue_split(t, o.array, vcfs[i].array) if split else caller.enqueue(t, o.array)))
         while drain and fly:
             retire()
 

@@ -233,6 +233,38 @@ const char* bvc_shard_phase_name(int i);
 /* FP64 pipe microbenchmark (dependent-free DFMA chains on all SMs): returns TFLOP/s (2 flop/FMA). */
 int  bvc_measure_fp64_peak(int device, double* tflops);
 
+/* ---- Coded wire form: fewer bytes over a saturated host link ---------------------------------------------------------
+ * No counterpart in the reference.  bvc_enqueue's host->device copy of the entries is what bounds the host-buffer path (401 MB
+ * per 1 M-site C2 tile at 52 of the link's 55 GB/s; with 8 GPUs the box's host link saturates at 226 GB/s, DESIGN.md section
+ * 6), and a packed8 byte carries < 8 bits: a low-pass tile has ~42 frequent byte values (21 quals x 2 strands at the reference
+ * base).  The coded form sends W = 4, 5 or 6 bits per entry: a byte is made relative to its site's reference base (base field ->
+ * (base - ref) & 3), the tile's 2^W - 1 most frequent relative values become codes, every other entry is the escape code
+ * 2^W - 1 plus its packed8 byte in a side array -- and a kernel turns it back into the resident
+ * packed8 bytes (0.75 B + escapes in, 1 B out per entry), after which the path is the packed8 one, byte for byte.
+ *   words          bit stream: entries 32u .. 32u+31 occupy W consecutive words, entry j at bits [jW, jW+W) of that little-endian
+ *                  32W-bit string; ceil(n/32) * W words
+ *   escapes        the packed8 bytes of the escaped entries, in entry order
+ *   chunk_escapes  [ceil(n / BVC_CODED_CHUNK) + 1] number of escapes before each chunk of BVC_CODED_CHUNK entries
+ * bvc_encode_codes builds it from a tile's packed8 / entry_off / ref_base into caller buffers (words: bvc_coded_words(n, 6) words, escapes: n/8 + 16
+ * bytes, chunk_escapes: n / BVC_CODED_CHUNK + 2 words) and leaves out->bits = 0 when it would not pay (escapes > n/8 or
+ * < 10 % saved: send packed8).  bvc_enqueue_split_coded is bvc_enqueue_split with (tile->packed8, code, qual) == NULL and the
+ * coded arrays instead; tile->qual_dict / n_qual_dict as for packed8.  bvc_decode_codes_host decodes on the host (tests). */
+#define BVC_CODED_CHUNK 8192
+typedef struct bvc_coded_tile {
+    int32_t bits;                 /* W: 4, 5 or 6; 0 = not coded */
+    int32_t n_codes;              /* direct codes in use (<= 2^W - 1) */
+    uint8_t code_byte[64];        /* code -> packed8 byte */
+    const uint32_t* words;
+    const uint8_t*  escapes;
+    const uint32_t* chunk_escapes;
+    int64_t n_escape;
+} bvc_coded_tile;
+size_t bvc_coded_words(int64_t n_entries, int bits);
+int  bvc_encode_codes(const bvc_tile* tile /* packed8, entry_off, ref_base */, uint32_t* words, uint8_t* escapes, uint32_t* chunk_escapes, bvc_coded_tile* out);
+int  bvc_decode_codes_host(const bvc_coded_tile* coded, const bvc_tile* tile /* entry_off, ref_base */, uint8_t* packed8_out);
+int  bvc_enqueue_split_coded(bvc_ctx* ctx, const bvc_tile* tile, const bvc_coded_tile* coded, bvc_site_core* core, bvc_site_result* vcf,
+                             int32_t vcf_cap, uint64_t* ticket);
+
 /* ---- Allocation-free call -------------------------------------------------------------------------------------
  * No counterpart in the reference: added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same records as
