@@ -94,6 +94,20 @@ def main():
         nbad, lines = compare_records(out.array.copy(), ref, max_flagged_fraction=0.1)
         assert nbad == 0, "\n".join(lines)
     print("bvc_call_sites_noalloc x2: ok", flush=True)
+    # the coded wire form (decode_codes_kernel writes the resident bytes 32 at a time: tails of every alignment)
+    for n_sites, seed in ((2000, 18), (1777, 19), (4099, 20)):
+        t = B.synth_tile(700, n_sites, 0.6, "lowpass", seed=seed, indel_frac=0.01)
+        assert t.pack8()
+        cod = B.CodedArrays(t)
+        assert cod.bits == 6
+        c = B.BaseTypeCaller(700, max_sites=t.n_sites, max_entries=t.n_entries)
+        core = np.zeros(t.n_sites, B.SITE_CORE_DTYPE)
+        vcf = np.zeros(t.n_sites, B.SITE_RESULT_DTYPE)
+        c.wait_split(c.enqueue_split_coded(t, cod, core, vcf))
+        ref = c.call_sites(t)
+        c.close()
+        assert np.array_equal(core["depth"], ref["depth"]) and np.array_equal(core["cvg_strand"], ref["cvg_strand"]) and np.array_equal(core["lrt_ok"], ref["lrt_ok"])
+    print("coded wire form x3: ok", flush=True)
     print("sanitize_run: all tiles agree with the oracle")
 
 
